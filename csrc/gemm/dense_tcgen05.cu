@@ -1,0 +1,399 @@
+// K3: Dense-layer GEMM family on 5th-gen tensor cores (tcgen05 + TMEM + TMA).
+//
+// One warp-specialised, persistent kernel computes
+//     D[Mo, No] = sum_r A(Mo, r) * B(No, r)            (bf16 x bf16 -> fp32 in TMEM)
+// with either operand K-major (row-major [rows, R]) or MN-major (row-major [R, rows]),
+// so the three GEMMs of a Dense layer need no transposes:
+//     forward  Y  = act(X W^T + b)        A = X  (K-major)   B = W  (K-major)
+//     dgrad    dX = (dY W) * relu'(X)     A = dY (K-major)   B = W  (MN-major)
+//     wgrad    dW += dY^T X               A = dY (MN-major)  B = X  (MN-major), split over batch
+// Replaces the reference's Dense stacks over MKL sgemm
+// (zoo/.../models/recommendation/NeuralCF.scala:73-96, WideAndDeep.scala:146-157) and the
+// separate bias/activation passes of BigDL's Linear+ReLU modules.
+//
+// Roles per CTA (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
+// warp 2 = TMEM allocator, warps 4-7 = epilogue (TMEM -> registers -> global).
+// Pipelines: 4-stage smem ring (TMA <-> MMA) and a 2-stage TMEM accumulator ring
+// (MMA <-> epilogue) so the epilogue of tile i overlaps the main loop of tile i+1.
+#include "../common/zoo_common.cuh"
+
+namespace zoo {
+
+constexpr int kBlockM = 128;       // UMMA M
+constexpr int kBlockK = 64;        // 64 bf16 = 128 B = one swizzle-128B row
+constexpr int kUmmaK = 16;
+constexpr int kMaxN = 256;         // UMMA N upper bound
+constexpr int kStages = 4;
+constexpr int kAccStages = 2;
+constexpr int kABytes = kBlockM * kBlockK * 2;   // 16 KiB
+constexpr int kBBytes = kMaxN * kBlockK * 2;     // 32 KiB
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // + alignment slack
+constexpr int kThreads = 256;
+constexpr int kMnBoxBytes = kBlockK * 128;       // one MN-major TMA box: 64 k-rows x 128 B
+
+enum Epilogue : int {
+  EPI_BIAS_ACT = 0,   // out(bf16) = act(acc + bias[n])
+  EPI_MASK = 1,       // out(bf16) = acc * (mask[m,n] > 0)          (mask may be null)
+  EPI_RED_F32 = 2     // out(fp32) += acc                           (split-K partial sums)
+};
+enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2, ACT_SIGMOID = 3, ACT_TANH = 4 };
+
+struct GemmArgs {
+  int Mo, No, R;            // output rows, output cols, reduction length
+  int block_n;              // UMMA N for this launch (multiple of 16, <= 256)
+  int a_mn, b_mn;           // 1 = MN-major operand
+  int m_blocks, n_blocks, k_splits, kb_per_split;
+  int epilogue, act;
+  long long ldd;            // leading dimension of out (elements)
+  long long ldmask;         // leading dimension of mask (elements)
+  void* out;
+  const float* bias;                  // [No] fp32 or null
+  const __nv_bfloat16* mask;          // [Mo, ldmask] or null
+};
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+  switch (act) {
+    case ACT_RELU: return fmaxf(v, 0.f);
+    case ACT_GELU: return 0.5f * v * (1.f + erff(v * 0.70710678118654752f));  // exact erf GELU
+    case ACT_SIGMOID: return 1.f / (1.f + __expf(-v));
+    case ACT_TANH: return tanhf(v);
+    default: return v;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                     const __grid_constant__ CUtensorMap tmap_b,
+                     const GemmArgs g) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ __align__(8) uint64_t empty_bar[kStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar[kAccStages];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[kAccStages];
+  __shared__ uint32_t tmem_base_slot;
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = threadIdx.x & 31u;
+  // 128B-swizzled tiles must start on a 1024 B boundary.
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < kAccStages; ++i) { mbar_init(&tmem_full_bar[i], 1); mbar_init(&tmem_empty_bar[i], 4); }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(&tmem_base_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  const int total_work = g.m_blocks * g.n_blocks * g.k_splits;
+  const int total_kb = (g.R + kBlockK - 1) / kBlockK;
+  const uint32_t a_stage_bytes = kABytes;
+  const uint32_t b_boxes = g.b_mn ? (uint32_t)((g.block_n + 63) / 64) : 1u;
+  const uint32_t b_stage_bytes = g.b_mn ? b_boxes * kMnBoxBytes : (uint32_t)g.block_n * 128u;
+
+  if (warp == 0) {
+    // ===================== TMA producer (one elected lane) =====================
+    if (elect_one()) {
+      uint32_t stage = 0, phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int ks = w % g.k_splits;
+        const int n_blk = (w / g.k_splits) % g.n_blocks;
+        const int m_blk = w / (g.k_splits * g.n_blocks);
+        const int kb0 = ks * g.kb_per_split;
+        const int kb1 = min(kb0 + g.kb_per_split, total_kb);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          uint8_t* sa = smem_al + stage * kStageBytes;
+          uint8_t* sb = sa + kABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], a_stage_bytes + b_stage_bytes);
+          const int r0 = kb * kBlockK;
+          if (!g.a_mn) {
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], r0, m_blk * kBlockM);
+          } else {
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], m_blk * kBlockM, r0);
+            tma_load_2d(sa + kMnBoxBytes, &tmap_a, &full_bar[stage], m_blk * kBlockM + 64, r0);
+          }
+          if (!g.b_mn) {
+            tma_load_2d(sb, &tmap_b, &full_bar[stage], r0, n_blk * g.block_n);
+          } else {
+            for (uint32_t bx = 0; bx < b_boxes; ++bx)
+              tma_load_2d(sb + bx * kMnBoxBytes, &tmap_b, &full_bar[stage],
+                          n_blk * g.block_n + (int)bx * 64, r0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one elected lane) =======================
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc_bf16(kBlockM, (uint32_t)g.block_n, (uint32_t)g.a_mn, (uint32_t)g.b_mn);
+      uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int ks = w % g.k_splits;
+        const int kb0 = ks * g.kb_per_split;
+        const int kb1 = min(kb0 + g.kb_per_split, total_kb);
+        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * kMaxN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * kStageBytes;
+          const uint32_t sb = sa + kABytes;
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            // K-major: step 16 elements (32 B) inside the swizzled 128 B row.
+            // MN-major: step 16 k-rows (16 x 128 B); LBO = next 64 MN elements (next TMA box).
+            const uint64_t da = g.a_mn ? make_smem_desc_sw128(sa + k * 2048, kMnBoxBytes, 1024)
+                                       : make_smem_desc_sw128(sa + k * 32, 16, 1024);
+            const uint64_t db = g.b_mn ? make_smem_desc_sw128(sb + k * 2048, kMnBoxBytes, 1024)
+                                       : make_smem_desc_sw128(sb + k * 32, 16, 1024);
+            umma_bf16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);             // frees the smem slot when the MMAs retire
+          if (kb == kb1 - 1) umma_commit(&tmem_full_bar[acc]);  // accumulator complete
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+        if (kb1 <= kb0) umma_commit(&tmem_full_bar[acc]);  // empty split: still hand the stage over
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== Epilogue warps (TMEM -> regs -> global) =============
+    const uint32_t q = warp & 3u;  // TMEM lane quarter this warp may access
+    uint32_t acc = 0, acc_phase = 0;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      const int ks = w % g.k_splits;
+      const int n_blk = (w / g.k_splits) % g.n_blocks;
+      const int m_blk = w / (g.k_splits * g.n_blocks);
+      const bool has_work = (ks * g.kb_per_split) < total_kb;
+      mbar_wait(&tmem_full_bar[acc], acc_phase);
+      tc_fence_after();
+      const long long row = (long long)m_blk * kBlockM + q * 32 + lane;
+      const int col0 = n_blk * g.block_n;
+      const uint32_t taddr = tmem_base + acc * kMaxN + ((q * 32u) << 16);
+      for (int c = 0; c < g.block_n; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c, r);
+        tmem_ld_wait();
+        if (row < g.Mo && has_work) {
+          const int col = col0 + c;
+          if (g.epilogue == EPI_RED_F32) {
+            float* o = reinterpret_cast<float*>(g.out) + row * g.ldd + col;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              if (col + j + 4 <= g.No) {
+                red_add_f32x4(o + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                              __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+              } else {
+                for (int t = 0; t < 4; ++t)
+                  if (col + j + t < g.No) atomicAdd(o + j + t, __uint_as_float(r[j + t]));
+              }
+            }
+          } else {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + row * g.ldd + col;
+            const __nv_bfloat16* mk = g.mask ? g.mask + row * g.ldmask + col : nullptr;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              float v[8];
+#pragma unroll
+              for (int t = 0; t < 8; ++t) v[t] = __uint_as_float(r[j + t]);
+              if (col + j + 8 <= g.No) {
+                if (g.epilogue == EPI_BIAS_ACT) {
+                  if (g.bias) {
+                    const float4 b0 = *reinterpret_cast<const float4*>(g.bias + col + j);
+                    const float4 b1 = *reinterpret_cast<const float4*>(g.bias + col + j + 4);
+                    v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+                    v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+                  }
+#pragma unroll
+                  for (int t = 0; t < 8; ++t) v[t] = apply_act(v[t], g.act);
+                } else if (mk) {
+                  const uint4 m4 = *reinterpret_cast<const uint4*>(mk + j);
+                  const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
+#pragma unroll
+                  for (int t = 0; t < 4; ++t) {
+                    const float2 f = unpack_bf16(mw[t]);
+                    if (!(f.x > 0.f)) v[2 * t] = 0.f;
+                    if (!(f.y > 0.f)) v[2 * t + 1] = 0.f;
+                  }
+                }
+                uint4 pk;
+                pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]);
+                pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
+                *reinterpret_cast<uint4*>(o + j) = pk;
+              } else {
+                for (int t = 0; t < 8; ++t) {
+                  if (col + j + t < g.No) {
+                    float x = v[t];
+                    if (g.epilogue == EPI_BIAS_ACT) {
+                      if (g.bias) x += g.bias[col + j + t];
+                      x = apply_act(x, g.act);
+                    } else if (mk) {
+                      if (!(__bfloat162float(mk[j + t]) > 0.f)) x = 0.f;
+                    }
+                    o[j + t] = __float2bfloat16(x);
+                  }
+                }
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ----------------------------------------------------------------- host side --
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<PFN_encodeTiled>(p);
+  }
+  return fn;
+}
+
+// rows x cols bf16 matrix, row-major with leading dimension ld (elements).
+static int make_tmap(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld,
+                     int box_cols, int box_rows) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) { zoo_set_last_error("cuTensorMapEncodeTiled unavailable", __FILE__, __LINE__); return ZOO_ERR_CUDA; }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    zoo_set_last_error("cuTensorMapEncodeTiled failed", __FILE__, __LINE__);
+    return ZOO_ERR_CUDA;
+  }
+  return ZOO_OK;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (!g_num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+static int launch(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn,
+                  GemmArgs g, int max_ctas, cudaStream_t stream) {
+  if (!A || !B || !g.out || g.Mo <= 0 || g.No <= 0 || g.R <= 0) {
+    zoo_set_last_error("dense_tcgen05: null pointer or empty shape", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  if ((lda % 8) || (ldb % 8) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) {
+    zoo_set_last_error("dense_tcgen05: operands need 16-byte aligned rows (ld % 8 == 0)", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  g.a_mn = a_mn; g.b_mn = b_mn;
+  // UMMA N: whole output width when it fits, rounded up to a multiple of 16.
+  int bn = g.No >= kMaxN ? kMaxN : ((g.No + 15) / 16) * 16;
+  g.block_n = bn;
+  g.m_blocks = (g.Mo + kBlockM - 1) / kBlockM;
+  g.n_blocks = (g.No + bn - 1) / bn;
+  const int total_kb = (g.R + kBlockK - 1) / kBlockK;
+  if (g.epilogue == EPI_RED_F32) {
+    int want = max_ctas / (g.m_blocks * g.n_blocks);
+    if (want < 1) want = 1;
+    if (want > total_kb) want = total_kb;
+    g.kb_per_split = (total_kb + want - 1) / want;
+    g.k_splits = (total_kb + g.kb_per_split - 1) / g.kb_per_split;
+  } else {
+    g.k_splits = 1;
+    g.kb_per_split = total_kb;
+  }
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn) rc = make_tmap(&ta, A, g.Mo, g.R, lda, kBlockK, kBlockM);
+  else       rc = make_tmap(&ta, A, g.R, g.Mo, lda, 64, kBlockK);
+  if (rc) return rc;
+  if (!b_mn) rc = make_tmap(&tb, B, g.No, g.R, ldb, kBlockK, bn);
+  else       rc = make_tmap(&tb, B, g.R, g.No, ldb, 64, kBlockK);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    ZOO_CUDA_CHECK(cudaFuncSetAttribute(dense_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr_set = true;
+  }
+  const int total_work = g.m_blocks * g.n_blocks * g.k_splits;
+  const int grid = total_work < max_ctas ? total_work : max_ctas;
+  dense_tcgen05_kernel<<<grid, kThreads, kSmemBytes, stream>>>(ta, tb, g);
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
+}
+
+}  // namespace zoo
+
+using namespace zoo;
+
+// Y[M,N] (bf16, ldy) = act(X[M,K] (bf16, ldx) * W[N,K]^T (bf16, ldw) + bias[N] (fp32 or null))
+ZOO_API int zoo_dense_fwd_bf16(const void* x, long long ldx, const void* w, long long ldw, const float* bias,
+                               void* y, long long ldy, int M, int N, int K, int act, void* stream) {
+  GemmArgs g{};
+  g.Mo = M; g.No = N; g.R = K; g.epilogue = EPI_BIAS_ACT; g.act = act;
+  g.out = y; g.ldd = ldy; g.bias = bias; g.mask = nullptr; g.ldmask = 0;
+  if (ldy % 8 || ((uintptr_t)y & 15)) { zoo_set_last_error("dense_fwd: ldy % 8 != 0", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+  return launch(x, ldx, 0, w, ldw, 0, g, num_sms(), (cudaStream_t)stream);
+}
+
+// dX[M,K] (bf16, lddx) = (dY[M,N] (bf16, lddy) * W[N,K] (bf16, ldw)) * (mask[M,K] > 0)   (mask may be null)
+ZOO_API int zoo_dense_dgrad_bf16(const void* dy, long long lddy, const void* w, long long ldw, const void* mask,
+                                 long long ldmask, void* dx, long long lddx, int M, int N, int K, void* stream) {
+  GemmArgs g{};
+  g.Mo = M; g.No = K; g.R = N; g.epilogue = EPI_MASK; g.act = ACT_NONE;
+  g.out = dx; g.ldd = lddx; g.bias = nullptr; g.mask = (const __nv_bfloat16*)mask; g.ldmask = ldmask;
+  if (lddx % 8 || ((uintptr_t)dx & 15) || (mask && (ldmask % 8 || ((uintptr_t)mask & 15)))) {
+    zoo_set_last_error("dense_dgrad: output/mask rows must be 16-byte aligned", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  return launch(dy, lddy, 0, w, ldw, 1, g, num_sms(), (cudaStream_t)stream);
+}
+
+// dW[N,K] (fp32, lddw) += dY[M,N]^T (bf16, lddy) * X[M,K] (bf16, ldx); split over the batch dimension.
+ZOO_API int zoo_dense_wgrad_bf16(const void* dy, long long lddy, const void* x, long long ldx, float* dw,
+                                 long long lddw, int M, int N, int K, void* stream) {
+  GemmArgs g{};
+  g.Mo = N; g.No = K; g.R = M; g.epilogue = EPI_RED_F32; g.act = ACT_NONE;
+  g.out = dw; g.ldd = lddw; g.bias = nullptr; g.mask = nullptr; g.ldmask = 0;
+  if (lddw % 4 || ((uintptr_t)dw & 15)) { zoo_set_last_error("dense_wgrad: lddw % 4 != 0", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+  return launch(dy, lddy, 1, x, ldx, 1, g, num_sms(), (cudaStream_t)stream);
+}

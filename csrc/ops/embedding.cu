@@ -1,0 +1,487 @@
+// K2 / K4: embedding lookup and its sparse backward on sm_100a.
+//
+// Forward (K2) is a ONE-SIDED gather: table rows are sharded across GPUs (row r lives on
+// GPU r % world at local row r / world) and every GPU reads the rows it needs straight from
+// the owner's HBM through NVLink peer pointers.  Index dispatch, row gather and the combine
+// all-to-all of the classic three-step design collapse into one kernel: the only bytes that
+// cross NVLink are the B x D result rows, and no index traffic is sent at all.  Optional
+// epilogues write into a column window of a wider activation buffer (fused concat) and
+// multiply two gathered rows (the GMF branch of NeuralCF).
+//
+// Backward (K4): gradient rows are routed to the owner's mailbox with P2P stores, the owner
+// de-duplicates rows without sorting (atomicMin election of one representative entry per row,
+// fp32 vector reductions only for the duplicates) and applies a fused sparse Adam / Adagrad /
+// SGD to the touched rows only.
+//
+// Replaces LookupTable / LookupTableSparse inside zoo Embedding / SparseEmbedding
+// (zoo/.../pipeline/api/keras/layers/Embedding.scala:82-101, SparseEmbedding.scala:76-89),
+// the GMF merge of NeuralCF.scala:83-89, and the dense-table all-reduce + dense optimizer
+// pass the reference performs for embedding gradients (Topology.scala:1187-1206).
+#include "../common/zoo_common.cuh"
+#include <limits.h>
+
+namespace zoo {
+
+constexpr int kMaxPeers = 8;
+
+struct ShardPtrs {
+  const void* p[kMaxPeers];
+};
+struct ShardPtrsMut {
+  void* p[kMaxPeers];
+};
+
+template <typename T> struct Vec;  // 16-byte vector traits
+template <> struct Vec<float> { static constexpr int N = 4; };
+template <> struct Vec<__nv_bfloat16> { static constexpr int N = 8; };
+
+template <typename T>
+__device__ __forceinline__ void load_vec(const T* p, float (&v)[Vec<T>::N]);
+template <>
+__device__ __forceinline__ void load_vec<float>(const float* p, float (&v)[4]) {
+  const float4 f = *reinterpret_cast<const float4*>(p);
+  v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+}
+template <>
+__device__ __forceinline__ void load_vec<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+__device__ __forceinline__ float to_f(float x) { return x; }
+__device__ __forceinline__ float to_f(__nv_bfloat16 x) { return __bfloat162float(x); }
+
+template <typename T>
+__device__ __forceinline__ const T* row_ptr(const ShardPtrs& s, long long id, int world, int D) {
+  const int owner = world > 1 ? (int)(id % world) : 0;
+  const long long local = world > 1 ? id / world : id;
+  return reinterpret_cast<const T*>(s.p[owner]) + local * (long long)D;
+}
+
+// One warp per (sample, slot). ids: [B, id_stride] int64, column id_col (and id_col2 for the
+// second table when MUL).  Rows whose id is out of [0, total_rows) produce zeros.
+// bag > 1: ids[b, id_col .. id_col+bag) are pooled (sum, or mean when mean != 0), negative ids skipped.
+template <typename T, bool MUL, bool VEC>
+__global__ void __launch_bounds__(256)
+embedding_gather_kernel(const long long* __restrict__ ids, int id_stride, int id_col, int id_col2,
+                        int B, int bag, int mean, ShardPtrs ta, long long rows_a, ShardPtrs tb,
+                        long long rows_b, int world, int D, __nv_bfloat16* __restrict__ out,
+                        long long ldo, __nv_bfloat16* __restrict__ save_a, __nv_bfloat16* __restrict__ save_b) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= B) return;
+  const long long* idr = ids + (long long)warp * id_stride;
+  __nv_bfloat16* o = out + (long long)warp * ldo;
+  constexpr int VN = Vec<T>::N;
+  if (VEC) {
+    for (int c = lane * VN; c < D; c += 32 * VN) {
+      float acc[VN];
+#pragma unroll
+      for (int t = 0; t < VN; ++t) acc[t] = 0.f;
+      int cnt = 0;
+      for (int j = 0; j < bag; ++j) {
+        const long long ia = idr[id_col + j];
+        if (ia < 0 || ia >= rows_a) continue;
+        float va[VN];
+        load_vec<T>(row_ptr<T>(ta, ia, world, D) + c, va);
+        if (MUL) {
+          const long long ib = idr[id_col2 + j];
+          float vb[VN];
+          if (ib >= 0 && ib < rows_b) {
+            load_vec<T>(row_ptr<T>(tb, ib, world, D) + c, vb);
+          } else {
+#pragma unroll
+            for (int t = 0; t < VN; ++t) vb[t] = 0.f;
+          }
+          if (save_a) {  // keep both factors (bf16) for the product rule in backward
+            for (int t = 0; t < VN; ++t) {
+              save_a[(long long)warp * D + c + t] = __float2bfloat16(va[t]);
+              save_b[(long long)warp * D + c + t] = __float2bfloat16(vb[t]);
+            }
+          }
+#pragma unroll
+          for (int t = 0; t < VN; ++t) va[t] *= vb[t];
+        }
+#pragma unroll
+        for (int t = 0; t < VN; ++t) acc[t] += va[t];
+        ++cnt;
+      }
+      if (mean && cnt > 1) {
+        const float s = 1.f / cnt;
+#pragma unroll
+        for (int t = 0; t < VN; ++t) acc[t] *= s;
+      }
+      if (VN == 8) {
+        uint4 pk;
+        pk.x = pack_bf16(acc[0], acc[1]); pk.y = pack_bf16(acc[2], acc[3]);
+        pk.z = pack_bf16(acc[4 % VN], acc[5 % VN]); pk.w = pack_bf16(acc[6 % VN], acc[7 % VN]);
+        *reinterpret_cast<uint4*>(o + c) = pk;
+      } else {
+        uint2 pk;
+        pk.x = pack_bf16(acc[0], acc[1]); pk.y = pack_bf16(acc[2], acc[3]);
+        *reinterpret_cast<uint2*>(o + c) = pk;
+      }
+    }
+  } else {
+    for (int c = lane; c < D; c += 32) {
+      float acc = 0.f;
+      int cnt = 0;
+      for (int j = 0; j < bag; ++j) {
+        const long long ia = idr[id_col + j];
+        if (ia < 0 || ia >= rows_a) continue;
+        float va = to_f(row_ptr<T>(ta, ia, world, D)[c]);
+        if (MUL) {
+          const long long ib = idr[id_col2 + j];
+          const float vb = (ib >= 0 && ib < rows_b) ? to_f(row_ptr<T>(tb, ib, world, D)[c]) : 0.f;
+          if (save_a) {
+            save_a[(long long)warp * D + c] = __float2bfloat16(va);
+            save_b[(long long)warp * D + c] = __float2bfloat16(vb);
+          }
+          va *= vb;
+        }
+        acc += va;
+        ++cnt;
+      }
+      if (mean && cnt > 1) acc /= cnt;
+      o[c] = __float2bfloat16(acc);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- backward ---
+// Entry e of a table's backward = (row id, gradient row).  The gradient row is
+//   dOut[b, 0:D] (bf16, leading dim ldg)           optionally times
+//   mul[b, 0:D]  (bf16, leading dim ldmul)         (the other factor saved by the GMF forward).
+struct BwdEntries {
+  const long long* ids; int id_stride; int id_col; int bag;  // E = B * bag entries
+  const __nv_bfloat16* dout; long long ldg;
+  const __nv_bfloat16* mul; long long ldmul;                 // optional elementwise multiplier rows
+  float grad_scale;                                          // e.g. 1/bag for mean pooling
+};
+
+__device__ __forceinline__ long long entry_row(const BwdEntries& en, int e) {
+  const int b = e / en.bag, j = e - b * en.bag;
+  return en.ids[(long long)b * en.id_stride + en.id_col + j];
+}
+
+// Pass 1: elect, per touched row, the smallest entry index as its representative.
+__global__ void __launch_bounds__(256)
+emb_mark_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* __restrict__ rep_of_row) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  const long long id = entry_row(en, e);
+  if (id < 0 || id >= rows) return;
+  if (world > 1 && (int)(id % world) != rank) return;
+  const long long local = world > 1 ? id / world : id;
+  atomicMin(rep_of_row + local, e);
+}
+
+template <bool VEC>
+__device__ __forceinline__ void entry_grad(const BwdEntries& en, int e, int c, float (&g)[4]) {
+  const int b = e / en.bag;
+  const __nv_bfloat16* gp = en.dout + (long long)b * en.ldg + c;
+  if (VEC) {
+    const uint2 u = *reinterpret_cast<const uint2*>(gp);
+    const float2 a = unpack_bf16(u.x), d = unpack_bf16(u.y);
+    g[0] = a.x; g[1] = a.y; g[2] = d.x; g[3] = d.y;
+  } else {
+    g[0] = __bfloat162float(gp[0]); g[1] = g[2] = g[3] = 0.f;
+  }
+  if (en.mul) {
+    const __nv_bfloat16* mp = en.mul + (long long)b * en.ldmul + c;
+    if (VEC) {
+      const uint2 u = *reinterpret_cast<const uint2*>(mp);
+      const float2 a = unpack_bf16(u.x), d = unpack_bf16(u.y);
+      g[0] *= a.x; g[1] *= a.y; g[2] *= d.x; g[3] *= d.y;
+    } else {
+      g[0] *= __bfloat162float(mp[0]);
+    }
+  }
+  g[0] *= en.grad_scale; g[1] *= en.grad_scale; g[2] *= en.grad_scale; g[3] *= en.grad_scale;
+}
+
+// Pass 2: entries that lost the election add their gradient into the representative's
+// accumulation row (fp32, vector red) and flag it.  One warp per entry.
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+emb_accum_kernel(BwdEntries en, int E, long long rows, int world, int rank, const int* __restrict__ rep_of_row,
+                 int D, float* __restrict__ accum, int* __restrict__ dup_flag) {
+  const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (e >= E) return;
+  const long long id = entry_row(en, e);
+  if (id < 0 || id >= rows) return;
+  if (world > 1 && (int)(id % world) != rank) return;
+  const long long local = world > 1 ? id / world : id;
+  const int rep = rep_of_row[local];
+  if (rep == e) return;
+  float* arow = accum + (long long)rep * D;
+  if (VEC) {
+    for (int c = lane * 4; c < D; c += 128) {
+      float g[4];
+      entry_grad<true>(en, e, c, g);
+      red_add_f32x4(arow + c, g[0], g[1], g[2], g[3]);
+    }
+  } else {
+    for (int c = lane; c < D; c += 32) {
+      float g[4];
+      entry_grad<false>(en, e, c, g);
+      atomicAdd(arow + c, g[0]);
+    }
+  }
+  if (lane == 0) dup_flag[rep] = 1;
+}
+
+enum SparseOpt : int { SOPT_SGD = 0, SOPT_ADAM = 1, SOPT_ADAGRAD = 2 };
+
+// hyper[] layout (device memory, fp32): lr, beta1, beta2, eps, weight_decay, step (as float)
+struct SparseState {
+  float* w;                 // fp32 master rows  [rows_local, D]
+  __nv_bfloat16* w16;       // optional bf16 shadow read by the forward gather (may be null)
+  float* m;                 // Adam first moment / Adagrad accumulator
+  float* v;                 // Adam second moment (null otherwise)
+};
+
+// Pass 3: representatives apply the optimizer to their row and reset the scratch they used.
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+emb_apply_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* __restrict__ rep_of_row,
+                 int D, float* __restrict__ accum, int* __restrict__ dup_flag, SparseState st, int opt,
+                 const float* __restrict__ hyper) {
+  const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (e >= E) return;
+  const long long id = entry_row(en, e);
+  if (id < 0 || id >= rows) return;
+  if (world > 1 && (int)(id % world) != rank) return;
+  const long long local = world > 1 ? id / world : id;
+  if (rep_of_row[local] != e) return;
+  const bool dup = dup_flag[e] != 0;
+  const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5];
+  float bc1 = 1.f, bc2 = 1.f;
+  if (opt == SOPT_ADAM) {
+    bc1 = 1.f - powf(b1, step);
+    bc2 = 1.f - powf(b2, step);
+  }
+  float* wrow = st.w + local * (long long)D;
+  float* arow = accum + (long long)e * D;
+  constexpr int STEP = VEC ? 4 : 1;
+  for (int c = lane * STEP; c < D; c += 32 * STEP) {
+    float g[4];
+    entry_grad<VEC>(en, e, c, g);
+    float w[4], m[4] = {0, 0, 0, 0}, v[4] = {0, 0, 0, 0};
+    if (VEC) {
+      if (dup) {
+        const float4 a = *reinterpret_cast<const float4*>(arow + c);
+        g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w;
+        *reinterpret_cast<float4*>(arow + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      const float4 w4 = *reinterpret_cast<const float4*>(wrow + c);
+      w[0] = w4.x; w[1] = w4.y; w[2] = w4.z; w[3] = w4.w;
+      if (st.m) { const float4 t = *reinterpret_cast<const float4*>(st.m + local * (long long)D + c); m[0] = t.x; m[1] = t.y; m[2] = t.z; m[3] = t.w; }
+      if (st.v) { const float4 t = *reinterpret_cast<const float4*>(st.v + local * (long long)D + c); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
+    } else {
+      if (dup) { g[0] += arow[c]; arow[c] = 0.f; }
+      w[0] = wrow[c];
+      if (st.m) m[0] = st.m[local * (long long)D + c];
+      if (st.v) v[0] = st.v[local * (long long)D + c];
+    }
+#pragma unroll
+    for (int t = 0; t < STEP; ++t) {
+      float gg = g[t] + wd * w[t];
+      if (opt == SOPT_ADAM) {
+        m[t] = b1 * m[t] + (1.f - b1) * gg;
+        v[t] = b2 * v[t] + (1.f - b2) * gg * gg;
+        w[t] -= lr * (m[t] / bc1) / (sqrtf(v[t] / bc2) + eps);
+      } else if (opt == SOPT_ADAGRAD) {
+        m[t] += gg * gg;
+        w[t] -= lr * gg / (sqrtf(m[t]) + eps);
+      } else {
+        w[t] -= lr * gg;
+      }
+    }
+    if (VEC) {
+      *reinterpret_cast<float4*>(wrow + c) = make_float4(w[0], w[1], w[2], w[3]);
+      if (st.m) *reinterpret_cast<float4*>(st.m + local * (long long)D + c) = make_float4(m[0], m[1], m[2], m[3]);
+      if (st.v) *reinterpret_cast<float4*>(st.v + local * (long long)D + c) = make_float4(v[0], v[1], v[2], v[3]);
+      if (st.w16) {
+        uint2 pk; pk.x = pack_bf16(w[0], w[1]); pk.y = pack_bf16(w[2], w[3]);
+        *reinterpret_cast<uint2*>(st.w16 + local * (long long)D + c) = pk;
+      }
+    } else {
+      wrow[c] = w[0];
+      if (st.m) st.m[local * (long long)D + c] = m[0];
+      if (st.v) st.v[local * (long long)D + c] = v[0];
+      if (st.w16) st.w16[local * (long long)D + c] = __float2bfloat16(w[0]);
+    }
+  }
+  __syncwarp();
+  if (lane == 0) {
+    rep_of_row[local] = INT_MAX;
+    if (dup) dup_flag[e] = 0;
+  }
+}
+
+// Dense-gradient mode (exact reference semantics for small tables): dTable[id] += dOut rows.
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+emb_dense_grad_kernel(BwdEntries en, int E, long long rows, int D, float* __restrict__ dtable) {
+  const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (e >= E) return;
+  const long long id = entry_row(en, e);
+  if (id < 0 || id >= rows) return;
+  float* drow = dtable + id * (long long)D;
+  if (VEC) {
+    for (int c = lane * 4; c < D; c += 128) {
+      float g[4];
+      entry_grad<true>(en, e, c, g);
+      red_add_f32x4(drow + c, g[0], g[1], g[2], g[3]);
+    }
+  } else {
+    for (int c = lane; c < D; c += 32) {
+      float g[4];
+      entry_grad<false>(en, e, c, g);
+      atomicAdd(drow + c, g[0]);
+    }
+  }
+}
+
+__global__ void fill_i32_kernel(int* p, long long n, int v) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) p[i] = v;
+}
+
+static ShardPtrs make_ptrs(const void* const* tabs, int world) {
+  ShardPtrs s{};
+  for (int i = 0; i < kMaxPeers; ++i) s.p[i] = (tabs && i < world) ? tabs[i] : nullptr;
+  return s;
+}
+
+}  // namespace zoo
+
+using namespace zoo;
+
+// out[b, 0:D] (bf16, leading dim ldo) = pool_j table[ids[b, id_col + j]]  (x table2[ids[b, id_col2 + j]] if tables2)
+//   tables / tables2 : host arrays of `world` device pointers (one shard per GPU; peers via P2P)
+//   table_dtype      : 0 = fp32 rows, 1 = bf16 rows
+//   rows_a / rows_b  : global (unsharded) row counts
+//   save_a / save_b  : optional [B, D] bf16 buffers receiving the two factors of a product (bag must be 1)
+ZOO_API int zoo_embedding_gather(const long long* ids, int id_stride, int id_col, int id_col2, int B, int bag,
+                                 int mean, const void* const* tables, long long rows_a,
+                                 const void* const* tables2, long long rows_b, int world, int D,
+                                 int table_dtype, void* out, long long ldo, void* save_a, void* save_b,
+                                 void* stream) {
+  if (!ids || !tables || !out || B < 0 || D <= 0 || world < 1 || world > kMaxPeers || bag < 1 ||
+      ((save_a != nullptr) != (save_b != nullptr)) || (save_a && (!tables2 || bag != 1))) {
+    zoo_set_last_error("embedding_gather: bad arguments", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  if (B == 0) return ZOO_OK;
+  const ShardPtrs ta = make_ptrs(tables, world);
+  const ShardPtrs tb = make_ptrs(tables2, world);
+  const bool mul = tables2 != nullptr;
+  const int vn = table_dtype == 0 ? 4 : 8;
+  bool vec = (D % vn == 0) && (ldo % vn == 0) && (((uintptr_t)out & (vn * 2 - 1)) == 0);
+  for (int i = 0; i < world && vec; ++i) {
+    if ((uintptr_t)ta.p[i] & 15) vec = false;
+    if (mul && ((uintptr_t)tb.p[i] & 15)) vec = false;
+  }
+  const int threads = 256;
+  const long long blocks = ((long long)B * 32 + threads - 1) / threads;
+  cudaStream_t s = (cudaStream_t)stream;
+  __nv_bfloat16* o = (__nv_bfloat16*)out;
+  __nv_bfloat16* sa = (__nv_bfloat16*)save_a;
+  __nv_bfloat16* sb = (__nv_bfloat16*)save_b;
+#define ZOO_GATHER(T, MUL, VEC)                                                                     \
+  embedding_gather_kernel<T, MUL, VEC><<<(unsigned)blocks, threads, 0, s>>>(                        \
+      ids, id_stride, id_col, id_col2, B, bag, mean, ta, rows_a, tb, rows_b, world, D, o, ldo, sa, sb)
+  if (table_dtype == 0) {
+    if (mul) { if (vec) ZOO_GATHER(float, true, true); else ZOO_GATHER(float, true, false); }
+    else     { if (vec) ZOO_GATHER(float, false, true); else ZOO_GATHER(float, false, false); }
+  } else {
+    if (mul) { if (vec) ZOO_GATHER(__nv_bfloat16, true, true); else ZOO_GATHER(__nv_bfloat16, true, false); }
+    else     { if (vec) ZOO_GATHER(__nv_bfloat16, false, true); else ZOO_GATHER(__nv_bfloat16, false, false); }
+  }
+#undef ZOO_GATHER
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
+}
+
+// Scratch owned by the caller (see zoo/ops/embedding.py):
+//   rep_of_row : int32 [rows_local]  -- must be INT_MAX everywhere on entry; restored on exit
+//   accum      : fp32  [E, D]        -- must be zero on entry; restored on exit
+//   dup_flag   : int32 [E]           -- must be zero on entry; restored on exit
+ZOO_API int zoo_embedding_scratch_init(int* rep_of_row, long long rows_local, void* stream) {
+  if (!rep_of_row || rows_local <= 0) return ZOO_ERR_ARG;
+  fill_i32_kernel<<<1024, 256, 0, (cudaStream_t)stream>>>(rep_of_row, rows_local, INT_MAX);
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
+}
+
+// Fused sparse optimizer step for the table shard owned by `rank`.
+//   ids/dout describe ALL entries visible to this GPU (world == 1: its own batch; world > 1: the
+//   mailbox the peers filled); entries owned by other ranks are skipped.
+//   mul (optional, bf16 [B, ldmul]): gradient rows are multiplied elementwise by mul rows
+//   (the other factor of a GMF product, saved by the forward).
+//   opt: 0 = SGD, 1 = Adam (lazy / touched rows only), 2 = Adagrad.   hyper: device fp32[6] =
+//   {lr, beta1, beta2, eps, weight_decay, step}.
+ZOO_API int zoo_embedding_sparse_update(const long long* ids, int id_stride, int id_col, int B, int bag,
+                                        const void* dout, long long ldg, const void* mul, long long ldmul,
+                                        float grad_scale, long long rows, int world, int rank, int D,
+                                        float* w, void* w16, float* m, float* v, int opt, const float* hyper,
+                                        int* rep_of_row, float* accum, int* dup_flag, void* stream) {
+  if (!ids || !dout || !w || !hyper || !rep_of_row || !accum || !dup_flag || D <= 0 || bag < 1 || world < 1 ||
+      world > kMaxPeers || rank < 0 || rank >= world) {
+    zoo_set_last_error("embedding_sparse_update: bad arguments", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  if ((opt == SOPT_ADAM && (!m || !v)) || (opt == SOPT_ADAGRAD && !m)) {
+    zoo_set_last_error("embedding_sparse_update: optimizer state missing", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  const int E = B * bag;
+  if (E == 0) return ZOO_OK;
+  BwdEntries en{ids, id_stride, id_col, bag, (const __nv_bfloat16*)dout, ldg, (const __nv_bfloat16*)mul, ldmul, grad_scale};
+  SparseState st{w, (__nv_bfloat16*)w16, opt == SOPT_SGD ? nullptr : m, opt == SOPT_ADAM ? v : nullptr};
+  const bool vec = (D % 4 == 0) && (ldg % 4 == 0) && (((uintptr_t)dout & 7) == 0) && (((uintptr_t)w & 15) == 0) &&
+                   (((uintptr_t)accum & 15) == 0) && (!m || ((uintptr_t)m & 15) == 0) &&
+                   (!v || ((uintptr_t)v & 15) == 0) && (!w16 || ((uintptr_t)w16 & 7) == 0) &&
+                   (!mul || ((ldmul % 4 == 0) && ((uintptr_t)mul & 7) == 0));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int threads = 256;
+  emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row);
+  const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
+  if (vec) {
+    emb_accum_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
+    emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
+  } else {
+    emb_accum_kernel<false><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
+    emb_apply_kernel<false><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
+  }
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
+}
+
+// Dense gradient: dtable[ids] += dout rows (fp32 atomics); used when the table is trained as a
+// dense parameter exactly like the reference does.
+ZOO_API int zoo_embedding_dense_grad(const long long* ids, int id_stride, int id_col, int B, int bag,
+                                     const void* dout, long long ldg, const void* mul, long long ldmul,
+                                     float grad_scale, long long rows, int D, float* dtable, void* stream) {
+  if (!ids || !dout || !dtable || D <= 0 || bag < 1) {
+    zoo_set_last_error("embedding_dense_grad: bad arguments", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  const int E = B * bag;
+  if (E == 0) return ZOO_OK;
+  BwdEntries en{ids, id_stride, id_col, bag, (const __nv_bfloat16*)dout, ldg, (const __nv_bfloat16*)mul, ldmul, grad_scale};
+  const bool vec = (D % 4 == 0) && (ldg % 4 == 0) && (((uintptr_t)dout & 7) == 0) && (((uintptr_t)dtable & 15) == 0) &&
+                   (!mul || ((ldmul % 4 == 0) && ((uintptr_t)mul & 7) == 0));
+  const int threads = 256;
+  const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
+  if (vec) emb_dense_grad_kernel<true><<<wb, threads, 0, (cudaStream_t)stream>>>(en, E, rows, D, dtable);
+  else     emb_dense_grad_kernel<false><<<wb, threads, 0, (cudaStream_t)stream>>>(en, E, rows, D, dtable);
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
+}

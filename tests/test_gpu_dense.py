@@ -1,0 +1,107 @@
+"""tcgen05 Dense GEMM family vs a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(x):
+    return x.to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 256, 256), (1000, 128, 256), (4096, 256, 320), (333, 40, 72),
+                                   (65536, 256, 256), (512, 5, 128), (130, 16, 8), (2048, 512, 128)])
+@pytest.mark.parametrize("act", [None, "relu"])
+def test_dense_fwd(M, N, K, act):
+    from zoo.ops.dense import dense_forward
+
+    torch.manual_seed(0)
+    x = _bf(torch.randn(M, K, device="cuda"))
+    w = _bf(torch.randn(N, K, device="cuda") / K ** 0.5)
+    b = torch.randn(N, device="cuda")
+    y = dense_forward(x, w, b, act)
+    ref = x.float() @ w.float().t() + b
+    if act == "relu":
+        ref = torch.relu(ref)
+    torch.cuda.synchronize()
+    assert y.shape == (M, N)
+    torch.testing.assert_close(y.float(), ref, atol=3e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("act", ["gelu", "sigmoid", "tanh"])
+def test_dense_fwd_other_acts(act):
+    from zoo.ops.dense import dense_forward, _act_torch
+
+    torch.manual_seed(1)
+    x = _bf(torch.randn(300, 96, device="cuda"))
+    w = _bf(torch.randn(48, 96, device="cuda") / 10)
+    y = dense_forward(x, w, None, act)
+    ref = _act_torch(x.float() @ w.float().t(), act)
+    torch.testing.assert_close(y.float(), ref, atol=2e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 256, 256), (1000, 128, 256), (4096, 64, 128), (333, 40, 72),
+                                   (512, 5, 128), (65536, 128, 256)])
+@pytest.mark.parametrize("masked", [False, True])
+def test_dense_dgrad(M, N, K, masked):
+    from zoo.ops.dense import dense_dgrad
+
+    torch.manual_seed(2)
+    ldn = (N + 7) // 8 * 8
+    dy = torch.zeros(M, ldn, device="cuda", dtype=torch.bfloat16)
+    dy[:, :N] = _bf(torch.randn(M, N, device="cuda"))
+    dy = dy[:, :N]
+    w = _bf(torch.randn(N, K, device="cuda") / N ** 0.5)
+    mask = _bf(torch.randn(M, K, device="cuda")) if masked else None
+    dx = dense_dgrad(dy, w, mask)
+    ref = dy.float() @ w.float()
+    if masked:
+        ref = ref * (mask.float() > 0)
+    torch.testing.assert_close(dx.float(), ref, atol=3e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 256, 256), (1000, 128, 256), (4096, 64, 128), (333, 40, 72),
+                                   (512, 5, 128), (65536, 256, 256), (70000, 16, 264)])
+def test_dense_wgrad(M, N, K):
+    from zoo.ops.dense import dense_wgrad
+
+    torch.manual_seed(3)
+    ldn = (N + 7) // 8 * 8
+    dy = torch.zeros(M, ldn, device="cuda", dtype=torch.bfloat16)
+    dy[:, :N] = _bf(torch.randn(M, N, device="cuda"))
+    dy = dy[:, :N]
+    x = _bf(torch.randn(M, K, device="cuda"))
+    dw = torch.ones(N, K, device="cuda")  # accumulates on top of existing contents
+    dense_wgrad(dy, x, dw)
+    ref = dy.float().t() @ x.float() + 1.0
+    scale = max(1.0, M ** 0.5)
+    torch.testing.assert_close(dw / scale, ref / scale, atol=2e-2, rtol=2e-2)
+
+
+def test_colsum():
+    from zoo.ops.dense import colsum
+
+    dy = _bf(torch.randn(5000, 72, device="cuda"))
+    out = torch.zeros(72, device="cuda")
+    colsum(dy, out)
+    torch.testing.assert_close(out, dy.float().sum(0), atol=1e-2, rtol=1e-3)
+
+
+def test_fused_mlp_autograd_matches_torch():
+    from zoo.ops.dense import FusedMLP
+
+    torch.manual_seed(4)
+    mlp = FusedMLP(64, [128, 64, 32]).cuda()
+    x = torch.randn(512, 64, device="cuda")
+    xk = x.to(torch.bfloat16).requires_grad_(True)
+    y = mlp(xk)
+    y.float().pow(2).mean().backward()
+    # reference in fp32 with the same (bf16-rounded) weights
+    xr = x.to(torch.bfloat16).float().requires_grad_(True)
+    h = xr
+    for layer in mlp:
+        h = torch.relu(h @ layer.weight.detach().to(torch.bfloat16).float().t() + layer.bias.detach())
+    h.pow(2).mean().backward()
+    torch.testing.assert_close(y.float(), h, atol=3e-2, rtol=3e-2)
+    torch.testing.assert_close(xk.grad.float(), xr.grad, atol=2e-3, rtol=5e-2)
+    assert mlp[0].weight.grad is not None and torch.isfinite(mlp[0].weight.grad).all()

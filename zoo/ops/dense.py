@@ -1,0 +1,225 @@
+"""Dense (Linear + bias + activation) on tcgen05 tensor cores.
+
+`fused_dense(x, weight, bias, act)` runs the forward GEMM, the input-gradient GEMM (with the
+ReLU mask of the producing layer fused into its epilogue) and the weight-gradient GEMM of
+``csrc/gemm/dense_tcgen05.cu``.  On CPU (unit tests, gloo plumbing runs) the same math is done
+with plain torch ops.
+
+Replaces zoo keras ``Dense`` (reference zoo/.../pipeline/api/keras/layers/Dense.scala) and the
+Linear+ReLU stacks of NeuralCF / WideAndDeep (NeuralCF.scala:73-96, WideAndDeep.scala:146-157).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..native import lib as _nl
+
+ACT_IDS = {None: 0, "linear": 0, "none": 0, "relu": 1, "gelu": 2, "sigmoid": 3, "tanh": 4}
+
+
+def _act_torch(y, act):
+    if act in (None, "linear", "none"):
+        return y
+    if act == "relu":
+        return torch.relu(y)
+    if act == "gelu":
+        return F.gelu(y)
+    if act == "sigmoid":
+        return torch.sigmoid(y)
+    if act == "tanh":
+        return torch.tanh(y)
+    raise ValueError(f"unsupported activation {act!r}")
+
+
+def _use_kernel(x: torch.Tensor) -> bool:
+    return x.is_cuda
+
+
+def _aligned(t: torch.Tensor) -> bool:
+    return t.stride(-1) == 1 and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0
+
+
+def dense_forward(x16: torch.Tensor, w16: torch.Tensor, bias: torch.Tensor | None, act, out: torch.Tensor | None = None):
+    """y = act(x16 @ w16.T + bias) with bf16 operands on the tcgen05 kernel.  `out` may be a
+    column window of a wider buffer (fused concat)."""
+    M, K = x16.shape
+    N = w16.shape[0]
+    if out is None:
+        ldn = (N + 7) // 8 * 8
+        out = torch.empty((M, ldn), dtype=torch.bfloat16, device=x16.device)[:, :N]
+    lib = _nl.cuda_lib()
+    if not (_aligned(x16) and _aligned(w16) and _aligned(out)):
+        raise _nl.NativeError("dense_forward: operands must have 16-byte aligned rows (pad K/N to a multiple of 8)")
+    _nl.check(lib.zoo_dense_fwd_bf16(x16.data_ptr(), x16.stride(0), w16.data_ptr(), w16.stride(0), _nl.ptr(bias),
+                                     out.data_ptr(), out.stride(0), M, N, K, ACT_IDS[act], _nl.stream_ptr()),
+              "zoo_dense_fwd_bf16")
+    return out
+
+
+def dense_dgrad(dy16, w16, mask16=None, out=None):
+    """dx = (dy16 @ w16) * (mask16 > 0)."""
+    M, N = dy16.shape
+    K = w16.shape[1]
+    if out is None:
+        ldk = (K + 7) // 8 * 8
+        out = torch.empty((M, ldk), dtype=torch.bfloat16, device=dy16.device)[:, :K]
+    lib = _nl.cuda_lib()
+    _nl.check(lib.zoo_dense_dgrad_bf16(dy16.data_ptr(), dy16.stride(0), w16.data_ptr(), w16.stride(0),
+                                       _nl.ptr(mask16), mask16.stride(0) if mask16 is not None else 0,
+                                       out.data_ptr(), out.stride(0), M, N, K, _nl.stream_ptr()),
+              "zoo_dense_dgrad_bf16")
+    return out
+
+
+def dense_wgrad(dy16, x16, dw32):
+    """dw32 += dy16.T @ x16  (fp32 accumulation straight into the gradient arena)."""
+    M, N = dy16.shape
+    K = x16.shape[1]
+    lib = _nl.cuda_lib()
+    _nl.check(lib.zoo_dense_wgrad_bf16(dy16.data_ptr(), dy16.stride(0), x16.data_ptr(), x16.stride(0),
+                                       dw32.data_ptr(), dw32.stride(0), M, N, K, _nl.stream_ptr()),
+              "zoo_dense_wgrad_bf16")
+    return dw32
+
+
+def colsum(dy16, db32):
+    """db32 += dy16.sum(0)."""
+    lib = _nl.cuda_lib()
+    _nl.check(lib.zoo_colsum_bf16(dy16.data_ptr(), dy16.stride(0), dy16.shape[0], dy16.shape[1], db32.data_ptr(),
+                                  _nl.stream_ptr()), "zoo_colsum_bf16")
+    return db32
+
+
+class _FusedDenseFn(torch.autograd.Function):
+    """CUDA path.  Weight/bias gradients are accumulated straight into `.grad`-like fp32 buffers
+    when the parameters carry ``_zoo_grad`` views (set by the flat-parameter arena)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False):
+        x16 = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
+        if not _aligned(x16):
+            x16 = _pad_cols(x16)
+        y = dense_forward(x16, w16, bias, act)
+        ctx.act = act
+        ctx.relu_input = relu_input
+        ctx.skip_relu_bwd = skip_relu_bwd
+        ctx.in_dtype = x.dtype
+        ctx.save_for_backward(x16, w16, y if act == "relu" else None, weight, bias)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x16, w16, y, weight, bias = ctx.saved_tensors
+        dy16 = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
+        if ctx.act == "relu":
+            if not ctx.skip_relu_bwd:  # otherwise the consumer's dgrad epilogue already applied the mask
+                dy16 = torch.where(y > 0, dy16, torch.zeros_like(dy16))
+        elif ctx.act not in (None, "linear", "none"):
+            raise NotImplementedError("fused backward supports linear/relu epilogues; use torch for others")
+        if not _aligned(dy16):
+            dy16 = _pad_cols(dy16)
+        K = weight.shape[1]
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = dense_dgrad(dy16, w16[:, :K] if w16.shape[1] != K else w16, x16[:, :K] if ctx.relu_input else None)
+            if dx.dtype != ctx.in_dtype:
+                dx = dx.to(ctx.in_dtype)
+        gw = getattr(weight, "_zoo_grad", None)
+        dw_ret = None
+        if gw is not None:
+            dense_wgrad(dy16, x16[:, :K], gw)
+        elif ctx.needs_input_grad[1]:
+            dw_ret = torch.zeros_like(weight, dtype=torch.float32)
+            dense_wgrad(dy16, x16[:, :K], dw_ret)
+        db_ret = None
+        if bias is not None:
+            gb = getattr(bias, "_zoo_grad", None)
+            if gb is not None:
+                colsum(dy16, gb)
+            elif ctx.needs_input_grad[2]:
+                db_ret = torch.zeros_like(bias, dtype=torch.float32)
+                colsum(dy16, db_ret)
+        return dx, dw_ret, db_ret, None, None, None, None
+
+
+def _pad_cols(t: torch.Tensor) -> torch.Tensor:
+    """Copy into a buffer whose row stride is a multiple of 8 elements (TMA needs 16-byte rows)."""
+    M, K = t.shape
+    ld = (K + 7) // 8 * 8
+    buf = torch.zeros((M, ld), dtype=t.dtype, device=t.device)
+    buf[:, :K] = t
+    return buf[:, :K]
+
+
+class FusedDense(nn.Module):
+    """Linear + bias + activation.  fp32 master weights (optimizer state lives in the flat arena),
+    bf16 shadow weights for the tensor-core GEMMs, refreshed by the fused optimizer kernel or
+    lazily here when the master changes."""
+
+    def __init__(self, in_features, out_features, activation=None, bias=True, init="glorot_uniform",
+                 relu_input=False):
+        super().__init__()
+        self.in_features, self.out_features = int(in_features), int(out_features)
+        self.activation = activation if activation not in ("linear", "none") else None
+        self.relu_input = relu_input  # input is the output of a ReLU: fuse its mask into dgrad
+        self.skip_relu_bwd = False    # set when the ONLY consumer is a FusedDense with relu_input=True
+        self.weight = nn.Parameter(torch.empty(out_features, in_features))
+        self.bias = nn.Parameter(torch.zeros(out_features)) if bias else None
+        self.register_buffer("weight_bf16", torch.zeros(out_features, (in_features + 7) // 8 * 8, dtype=torch.bfloat16),
+                             persistent=False)
+        self._shadow_version = -1
+        self.reset_parameters(init)
+
+    def reset_parameters(self, init="glorot_uniform"):
+        if init in ("glorot_uniform", "xavier"):
+            nn.init.xavier_uniform_(self.weight)
+        elif init == "uniform":
+            nn.init.uniform_(self.weight, -0.05, 0.05)
+        elif init == "normal":
+            nn.init.normal_(self.weight, 0.0, 0.05)
+        else:
+            nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        self._shadow_version = -1
+
+    def refresh_shadow(self, force=False):
+        v = self.weight._version
+        if force or v != self._shadow_version or self.weight_bf16.device != self.weight.device:
+            with torch.no_grad():
+                self.weight_bf16[:, : self.in_features].copy_(self.weight)
+            self._shadow_version = self.weight._version
+
+    def mark_shadow_fresh(self):
+        """Called by the fused optimizer after it wrote the bf16 shadow itself."""
+        self._shadow_version = self.weight._version
+
+    def forward(self, x):
+        if _use_kernel(x):
+            lead = x.shape[:-1]
+            x2 = x.reshape(-1, x.shape[-1])
+            self.refresh_shadow()
+            y = _FusedDenseFn.apply(x2, self.weight, self.bias, self.weight_bf16, self.activation, self.relu_input,
+                                    self.skip_relu_bwd)
+            return y.reshape(*lead, self.out_features)
+        y = F.linear(x.to(self.weight.dtype), self.weight, self.bias)
+        return _act_torch(y, self.activation)
+
+    def extra_repr(self):
+        return f"{self.in_features}, {self.out_features}, activation={self.activation}"
+
+
+class FusedMLP(nn.Sequential):
+    """Dense(+ReLU) tower; every hidden layer feeds the next layer's dgrad its ReLU mask."""
+
+    def __init__(self, in_features, hidden, activation="relu", last_activation=None, init="glorot_uniform"):
+        layers, prev, prev_relu = [], in_features, False
+        for i, h in enumerate(hidden):
+            act = activation if i < len(hidden) - 1 or last_activation is None else last_activation
+            layers.append(FusedDense(prev, h, activation=act, init=init, relu_input=prev_relu))
+            prev, prev_relu = h, act == "relu"
+        for a, b in zip(layers[:-1], layers[1:]):
+            a.skip_relu_bwd = b.relu_input
+        super().__init__(*layers)

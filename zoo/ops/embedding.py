@@ -1,0 +1,280 @@
+"""Embedding tables: one-sided NVLink gather forward, sort-free sparse optimizer backward.
+
+Python face of ``csrc/ops/embedding.cu`` (kernels K2/K4).  An :class:`EmbeddingTable` owns one
+row-shard of a table (``row r`` lives on rank ``r % world`` at local row ``r // world``) with
+fp32 master rows, optional bf16 shadow rows for the gather, and the optimizer state of the
+rows it owns.  `multi_lookup` gathers several tables into ONE activation buffer (the concat
+is fused away) and `lookup_mul` produces the GMF product of two tables.
+
+In *sparse* mode (default on GPU) the optimizer runs inside backward on the touched rows only
+(lazy Adam / Adagrad / SGD, like ``torch.optim.SparseAdam``); in *dense* mode the table is an
+ordinary parameter whose full gradient is produced with fp32 atomics -- that is the exact
+semantics of the reference, which treats ``Embedding`` as a dense ``LookupTable`` parameter
+(zoo/.../pipeline/api/keras/layers/Embedding.scala:82-101) and is what the CPU path does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..native import lib as _nl
+
+SPARSE_OPTS = {"sgd": 0, "adam": 1, "adagrad": 2}
+INT_MAX = 2**31 - 1
+
+
+class EmbeddingTable(nn.Module):
+    def __init__(self, num_embeddings, embedding_dim, init="uniform", init_scale=0.05, sparse=True,
+                 optimizer="adam", lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
+                 world=1, rank=0, shadow_bf16=False, padding_idx=None):
+        super().__init__()
+        self.num_embeddings, self.embedding_dim = int(num_embeddings), int(embedding_dim)
+        self.world, self.rank = int(world), int(rank)
+        self.sparse = bool(sparse)
+        self.optimizer = optimizer
+        self.opt_cfg = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+        self.padding_idx = padding_idx
+        self.rows_local = (self.num_embeddings + self.world - 1) // self.world
+        w = torch.empty(self.rows_local, self.embedding_dim)
+        if init == "uniform":
+            w.uniform_(-init_scale, init_scale)
+        elif init == "normal":
+            w.normal_(0.0, init_scale)
+        elif init == "zeros":
+            w.zero_()
+        else:
+            nn.init.xavier_uniform_(w)
+        if padding_idx is not None and self.world == 1:
+            w[padding_idx].zero_()
+        self.weight = nn.Parameter(w)
+        # Sparse mode updates rows inside backward; this 1-element parameter only anchors the
+        # lookup in the autograd graph (its own gradient is always None).
+        self.anchor = nn.Parameter(torch.zeros(1))
+        self.shadow_bf16 = shadow_bf16
+        self._peer_ptrs = None       # list[int] of device pointers (one per rank) when world > 1
+        self._peer_ptrs16 = None
+        self._state_ready = False
+        self._ptr_arr = None
+
+    def _apply(self, fn, *a, **kw):
+        super()._apply(fn, *a, **kw)
+        # On a GPU a sparse table leaves the dense optimizer: its rows are updated in backward.
+        self.weight.requires_grad_(not (self.sparse and self.weight.is_cuda))
+        self._state_ready = False
+        return self
+
+    @property
+    def fused_sparse(self):
+        return self.sparse and self.weight.is_cuda
+
+    # ------------------------------------------------------------------ state --
+    def _ensure_state(self):
+        """Allocate optimizer state + backward scratch lazily on the table's device."""
+        if self._state_ready and self.hyper.device == self.weight.device:
+            return
+        dev = self.weight.device
+        z = lambda: torch.zeros_like(self.weight.data, dtype=torch.float32)
+        self.exp_avg = z() if self.optimizer in ("adam", "adagrad") else None
+        self.exp_avg_sq = z() if self.optimizer == "adam" else None
+        self.weight16 = self.weight.data.to(torch.bfloat16) if self.shadow_bf16 else None
+        c = self.opt_cfg
+        h = torch.zeros(16, dtype=torch.float32)
+        h[0], h[1], h[2], h[3], h[4], h[5], h[6] = c["lr"], c["betas"][0], c["betas"][1], c["eps"], c["weight_decay"], 0.0, 1.0
+        self.hyper = h.to(dev)
+        if dev.type == "cuda":
+            self.rep_of_row = torch.full((self.rows_local,), INT_MAX, dtype=torch.int32, device=dev)
+        self._scratch_E = 0
+        self.accum = None
+        self.dup_flag = None
+        self._state_ready = True
+
+    def _ensure_scratch(self, E):
+        if self._scratch_E < E:
+            dev = self.weight.device
+            self.accum = torch.zeros((E, self.embedding_dim), dtype=torch.float32, device=dev)
+            self.dup_flag = torch.zeros((E,), dtype=torch.int32, device=dev)
+            self._scratch_E = E
+
+    def set_lr(self, lr):
+        self.opt_cfg["lr"] = lr
+        if self._state_ready:
+            self.hyper[0] = lr
+
+    def set_peers(self, ptrs, ptrs16=None):
+        """Device pointers of every rank's shard (symmetric heap); index = rank."""
+        self._peer_ptrs, self._peer_ptrs16, self._ptr_arr = list(ptrs), (list(ptrs16) if ptrs16 else None), None
+
+    def table_ptrs(self):
+        """(ctypes void*[world], dtype id) for the gather kernel."""
+        use16 = self.shadow_bf16 and getattr(self, "weight16", None) is not None
+        if self.world == 1:
+            p = [self.weight16.data_ptr() if use16 else self.weight.data_ptr()]
+        else:
+            p = self._peer_ptrs16 if use16 else self._peer_ptrs
+            if p is None:
+                raise _nl.NativeError("EmbeddingTable(world>1) needs set_peers() from the symmetric heap")
+        arr = (C.c_void_p * len(p))(*p)
+        return arr, (1 if use16 else 0)
+
+    # --------------------------------------------------------------- CPU path --
+    def lookup_torch(self, ids):
+        return F.embedding(ids, self.weight)
+
+    def extra_repr(self):
+        return f"{self.num_embeddings}, {self.embedding_dim}, world={self.world}, sparse={self.sparse}, opt={self.optimizer}"
+
+
+class _LookupSpec:
+    __slots__ = ("table", "col", "bag", "mean", "mul_table", "mul_col")
+
+    def __init__(self, table, col, bag=1, mean=False, mul_table=None, mul_col=None):
+        self.table, self.col, self.bag, self.mean = table, int(col), int(bag), bool(mean)
+        self.mul_table, self.mul_col = mul_table, (int(mul_col) if mul_col is not None else None)
+
+    @property
+    def dim(self):
+        return self.table.embedding_dim
+
+
+def _gather_into(ids, spec, out_window, save_a=None, save_b=None):
+    lib = _nl.cuda_lib()
+    ta, dt = spec.table.table_ptrs()
+    tb, rows_b = None, 0
+    if spec.mul_table is not None:
+        tb, dt2 = spec.mul_table.table_ptrs()
+        if dt2 != dt:
+            raise _nl.NativeError("lookup_mul: both tables must use the same row dtype")
+        rows_b = spec.mul_table.num_embeddings
+    _nl.check(lib.zoo_embedding_gather(ids.data_ptr(), ids.stride(0), spec.col, spec.mul_col or 0, ids.shape[0], spec.bag,
+                                       int(spec.mean), ta, spec.table.num_embeddings, tb, rows_b, spec.table.world,
+                                       spec.dim, dt, out_window.data_ptr(), out_window.stride(0), _nl.ptr(save_a),
+                                       _nl.ptr(save_b), _nl.stream_ptr()), "zoo_embedding_gather")
+
+
+def _sparse_update(table, ids, col, bag, dout_window, mul, grad_scale):
+    lib = _nl.cuda_lib()
+    table._ensure_state()
+    E = ids.shape[0] * bag
+    table._ensure_scratch(E)
+    _nl.check(lib.zoo_hyper_step(table.hyper.data_ptr(), _nl.stream_ptr()), "zoo_hyper_step")
+    _nl.check(lib.zoo_embedding_sparse_update(
+        ids.data_ptr(), ids.stride(0), col, ids.shape[0], bag, dout_window.data_ptr(), dout_window.stride(0),
+        _nl.ptr(mul), mul.stride(0) if mul is not None else 0, float(grad_scale), table.num_embeddings, table.world,
+        table.rank, table.embedding_dim, table.weight.data_ptr(), _nl.ptr(getattr(table, "weight16", None)),
+        _nl.ptr(table.exp_avg), _nl.ptr(table.exp_avg_sq), SPARSE_OPTS[table.optimizer], table.hyper.data_ptr(),
+        table.rep_of_row.data_ptr(), table.accum.data_ptr(), table.dup_flag.data_ptr(), _nl.stream_ptr()),
+        "zoo_embedding_sparse_update")
+
+
+def _dense_grad(table, ids, col, bag, dout_window, mul, grad_scale):
+    lib = _nl.cuda_lib()
+    g = getattr(table.weight, "_zoo_grad", None)
+    ret = None
+    if g is None:
+        g = ret = torch.zeros_like(table.weight, dtype=torch.float32)
+    _nl.check(lib.zoo_embedding_dense_grad(ids.data_ptr(), ids.stride(0), col, ids.shape[0], bag, dout_window.data_ptr(),
+                                           dout_window.stride(0), _nl.ptr(mul), mul.stride(0) if mul is not None else 0,
+                                           float(grad_scale), table.num_embeddings, table.embedding_dim, g.data_ptr(),
+                                           _nl.stream_ptr()), "zoo_embedding_dense_grad")
+    return ret
+
+
+class _MultiLookupFn(torch.autograd.Function):
+    """Gather every spec into its column window of one [B, sum(D)] bf16 buffer."""
+
+    @staticmethod
+    def forward(ctx, ids, specs, *weights):
+        B = ids.shape[0]
+        total = sum(s.dim for s in specs)
+        ld = (total + 7) // 8 * 8
+        out = torch.empty((B, ld), dtype=torch.bfloat16, device=ids.device)
+        if ld != total:
+            out[:, total:].zero_()
+        saves, off = [], 0
+        for s in specs:
+            s.table._ensure_state()
+            sa = sb = None
+            if s.mul_table is not None:
+                s.mul_table._ensure_state()
+                sa = torch.empty((B, s.dim), dtype=torch.bfloat16, device=ids.device)
+                sb = torch.empty((B, s.dim), dtype=torch.bfloat16, device=ids.device)
+            _gather_into(ids, s, out[:, off:off + s.dim], sa, sb)
+            saves += [sa, sb]
+            off += s.dim
+        ctx.specs = specs
+        ctx.total = total
+        ctx.save_for_backward(ids, *[t for t in saves if t is not None])
+        ctx.has_save = [t is not None for t in saves]
+        return out[:, :total]
+
+    @staticmethod
+    def backward(ctx, dout):
+        ids = ctx.saved_tensors[0]
+        saved = list(ctx.saved_tensors[1:])
+        specs = ctx.specs
+        d16 = dout if dout.dtype == torch.bfloat16 else dout.to(torch.bfloat16)
+        if d16.stride(-1) != 1:
+            d16 = d16.contiguous()
+        grads, off, si = [], 0, 0
+        for k, s in enumerate(specs):
+            win = d16[:, off:off + s.dim]
+            sa = sb = None
+            if ctx.has_save[2 * k]:
+                sa, sb = saved[si], saved[si + 1]
+                si += 2
+            scale = 1.0 / s.bag if (s.mean and s.bag > 1) else 1.0
+            pairs = [(s.table, s.col, sb)]
+            if s.mul_table is not None:
+                pairs.append((s.mul_table, s.mul_col, sa))
+            for table, col, mul in pairs:
+                if table.sparse:
+                    _sparse_update(table, ids, col, s.bag, win, mul, scale)
+                    grads.append(None)
+                else:
+                    grads.append(_dense_grad(table, ids, col, s.bag, win, mul, scale))
+            off += s.dim
+        return (None, None, *grads)
+
+
+def _flat_tables(specs):
+    ts = []
+    for s in specs:
+        ts.append(s.table)
+        if s.mul_table is not None:
+            ts.append(s.mul_table)
+    return ts
+
+
+def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None):
+    """ids: int64 [B, ncols].  specs: list of _LookupSpec.  Returns bf16 [B, sum(D)] on GPU, fp32 on CPU."""
+    if ids.dim() == 1:
+        ids = ids.unsqueeze(1)
+    if ids.is_cuda:
+        if ids.dtype != torch.int64:
+            ids = ids.long()
+        weights = [t.anchor if t.sparse else t.weight for t in _flat_tables(specs)]
+        return _MultiLookupFn.apply(ids, specs, *weights)
+    outs = []
+    for s in specs:
+        idc = ids[:, s.col:s.col + s.bag].long()
+        e = s.table.lookup_torch(idc)  # [B, bag, D]
+        if s.mul_table is not None:
+            e = e * s.mul_table.lookup_torch(ids[:, s.mul_col:s.mul_col + s.bag].long())
+        e = e.mean(1) if (s.mean and s.bag > 1) else e.sum(1)
+        outs.append(e)
+    return torch.cat(outs, dim=1) if len(outs) > 1 else outs[0]
+
+
+def lookup(ids, table, col=0, bag=1, mean=False, anchor=None):
+    return multi_lookup(ids, [_LookupSpec(table, col, bag, mean)], anchor)
+
+
+def lookup_mul(ids, table_a, col_a, table_b, col_b, anchor=None):
+    """GMF branch: table_a[ids[:, col_a]] * table_b[ids[:, col_b]]."""
+    return multi_lookup(ids, [_LookupSpec(table_a, col_a, 1, False, table_b, col_b)], anchor)
+
+
+LookupSpec = _LookupSpec
