@@ -1,0 +1,234 @@
+#!/usr/bin/env python
+"""Headline benchmark of zoo-b200 (driver contract: see the task statement / DESIGN.md).
+
+    python bench.py --gpus N --steps K --warmup W [--config ncf|ncf-ml1m|wnd|resnet50|serving]
+    python bench.py --impl reference ...        # the unmodified reference (not runnable offline)
+
+Default config = BASELINE.json config 3: NeuralCF with large embedding tables (12.5 M users x
+1.25 M items PER GPU, i.e. 100 M x 10 M on 8 GPUs, dim 128), row-sharded across the GPUs, MLP
+256-256-128-64, 5 rating classes, Adam, bf16 compute, batch 65,536 per GPU (weak scaling).
+Metric: training samples/second over the whole job.  Data is synthetic (uniform random ids and
+ratings), weights are random-init.
+
+Two measurements are reported:
+  value  -- device time (CUDA events, max over ranks) of K full training steps
+            (forward, fused loss, backward with in-backward sparse Adam, dense optimizer) on
+            batches that already sit in HBM;
+  e2e    -- the same K steps through the public API (`Estimator.from_torch(...).fit`) with every
+            batch copied from pinned host memory and the loss read back to the host every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="zoo", choices=["zoo", "reference"])
+    ap.add_argument("--config", default="ncf")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = config default)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink table sizes (debug only; marks the run invalid)")
+    return ap.parse_args()
+
+
+REFERENCE_UNAVAILABLE = ("reference is a Spark/BigDL JVM stack: pip install of /root/reference fails offline "
+                         "(pyzoo/setup.py needs the Maven-built dist/ jar; no java/mvn/pyspark/bigdl on the box)")
+
+
+class ClockSampler:
+    """nvidia-smi sampler running DURING the timed regions (profiling recipe's clocks line)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "50", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, windows):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.proc.terminate()
+        inside = [r for t, r in self.rows if any(a <= t <= b for a, b in windows)] or [r for _, r in self.rows]
+        sm, mx, reasons = [], [], set()
+        for r in inside:
+            f = [x.strip() for x in r.split(",")]
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(inside)}
+
+
+def build_ncf(args, ctx, torch):
+    from zoo.models.recommendation import NeuralCF
+    from zoo.pipeline.api.keras.objectives import SparseCategoricalCrossEntropy
+
+    W = ctx.world_size
+    if args.config == "ncf":
+        users, items = int(12_500_000 * args.scale) * W, int(1_250_000 * args.scale) * W
+        dims = dict(user_embed=128, item_embed=128, hidden_layers=[256, 128, 64], mf_embed=64)
+        batch = args.batch or 65536
+        model_name = "NeuralCF(100Mx10M@8GPU, dim128, MLP 256-256-128-64)"
+    else:  # ncf-ml1m: the reference's example config (NeuralCFexample.scala:35-38,81-88)
+        users, items = 6040, 3706
+        dims = dict(user_embed=20, item_embed=20, hidden_layers=[20, 10], mf_embed=20)
+        batch = args.batch or 8000
+        model_name = "NeuralCF(ML-1M 6040x3706, embed 20, MLP 40-20-10)"
+    model = NeuralCF(users, items, 5, sparse=True, world=W, rank=ctx.rank, device=ctx.device, **dims)
+    loss = SparseCategoricalCrossEntropy(zero_based_label=False, padding_value=None)
+
+    def make_batches(n, device, pin=False):
+        g = torch.Generator(device="cpu").manual_seed(1234 + ctx.rank)
+        out = []
+        for _ in range(n):
+            x = torch.stack([torch.randint(1, users + 1, (batch,), generator=g),
+                             torch.randint(1, items + 1, (batch,), generator=g)], 1)
+            y = torch.randint(1, 6, (batch,), generator=g)
+            out.append((x.to(device), y.to(device)) if device.type == "cuda" else (x, y))
+        return out
+
+    return dict(model=model, loss=loss, batch=batch, make_batches=make_batches, model_name=model_name,
+                parallelism=("single" if W == 1 else f"dp{W} dense + row-sharded tables x{W}"),
+                extra={"users": users, "items": items, "lr": 1e-3, "optimizer": "adam(dense)+lazy-adam(tables)"})
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
+        return 0
+    import torch
+
+    from zoo.common.nncontext import init_nncontext
+    from zoo.native import lib as nl
+    from zoo.pipeline.estimator import Estimator
+
+    ctx = init_nncontext()
+    if not ctx.is_gpu:
+        print(json.dumps({"error": "bench.py needs a CUDA device"}))
+        return 1
+    dev = ctx.device
+    if args.config in ("ncf", "ncf-ml1m"):
+        cfg = build_ncf(args, ctx, torch)
+    else:
+        from benchmarks.configs import build_other  # wnd / resnet50 / serving
+
+        cfg = build_other(args, ctx, torch)
+    if cfg.get("custom_run"):
+        return cfg["custom_run"](args, ctx)
+
+    opt = torch.optim.Adam([p for p in cfg["model"].parameters() if p.requires_grad] or [torch.zeros(1, requires_grad=True)],
+                           lr=cfg["extra"].get("lr", 1e-3))
+    est = Estimator.from_torch(model=cfg["model"], optimizer=opt, loss=cfg["loss"], ctx=ctx)
+    eng = est.engine
+    eng.prepare()
+    crit = cfg["loss"].to(dev)
+    K, Wm = args.steps, max(args.warmup, 3)
+    from zoo.feature.common import MiniBatch
+
+    # ---------------- device-timed region: batches resident in HBM -----------------------
+    pool = cfg["make_batches"](min(K + Wm, 64), dev)
+    sampler = ClockSampler(dev.index or 0)
+    barrier = (lambda: torch.distributed.barrier()) if ctx.world_size > 1 else (lambda: None)
+    for i in range(Wm):
+        x, y = pool[i % len(pool)]
+        eng.train_step(crit, MiniBatch(x, y, cfg["batch"]))
+    barrier(); torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = nl.LAUNCH_COUNT["n"]
+    t0 = time.time()
+    ev0.record()
+    for i in range(K):
+        x, y = pool[(Wm + i) % len(pool)]
+        loss = eng.train_step(crit, MiniBatch(x, y, cfg["batch"]))
+    ev1.record()
+    barrier(); torch.cuda.synchronize()
+    t1 = time.time()
+    launches = nl.LAUNCH_COUNT["n"] - n0
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    if ctx.world_size > 1:
+        torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+    ms_total = float(ms)
+    loss_val = float(loss)
+    del pool
+
+    # ---------------- end to end through the public API ----------------------------------
+    e2e, win2 = None, None
+    if not args.no_e2e:
+        from zoo.feature.common import FeatureSet
+
+        host = cfg["make_batches"](min(K + Wm, 48), torch.device("cpu"))
+        X = torch.cat([b[0] for b in host]); Y = torch.cat([b[1] for b in host])
+        fs = FeatureSet(features=X, labels=Y, memory_type="DRAM", shuffle=False)  # pinned host cache
+        marks = {}
+
+        def on_step(it, loss_t):
+            k = marks.setdefault("n", 0)
+            if k == Wm:
+                torch.cuda.synchronize(); barrier(); marks["t0"] = time.time()
+            marks["n"] = k + 1
+
+        eng.on_step = on_step
+        eng.async_loss = True
+        h0 = est.engine
+        est.fit(fs, batch_size=cfg["batch"] * ctx.world_size, max_steps=Wm + K, log_every=1, shard=False)
+        torch.cuda.synchronize(); barrier()
+        marks["t1"] = time.time()
+        eng.on_step = None
+        dt = torch.tensor([marks["t1"] - marks["t0"]], device=dev, dtype=torch.float64)
+        if ctx.world_size > 1:
+            torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
+        win2 = (marks["t0"], marks["t1"])
+        bi = cfg["batch"] * (X.shape[1] * X.element_size() + Y.element_size())
+        e2e = {"value": K * cfg["batch"] * ctx.world_size / float(dt), "unit": "samples/s", "h2d_bytes_per_step": bi,
+               "d2h_bytes_per_step": 4, "ms_per_step": float(dt) * 1e3 / K}
+    clocks = sampler.stop([(t0, t1)] + ([win2] if win2 else []))
+
+    if ctx.rank == 0:
+        value = K * cfg["batch"] * ctx.world_size / (ms_total / 1e3)
+        out = {"metric": "NCF training samples/sec" if args.config.startswith("ncf") else cfg.get("metric", "samples/sec"),
+               "value": value, "unit": "samples/s", "n_gpus": ctx.world_size, "steps": K, "warmup": Wm,
+               "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "bf16", "data": "synthetic", "impl": "zoo-b200",
+               "config": {"model": cfg["model_name"], "global_batch": cfg["batch"] * ctx.world_size, "seq_len": None,
+                          "parallelism": cfg["parallelism"],
+                          "l2_policy": "embedding working set >> L2 (tables GBs); a distinct random batch every step",
+                          **cfg["extra"]},
+               "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": loss_val,
+               "invalid_debug_scale": args.scale if args.scale != 1.0 else None}
+        print(json.dumps(out))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

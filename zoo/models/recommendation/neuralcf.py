@@ -1,0 +1,63 @@
+"""NeuralCF: neural collaborative filtering (GMF + MLP).
+
+Reference: pyzoo/zoo/models/recommendation/neuralcf.py:30-99 and
+zoo/src/main/scala/.../models/recommendation/NeuralCF.scala:45-103.  Same constructor arguments
+and the same graph: four embedding tables of `count + 1` rows (ids are 1-based; row 0 is the
+reference's AddConstant offset slot), MLP tower over concat(user, item) with ReLU Dense layers,
+GMF = element-wise product of the MF embeddings, concat -> Dense(class_num) -> softmax.
+Python-side initialisation is `uniform` (neuralcf.py:73-87).
+
+B200 execution: both MLP lookups are ONE gather into the tower's input buffer (concat fused
+away), the GMF product is formed inside the gather kernel, the tower runs on the tcgen05 GEMM
+kernel, the softmax lives in the fused loss kernel during training, and in sparse mode the four
+tables are updated inside backward by the fused sparse optimizer (touched rows only).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from ...ops.dense import FusedDense, FusedMLP
+from ...ops.embedding import EmbeddingTable, LookupSpec, multi_lookup
+from .recommender import Recommender
+
+
+class NeuralCF(Recommender):
+    def __init__(self, user_count, item_count, class_num, user_embed=20, item_embed=20, hidden_layers=(40, 20, 10),
+                 include_mf=True, mf_embed=20, bigdl_type="float", sparse=True, world=1, rank=0, shadow_bf16=False,
+                 device=None):
+        super().__init__()
+        self.user_count, self.item_count, self.class_num = int(user_count), int(item_count), int(class_num)
+        self.user_embed, self.item_embed = int(user_embed), int(item_embed)
+        self.hidden_layers = [int(u) for u in hidden_layers]
+        self.include_mf, self.mf_embed = bool(include_mf), int(mf_embed)
+        self._record_config(user_count=self.user_count, item_count=self.item_count, class_num=self.class_num,
+                            user_embed=self.user_embed, item_embed=self.item_embed, hidden_layers=self.hidden_layers,
+                            include_mf=self.include_mf, mf_embed=self.mf_embed)
+        kw = dict(init="uniform", sparse=sparse, world=world, rank=rank, shadow_bf16=shadow_bf16, device=device)
+        self.mlp_user_embed = EmbeddingTable(self.user_count + 1, self.user_embed, **kw)
+        self.mlp_item_embed = EmbeddingTable(self.item_count + 1, self.item_embed, **kw)
+        self.mlp = FusedMLP(self.user_embed + self.item_embed, self.hidden_layers, activation="relu")
+        last_in = self.hidden_layers[-1]
+        if self.include_mf:
+            assert self.mf_embed > 0
+            self.mf_user_embed = EmbeddingTable(self.user_count + 1, self.mf_embed, **kw)
+            self.mf_item_embed = EmbeddingTable(self.item_count + 1, self.mf_embed, **kw)
+            last_in += self.mf_embed
+        self.linear_last = FusedDense(last_in, self.class_num, activation=None)
+
+    def logits_kind(self):
+        return "softmax"
+
+    def forward_logits(self, x):
+        """x: [B, 2] (user_id, item_id), 1-based like the reference."""
+        ids = x.long() if x.dtype != torch.int64 else x
+        h = multi_lookup(ids, [LookupSpec(self.mlp_user_embed, 0), LookupSpec(self.mlp_item_embed, 1)])
+        h = self.mlp(h)
+        if self.include_mf:
+            mf = multi_lookup(ids, [LookupSpec(self.mf_user_embed, 0, mul_table=self.mf_item_embed, mul_col=1)])
+            h = torch.cat([h, mf.to(h.dtype)], dim=1)
+        return self.linear_last(h)
+
+    def forward(self, x):
+        return torch.softmax(self.forward_logits(x).float(), dim=-1)

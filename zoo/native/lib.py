@@ -95,7 +95,13 @@ def register_cuda_sigs(sigs: dict):
         _bind(_cuda, sigs)
 
 
+LAUNCH_COUNT = {"n": 0}
+_KERNELS_PER_CALL = {"zoo_embedding_sparse_update": 3, "zoo_sumsq": 1}
+
+
 def check(rc: int, what: str = ""):
+    """Raise on a non-zero status; also counts kernel launches (each launcher = 1 kernel unless listed)."""
+    LAUNCH_COUNT["n"] += _KERNELS_PER_CALL.get(what, 1)
     if rc != 0:
         msg = cuda_lib().zoo_last_error().decode(errors="replace")
         raise NativeError(f"{what or 'native call'} failed (code {rc}): {msg}")

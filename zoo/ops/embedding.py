@@ -29,7 +29,7 @@ INT_MAX = 2**31 - 1
 class EmbeddingTable(nn.Module):
     def __init__(self, num_embeddings, embedding_dim, init="uniform", init_scale=0.05, sparse=True,
                  optimizer="adam", lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
-                 world=1, rank=0, shadow_bf16=False, padding_idx=None):
+                 world=1, rank=0, shadow_bf16=False, padding_idx=None, device=None):
         super().__init__()
         self.num_embeddings, self.embedding_dim = int(num_embeddings), int(embedding_dim)
         self.world, self.rank = int(world), int(rank)
@@ -38,7 +38,7 @@ class EmbeddingTable(nn.Module):
         self.opt_cfg = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         self.padding_idx = padding_idx
         self.rows_local = (self.num_embeddings + self.world - 1) // self.world
-        w = torch.empty(self.rows_local, self.embedding_dim)
+        w = torch.empty(self.rows_local, self.embedding_dim, device=device)  # big tables: initialise on the GPU
         if init == "uniform":
             w.uniform_(-init_scale, init_scale)
         elif init == "normal":

@@ -1,0 +1,249 @@
+"""KerasNet / Model / Sequential: the keras-style training face.
+
+Reference: pyzoo/zoo/pipeline/api/keras/engine/topology.py:31-403 and
+zoo/src/main/scala/.../pipeline/api/keras/models/Topology.scala:65-961 -- `compile`
+(string names -> optim/loss/metrics), `fit` (arrays / FeatureSet / ImageSet / TextSet),
+`evaluate`, `predict`, `predict_classes`, `set_tensorboard`, `get_train_summary`,
+`get_validation_summary`, `set_checkpoint`, gradient clipping, `summary`, `saveModel`.
+A KerasNet here is a ``torch.nn.Module``; layers are ``zoo.pipeline.api.keras.layers``.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .....common.triggers import EveryEpoch, MaxEpoch
+from .....feature.common import FeatureSet
+from ..metrics import to_metric
+from ..objectives import to_loss
+
+
+class KerasNet(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self._engine = None
+        self._compiled = None
+        self._pending = {}
+
+    # -- engine plumbing -------------------------------------------------------------
+    def _get_engine(self, optimizer=None):
+        from ....engine import TrainingEngine
+
+        if self._engine is None:
+            self._engine = TrainingEngine(self, optimizer)
+            p = self._pending
+            if "tb" in p:
+                self._engine.set_tensorboard(*p["tb"])
+            if "ckpt" in p:
+                self._engine.set_checkpoint(*p["ckpt"])
+            if "clip" in p:
+                self._engine.clip = p["clip"]
+        return self._engine
+
+    def compile(self, optimizer, loss, metrics=None):
+        """optimizer: name | OptimMethod | torch optimizer | dict per sub-module; loss: name | LossFunction | callable."""
+        loss = to_loss(loss)
+        self._compiled = dict(optimizer=optimizer, loss=loss, metrics=[to_metric(m, loss) for m in (metrics or [])])
+        if self._engine is not None:  # re-compile: keep weights, rebuild optimizer state
+            self._engine.close()
+            self._engine = None
+        self._get_engine(optimizer)
+        return self
+
+    def set_tensorboard(self, log_dir, app_name):
+        self._pending["tb"] = (log_dir, app_name)
+        if self._engine is not None:
+            self._engine.set_tensorboard(log_dir, app_name)
+
+    def get_train_summary(self, tag=None):
+        s = self._engine.train_summary if self._engine else None
+        return [] if s is None else s.read_scalar(tag)
+
+    def get_validation_summary(self, tag=None):
+        s = self._engine.val_summary if self._engine else None
+        return [] if s is None else s.read_scalar(tag)
+
+    def set_checkpoint(self, path, over_write=True):
+        self._pending["ckpt"] = (path, over_write)
+        if self._engine is not None:
+            self._engine.set_checkpoint(path, over_write)
+
+    def clear_gradient_clipping(self):
+        self._pending.pop("clip", None)
+        if self._engine is not None:
+            self._engine.clear_gradient_clipping()
+
+    def set_constant_gradient_clipping(self, min, max):
+        self._pending["clip"] = ("const", float(min), float(max))
+        if self._engine is not None:
+            self._engine.set_constant_gradient_clipping(min, max)
+
+    def set_gradient_clipping_by_l2_norm(self, clip_norm):
+        self._pending["clip"] = ("l2", float(clip_norm))
+        if self._engine is not None:
+            self._engine.set_gradient_clipping_by_l2_norm(clip_norm)
+
+    def set_evaluate_status(self):
+        self.eval()
+        return self
+
+    # -- fit / evaluate / predict ------------------------------------------------------
+    @staticmethod
+    def _as_set(x, y=None):
+        if isinstance(x, FeatureSet):
+            return x
+        if hasattr(x, "to_feature_set"):
+            return x.to_feature_set()
+        if isinstance(x, (list, tuple)) and x and not isinstance(x[0], (np.ndarray, torch.Tensor)):
+            return FeatureSet.sample_rdd(x)
+        return FeatureSet.numpy(x, y)
+
+    def fit(self, x, y=None, batch_size=32, nb_epoch=10, validation_split=0, validation_data=None, distributed=True):
+        if self._compiled is None:
+            raise RuntimeError("compile(optimizer, loss, metrics) must be called before fit")
+        if validation_split and validation_data is None and isinstance(x, np.ndarray) and y is not None:
+            if not 0 <= validation_split <= 1:
+                raise TypeError("validation split must in range [0, 1]")
+            k = int(len(x) * (1 - validation_split))
+            validation_data, x, y = (x[k:], y[k:]), x[:k], y[:k]
+        train = self._as_set(x, y)
+        val = None
+        if validation_data is not None:
+            val = self._as_set(*validation_data) if isinstance(validation_data, (tuple, list)) and len(validation_data) == 2 \
+                else self._as_set(validation_data)
+        eng = self._get_engine(self._compiled["optimizer"])
+        end = MaxEpoch(eng.state["epoch"] + nb_epoch - 1)
+        trig = EveryEpoch() if (val is not None or eng.ckpt_dir is not None) else None
+        eng.train(train, self._compiled["loss"], end, trig, val, self._compiled["metrics"] or (["loss"] if val is not None else None),
+                  batch_size)
+        return self
+
+    def evaluate(self, x, y=None, batch_size=32):
+        if self._compiled is None:
+            raise RuntimeError("compile(...) must be called before evaluate")
+        eng = self._get_engine(self._compiled["optimizer"])
+        methods = [to_metric("loss", self._compiled["loss"])] + list(self._compiled["metrics"])
+        res = eng.evaluate(self._as_set(x, y), methods, batch_size, self._compiled["loss"])
+        return [r.value for r in res]
+
+    def predict(self, x, batch_per_thread=4, distributed=True, batch_size=None):
+        eng = self._get_engine((self._compiled or {}).get("optimizer"))
+        bs = batch_size or max(int(batch_per_thread), 1) * 256
+        return eng.predict(self._as_set(x), bs)
+
+    def predict_classes(self, x, batch_per_thread=4, zero_based_label=True, batch_size=None):
+        p = self.predict(x, batch_per_thread, batch_size=batch_size)
+        c = np.asarray(p).argmax(-1)
+        return c if zero_based_label else c + 1
+
+    # -- misc ----------------------------------------------------------------------------
+    def get_layer(self, name):
+        for n, m in self.named_modules():
+            if n == name or getattr(m, "zoo_name", None) == name:
+                return m
+        raise KeyError(f"no layer named {name!r}")
+
+    @property
+    def layers(self):
+        return list(self.children())
+
+    def flattened_layers(self, include_container=False):
+        return [m for m in self.modules() if include_container or not list(m.children())]
+
+    def summary(self, line_length=120, positions=(.33, .55, .67, 1.)):
+        rows, total = [], 0
+        for n, m in self.named_modules():
+            if n and not list(m.children()):
+                k = sum(p.numel() for p in m.parameters(recurse=False))
+                total += k
+                rows.append((f"{n} ({type(m).__name__})", m.extra_repr()[:40], k))
+        w = [int(line_length * p) for p in positions]
+        print("_" * line_length)
+        print("Layer (type)".ljust(w[0]) + "Config".ljust(w[1] - w[0]) + "Param #")
+        print("=" * line_length)
+        for a, b, k in rows:
+            print(a[:w[0] - 1].ljust(w[0]) + b.ljust(w[1] - w[0]) + str(k))
+        print("=" * line_length)
+        print(f"Total params: {total:,}")
+        return total
+
+    def save(self, path, over_write=False):
+        return self.saveModel(path, None, over_write)
+
+    def saveModel(self, modelPath, weightPath=None, over_write=False):
+        if os.path.exists(modelPath) and not over_write:
+            raise IOError(f"{modelPath} exists; pass over_write=True")
+        torch.save(self, modelPath)
+
+    def to_model(self):
+        return self
+
+
+class Sequential(KerasNet):
+    """Linear stack of layers: `model.add(layer)`."""
+
+    def __init__(self, layers=None, name=None):
+        super().__init__()
+        self.seq = nn.ModuleList()
+        self.zoo_name = name
+        for l in layers or []:
+            self.add(l)
+
+    def add(self, layer):
+        if hasattr(layer, "build_from") and len(self.seq):
+            layer.build_from(self.get_output_shape())
+        self.seq.append(layer)
+        return self
+
+    def get_output_shape(self):
+        shp = None
+        for l in self.seq:
+            if hasattr(l, "compute_output_shape"):
+                shp = l.compute_output_shape(shp)
+        return shp
+
+    def forward(self, *xs):
+        x = xs[0] if len(xs) == 1 else xs
+        for l in self.seq:
+            x = l(*x) if isinstance(x, tuple) and getattr(l, "multi_input", False) else l(x)
+        return x
+
+    def logits_kind(self):
+        last = self.seq[-1] if len(self.seq) else None
+        return getattr(last, "final_activation_kind", None) if hasattr(last, "strip_final_activation") else None
+
+    def forward_logits(self, *xs):
+        """Everything but a trailing softmax/sigmoid activation (enables the fused loss kernels)."""
+        last = self.seq[-1] if len(self.seq) else None
+        strip = getattr(last, "strip_final_activation", None)
+        x = xs[0] if len(xs) == 1 else xs
+        for l in list(self.seq)[:-1]:
+            x = l(x)
+        if last is None:
+            return x
+        return strip(x) if strip is not None else last(x)
+
+
+class Model(KerasNet):
+    """Functional graph container: `Model(input, output)` over symbolic `Variable`s
+    (zoo.pipeline.api.autograd) or a plain callable."""
+
+    def __init__(self, input=None, output=None, name=None, fn=None):
+        super().__init__()
+        self.zoo_name = name
+        if fn is not None:
+            self.fn = fn
+            self.graph = None
+        else:
+            from ...autograd import GraphModule
+
+            self.graph = GraphModule(input, output)
+            self.fn = None
+
+    def forward(self, *xs):
+        if self.graph is not None:
+            return self.graph(*xs)
+        return self.fn(*xs)
