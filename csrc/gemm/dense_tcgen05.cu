@@ -11,8 +11,9 @@
 // (zoo/.../models/recommendation/NeuralCF.scala:73-96, WideAndDeep.scala:146-157) and the
 // separate bias/activation passes of BigDL's Linear+ReLU modules.
 //
-// Roles per CTA (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
-// warp 2 = TMEM allocator, warps 4-7 = epilogue (TMEM -> registers -> global).
+// Roles per CTA (384 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
+// warp 2 = TMEM allocator, warps 4-11 = epilogue (TMEM -> registers -> global; two warps per
+// TMEM lane quarter so every SM sub-partition has two epilogue warps to interleave).
 // Pipelines: 4-stage smem ring (TMA <-> MMA) and a 2-stage TMEM accumulator ring
 // (MMA <-> epilogue) so the epilogue of tile i overlaps the main loop of tile i+1.
 #include "../common/zoo_common.cuh"
@@ -29,7 +30,8 @@ constexpr int kABytes = kBlockM * kBlockK * 2;   // 16 KiB
 constexpr int kBBytes = kMaxN * kBlockK * 2;     // 32 KiB
 constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // + alignment slack
-constexpr int kThreads = 256;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 128 + kEpiWarps * 32;  // 4 control warps + 8 epilogue warps
 constexpr int kMnBoxBytes = kBlockK * 128;       // one MN-major TMA box: 64 k-rows x 128 B
 
 enum Epilogue : int {
@@ -47,21 +49,81 @@ struct GemmArgs {
   int epilogue, act;
   long long ldd;            // leading dimension of out (elements)
   long long ldmask;         // leading dimension of mask (elements)
+  int mask_cols;            // the mask applies to output columns [0, mask_cols) only
   void* out;
   const float* bias;                  // [No] fp32 or null
   const __nv_bfloat16* mask;          // [Mo, ldmask] or null
 };
 
-__device__ __forceinline__ float apply_act(float v, int act) {
-  switch (act) {
-    case ACT_RELU: return fmaxf(v, 0.f);
-    case ACT_GELU: return 0.5f * v * (1.f + erff(v * 0.70710678118654752f));  // exact erf GELU
-    case ACT_SIGMOID: return 1.f / (1.f + __expf(-v));
-    case ACT_TANH: return tanhf(v);
-    default: return v;
+template <int ACT>
+__device__ __forceinline__ float act_fn(float v) {
+  if (ACT == ACT_RELU) return fmaxf(v, 0.f);
+  if (ACT == ACT_GELU) return 0.5f * v * (1.f + erff(v * 0.70710678118654752f));  // exact erf GELU
+  if (ACT == ACT_SIGMOID) return 1.f / (1.f + __expf(-v));
+  if (ACT == ACT_TANH) return tanhf(v);
+  return v;
+}
+
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
+}
+
+// One 32-column chunk of the accumulator tile -> global memory.  FULL == true: the whole chunk is
+// inside the matrix (no per-element guards, 16-byte accesses only).
+template <int EPI, int ACT, bool FULL>
+__device__ __forceinline__ void epilogue_chunk(const GemmArgs& g, const uint32_t (&r)[32], long long row, int col,
+                                               const float* __restrict__ s_bias /* of this chunk */,
+                                               const uint4 (&mk)[4]) {
+  if (EPI == EPI_RED_F32) {
+    float* o = reinterpret_cast<float*>(g.out) + row * g.ldd + col;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      if (FULL || col + j + 4 <= g.No) {
+        red_add_f32x4(o + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                      __uint_as_float(r[j + 3]));
+      } else {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+          if (col + j + t < g.No) atomicAdd(o + j + t, __uint_as_float(r[j + t]));
+      }
+    }
+    return;
+  }
+  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + row * g.ldd + col;
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    float v[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) v[t] = __uint_as_float(r[j + t]);
+    if (EPI == EPI_BIAS_ACT) {
+#pragma unroll
+      for (int t = 0; t < 8; ++t) v[t] = act_fn<ACT>(v[t] + s_bias[j + t]);
+    } else {  // EPI_MASK
+      if (g.mask && col + j < g.mask_cols) {
+        const uint4 m4 = mk[j >> 3];
+        const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const float2 f = unpack_bf16(mw[t]);
+          if (!(f.x > 0.f)) v[2 * t] = 0.f;
+          if (!(f.y > 0.f)) v[2 * t + 1] = 0.f;
+        }
+      }
+    }
+    if (FULL || col + j + 8 <= g.No) {
+      uint4 pk;
+      pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]);
+      pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
+      *reinterpret_cast<uint4*>(o + j) = pk;
+    } else {
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (col + j + t < g.No) o[j + t] = __float2bfloat16(v[t]);
+    }
   }
 }
 
+template <int EPI, int ACT>
 __global__ void __launch_bounds__(kThreads, 1)
 dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                      const __grid_constant__ CUtensorMap tmap_b,
@@ -72,6 +134,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   __shared__ __align__(8) uint64_t tmem_full_bar[kAccStages];
   __shared__ __align__(8) uint64_t tmem_empty_bar[kAccStages];
   __shared__ uint32_t tmem_base_slot;
+  __shared__ __align__(16) float s_bias[kMaxN];
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31u;
@@ -85,10 +148,12 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < kAccStages; ++i) { mbar_init(&tmem_full_bar[i], 1); mbar_init(&tmem_empty_bar[i], 4); }
+    for (int i = 0; i < kAccStages; ++i) { mbar_init(&tmem_full_bar[i], 1); mbar_init(&tmem_empty_bar[i], kEpiWarps); }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(&tmem_base_slot, 512);
+  if (EPI == EPI_BIAS_ACT && g.n_blocks == 1 && threadIdx.x < kMaxN)   // bias of the only N block, once
+    s_bias[threadIdx.x] = (g.bias && (int)threadIdx.x < g.No) ? g.bias[threadIdx.x] : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -169,84 +234,60 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
   } else if (warp >= 4) {
-    // ===================== Epilogue warps (TMEM -> regs -> global) =============
-    const uint32_t q = warp & 3u;  // TMEM lane quarter this warp may access
+    // ============ Epilogue: 8 warps (TMEM -> registers -> global) ==============
+    // Warp w may only touch TMEM lanes 32*(w%4)..+31; warps 4-7 take the first half of the
+    // 32-column chunks of a tile, warps 8-11 the second half.
+    const uint32_t q = warp & 3u;
+    const uint32_t half = (warp - 4u) >> 2;
+    const int nchunks = (g.block_n + 31) / 32;
+    const int c_begin = half == 0 ? 0 : (nchunks + 1) / 2;
+    const int c_end = half == 0 ? (nchunks + 1) / 2 : nchunks;
     uint32_t acc = 0, acc_phase = 0;
+    int bias_blk = g.n_blocks == 1 ? 0 : -1;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
       const int ks = w % g.k_splits;
       const int n_blk = (w / g.k_splits) % g.n_blocks;
       const int m_blk = w / (g.k_splits * g.n_blocks);
       const bool has_work = (ks * g.kb_per_split) < total_kb;
+      if (EPI == EPI_BIAS_ACT && n_blk != bias_blk) {   // N > 256: reload this block's bias slice
+        named_bar_sync(1, kEpiWarps * 32);
+        const int t = threadIdx.x - 128;
+        const int n = n_blk * g.block_n + t;
+        if (t < kMaxN) s_bias[t] = (g.bias && t < g.block_n && n < g.No) ? g.bias[n] : 0.f;
+        named_bar_sync(1, kEpiWarps * 32);
+        bias_blk = n_blk;
+      }
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tc_fence_after();
       const long long row = (long long)m_blk * kBlockM + q * 32 + lane;
       const int col0 = n_blk * g.block_n;
       const uint32_t taddr = tmem_base + acc * kMaxN + ((q * 32u) << 16);
-      for (int c = 0; c < g.block_n; c += 32) {
+      const bool row_ok = row < g.Mo && has_work;
+      for (int c = c_begin; c < c_end; ++c) {
+        const int col = col0 + c * 32;
         uint32_t r[32];
-        tmem_ld_32x32(taddr + c, r);
+        tmem_ld_32x32(taddr + c * 32, r);
+        uint4 mk[4];
+        const bool full = col + 32 <= g.No;
+        if (EPI == EPI_MASK && g.mask && row_ok && full && col < g.mask_cols) {   // issue the mask loads under the TMEM latency
+          const uint4* mp = reinterpret_cast<const uint4*>(g.mask + row * g.ldmask + col);
+#pragma unroll
+          for (int t = 0; t < 4; ++t) mk[t] = ld_nc_u4(mp + t);
+        }
         tmem_ld_wait();
-        if (row < g.Mo && has_work) {
-          const int col = col0 + c;
-          if (g.epilogue == EPI_RED_F32) {
-            float* o = reinterpret_cast<float*>(g.out) + row * g.ldd + col;
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              if (col + j + 4 <= g.No) {
-                red_add_f32x4(o + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]),
-                              __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
-              } else {
-                for (int t = 0; t < 4; ++t)
-                  if (col + j + t < g.No) atomicAdd(o + j + t, __uint_as_float(r[j + t]));
-              }
-            }
+        if (row_ok) {
+          if (full) {
+            epilogue_chunk<EPI, ACT, true>(g, r, row, col, s_bias + c * 32, mk);
           } else {
-            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + row * g.ldd + col;
-            const __nv_bfloat16* mk = g.mask ? g.mask + row * g.ldmask + col : nullptr;
+            if (EPI == EPI_MASK && g.mask && col < g.mask_cols) {
+              const __nv_bfloat16* mp = g.mask + row * g.ldmask + col;
+              __nv_bfloat16 tmp[32];
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              float v[8];
+              for (int t = 0; t < 32; ++t) tmp[t] = (col + t < g.No) ? mp[t] : __float2bfloat16(0.f);
 #pragma unroll
-              for (int t = 0; t < 8; ++t) v[t] = __uint_as_float(r[j + t]);
-              if (col + j + 8 <= g.No) {
-                if (g.epilogue == EPI_BIAS_ACT) {
-                  if (g.bias) {
-                    const float4 b0 = *reinterpret_cast<const float4*>(g.bias + col + j);
-                    const float4 b1 = *reinterpret_cast<const float4*>(g.bias + col + j + 4);
-                    v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-                    v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
-                  }
-#pragma unroll
-                  for (int t = 0; t < 8; ++t) v[t] = apply_act(v[t], g.act);
-                } else if (mk) {
-                  const uint4 m4 = *reinterpret_cast<const uint4*>(mk + j);
-                  const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
-#pragma unroll
-                  for (int t = 0; t < 4; ++t) {
-                    const float2 f = unpack_bf16(mw[t]);
-                    if (!(f.x > 0.f)) v[2 * t] = 0.f;
-                    if (!(f.y > 0.f)) v[2 * t + 1] = 0.f;
-                  }
-                }
-                uint4 pk;
-                pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]);
-                pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
-                *reinterpret_cast<uint4*>(o + j) = pk;
-              } else {
-                for (int t = 0; t < 8; ++t) {
-                  if (col + j + t < g.No) {
-                    float x = v[t];
-                    if (g.epilogue == EPI_BIAS_ACT) {
-                      if (g.bias) x += g.bias[col + j + t];
-                      x = apply_act(x, g.act);
-                    } else if (mk) {
-                      if (!(__bfloat162float(mk[j + t]) > 0.f)) x = 0.f;
-                    }
-                    o[j + t] = __float2bfloat16(x);
-                  }
-                }
-              }
+              for (int t = 0; t < 4; ++t) mk[t] = reinterpret_cast<const uint4*>(tmp)[t];
             }
+            epilogue_chunk<EPI, ACT, false>(g, r, row, col, s_bias + c * 32, mk);
           }
         }
       }
@@ -349,14 +390,26 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
   if (!b_mn) rc = make_tmap(&tb, B, g.No, g.R, ldb, kBlockK, bn);
   else       rc = make_tmap(&tb, B, g.R, g.No, ldb, 64, kBlockK);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
-    ZOO_CUDA_CHECK(cudaFuncSetAttribute(dense_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set = true;
-  }
   const int total_work = g.m_blocks * g.n_blocks * g.k_splits;
   const int grid = total_work < max_ctas ? total_work : max_ctas;
-  dense_tcgen05_kernel<<<grid, kThreads, kSmemBytes, stream>>>(ta, tb, g);
+#define ZOO_LAUNCH(EPI, ACT)                                                                                   \
+  do {                                                                                                         \
+    static bool attr_set = false;                                                                              \
+    if (!attr_set) {                                                                                           \
+      ZOO_CUDA_CHECK(cudaFuncSetAttribute(dense_tcgen05_kernel<EPI, ACT>,                                      \
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));          \
+      attr_set = true;                                                                                         \
+    }                                                                                                          \
+    dense_tcgen05_kernel<EPI, ACT><<<grid, kThreads, kSmemBytes, stream>>>(ta, tb, g);                         \
+  } while (0)
+  if (g.epilogue == EPI_RED_F32) ZOO_LAUNCH(EPI_RED_F32, ACT_NONE);
+  else if (g.epilogue == EPI_MASK) ZOO_LAUNCH(EPI_MASK, ACT_NONE);
+  else if (g.act == ACT_RELU) ZOO_LAUNCH(EPI_BIAS_ACT, ACT_RELU);
+  else if (g.act == ACT_GELU) ZOO_LAUNCH(EPI_BIAS_ACT, ACT_GELU);
+  else if (g.act == ACT_SIGMOID) ZOO_LAUNCH(EPI_BIAS_ACT, ACT_SIGMOID);
+  else if (g.act == ACT_TANH) ZOO_LAUNCH(EPI_BIAS_ACT, ACT_TANH);
+  else ZOO_LAUNCH(EPI_BIAS_ACT, ACT_NONE);
+#undef ZOO_LAUNCH
   ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;
 }
@@ -376,11 +429,15 @@ ZOO_API int zoo_dense_fwd_bf16(const void* x, long long ldx, const void* w, long
 }
 
 // dX[M,K] (bf16, lddx) = (dY[M,N] (bf16, lddy) * W[N,K] (bf16, ldw)) * (mask[M,K] > 0)   (mask may be null)
+// mask_cols: the ReLU mask covers dX columns [0, mask_cols) (multiple of 8; <= 0 means all K columns).
 ZOO_API int zoo_dense_dgrad_bf16(const void* dy, long long lddy, const void* w, long long ldw, const void* mask,
-                                 long long ldmask, void* dx, long long lddx, int M, int N, int K, void* stream) {
+                                 long long ldmask, int mask_cols, void* dx, long long lddx, int M, int N, int K,
+                                 void* stream) {
   GemmArgs g{};
   g.Mo = M; g.No = K; g.R = N; g.epilogue = EPI_MASK; g.act = ACT_NONE;
   g.out = dx; g.ldd = lddx; g.bias = nullptr; g.mask = (const __nv_bfloat16*)mask; g.ldmask = ldmask;
+  g.mask_cols = (mask_cols <= 0 || mask_cols > K) ? K : mask_cols;
+  if (g.mask_cols % 8 && g.mask_cols != K) { zoo_set_last_error("dense_dgrad: mask_cols must be a multiple of 8", __FILE__, __LINE__); return ZOO_ERR_ARG; }
   if (lddx % 8 || ((uintptr_t)dx & 15) || (mask && (ldmask % 8 || ((uintptr_t)mask & 15)))) {
     zoo_set_last_error("dense_dgrad: output/mask rows must be 16-byte aligned", __FILE__, __LINE__);
     return ZOO_ERR_ARG;

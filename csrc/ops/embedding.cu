@@ -94,9 +94,15 @@ embedding_gather_kernel(const long long* __restrict__ ids, int id_stride, int id
             for (int t = 0; t < VN; ++t) vb[t] = 0.f;
           }
           if (save_a) {  // keep both factors (bf16) for the product rule in backward
-            for (int t = 0; t < VN; ++t) {
-              save_a[(long long)warp * D + c + t] = __float2bfloat16(va[t]);
-              save_b[(long long)warp * D + c + t] = __float2bfloat16(vb[t]);
+            __nv_bfloat16* pa = save_a + (long long)warp * D + c;
+            __nv_bfloat16* pb = save_b + (long long)warp * D + c;
+#pragma unroll
+            for (int t = 0; t < VN; t += 4) {
+              uint2 ua, ub;
+              ua.x = pack_bf16(va[t], va[t + 1]); ua.y = pack_bf16(va[t + 2], va[t + 3]);
+              ub.x = pack_bf16(vb[t], vb[t + 1]); ub.y = pack_bf16(vb[t + 2], vb[t + 3]);
+              *reinterpret_cast<uint2*>(pa + t) = ua;
+              *reinterpret_cast<uint2*>(pb + t) = ub;
             }
           }
 #pragma unroll
@@ -201,35 +207,47 @@ __device__ __forceinline__ void entry_grad(const BwdEntries& en, int e, int c, f
 }
 
 // Pass 2: entries that lost the election add their gradient into the representative's
-// accumulation row (fp32, vector red) and flag it.  One warp per entry.
+// accumulation row (fp32, vector red) and flag it.  A warp scans 32 entries at once (one per
+// lane) and then cooperates on each loser, so tables without duplicates cost one coalesced
+// pass over ids + rep_of_row and nothing else.
 template <bool VEC>
 __global__ void __launch_bounds__(256)
 emb_accum_kernel(BwdEntries en, int E, long long rows, int world, int rank, const int* __restrict__ rep_of_row,
                  int D, float* __restrict__ accum, int* __restrict__ dup_flag) {
-  const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (e >= E) return;
-  const long long id = entry_row(en, e);
-  if (id < 0 || id >= rows) return;
-  if (world > 1 && (int)(id % world) != rank) return;
-  const long long local = world > 1 ? id / world : id;
-  const int rep = rep_of_row[local];
-  if (rep == e) return;
-  float* arow = accum + (long long)rep * D;
-  if (VEC) {
-    for (int c = lane * 4; c < D; c += 128) {
-      float g[4];
-      entry_grad<true>(en, e, c, g);
-      red_add_f32x4(arow + c, g[0], g[1], g[2], g[3]);
-    }
-  } else {
-    for (int c = lane; c < D; c += 32) {
-      float g[4];
-      entry_grad<false>(en, e, c, g);
-      atomicAdd(arow + c, g[0]);
+  const int e_mine = warp_global * 32 + lane;
+  int rep_mine = -1;
+  if (e_mine < E) {
+    const long long id = entry_row(en, e_mine);
+    if (id >= 0 && id < rows && !(world > 1 && (int)(id % world) != rank)) {
+      const long long local = world > 1 ? id / world : id;
+      const int rep = rep_of_row[local];
+      if (rep != e_mine) rep_mine = rep;
     }
   }
-  if (lane == 0) dup_flag[rep] = 1;
+  unsigned losers = __ballot_sync(0xffffffffu, rep_mine >= 0);
+  while (losers) {
+    const int src = __ffs(losers) - 1;
+    losers &= losers - 1;
+    const int e = warp_global * 32 + src;
+    const int rep = __shfl_sync(0xffffffffu, rep_mine, src);
+    float* arow = accum + (long long)rep * D;
+    if (VEC) {
+      for (int c = lane * 4; c < D; c += 128) {
+        float g[4];
+        entry_grad<true>(en, e, c, g);
+        red_add_f32x4(arow + c, g[0], g[1], g[2], g[3]);
+      }
+    } else {
+      for (int c = lane; c < D; c += 32) {
+        float g[4];
+        entry_grad<false>(en, e, c, g);
+        atomicAdd(arow + c, g[0]);
+      }
+    }
+    if (lane == 0) dup_flag[rep] = 1;
+  }
 }
 
 enum SparseOpt : int { SOPT_SGD = 0, SOPT_ADAM = 1, SOPT_ADAGRAD = 2 };
@@ -453,11 +471,12 @@ ZOO_API int zoo_embedding_sparse_update(const long long* ids, int id_stride, int
   const int threads = 256;
   emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row);
   const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
+  const unsigned ab = (unsigned)((E + threads - 1) / threads);  // accum: one lane per entry
   if (vec) {
-    emb_accum_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
+    emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
     emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
   } else {
-    emb_accum_kernel<false><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
+    emb_accum_kernel<false><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
     emb_apply_kernel<false><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
   }
   ZOO_CUDA_CHECK(cudaGetLastError());

@@ -79,6 +79,72 @@ softmax_nll_kernel(const T* __restrict__ logits, long long ldl, const long long*
   }
 }
 
+// Few classes (C <= 16, e.g. 5 ratings or binary): one THREAD per row, the row lives in registers.
+template <typename T>
+__global__ void __launch_bounds__(256)
+softmax_nll_small_kernel(const T* __restrict__ logits, long long ldl, const long long* __restrict__ labels, int B, int C,
+                         int label_offset, long long padding_value, int has_padding, const float* __restrict__ class_w,
+                         float eps, float loss_scale, float grad_scale, float* __restrict__ loss_out,
+                         float* __restrict__ row_loss, T* __restrict__ dlogits, long long ldd, float* __restrict__ probs,
+                         long long ldp) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float blk_loss[8];
+  __shared__ float blk_cnt[8];
+  float l = 0.f, cnt = 0.f;
+  if (row < B) {
+    const T* x = logits + (long long)row * ldl;
+    float v[16];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      v[c] = c < C ? ldf(x + c) : -INFINITY;
+      mx = fmaxf(mx, v[c]);
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      v[c] = c < C ? __expf(v[c] - mx) : 0.f;
+      sum += v[c];
+    }
+    const float inv = 1.f / sum;
+    const long long raw = labels[row];
+    const bool pad = has_padding && raw == padding_value;
+    const long long t = raw - label_offset;
+    const bool valid = !pad && t >= 0 && t < C;
+    float w = 1.f, pt = 1.f;
+    bool clipped = false;
+    if (valid) {
+      w = class_w ? class_w[t] : 1.f;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) if (c == (int)t) pt = v[c] * inv;
+      clipped = (pt < eps) || (pt > 1.f - eps);
+      pt = fminf(fmaxf(pt, eps), 1.f - eps);
+      l = -w * __logf(pt);
+      cnt = 1.f;
+    }
+    const float gs = (valid && !clipped) ? w * grad_scale : 0.f;
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      if (c < C) {
+        const float p = v[c] * inv;
+        if (probs) probs[(long long)row * ldp + c] = p;
+        if (dlogits) stf(dlogits + (long long)row * ldd + c, gs * (p - (c == (int)t ? 1.f : 0.f)));
+      }
+    }
+    if (row_loss) row_loss[row] = l;
+  }
+  l = warp_sum(l);
+  cnt = warp_sum(cnt);
+  if ((threadIdx.x & 31) == 0) { blk_loss[threadIdx.x >> 5] = l; blk_cnt[threadIdx.x >> 5] = cnt; }
+  __syncthreads();
+  if (threadIdx.x == 0 && loss_out) {
+    float a = 0.f, n = 0.f;
+    for (int i = 0; i < 8; ++i) { a += blk_loss[i]; n += blk_cnt[i]; }
+    atomicAdd(loss_out, a * loss_scale);
+    atomicAdd(loss_out + 1, n);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 sigmoid_bce_kernel(const T* __restrict__ logits, const float* __restrict__ targets, long long n, int from_probs,
@@ -124,6 +190,19 @@ ZOO_API int zoo_softmax_nll(const void* logits, long long ldl, const long long* 
   if (B == 0) return ZOO_OK;
   const unsigned blocks = (unsigned)(((long long)B * 32 + 255) / 256);
   cudaStream_t s = (cudaStream_t)stream;
+  if (C <= 16) {
+    const unsigned sb = (unsigned)((B + 255) / 256);
+    if (dtype == 0)
+      softmax_nll_small_kernel<float><<<sb, 256, 0, s>>>((const float*)logits, ldl, labels, B, C, label_offset, padding_value,
+                                                         has_padding, class_w, eps, loss_scale, grad_scale, loss_out, row_loss,
+                                                         (float*)dlogits, ldd, probs, ldp);
+    else
+      softmax_nll_small_kernel<__nv_bfloat16><<<sb, 256, 0, s>>>((const __nv_bfloat16*)logits, ldl, labels, B, C, label_offset,
+                                                                 padding_value, has_padding, class_w, eps, loss_scale, grad_scale,
+                                                                 loss_out, row_loss, (__nv_bfloat16*)dlogits, ldd, probs, ldp);
+    ZOO_CUDA_CHECK(cudaGetLastError());
+    return ZOO_OK;
+  }
   if (dtype == 0)
     softmax_nll_kernel<float><<<blocks, 256, 0, s>>>((const float*)logits, ldl, labels, B, C, label_offset, padding_value,
                                                      has_padding, class_w, eps, loss_scale, grad_scale, loss_out, row_loss,

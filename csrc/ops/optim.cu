@@ -61,8 +61,10 @@ dense_opt_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
 
 // hyper[H_STEP] += 1 (keeps the bias-correction step on the device so the launch sequence is
 // identical every iteration and can be replayed from a CUDA graph).
-__global__ void hyper_step_kernel(float* hyper) {
-  if (threadIdx.x == 0 && blockIdx.x == 0) hyper[H_STEP] += 1.f;
+__global__ void hyper_step_kernel(float* hyper, const float* __restrict__ src) {
+  // Optional refresh of every slot but the step from a staging copy of the host-side values.
+  if (src && threadIdx.x < ZOO_HYPER_LEN && threadIdx.x != H_STEP) hyper[threadIdx.x] = src[threadIdx.x];
+  if (threadIdx.x == 0) hyper[H_STEP] += 1.f;
 }
 
 // Sum of squares with a scratch array of per-block partials, finished by the last block.
@@ -125,25 +127,44 @@ clip_kernel(float* __restrict__ g, long long n, const float* __restrict__ sumsq,
 }
 
 // out[c] += sum_r x[r, c]   (bias gradient of a Dense layer; x bf16 with leading dim ldx, out fp32)
+// Each thread owns 8 consecutive columns (one 16-byte load per row); `lpr` lanes cover a row
+// and a warp walks 32/lpr rows at a time.  Requires ldx % 8 == 0 (checked by the launcher).
 __global__ void __launch_bounds__(256)
 colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int rows, int cols, float* __restrict__ out,
-                   int rows_per_block) {
-  // block = 256 threads = 32 column lanes x 8 row groups; grid.x over column tiles of 32, grid.y over row chunks
-  __shared__ float red[8][33];
-  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
-  const int rg = threadIdx.x >> 5;
+                   int rows_per_block, int lpr, int col_base) {
+  __shared__ float red[8][32][9];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int sub = lane % lpr;              // which 8-column group of the row
+  const int rsel = lane / lpr;             // which row of the warp's row bundle
+  const int rows_per_warp = 32 / lpr;
+  const int c0 = col_base + blockIdx.x * (lpr * 8) + sub * 8;
   const int r0 = blockIdx.y * rows_per_block;
   const int r1 = min(rows, r0 + rows_per_block);
-  float acc = 0.f;
-  if (c < cols)
-    for (int r = r0 + rg; r < r1; r += 8) acc += __bfloat162float(x[(long long)r * ldx + c]);
-  red[rg][threadIdx.x & 31] = acc;
-  __syncthreads();
-  if (rg == 0 && c < cols) {
-    float s = 0.f;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (c0 < cols) {
+    const bool full = c0 + 8 <= cols;
+    for (int r = r0 + wid * rows_per_warp + rsel; r < r1; r += 8 * rows_per_warp) {
+      const __nv_bfloat16* p = x + (long long)r * ldx + c0;
+      if (full) {
+        const uint4 u = ld_nc_u4(p);
+        const float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
+        acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += c.x; acc[5] += c.y; acc[6] += d.x; acc[7] += d.y;
+      } else {
+        for (int t = 0; t < 8; ++t) if (c0 + t < cols) acc[t] += __bfloat162float(p[t]);
+      }
+    }
+  }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) s += red[i][threadIdx.x];
-    atomicAdd(out + c, s);
+  for (int t = 0; t < 8; ++t) red[wid][lane][t] = acc[t];
+  __syncthreads();
+  // thread (t8 = threadIdx.x % 8 column, g = threadIdx.x / 8 -> 8-column group `sub`) finishes the reduction
+  const int t8 = threadIdx.x & 7, sg = threadIdx.x >> 3;
+  if (sg < lpr) {
+    float s = 0.f;
+    for (int w = 0; w < 8; ++w)
+      for (int rr = 0; rr < rows_per_warp; ++rr) s += red[w][rr * lpr + sg][t8];
+    const int c = col_base + blockIdx.x * (lpr * 8) + sg * 8 + t8;
+    if (c < cols) atomicAdd(out + c, s);
   }
 }
 
@@ -182,9 +203,9 @@ ZOO_API int zoo_dense_opt_step(float* p, float* g, float* m, float* v, void* p16
   return ZOO_OK;
 }
 
-ZOO_API int zoo_hyper_step(float* hyper, void* stream) {
+ZOO_API int zoo_hyper_step(float* hyper, const float* src, void* stream) {
   if (!hyper) return ZOO_ERR_ARG;
-  hyper_step_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(hyper);
+  hyper_step_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(hyper, src);
   ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;
 }
@@ -220,15 +241,22 @@ ZOO_API int zoo_clip_const(float* g, long long n, float lo, float hi, void* stre
 }
 
 ZOO_API int zoo_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* out, void* stream) {
-  if (!x || !out || rows < 0 || cols <= 0) return ZOO_ERR_ARG;
+  if (!x || !out || rows < 0 || cols <= 0 || (ldx % 8) || ((uintptr_t)x & 15)) {
+    zoo_set_last_error("colsum_bf16: bad arguments (rows need 16-byte alignment)", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
   if (rows == 0) return ZOO_OK;
-  const int col_tiles = (cols + 31) / 32;
+  int groups = (cols + 7) / 8;             // 8-column groups per row
+  int lpr = 1;
+  while (lpr < groups && lpr < 32) lpr <<= 1;
+  const int col_tiles = (groups + lpr - 1) / lpr;
   int chunks = (148 * 4) / col_tiles;
   if (chunks < 1) chunks = 1;
   int rpb = (rows + chunks - 1) / chunks;
-  if (rpb < 64) rpb = 64;
+  const int min_rows = 8 * (32 / lpr) * 4;
+  if (rpb < min_rows) rpb = min_rows;
   chunks = (rows + rpb - 1) / rpb;
-  colsum_bf16_kernel<<<dim3(col_tiles, chunks), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ldx, rows, cols, out, rpb);
+  colsum_bf16_kernel<<<dim3(col_tiles, chunks), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ldx, rows, cols, out, rpb, lpr, 0);
   ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;
 }

@@ -78,13 +78,29 @@ def test_dense_wgrad(M, N, K):
     torch.testing.assert_close(dw / scale, ref / scale, atol=2e-2, rtol=2e-2)
 
 
+def test_dense_dgrad_partial_mask():
+    from zoo.ops.dense import dense_dgrad
+
+    torch.manual_seed(7)
+    M, N, K = 1000, 8, 128
+    dy = _bf(torch.randn(M, N, device="cuda"))
+    w = _bf(torch.randn(N, K, device="cuda"))
+    mask = _bf(torch.randn(M, K, device="cuda"))
+    dx = dense_dgrad(dy, w, mask, mask_cols=64)
+    ref = dy.float() @ w.float()
+    ref[:, :64] = ref[:, :64] * (mask[:, :64].float() > 0)
+    torch.testing.assert_close(dx.float(), ref, atol=3e-2, rtol=2e-2)
+
+
 def test_colsum():
     from zoo.ops.dense import colsum
 
-    dy = _bf(torch.randn(5000, 72, device="cuda"))
-    out = torch.zeros(72, device="cuda")
-    colsum(dy, out)
-    torch.testing.assert_close(out, dy.float().sum(0), atol=1e-2, rtol=1e-3)
+    for rows, cols in [(5000, 72), (65536, 256), (777, 8), (4096, 64), (3000, 520), (100, 5)]:
+        ld = (cols + 7) // 8 * 8
+        dy = _bf(torch.randn(rows, ld, device="cuda"))[:, :cols]
+        out = torch.zeros(cols, device="cuda")
+        colsum(dy, out)
+        torch.testing.assert_close(out, dy.float().sum(0), atol=2e-2, rtol=2e-3)
 
 
 def test_fused_mlp_autograd_matches_torch():

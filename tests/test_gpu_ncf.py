@@ -56,3 +56,35 @@ def test_smoke_entry():
     import __graft_entry__ as g
 
     g.smoke()
+
+
+def test_cuda_graph_step_matches_eager():
+    from zoo.common.nncontext import init_nncontext
+    from zoo.feature.common import MiniBatch
+    from zoo.models.recommendation import NeuralCF
+    from zoo.pipeline.api.keras.objectives import SparseCategoricalCrossEntropy
+    from zoo.pipeline.estimator import Estimator
+
+    ctx = init_nncontext()
+    torch.manual_seed(0)
+    base = NeuralCF(500, 300, 5, user_embed=64, item_embed=64, hidden_layers=[128, 64], mf_embed=32)
+    x, y = _data(500, 300, 5, 8 * 1024)
+    xs = torch.from_numpy(x).cuda().split(1024)
+    ys = torch.from_numpy(y).cuda().split(1024)
+    results = []
+    for use_graph in (False, True):
+        m = copy.deepcopy(base)
+        est = Estimator.from_torch(model=m, optimizer=torch.optim.Adam(m.parameters(), lr=1e-2),
+                                   loss=SparseCategoricalCrossEntropy(zero_based_label=False, padding_value=None), ctx=ctx)
+        est.engine.use_cuda_graph = use_graph
+        est.engine.prepare()
+        losses = []
+        for a, b in zip(xs, ys):
+            losses.append(float(est.engine.train_step(est.loss.cuda(), MiniBatch(a, b, 1024))))
+        torch.cuda.synchronize()
+        assert (est.engine._graph is not None and est.engine._graph["graph"] is not None) == use_graph
+        results.append((losses, m.linear_last.weight.detach().clone(), m.mlp_user_embed.weight.detach().clone()))
+    (l0, w0, e0), (l1, w1, e1) = results
+    torch.testing.assert_close(torch.tensor(l0), torch.tensor(l1), atol=2e-3, rtol=2e-3)
+    torch.testing.assert_close(w0, w1, atol=1e-3, rtol=1e-2)
+    assert (e0 - e1).abs().max() < 1e-2 and ((e0 - e1).abs() > 1e-3).float().mean() < 1e-3

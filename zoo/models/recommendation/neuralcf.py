@@ -44,7 +44,14 @@ class NeuralCF(Recommender):
             self.mf_user_embed = EmbeddingTable(self.user_count + 1, self.mf_embed, **kw)
             self.mf_item_embed = EmbeddingTable(self.item_count + 1, self.mf_embed, **kw)
             last_in += self.mf_embed
-        self.linear_last = FusedDense(last_in, self.class_num, activation=None)
+        # The last layer's dgrad applies the ReLU mask of the MLP output (first columns of its
+        # input) in its epilogue, so the tower's last ReLU needs no separate backward pass.
+        fuse_mask = self.hidden_layers[-1] % 8 == 0
+        self.linear_last = FusedDense(last_in, self.class_num, activation=None, relu_input=fuse_mask,
+                                      relu_input_cols=self.hidden_layers[-1] if self.include_mf else 0)
+        self.mlp[-1].skip_relu_bwd = fuse_mask
+
+    graph_safe = True  # static shapes, no host-side control flow: the step can be CUDA-graph captured
 
     def logits_kind(self):
         return "softmax"

@@ -125,6 +125,8 @@ class WideAndDeep(Recommender):
             self.deep_part = _DeepPart((ci.indicator_dims, ci.embed_in_dims, ci.embed_out_dims, len(ci.continuous_cols)),
                                        self.hidden_layers, self.class_num, sparse)
 
+    graph_safe = True  # static shapes, no host-side control flow: the step can be CUDA-graph captured
+
     def logits_kind(self):
         return "softmax"
 

@@ -21,7 +21,7 @@ c_void_p, c_int, c_ll, c_float = C.c_void_p, C.c_int, C.c_longlong, C.c_float
 # name -> argtypes (all launchers return int; 0 == ok)
 _CUDA_SIGS = {
     "zoo_dense_fwd_bf16": [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_int, c_void_p],
-    "zoo_dense_dgrad_bf16": [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_ll, c_int, c_int, c_int, c_void_p],
+    "zoo_dense_dgrad_bf16": [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_ll, c_int, c_void_p, c_ll, c_int, c_int, c_int, c_void_p],
     "zoo_dense_wgrad_bf16": [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_ll, c_int, c_int, c_int, c_void_p],
     "zoo_embedding_gather": [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_ll, c_void_p, c_ll, c_int,
                              c_int, c_int, c_void_p, c_ll, c_void_p, c_void_p, c_void_p],
@@ -32,7 +32,7 @@ _CUDA_SIGS = {
     "zoo_embedding_dense_grad": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_ll, c_void_p, c_ll, c_float, c_ll,
                                  c_int, c_void_p, c_void_p],
     "zoo_dense_opt_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_void_p, c_int, c_void_p],
-    "zoo_hyper_step": [c_void_p, c_void_p],
+    "zoo_hyper_step": [c_void_p, c_void_p, c_void_p],
     "zoo_sumsq": [c_void_p, c_ll, c_void_p, c_void_p, c_int, c_void_p],
     "zoo_clip_l2": [c_void_p, c_ll, c_void_p, c_float, c_void_p],
     "zoo_clip_const": [c_void_p, c_ll, c_float, c_float, c_void_p],

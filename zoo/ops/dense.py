@@ -60,8 +60,8 @@ def dense_forward(x16: torch.Tensor, w16: torch.Tensor, bias: torch.Tensor | Non
     return out
 
 
-def dense_dgrad(dy16, w16, mask16=None, out=None):
-    """dx = (dy16 @ w16) * (mask16 > 0)."""
+def dense_dgrad(dy16, w16, mask16=None, out=None, mask_cols=0):
+    """dx = (dy16 @ w16) * (mask16 > 0); with mask_cols > 0 only columns [0, mask_cols) are masked."""
     M, N = dy16.shape
     K = w16.shape[1]
     if out is None:
@@ -69,7 +69,7 @@ def dense_dgrad(dy16, w16, mask16=None, out=None):
         out = torch.empty((M, ldk), dtype=torch.bfloat16, device=dy16.device)[:, :K]
     lib = _nl.cuda_lib()
     _nl.check(lib.zoo_dense_dgrad_bf16(dy16.data_ptr(), dy16.stride(0), w16.data_ptr(), w16.stride(0),
-                                       _nl.ptr(mask16), mask16.stride(0) if mask16 is not None else 0,
+                                       _nl.ptr(mask16), mask16.stride(0) if mask16 is not None else 0, int(mask_cols),
                                        out.data_ptr(), out.stride(0), M, N, K, _nl.stream_ptr()),
               "zoo_dense_dgrad_bf16")
     return out
@@ -99,7 +99,7 @@ class _FusedDenseFn(torch.autograd.Function):
     when the parameters carry ``_zoo_grad`` views (set by the flat-parameter arena)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False):
+    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False, relu_input_cols=0):
         x16 = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
         if not _aligned(x16):
             x16 = _pad_cols(x16)
@@ -107,6 +107,7 @@ class _FusedDenseFn(torch.autograd.Function):
         ctx.act = act
         ctx.relu_input = relu_input
         ctx.skip_relu_bwd = skip_relu_bwd
+        ctx.relu_input_cols = relu_input_cols
         ctx.in_dtype = x.dtype
         ctx.save_for_backward(x16, w16, y if act == "relu" else None, weight, bias)
         return y
@@ -125,7 +126,8 @@ class _FusedDenseFn(torch.autograd.Function):
         K = weight.shape[1]
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = dense_dgrad(dy16, w16[:, :K] if w16.shape[1] != K else w16, x16[:, :K] if ctx.relu_input else None)
+            dx = dense_dgrad(dy16, w16[:, :K] if w16.shape[1] != K else w16, x16[:, :K] if ctx.relu_input else None,
+                             mask_cols=ctx.relu_input_cols)
             if dx.dtype != ctx.in_dtype:
                 dx = dx.to(ctx.in_dtype)
         gw = getattr(weight, "_zoo_grad", None)
@@ -143,7 +145,7 @@ class _FusedDenseFn(torch.autograd.Function):
             elif ctx.needs_input_grad[2]:
                 db_ret = torch.zeros_like(bias, dtype=torch.float32)
                 colsum(dy16, db_ret)
-        return dx, dw_ret, db_ret, None, None, None, None
+        return dx, dw_ret, db_ret, None, None, None, None, None
 
 
 def _pad_cols(t: torch.Tensor) -> torch.Tensor:
@@ -161,11 +163,12 @@ class FusedDense(nn.Module):
     lazily here when the master changes."""
 
     def __init__(self, in_features, out_features, activation=None, bias=True, init="glorot_uniform",
-                 relu_input=False):
+                 relu_input=False, relu_input_cols=0):
         super().__init__()
         self.in_features, self.out_features = int(in_features), int(out_features)
         self.activation = activation if activation not in ("linear", "none") else None
         self.relu_input = relu_input  # input is the output of a ReLU: fuse its mask into dgrad
+        self.relu_input_cols = int(relu_input_cols)  # >0: only the first columns of the input are ReLU outputs
         self.skip_relu_bwd = False    # set when the ONLY consumer is a FusedDense with relu_input=True
         self.weight = nn.Parameter(torch.empty(out_features, in_features))
         self.bias = nn.Parameter(torch.zeros(out_features)) if bias else None
@@ -202,7 +205,7 @@ class FusedDense(nn.Module):
             x2 = x.reshape(-1, x.shape[-1])
             self.refresh_shadow()
             y = _FusedDenseFn.apply(x2, self.weight, self.bias, self.weight_bf16, self.activation, self.relu_input,
-                                    self.skip_relu_bwd)
+                                    self.skip_relu_bwd, self.relu_input_cols)
             return y.reshape(*lead, self.out_features)
         y = F.linear(x.to(self.weight.dtype), self.weight, self.bias)
         return _act_torch(y, self.activation)

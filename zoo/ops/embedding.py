@@ -159,7 +159,7 @@ def _sparse_update(table, ids, col, bag, dout_window, mul, grad_scale):
     table._ensure_state()
     E = ids.shape[0] * bag
     table._ensure_scratch(E)
-    _nl.check(lib.zoo_hyper_step(table.hyper.data_ptr(), _nl.stream_ptr()), "zoo_hyper_step")
+    _nl.check(lib.zoo_hyper_step(table.hyper.data_ptr(), None, _nl.stream_ptr()), "zoo_hyper_step")
     _nl.check(lib.zoo_embedding_sparse_update(
         ids.data_ptr(), ids.stride(0), col, ids.shape[0], bag, dout_window.data_ptr(), dout_window.stride(0),
         _nl.ptr(mul), mul.stride(0) if mul is not None else 0, float(grad_scale), table.num_embeddings, table.world,

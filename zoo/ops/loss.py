@@ -15,6 +15,9 @@ import torch
 from ..native import lib as _nl
 
 EPS = 1e-8
+# Set by the training engine around its own `loss.backward()`: the upstream gradient of the loss
+# is exactly 1, so backward hands the kernel-produced dlogits straight on (no extra multiply).
+UNIT_UPSTREAM = {"on": False}
 
 
 def softmax_nll_reference(logits, labels, zero_based_label=True, padding_value=None, class_weights=None,
@@ -48,7 +51,11 @@ class _SoftmaxNLLFn(torch.autograd.Function):
             logits = logits.contiguous()
         labels = labels.long().contiguous()
         out = torch.zeros(2, dtype=torch.float32, device=logits.device)
-        dlog = torch.empty_like(logits)
+        ld = (Cn + 7) // 8 * 8  # padded rows: the next consumer is a TMA-fed GEMM (16-byte rows)
+        dlog = torch.empty((B, ld), dtype=logits.dtype, device=logits.device)
+        if ld != Cn:
+            dlog[:, Cn:].zero_()
+        dlog = dlog[:, :Cn]
         has_pad = padding_value is not None
         # mean over B is folded into the kernel; with padding the divisor is only known afterwards
         scale = (1.0 / max(B, 1)) if (size_average and not has_pad) else 1.0
@@ -68,7 +75,10 @@ class _SoftmaxNLLFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (dlog,) = ctx.saved_tensors
-        return dlog * g.to(dlog.dtype), None, None, None, None, None, None
+        if UNIT_UPSTREAM["on"]:
+            return dlog, None, None, None, None, None, None
+        full = dlog.as_strided((dlog.shape[0], dlog.stride(0)), (dlog.stride(0), 1)) * g.to(dlog.dtype)
+        return full[:, :dlog.shape[1]], None, None, None, None, None, None
 
 
 def softmax_nll(logits, labels, zero_based_label=True, padding_value=None, class_weights=None, size_average=True,

@@ -42,6 +42,9 @@ class LocalSync:
     def step(self):
         self.fopt.step()
 
+    def graph_safe(self):
+        return True
+
     def close(self):
         pass
 
@@ -66,6 +69,9 @@ class AllReduceSync(LocalSync):
 
     def fopt_buffers(self):
         return []
+
+    def graph_safe(self):
+        return False
 
     def step(self):
         import torch.distributed as dist

@@ -210,6 +210,7 @@ class FusedOptimizer:
         if dev.type == "cuda":
             self.hyper_host = self.hyper_host.pin_memory()
         self.hyper_dev = self.hyper_host.to(dev)
+        self.hyper_stage = None
         self.grad_scale = 1.0
         self._lr_now = [g.cfg.lr for g in groups]
         self._dirty = True
@@ -217,6 +218,15 @@ class FusedOptimizer:
         self._norm_scratch = None
         self.clip_l2 = None
         self.clip_const = None
+        self.graph_mode = False   # inside a captured step: hyper-parameters are re-read from pinned memory
+
+    def pre_graph_replay(self):
+        """Host-side part of a step whose device part is replayed from a CUDA graph."""
+        self.step_count += 1
+        self._apply_schedules()
+        for i in range(len(self.groups)):
+            self.hyper_host[i, H_LR] = self._lr_now[i]
+            self.hyper_host[i, H_GSCALE] = self.grad_scale
 
     # -- configuration ---------------------------------------------------------
     @staticmethod
@@ -269,16 +279,20 @@ class FusedOptimizer:
         self.clip_l2 = self.clip_const = None
 
     def _sync_hyper(self):
-        if not self._dirty:
-            return
+        """Push host-side hyper-parameters (lr after schedules, gradient scale) to the device: one
+        contiguous pinned->device copy into a staging buffer; `zoo_hyper_step` then merges it into
+        the live array while advancing the device-side step.  Returns True when a refresh is due."""
+        if not self._dirty and not self.graph_mode:
+            return False
         for i, g in enumerate(self.groups):
             self.hyper_host[i, H_LR] = self._lr_now[i]
             self.hyper_host[i, H_GSCALE] = self.grad_scale
-        # step lives on the device (advanced by zoo_hyper_step); keep it when refreshing
         if self.arena.device.type == "cuda":
-            self.hyper_dev[:, :H_STEP].copy_(self.hyper_host[:, :H_STEP], non_blocking=True)
-            self.hyper_dev[:, H_GSCALE:].copy_(self.hyper_host[:, H_GSCALE:], non_blocking=True)
+            if self.hyper_stage is None:
+                self.hyper_stage = torch.zeros_like(self.hyper_dev)
+            self.hyper_stage.copy_(self.hyper_host, non_blocking=True)
         self._dirty = False
+        return True
 
     def _apply_schedules(self):
         for i, g in enumerate(self.groups):
@@ -316,14 +330,15 @@ class FusedOptimizer:
         a = self.arena
         self.step_count += 1
         self._apply_schedules()
-        self._sync_hyper()
+        refresh = self._sync_hyper()
         self.clip_gradients()
         if a.device.type == "cuda":
             lib, st = _nl.cuda_lib(), _nl.stream_ptr()
             for i, g in enumerate(self.groups):
                 n = g.end - g.start
                 hp = self.hyper_dev[i].data_ptr()
-                _nl.check(lib.zoo_hyper_step(hp, st), "zoo_hyper_step")
+                src = self.hyper_stage[i].data_ptr() if refresh else None
+                _nl.check(lib.zoo_hyper_step(hp, src, st), "zoo_hyper_step")
                 _nl.check(lib.zoo_dense_opt_step(
                     a.flat_p[g.start:].data_ptr(), a.flat_g[g.start:].data_ptr(),
                     self.m[g.start:].data_ptr() if (self.m is not None and g.cfg.needs_m) else None,

@@ -140,6 +140,8 @@ class TrainingEngine:
         self.last_throughput = 0.0
         self.on_step = None          # optional callback(iteration, loss_tensor) after every step
         self.async_loss = False      # read the loss back with a one-step lag (no pipeline stall)
+        self.use_cuda_graph = None   # None = auto (models that declare `graph_safe = True`)
+        self._graph = None
         self._loss_ring = None
         self._last_criterion = None
 
@@ -349,12 +351,66 @@ class TrainingEngine:
         out = m(*x) if isinstance(x, tuple) else m(x)
         return criterion(out, y), out
 
-    def train_step(self, criterion, batch: MiniBatch):
-        loss, _ = self.forward_loss(criterion, batch.inputs, batch.targets)
-        loss.backward()
+    def _eager_step(self, criterion, inputs, targets):
+        from ..ops import loss as _fused_loss
+
+        loss, _ = self.forward_loss(criterion, inputs, targets)
+        _fused_loss.UNIT_UPSTREAM["on"] = True   # we seed backward with exactly 1.0
+        try:
+            loss.backward()
+        finally:
+            _fused_loss.UNIT_UPSTREAM["on"] = False
         self._dp.step()          # gradient exchange fused with the optimizer
         self._after_step_shadows()
-        return loss
+        return loss.detach()
+
+    def _graph_enabled(self):
+        if self.device.type != "cuda":
+            return False
+        if self.use_cuda_graph is not None:
+            return bool(self.use_cuda_graph)
+        return bool(getattr(self.model, "graph_safe", False)) and self._dp.graph_safe()
+
+    def train_step(self, criterion, batch: MiniBatch):
+        """One optimizer step.  Launch-bound models replay the whole step (forward, loss, backward,
+        sparse + dense optimizers) from ONE CUDA graph: ~40 launches become one `cudaGraphLaunch`."""
+        if not self._graph_enabled():
+            return self._eager_step(criterion, batch.inputs, batch.targets)
+        g = self._graph
+        key = (id(criterion), tuple((tuple(t.shape), t.dtype) for t in _flatten(batch.inputs) + _flatten(batch.targets)))
+        if g is None or g["key"] != key:
+            g = self._graph = self._capture(criterion, batch, key)
+            if g["count"] <= g["warm"]:
+                return g["loss"]
+        if g["graph"] is None:          # still warming up eagerly
+            g["count"] += 1
+            loss = self._eager_step(criterion, batch.inputs, batch.targets)
+            if g["count"] > g["warm"]:
+                self._finish_capture(criterion, batch)
+            return loss
+        for dst, src in zip(g["static"], _flatten(batch.inputs) + _flatten(batch.targets)):
+            dst.copy_(src, non_blocking=True)
+        self.fopt.pre_graph_replay()
+        g["graph"].replay()
+        return g["loss"]
+
+    def _capture(self, criterion, batch, key):
+        g = {"key": key, "graph": None, "count": 1, "warm": 3, "static": None, "loss": None}
+        g["loss"] = self._eager_step(criterion, batch.inputs, batch.targets)
+        return g
+
+    def _finish_capture(self, criterion, batch):
+        g = self._graph
+        clone = lambda x: None if x is None else (tuple(t.clone() for t in x) if isinstance(x, (tuple, list)) else x.clone())
+        s_in, s_tg = clone(batch.inputs), clone(batch.targets)
+        g["static"] = _flatten(s_in) + _flatten(s_tg)
+        torch.cuda.synchronize()
+        self.fopt.graph_mode = True
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            g["loss"] = self._eager_step(criterion, s_in, s_tg)
+        self.fopt.step_count -= 1  # capture does not execute; the step is counted at replay
+        g["graph"] = graph
 
     def _make_set(self, data, batch_size=None, labels=None):
         if isinstance(data, FeatureSet):
