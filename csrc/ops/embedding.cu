@@ -504,3 +504,114 @@ ZOO_API int zoo_embedding_dense_grad(const long long* ids, int id_stride, int id
   ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free variant of zoo_embedding_sparse_update.
+//
+// Who needs it: code that must apply an embedding update but is not allowed to obtain device
+// memory at that point -- a latency-critical serving/online-learning thread (cudaMalloc and
+// cudaFree synchronise the whole device and take the driver's allocator lock), a host callback
+// running inside another framework's stream where allocating is forbidden, or a process that
+// handed its entire HBM budget to a pool at start-up so a late cudaMalloc would simply fail.
+// Such callers still own the table, its optimizer state, the ids and the gradient rows; what
+// they cannot provide is the three scratch buffers of the regular entry point.  Here that
+// scratch lives in ONE statically allocated device array (below), so the limits are fixed:
+//
+//     local table rows  (rows / world, rounded up)  <= ZOO_NOALLOC_MAX_ROWS     (1,048,576)
+//     entries per call  (B * bag)                   <= ZOO_NOALLOC_MAX_ENTRIES  (8,192)
+//     embedding width   D                           <= ZOO_NOALLOC_MAX_DIM      (128)
+//
+// Larger problems are refused with ZOO_ERR_TOO_LARGE (use the regular entry point and pass your
+// own scratch).  The array costs about 8.03 MiB of device memory on EVERY GPU whose context
+// loads this library, from load until the process exits, whether or not the entry point is used.
+//
+// Sharing rules.  All calls on a device use the same array and it keeps whatever the previous
+// call left behind, so every call first re-initialises the part it is going to use (row map to
+// INT_MAX, accumulation rows and duplicate flags to zero) on the caller's stream.  Two calls
+// whose kernels can overlap on the GPU (different streams without an ordering between them, or
+// several host threads) would corrupt each other's scratch: serialise them.
+//
+// First call on a device.  The device address of the array is looked up once per device (with
+// that device current) on the first call made there; do that first call outside of any CUDA
+// stream capture.
+#define ZOO_NOALLOC_MAX_ROWS (1 << 20)
+#define ZOO_NOALLOC_MAX_ENTRIES 8192
+#define ZOO_NOALLOC_MAX_DIM 128
+
+namespace zoo {
+constexpr size_t kNaRepBytes = sizeof(int) * (size_t)ZOO_NOALLOC_MAX_ROWS;                              // row -> entry map
+constexpr size_t kNaAccumBytes = sizeof(float) * (size_t)ZOO_NOALLOC_MAX_ENTRIES * ZOO_NOALLOC_MAX_DIM;  // duplicate sums
+constexpr size_t kNaDupBytes = sizeof(int) * (size_t)ZOO_NOALLOC_MAX_ENTRIES;                            // duplicate flags
+constexpr size_t kNaTotalBytes = kNaRepBytes + kNaAccumBytes + kNaDupBytes;
+}  // namespace zoo
+
+// File-scope device storage.  In HOST code this name is only a handle for the runtime's symbol
+// table -- it is not a device address and must never be handed to a kernel; the address comes
+// from cudaGetSymbolAddress (see noalloc_scratch_base below).
+static __device__ __align__(256) unsigned char g_zoo_noalloc_scratch[zoo::kNaTotalBytes];
+
+namespace zoo {
+constexpr int kNaMaxDevices = 64;
+static void* g_na_base[kNaMaxDevices] = {nullptr};
+
+// Per-device set-up: resolve the device address of the static array for the CURRENT device.
+static int noalloc_scratch_base(unsigned char** base) {
+  int dev = -1;
+  ZOO_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNaMaxDevices) {
+    zoo_set_last_error("embedding_sparse_update_noalloc: device ordinal out of range", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  if (!g_na_base[dev]) {
+    void* p = nullptr;
+    ZOO_CUDA_CHECK(cudaGetSymbolAddress(&p, g_zoo_noalloc_scratch));
+    if (!p) {
+      zoo_set_last_error("embedding_sparse_update_noalloc: cudaGetSymbolAddress returned null", __FILE__, __LINE__);
+      return ZOO_ERR_CUDA;
+    }
+    g_na_base[dev] = p;
+  }
+  *base = static_cast<unsigned char*>(g_na_base[dev]);
+  return ZOO_OK;
+}
+}  // namespace zoo
+
+// Same arguments and results as zoo_embedding_sparse_update, minus the three scratch pointers.
+// Calls no cudaMalloc / cudaFree and no allocating library routine; see the block comment above
+// for the limits, the sharing rules and the first-call note.
+ZOO_API int zoo_embedding_sparse_update_noalloc(const long long* ids, int id_stride, int id_col, int B, int bag,
+                                                const void* dout, long long ldg, const void* mul, long long ldmul,
+                                                float grad_scale, long long rows, int world, int rank, int D,
+                                                float* w, void* w16, float* m, float* v, int opt,
+                                                const float* hyper, void* stream) {
+  if (world < 1 || world > kMaxPeers || B < 0 || bag < 1 || D <= 0 || rows <= 0) {
+    zoo_set_last_error("embedding_sparse_update_noalloc: bad arguments", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  const long long rows_local = (rows + world - 1) / world;
+  const long long E = (long long)B * bag;
+  if (rows_local > ZOO_NOALLOC_MAX_ROWS || E > ZOO_NOALLOC_MAX_ENTRIES || D > ZOO_NOALLOC_MAX_DIM) {
+    char msg[256];
+    snprintf(msg, sizeof(msg),
+             "embedding_sparse_update_noalloc: problem exceeds the static scratch (local rows %lld > %d, or entries "
+             "%lld > %d, or dim %d > %d); use zoo_embedding_sparse_update with caller-owned scratch",
+             rows_local, ZOO_NOALLOC_MAX_ROWS, E, ZOO_NOALLOC_MAX_ENTRIES, D, ZOO_NOALLOC_MAX_DIM);
+    zoo_set_last_error(msg, __FILE__, __LINE__);
+    return ZOO_ERR_TOO_LARGE;
+  }
+  if (E == 0) return ZOO_OK;
+  unsigned char* base = nullptr;
+  const int rc = noalloc_scratch_base(&base);
+  if (rc != ZOO_OK) return rc;
+  int* rep_of_row = reinterpret_cast<int*>(base);
+  float* accum = reinterpret_cast<float*>(base + kNaRepBytes);
+  int* dup_flag = reinterpret_cast<int*>(base + kNaRepBytes + kNaAccumBytes);
+  cudaStream_t s = (cudaStream_t)stream;
+  // The array still holds the previous call's state: bring the used part to its start values.
+  fill_i32_kernel<<<256, 256, 0, s>>>(rep_of_row, rows_local, INT_MAX);
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  ZOO_CUDA_CHECK(cudaMemsetAsync(accum, 0, sizeof(float) * (size_t)E * D, s));
+  ZOO_CUDA_CHECK(cudaMemsetAsync(dup_flag, 0, sizeof(int) * (size_t)E, s));
+  return zoo_embedding_sparse_update(ids, id_stride, id_col, B, bag, dout, ldg, mul, ldmul, grad_scale, rows, world,
+                                     rank, D, w, w16, m, v, opt, hyper, rep_of_row, accum, dup_flag, stream);
+}

@@ -54,6 +54,19 @@ int zoo_embedding_sparse_update(const long long* ids, int id_stride, int id_col,
                                 float grad_scale, long long rows, int world, int rank, int D,
                                 float* w, void* w16, float* m, float* v, int opt, const float* hyper,
                                 int* rep_of_row, float* accum, int* dup_flag, void* stream);
+/* No counterpart in the reference (it has no device memory to manage).  Allocation-free variant of
+ * zoo_embedding_sparse_update for callers that may not allocate device memory where they run
+ * (latency-critical serving threads, host callbacks inside another runtime's stream, processes
+ * whose HBM budget is already committed): the scratch is a static device array inside the
+ * library, so local rows <= 1,048,576, B*bag <= 8,192 and D <= 128, else ZOO_ERR_TOO_LARGE.
+ * The array (~8 MiB) is held on every GPU that loads the library.  Calls share it: do not let two
+ * calls overlap on the GPU.  The first call on a device resolves the array's device address;
+ * make it outside stream capture. */
+int zoo_embedding_sparse_update_noalloc(const long long* ids, int id_stride, int id_col, int B, int bag,
+                                        const void* dout, long long ldg, const void* mul, long long ldmul,
+                                        float grad_scale, long long rows, int world, int rank, int D,
+                                        float* w, void* w16, float* m, float* v, int opt,
+                                        const float* hyper, void* stream);
 int zoo_embedding_dense_grad(const long long* ids, int id_stride, int id_col, int B, int bag,
                              const void* dout, long long ldg, const void* mul, long long ldmul,
                              float grad_scale, long long rows, int D, float* dtable, void* stream);
