@@ -1,0 +1,82 @@
+"""Fused reduce-scatter + optimizer + all-gather kernel (K1) and the flag barrier.
+
+Single-GPU tests run all ranks inside ONE cooperative launch (`emulate=1`): kernels that wait on
+one another must never be separate launches on one GPU.  The multi-GPU test spawns one process per
+GPU with torchrun and is skipped on boxes with fewer than 2 GPUs.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _arr(ts):
+    return (C.c_void_p * len(ts))(*[t.data_ptr() if t is not None else None for t in ts])
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("opt", ["adam", "sgd"])
+def test_rs_opt_ag_emulated_matches_torch(world, opt):
+    import zoo.parallel.symm  # registers signatures
+    from zoo.native import lib as nl
+    from zoo.parallel.flat import OPT_IDS, OptConfig
+
+    lib = nl.cuda_lib()
+    torch.manual_seed(0)
+    n = 4 * world * 1000
+    p0 = torch.randn(n, device="cuda")
+    ps = [p0.clone() for _ in range(world)]
+    p16 = [p0.to(torch.bfloat16) for _ in range(world)]
+    gs = [torch.randn(n, device="cuda") for _ in range(world)]
+    ms = [torch.zeros(n, device="cuda") for _ in range(world)]
+    vs = [torch.zeros(n, device="cuda") for _ in range(world)]
+    flags = [torch.zeros(2 * world * 64, dtype=torch.int32, device="cuda") for _ in range(world)]
+    epochs = [torch.zeros(64, dtype=torch.int32, device="cuda") for _ in range(world)]
+    cfg = OptConfig("adam", lr=1e-2) if opt == "adam" else OptConfig("sgd", lr=1e-2, b1=0.9)
+    ref_p = p0.clone().requires_grad_(True)
+    ref_opt = torch.optim.Adam([ref_p], lr=1e-2) if opt == "adam" else torch.optim.SGD([ref_p], lr=1e-2, momentum=0.9)
+    st = torch.cuda.current_stream().cuda_stream
+    for step in range(1, 4):
+        hv = torch.tensor(cfg.hyper_vector(step=float(step), gscale=1.0 / world), dtype=torch.float32, device="cuda")
+        hy = [hv] * world
+        gsum = sum(gs) / world
+        nl.check(lib.zoo_rs_opt_ag(_arr(gs), _arr(ps), _arr(p16), _arr(ms), _arr(vs), _arr(flags), _arr(epochs), _arr(hy),
+                                   0, n, world, 0, 1, OPT_IDS[cfg.name], 1, 8, st), "zoo_rs_opt_ag")
+        ref_p.grad = gsum.clone()
+        ref_opt.step()
+        torch.cuda.synchronize()
+        for r in range(world):
+            torch.testing.assert_close(ps[r], ref_p.detach(), atol=1e-5, rtol=1e-4)
+            torch.testing.assert_close(p16[r].float(), ref_p.detach(), atol=2e-2, rtol=2e-2)
+            assert float(gs[r].abs().sum()) == 0.0       # gradients zeroed for the next iteration
+        gs = [g.normal_() for g in gs]
+    assert int(epochs[0][0]) == 3
+
+
+def test_p2p_barrier_emulated():
+    import zoo.parallel.symm  # noqa: F401
+    from zoo.native import lib as nl
+
+    lib = nl.cuda_lib()
+    world = 8
+    flags = [torch.zeros(world, dtype=torch.int32, device="cuda") for _ in range(world)]
+    epochs = [torch.zeros(1, dtype=torch.int32, device="cuda") for _ in range(world)]
+    for _ in range(5):
+        nl.check(lib.zoo_p2p_barrier(_arr(flags), _arr(epochs), world, 0, 1, torch.cuda.current_stream().cuda_stream), "bar")
+    torch.cuda.synchronize()
+    assert all(int(e[0]) == 5 for e in epochs) and all(int(f.min()) == 5 for f in flags)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_dp_p2p_matches_nccl_multi_gpu():
+    n = min(torch.cuda.device_count(), 8)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(root, "tests", "mgpu_dp_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "MGPU_DP_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

@@ -87,6 +87,8 @@ def make_grad_sync(ctx, mode="auto"):
         mode = ctx.conf.get("zoo.comm.backend", "auto")
     if mode == "auto":
         mode = "p2p" if ctx.is_gpu else "gloo"
+    if mode in ("nccl", "gloo", "allreduce"):
+        return AllReduceSync(ctx)
     if mode == "p2p":
         try:
             from .p2p import P2PFusedSync

@@ -103,11 +103,12 @@ class FlatParamArena:
         self.device = device or named_params[0][1].device
         self.names = [n for n, _ in named_params]
         self.params = [p for _, p in named_params]
+        self.align = max(pad_to, _ALIGN)   # every tensor (hence every group boundary) starts on this many elements
         self.offsets, off = [], 0
         for p in self.params:
             self.offsets.append(off)
-            off += _round_up(p.numel(), _ALIGN)
-        self.numel = _round_up(off, max(pad_to, _ALIGN))
+            off += _round_up(p.numel(), self.align)
+        self.numel = _round_up(off, self.align)
         alloc = allocator or (lambda n, dtype: torch.zeros(n, dtype=dtype, device=self.device))
         self.flat_p = alloc(self.numel, torch.float32)
         self.flat_g = alloc(self.numel, torch.float32)
@@ -254,7 +255,7 @@ class FusedOptimizer:
             if cur is None or cur.name != str(k):
                 cur = ParamGroup(str(k), off, off, per_module[k] if k is not None else default_cfg)
                 groups.append(cur)
-            cur.end = off + _round_up(p.numel(), _ALIGN)
+            cur.end = off + _round_up(p.numel(), arena.align)
             cur.params.append(p)
         groups[-1].end = arena.numel
         return FusedOptimizer(arena, groups)

@@ -1,0 +1,105 @@
+"""P2PFusedSync: the product path of data-parallel training on GPUs.
+
+Gradient reduce-scatter, optimizer and weight all-gather are ONE kernel over NVLink peer memory
+(`csrc/comm/rs_opt_ag.cu`, kernel K1); this module owns its plumbing: the three arenas live in the
+symmetric heap, flags and epochs are allocated once, and a step is `zoo_hyper_step` +
+`zoo_rs_opt_ag` per parameter group.  torch.distributed (NCCL) is used only to exchange IPC
+handles and to broadcast the initial weights.
+"""
+from __future__ import annotations
+
+import torch
+
+from ..native import lib as _nl
+from .flat import OPT_IDS
+from .symm import get_heap, ptr_array
+
+
+class P2PFusedSync:
+    name = "p2p"
+
+    def __init__(self, ctx):
+        if not ctx.is_gpu:
+            raise RuntimeError("P2P path needs CUDA devices")
+        self.ctx = ctx
+        self.heap = get_heap(ctx)
+        self.fopt = None
+        self._bufs = []
+        self.max_grid = 64
+
+    # -- arena allocation in the symmetric heap -------------------------------------------
+    def allocator(self):
+        def alloc(n, dtype):
+            esize = torch.empty(0, dtype=dtype).element_size()
+            buf = self.heap.alloc(n * esize)
+            self._bufs.append(buf)
+            return buf.tensor(dtype, n)
+
+        return alloc
+
+    def pad_to(self):
+        return max(8, 4 * self.ctx.world_size)
+
+    def graph_safe(self):
+        return True
+
+    def attach(self, fopt):
+        self.fopt = fopt
+        W = self.ctx.world_size
+        fopt.set_grad_scale(1.0 / W)
+        a = fopt.arena
+        by_ptr = {b.local_ptr: b for b in self._bufs}
+        self.buf_p, self.buf_g = by_ptr[a.flat_p.data_ptr()], by_ptr[a.flat_g.data_ptr()]
+        self.buf_p16 = by_ptr[a.flat_p16.data_ptr()] if a.flat_p16 is not None else None
+        self.flag_buf = self.heap.alloc(4 * 2 * W * self.max_grid)
+        self.epoch = torch.zeros(self.max_grid, dtype=torch.int32, device=self.ctx.device)
+        self.bar_flags = self.heap.alloc(4 * W)
+        self.bar_epoch = torch.zeros(1, dtype=torch.int32, device=self.ctx.device)
+        r = self.ctx.rank
+        self._g = ptr_array(self.buf_g.ptrs)
+        self._p = ptr_array(self.buf_p.ptrs)
+        self._p16 = ptr_array(self.buf_p16.ptrs) if self.buf_p16 is not None else None
+        loc = lambda t: ptr_array([t.data_ptr() if (t is not None and i == r) else None for i in range(W)])
+        self._m, self._v = loc(fopt.m), loc(fopt.v)
+        self._flags = ptr_array(self.flag_buf.ptrs)
+        self._epoch = loc(self.epoch)
+        self._bflags = ptr_array(self.bar_flags.ptrs)
+        self._bepoch = loc(self.bar_epoch)
+
+    def broadcast_parameters(self):
+        import torch.distributed as dist
+
+        a = self.fopt.arena
+        dist.broadcast(a.flat_p, src=0)
+        if a.flat_p16 is not None:
+            a.flat_p16.copy_(a.flat_p)
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    def barrier(self):
+        """Device-side barrier on the current stream (no host sync, no NCCL)."""
+        _nl.check(_nl.cuda_lib().zoo_p2p_barrier(self._bflags, self._bepoch, self.ctx.world_size, self.ctx.rank, 0,
+                                                 _nl.stream_ptr()), "zoo_p2p_barrier")
+
+    def _grid_for(self, n):
+        per_rank_units = n // (4 * self.ctx.world_size)
+        return int(min(self.max_grid, max(4, (per_rank_units + 2047) // 2048)))
+
+    def step(self):
+        f = self.fopt
+        if f.clip_l2 is not None or f.clip_const is not None:
+            raise NotImplementedError("gradient clipping with the fused P2P exchange: use grad_sync='nccl'")
+        f.step_count += 1
+        f._apply_schedules()
+        refresh = f._sync_hyper()
+        lib, st, W, r = _nl.cuda_lib(), _nl.stream_ptr(), self.ctx.world_size, self.ctx.rank
+        for i, g in enumerate(f.groups):
+            hp = f.hyper_dev[i].data_ptr()
+            _nl.check(lib.zoo_hyper_step(hp, f.hyper_stage[i].data_ptr() if refresh else None, st), "zoo_hyper_step")
+            hy = ptr_array([hp if k == r else None for k in range(W)])
+            _nl.check(lib.zoo_rs_opt_ag(self._g, self._p, self._p16, self._m, self._v, self._flags, self._epoch, hy,
+                                        g.start, g.end, W, r, 0, OPT_IDS[g.cfg.name], 1, self._grid_for(g.end - g.start),
+                                        st), "zoo_rs_opt_ag")
+
+    def close(self):
+        pass
