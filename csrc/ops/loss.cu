@@ -157,12 +157,13 @@ sigmoid_bce_kernel(const T* __restrict__ logits, const float* __restrict__ targe
     const float x = ldf(logits + i);
     const float y = targets[i];
     const float p_raw = from_probs ? x : 1.f / (1.f + __expf(-x));
-    const float p = fminf(fmaxf(p_raw, eps), 1.f - eps);
-    acc += -(y * __logf(p) + (1.f - y) * __logf(1.f - p));
+    // 1 - 1e-8 rounds to 1 in fp32, so p and 1-p are floored separately (no log(0), no 0/0)
+    const float p = fmaxf(p_raw, eps), q = fmaxf(1.f - p_raw, eps);
+    acc += -(y * __logf(p) + (1.f - y) * __logf(q));
     if (dlogits) {
       float g;
-      if (from_probs) g = (p_raw < eps || p_raw > 1.f - eps) ? 0.f : (p - y) / (p * (1.f - p));
-      else g = p - y;
+      if (from_probs) g = -(p_raw < eps ? 0.f : y / p) + (1.f - p_raw < eps ? 0.f : (1.f - y) / q);
+      else g = p_raw - y;
       stf(dlogits + i, g * grad_scale);
     }
   }

@@ -74,8 +74,11 @@ class SessionRecommender(Recommender):
     def recommend_for_session(self, sessions, max_items, zero_based_label=True):
         """sessions: list of Samples / arrays (session[, history]).  Returns, per session, a list of
         (item, probability) of length `max_items`, best first."""
-        feats = [(s.features if hasattr(s, "features") else (list(s) if isinstance(s, (list, tuple)) else [s])) for s in sessions]
-        xs = [np.stack([np.asarray(f[i]) for f in feats]) for i in range(len(feats[0]))]
+        if isinstance(sessions, tuple) and all(hasattr(s, "ndim") and s.ndim == 2 for s in sessions):
+            xs = [np.asarray(s) for s in sessions]          # already batched: (session[B,L], history[B,H])
+        else:
+            feats = [(s.features if hasattr(s, "features") else (list(s) if isinstance(s, (list, tuple)) else [s])) for s in sessions]
+            xs = [np.stack([np.asarray(f[i]) for f in feats]) for i in range(len(feats[0]))]
         probs = torch.as_tensor(np.asarray(self.predict(xs[0] if len(xs) == 1 else xs)))
         top = probs.topk(int(max_items), dim=-1)
         off = 0 if zero_based_label else 1

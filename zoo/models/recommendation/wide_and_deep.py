@@ -149,4 +149,32 @@ class WideAndDeep(Recommender):
         return out
 
     def forward(self, *xs):
+        if len(xs) == 1 and isinstance(xs[0], (tuple, list)):
+            xs = tuple(xs[0])
         return torch.softmax(self.forward_logits(*xs).float(), dim=-1)
+
+    def example_inputs(self, n, rng=None, device=None):
+        """Random inputs of the right shapes and id ranges (tests, benchmarks, tracing)."""
+        import numpy as np
+
+        rng = rng or np.random.RandomState(0)
+        ci, out = self.column_info, []
+        if self.model_type in ("wide", "wide_n_deep"):
+            dims = ci.wide_base_dims + ci.wide_cross_dims
+            offs = np.concatenate([[0], np.cumsum(dims)[:-1]])
+            out.append(torch.from_numpy(np.stack([rng.randint(0, d, n) + o for d, o in zip(dims, offs)], 1).astype(np.int64)))
+        if self.model_type != "wide":
+            if self.has_ind:
+                ind = np.zeros((n, sum(ci.indicator_dims)), np.float32)
+                o = 0
+                for d in ci.indicator_dims:
+                    ind[np.arange(n), o + rng.randint(0, d, n)] = 1.0
+                    o += d
+                out.append(torch.from_numpy(ind))
+            if self.has_emb:
+                out.append(torch.from_numpy(np.stack([rng.randint(1, d + 1, n) for d in ci.embed_in_dims], 1).astype(np.int64)))
+            if self.has_cont:
+                out.append(torch.from_numpy(rng.rand(n, len(ci.continuous_cols)).astype(np.float32)))
+        if device is not None:
+            out = [t.to(device) for t in out]
+        return tuple(out)

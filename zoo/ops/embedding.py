@@ -260,9 +260,12 @@ def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None):
     outs = []
     for s in specs:
         idc = ids[:, s.col:s.col + s.bag].long()
-        e = s.table.lookup_torch(idc)  # [B, bag, D]
+        ok = (idc >= 0) & (idc < s.table.num_embeddings)      # out-of-range ids contribute nothing, as in the kernel
+        e = s.table.lookup_torch(idc.clamp(0, s.table.num_embeddings - 1)) * ok.unsqueeze(-1)  # [B, bag, D]
         if s.mul_table is not None:
-            e = e * s.mul_table.lookup_torch(ids[:, s.mul_col:s.mul_col + s.bag].long())
+            idb = ids[:, s.mul_col:s.mul_col + s.bag].long()
+            okb = (idb >= 0) & (idb < s.mul_table.num_embeddings)
+            e = e * (s.mul_table.lookup_torch(idb.clamp(0, s.mul_table.num_embeddings - 1)) * okb.unsqueeze(-1))
         e = e.mean(1) if (s.mean and s.bag > 1) else e.sum(1)
         outs.append(e)
     return torch.cat(outs, dim=1) if len(outs) > 1 else outs[0]

@@ -93,9 +93,9 @@ def softmax_nll(logits, labels, zero_based_label=True, padding_value=None, class
 
 def sigmoid_bce_reference(x, y, from_probs=False, size_average=True, eps=EPS):
     p = x.float() if from_probs else torch.sigmoid(x.float())
-    p = p.clamp(eps, 1.0 - eps)
     y = y.float()
-    per = -(y * torch.log(p) + (1.0 - y) * torch.log(1.0 - p))
+    # p and 1-p are floored separately: 1 - 1e-8 rounds to 1 in fp32 (would give 0 * log(0) = nan)
+    per = -(y * torch.log(p.clamp_min(eps)) + (1.0 - y) * torch.log((1.0 - p).clamp_min(eps)))
     return per.mean() if size_average else per.sum()
 
 

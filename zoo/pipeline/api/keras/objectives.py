@@ -85,9 +85,9 @@ class BinaryCrossEntropy(LossFunction):
     def forward(self, y_pred, y_true):
         if self.weights is None:
             return _fl.sigmoid_bce(y_pred.reshape(-1), y_true.reshape(-1), from_probs=True, size_average=self.size_average)
-        p = y_pred.float().clamp(EPS, 1 - EPS)
+        p = y_pred.float()
         y = y_true.float()
-        return self._reduce(-self.weights * (y * torch.log(p) + (1 - y) * torch.log(1 - p)))
+        return self._reduce(-self.weights * (y * torch.log(p.clamp_min(EPS)) + (1 - y) * torch.log((1 - p).clamp_min(EPS))))
 
     def from_logits(self, logits, y_true):
         return _fl.sigmoid_bce(logits.reshape(-1), y_true.reshape(-1), from_probs=False, size_average=self.size_average)

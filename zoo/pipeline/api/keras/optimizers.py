@@ -200,6 +200,15 @@ def to_opt_config(opt) -> OptConfig:
         return opt.to_config()
     if isinstance(opt, torch.optim.Optimizer):
         return OptConfig.from_torch(opt)
+    if isinstance(opt, type) and issubclass(opt, torch.optim.Optimizer):
+        # an optimizer CLASS: its torch defaults (lr 1e-3 where torch requires one)
+        probe = torch.nn.Parameter(torch.zeros(1))
+        try:
+            return OptConfig.from_torch(opt([probe]))
+        except TypeError:
+            return OptConfig.from_torch(opt([probe], lr=1e-3))
+    if isinstance(opt, type) and issubclass(opt, OptimMethod):
+        return opt().to_config()
     if isinstance(opt, str):
         k = opt.lower()
         table = {"sgd": lambda: SGD(learningrate=0.01), "adam": Adam, "rmsprop": RMSprop, "adagrad": lambda: Adagrad(0.01),

@@ -38,6 +38,7 @@ import torch.nn as nn
 from ..common.nncontext import get_context
 from ..common.triggers import EveryEpoch, MaxEpoch, ZooTrigger
 from ..feature.common import FeatureSet, MiniBatch
+from ..native import lib as _nl
 from ..parallel.flat import FusedOptimizer, OptConfig
 from ..tensorboard import TrainSummary, ValidationSummary
 from .api.keras.metrics import to_metric
@@ -392,10 +393,11 @@ class TrainingEngine:
             dst.copy_(src, non_blocking=True)
         self.fopt.pre_graph_replay()
         g["graph"].replay()
+        _nl.LAUNCH_COUNT["n"] += g["launches"]   # kernels of ours inside the replayed graph
         return g["loss"]
 
     def _capture(self, criterion, batch, key):
-        g = {"key": key, "graph": None, "count": 1, "warm": 3, "static": None, "loss": None}
+        g = {"key": key, "graph": None, "count": 1, "warm": 3, "static": None, "loss": None, "launches": 0}
         g["loss"] = self._eager_step(criterion, batch.inputs, batch.targets)
         return g
 
@@ -407,8 +409,11 @@ class TrainingEngine:
         torch.cuda.synchronize()
         self.fopt.graph_mode = True
         graph = torch.cuda.CUDAGraph()
+        n0 = _nl.LAUNCH_COUNT["n"]
         with torch.cuda.graph(graph):
             g["loss"] = self._eager_step(criterion, s_in, s_tg)
+        g["launches"] = _nl.LAUNCH_COUNT["n"] - n0
+        _nl.LAUNCH_COUNT["n"] = n0               # captured, not executed
         self.fopt.step_count -= 1  # capture does not execute; the step is counted at replay
         g["graph"] = graph
 
