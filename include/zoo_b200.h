@@ -93,6 +93,58 @@ int zoo_softmax_nll(const void* logits, long long ldl, const long long* labels, 
 int zoo_sigmoid_bce(const void* logits, const float* targets, long long n, int dtype, int from_probs, float eps,
                     float loss_scale, float grad_scale, float* loss_out, void* dlogits, void* stream);
 
+/* ---- K1: fused reduce-scatter + optimizer + all-gather over NVLink peer memory (csrc/comm/rs_opt_ag.cu)
+ * Replaces BigDL AllReduceParameter + OptimMethod.optimize (Topology.scala:1128,1187-1206).  Pointer
+ * arguments are HOST arrays of `world` device pointers (index = rank) into the symmetric heap. */
+int zoo_symm_alloc(long long nbytes, void** ptr, void* ipc_handle64);
+int zoo_symm_open(const void* ipc_handle64, void** ptr);
+int zoo_symm_close(void* ptr);
+int zoo_symm_free(void* ptr);
+int zoo_rs_opt_ag(void* const* g, void* const* p, void* const* p16, void* const* m, void* const* v,
+                  void* const* flags, void* const* epoch, void* const* hyper, long long start, long long end,
+                  int world, int rank, int device_slot, int opt, int zero_grad, int grid, void* stream);
+int zoo_p2p_barrier(void* const* flags, void* const* epoch, int world, int rank, int slot, void* stream);
+
+/* ---- K6: persistent LSTM / GRU, forward and backward-through-time (csrc/ops/rnn.cu) -----------
+ * Replaces the cell loops of LSTM.scala / GRU.scala / InternalRecurrent.scala and of the PyTorch
+ * AutoML models (VanillaLSTM_pytorch.py:29-56).  torch.nn.LSTM/GRU weight layout, fp32, H <= 128.
+ * `gates` holds x W_ih^T + b for all steps on entry and the activated gates on exit (save != 0);
+ * backward overwrites it with the pre-activation gate gradients. */
+int zoo_rnn_supported(int H);
+int zoo_lstm_forward(float* gates, const float* whh, const float* h0, const float* c0, float* hout, float* cout,
+                     float* hT, float* cT, int B, int T, int H, int save, void* stream);
+int zoo_lstm_backward(float* gates, const float* whh, const float* hout, const float* cout, const float* h0,
+                      const float* c0, const float* dy, long long dy_sb, long long dy_st, const float* dhT,
+                      const float* dcT, float* dh0, float* dc0, int B, int T, int H, void* stream);
+int zoo_gru_forward(const float* gx, float* saved, const float* whh, const float* bhn, const float* h0,
+                    float* hout, float* hT, int B, int T, int H, void* stream);
+int zoo_gru_backward(float* saved, const float* whh, const float* hout, const float* h0, const float* dy,
+                     long long dy_sb, long long dy_st, const float* dhT, float* dh0, int B, int T, int H,
+                     void* stream);
+
+/* ---- K7: dilated causal conv1d with fused bias/ReLU/dropout/residual epilogue (csrc/ops/tcn.cu) -
+ * North-star TCN forecaster (no TCN in the reference); also MTNet's CNN front-end
+ * (pyzoo/zoo/automl/model/MTNet_keras.py:398-406).  x [B,Cin,T], w [Cout,Cin,K], fp32. */
+int zoo_tcn_conv_forward(const float* x, const float* w, const float* bias, const float* res, float* out, int B,
+                         int Cin, int Cout, int T, int K, int dilation, int relu, float drop_p,
+                         unsigned long long seed, void* stream);
+int zoo_tcn_conv_dgrad(const float* g, const float* w, float* dx, int B, int Cin, int Cout, int T, int K,
+                       int dilation, void* stream);
+int zoo_tcn_prep_grad(const float* dout, const float* out, const float* res, float* g, float* dres, long long n,
+                      int relu, float drop_p, void* stream);
+
+/* ---- K13/K14/K15: serving pre/post-processing and recommender top-N (csrc/ops/serving.cu) ------
+ * PreProcessing.scala:24-43 + ClusterServing.scala:209-216; PostProcessing.scala:83-116;
+ * Recommender.scala:46-104.  dtype 0 fp32, 1 bf16. */
+int zoo_serving_preproc(const void* src, const long long* offsets, const int* hw, void* out, int B, int C, int OH,
+                        int OW, int RH, int RW, const float* mean /*host*/, const float* stdv /*host*/, int swap_rb,
+                        int chw, int out_bf16, void* stream);
+int zoo_serving_topk(const void* x, long long ldx, int rows, int n, int k, int dtype, int softmax, int* out_idx,
+                     float* out_val, void* stream);
+int zoo_pair_score(const void* probs, long long ldp, long long P, int C, int dtype, int* cls, float* prob,
+                   long long* rank_key, void* stream);
+int zoo_segment_head(const long long* keys, long long P, int n, unsigned char* keep, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,118 @@
+"""K7 (TCN conv), K13 (serving preprocess), K14 (top-k), K15 (recommend top-N) against CPU oracles."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("B,Cin,Cout,T,K,d", [(3, 5, 7, 50, 3, 1), (4, 16, 16, 130, 7, 4), (2, 30, 30, 257, 3, 64), (2, 8, 20, 40, 2, 8)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_causal_conv_fwd_bwd(B, Cin, Cout, T, K, d, with_res):
+    from zoo.ops.tcn import causal_conv1d, causal_conv1d_reference
+
+    torch.manual_seed(0)
+    x = torch.randn(B, Cin, T)
+    w = torch.randn(Cout, Cin, K) * 0.3
+    b = torch.randn(Cout) * 0.1
+    res = torch.randn(B, Cout, T) if with_res else None
+    leaves = [t.clone().requires_grad_(True) for t in (x, w, b)] + ([res.clone().requires_grad_(True)] if with_res else [None])
+    ref = causal_conv1d_reference(leaves[0], leaves[1], leaves[2], d, True, leaves[3])
+    wgt = torch.linspace(-1, 1, ref.numel()).reshape(ref.shape)
+    (ref * wgt).sum().backward()
+    dl = [t.detach().cuda().requires_grad_(True) for t in (x, w, b)] + ([res.cuda().requires_grad_(True)] if with_res else [None])
+    out = causal_conv1d(dl[0], dl[1], dl[2], d, True, dl[3])
+    (out * wgt.cuda()).sum().backward()
+    torch.testing.assert_close(out.detach().cpu(), ref.detach(), atol=1e-4, rtol=1e-4)
+    for a, r in zip(dl, leaves):
+        if a is not None:
+            torch.testing.assert_close(a.grad.cpu(), r.grad, atol=2e-3, rtol=2e-3)
+
+
+def test_tcn_block_dropout_and_training():
+    from zoo.ops.tcn import TemporalConvNet, causal_conv1d
+
+    torch.manual_seed(0)
+    x = torch.randn(4, 6, 64).cuda()
+    w = torch.randn(9, 6, 3).cuda()
+    y = causal_conv1d(x, w, None, 2, True, None, drop_p=0.5, training=True, seed=7)
+    y0 = causal_conv1d(x, w, None, 2, True, None)
+    kept = y != 0
+    frac = 1 - kept.float().sum() / (y0 != 0).float().sum()
+    assert 0.35 < frac.item() < 0.65
+    torch.testing.assert_close(y[kept], 2 * y0[kept])
+    y2 = causal_conv1d(x, w, None, 2, True, None, drop_p=0.5, training=True, seed=7)
+    assert torch.equal(y, y2)                       # same seed, same mask
+    net = TemporalConvNet(6, [8, 8, 4], kernel_size=3, dropout=0.1)
+    ref = copy.deepcopy(net).eval()
+    net.cuda().eval()
+    torch.testing.assert_close(net(x).cpu(), ref(x.cpu()), atol=1e-4, rtol=1e-3)
+    net.train()
+    opt = torch.optim.Adam(net.parameters(), 1e-2)
+    tgt = torch.randn(4, 4, 64).cuda()
+    l0 = None
+    for _ in range(40):
+        opt.zero_grad()
+        loss = (net(x) - tgt).pow(2).mean()
+        loss.backward()
+        opt.step()
+        l0 = l0 or loss.item()
+    assert loss.item() < l0
+
+
+@pytest.mark.parametrize("chw,swap,dtype", [(True, False, torch.float32), (False, True, torch.float32), (True, True, torch.bfloat16)])
+def test_serving_preproc(chw, swap, dtype):
+    from zoo.ops.serving_ops import preprocess_images, preprocess_reference
+
+    rng = np.random.RandomState(0)
+    imgs = [rng.randint(0, 256, (h, w, 3), dtype=np.uint8) for h, w in [(300, 400), (224, 224), (97, 513), (600, 350), (256, 256)]]
+    mean, std = [123.0, 117.0, 104.0], [58.0, 57.0, 57.5]
+    out = preprocess_images(imgs, (224, 224), (256, 256), mean, std, swap, chw, dtype, device="cuda")
+    ref = preprocess_reference(imgs, (224, 224), (256, 256), mean, std, swap, chw)
+    tol = dict(atol=3e-2, rtol=2e-2) if dtype == torch.bfloat16 else dict(atol=2e-4, rtol=1e-4)
+    torch.testing.assert_close(out.float().cpu(), ref, **tol)
+    # geometry agrees with OpenCV's INTER_LINEAR (cv2 uses fixed-point weights for u8: <= 1 grey level apart)
+    import cv2
+
+    o2 = preprocess_images(imgs[:1], (200, 320), None, None, None, False, False, torch.float32, device="cuda")[0].cpu().numpy()
+    c2 = cv2.resize(imgs[0], (320, 200), interpolation=cv2.INTER_LINEAR).astype(np.float32)
+    assert np.abs(o2 - c2).max() <= 1.01
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("n,k,softmax", [(1000, 5, True), (1000, 1, False), (37, 8, True), (5, 3, False)])
+def test_serving_topk(dtype, n, k, softmax):
+    from zoo.ops.serving_ops import topk
+
+    torch.manual_seed(0)
+    x = (torch.randn(67, n) * 3).to(dtype).cuda()
+    idx, val = topk(x, k, softmax)
+    xf = x.float().cpu()
+    ref = (torch.softmax(xf, -1) if softmax else xf).topk(k, dim=-1)
+    torch.testing.assert_close(val.cpu(), ref.values, atol=1e-5, rtol=1e-4)
+    # indices may differ only between exactly tied values
+    got = (torch.softmax(xf, -1) if softmax else xf).gather(1, idx.cpu().long())
+    torch.testing.assert_close(got, ref.values, atol=1e-5, rtol=1e-4)
+
+
+def test_recommend_topn():
+    from zoo.ops.recommend import pair_score, segmented_topn_order
+
+    torch.manual_seed(0)
+    P, C, U, N = 20000, 5, 300, 4
+    probs = torch.softmax(torch.randn(P, C), -1)
+    users = torch.randint(0, U, (P,))
+    cls_, p, key = pair_score(probs.cuda())
+    rc, rp, rkey = pair_score(probs)
+    assert torch.equal(cls_.cpu(), rc) and torch.equal(p.cpu(), rp) and torch.equal(key.cpu(), rkey)
+    sel = segmented_topn_order(users.cuda(), key, N).cpu()
+    ref = segmented_topn_order(users, rkey, N)
+    assert torch.equal(sel, ref)
+    # semantic check against a python groupby
+    by = {}
+    for i in range(P):
+        by.setdefault(int(users[i]), []).append((-int(rc[i]), -float(rp[i]), i))
+    want = [i for u in sorted(by) for _, _, i in sorted(by[u])[:N]]
+    assert sel.tolist() == want

@@ -1,0 +1,150 @@
+"""Cluster Serving batch pre/post-processing: faces of kernels K13 / K14 (``csrc/ops/serving.cu``).
+
+`preprocess_images` packs decoded uint8 HWC images (any sizes) into one pinned buffer, copies it
+once, and one kernel resizes (OpenCV INTER_LINEAR geometry), centre-crops, normalises and lays the
+batch out as [B,C,H,W] -- the reference does this per image with OpenCV and a Scala copy loop
+(zoo/.../serving/PreProcessing.scala:24-43, ClusterServing.scala:209-216).  `topk` is the
+`PostProcessing.topN` of the reference (PostProcessing.scala:83-92) for a whole batch.
+On CPU both functions compute the same thing with cv2 / torch (they are the oracles of the GPU tests).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from ..native import lib as _nl
+
+_V, _I, _L = C.c_void_p, C.c_int, C.c_longlong
+_nl.register_cuda_sigs({
+    "zoo_serving_preproc": [_V, _V, _V, _V, _I, _I, _I, _I, _I, _I, _V, _V, _I, _I, _I, _V],
+    "zoo_serving_topk": [_V, _L, _I, _I, _I, _I, _I, _V, _V, _V],
+})
+
+
+def preprocess_reference(images, out_hw, resize_hw=None, mean=None, std=None, swap_rb=False, chw=True):
+    """CPU oracle: float bilinear resize with the same geometry, crop, normalise."""
+    OH, OW = out_hw
+    RH, RW = resize_hw or out_hw
+    outs = []
+    for im in images:
+        im = np.asarray(im)
+        if im.ndim == 2:
+            im = im[:, :, None]
+        h, w, c = im.shape
+        ys = (np.arange(RH) + 0.5) * (h / RH) - 0.5
+        xs = (np.arange(RW) + 0.5) * (w / RW) - 0.5
+        y0 = np.floor(ys).astype(int); x0 = np.floor(xs).astype(int)
+        wy = ys - y0; wx = xs - x0
+        wy[y0 < 0] = 0; y0[y0 < 0] = 0
+        wx[x0 < 0] = 0; x0[x0 < 0] = 0
+        y1 = np.minimum(y0 + 1, h - 1); x1 = np.minimum(x0 + 1, w - 1)
+        wy[y0 >= h - 1] = 0; wx[x0 >= w - 1] = 0
+        y0 = np.minimum(y0, h - 1); x0 = np.minimum(x0, w - 1)
+        f = im.astype(np.float32)
+        top = f[y0][:, x0] + wx[None, :, None] * (f[y0][:, x1] - f[y0][:, x0])
+        bot = f[y1][:, x0] + wx[None, :, None] * (f[y1][:, x1] - f[y1][:, x0])
+        r = top + wy[:, None, None] * (bot - top)
+        cy, cx = (RH - OH) // 2, (RW - OW) // 2
+        r = r[cy:cy + OH, cx:cx + OW]
+        if swap_rb and c >= 3:
+            r = r[:, :, [2, 1, 0] + list(range(3, c))]
+        if mean is not None:
+            r = r - np.asarray(mean, np.float32)[:c]
+        if std is not None:
+            r = r / np.asarray(std, np.float32)[:c]
+        outs.append(r.transpose(2, 0, 1) if chw else r)
+    return torch.from_numpy(np.stack(outs).astype(np.float32))
+
+
+class ImageBatcher:
+    """Reusable pinned staging + device buffers for `preprocess_images` (one H2D copy per batch)."""
+
+    def __init__(self, device, max_bytes=64 << 20, max_batch=512):
+        self.device = torch.device(device)
+        self.host = torch.empty(max_bytes, dtype=torch.uint8).pin_memory()
+        self.meta_host = torch.empty(max_batch * 4, dtype=torch.int64).pin_memory()
+        self.dev = torch.empty(max_bytes, dtype=torch.uint8, device=self.device)
+        self.meta_dev = torch.empty(max_batch * 4, dtype=torch.int64, device=self.device)
+        self.max_batch = max_batch
+
+    def stage(self, images):
+        B = len(images)
+        if B > self.max_batch:
+            raise ValueError(f"batch {B} > max_batch {self.max_batch}")
+        off, hb = 0, self.host.numpy()
+        offs = self.meta_host[:B].numpy()
+        hw = self.meta_host[B:2 * B].numpy().view(np.int32)    # B int64 slots viewed as 2B int32 = [B,2]
+        C_ = None
+        for i, im in enumerate(images):
+            im = np.ascontiguousarray(im, dtype=np.uint8)
+            if im.ndim == 2:
+                im = im[:, :, None]
+            C_ = im.shape[2] if C_ is None else C_
+            if im.shape[2] != C_:
+                raise ValueError("all images of a batch must have the same channel count")
+            n = im.size
+            if off + n > hb.size:
+                raise ValueError("image batch exceeds the staging buffer")
+            hb[off:off + n] = im.reshape(-1)
+            offs[i] = off
+            hw[2 * i], hw[2 * i + 1] = im.shape[0], im.shape[1]
+            off += (n + 15) // 16 * 16
+        self.dev[:off].copy_(self.host[:off], non_blocking=True)
+        self.meta_dev[:2 * B].copy_(self.meta_host[:2 * B], non_blocking=True)
+        return B, C_, off
+
+
+_BATCHERS = {}
+
+
+def preprocess_images(images, out_hw, resize_hw=None, mean=None, std=None, swap_rb=False, chw=True, dtype=torch.float32,
+                      device=None, out=None, batcher=None):
+    """images: list of uint8 HWC arrays -> tensor [B,C,OH,OW] (or [B,OH,OW,C]) on `device`."""
+    device = torch.device(device) if device is not None else (torch.device("cuda") if torch.cuda.is_available() else torch.device("cpu"))
+    if device.type != "cuda":
+        return preprocess_reference(images, out_hw, resize_hw, mean, std, swap_rb, chw).to(dtype)
+    OH, OW = out_hw
+    RH, RW = resize_hw or out_hw
+    if batcher is None:
+        batcher = _BATCHERS.get(device)
+        if batcher is None:
+            batcher = _BATCHERS[device] = ImageBatcher(device)
+    B, Cc, _ = batcher.stage(images)
+    shape = (B, Cc, OH, OW) if chw else (B, OH, OW, Cc)
+    if out is None:
+        out = torch.empty(shape, dtype=dtype, device=device)
+    fa = lambda v: None if v is None else (C.c_float * 4)(*(list(np.asarray(v, np.float32).reshape(-1)) + [1.0] * 4)[:4])
+    m, s = fa(mean), fa(std)
+    _nl.check(_nl.cuda_lib().zoo_serving_preproc(batcher.dev.data_ptr(), batcher.meta_dev.data_ptr(),
+                                                 batcher.meta_dev[B:].data_ptr(), out.data_ptr(), B, Cc, OH, OW, RH, RW,
+                                                 C.cast(m, _V) if m is not None else None, C.cast(s, _V) if s is not None else None,
+                                                 int(swap_rb), int(chw), int(dtype == torch.bfloat16), _nl.stream_ptr()),
+              "zoo_serving_preproc")
+    return out
+
+
+def topk(x: torch.Tensor, k: int, softmax: bool = False):
+    """Per-row top-k of a [B, N] tensor -> (indices int32 [B,k], values fp32 [B,k]), best first."""
+    if x.dim() != 2:
+        x = x.reshape(x.shape[0], -1)
+    if not x.is_cuda or k > 8:
+        v = torch.softmax(x.float(), -1) if softmax else x.float()
+        t = v.topk(k, dim=-1)
+        return t.indices.int(), t.values
+    if x.dtype not in (torch.float32, torch.bfloat16):
+        x = x.float()
+    if x.stride(-1) != 1:
+        x = x.contiguous()
+    B, N = x.shape
+    idx = torch.empty((B, k), dtype=torch.int32, device=x.device)
+    val = torch.empty((B, k), dtype=torch.float32, device=x.device)
+    _nl.check(_nl.cuda_lib().zoo_serving_topk(x.data_ptr(), x.stride(0), B, N, k, 0 if x.dtype == torch.float32 else 1,
+                                              int(softmax), idx.data_ptr(), val.data_ptr(), _nl.stream_ptr()), "zoo_serving_topk")
+    return idx, val
+
+
+def format_topn(idx, val):
+    """The reference's result string for one row: ``[[idx,prob],...]`` (PostProcessing.scala:83-92)."""
+    return "[" + ",".join(f"[{int(i)},{float(v)}]" for i, v in zip(idx, val)) + "]"
