@@ -31,7 +31,7 @@ NVCC_FLAGS = [
     "-I", str(ROOT / "include"), "-I", str(CSRC),
 ]
 CXX = os.environ.get("CXX", "g++")
-CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-pthread", "-I", str(ROOT / "include"), "-I", str(CSRC)]
+CXX_FLAGS = ["-O2", "-msse4.2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-pthread", "-I", str(ROOT / "include"), "-I", str(CSRC)]
 
 
 def _digest(paths, flags) -> str:
