@@ -153,6 +153,8 @@ class FileWriter:
         return self
 
     def flush(self):
+        if self._closed:          # everything was flushed by close(); reading back afterwards is fine
+            return
         deadline = time.time() + 5
         while not self._q.empty() and time.time() < deadline:
             time.sleep(0.005)
