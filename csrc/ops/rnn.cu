@@ -27,6 +27,9 @@ namespace zoo {
 constexpr int kRnnRows = 4;  // batch rows per CTA
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+// gate activation and its derivative expressed through the activated value v
+__device__ __forceinline__ float gate_act(float x, int hard) { return hard ? fminf(fmaxf(fmaf(0.2f, x, 0.5f), 0.f), 1.f) : sigmoidf_(x); }
+__device__ __forceinline__ float gate_der(float v, int hard) { return hard ? ((v > 0.f && v < 1.f) ? 0.2f : 0.f) : v * (1.f - v); }
 __device__ __forceinline__ float tanhf_(float x) {
   // tanh(x) = 2*sigmoid(2x) - 1; exact enough in fp32 and NaN-free for large |x|
   return 2.f / (1.f + __expf(-2.f * x)) - 1.f;
@@ -52,6 +55,7 @@ struct RnnArgs {
   float* cT;           // [B,H] or null
   int B, T, H;
   int save;            // LSTM: write activated gates back into `gates`
+  int hard;            // inner (gate) activation: 0 sigmoid (torch), 1 hard_sigmoid (the zoo keras default)
 };
 
 // ---------------------------------------------------------------- LSTM forward --
@@ -112,7 +116,7 @@ __global__ void lstm_fwd_kernel(RnnArgs a) {
       }
 #pragma unroll
       for (int r = 0; r < kRnnRows; ++r) {
-        const float v = is_g ? tanhf_(acc[r]) : sigmoidf_(acc[r]);
+        const float v = is_g ? tanhf_(acc[r]) : gate_act(acc[r], a.hard);
         gs[r * NC + j] = v;
         if (a.save && b0 + r < a.B) a.gates[((size_t)(b0 + r) * T + t) * NC + j] = v;
       }
@@ -152,6 +156,7 @@ struct RnnBwdArgs {
   float* dh0;          // [B,H] or null
   float* dc0;          // [B,H] or null
   int B, T, H;
+  int hard;
 };
 
 // --------------------------------------------------------------- LSTM backward --
@@ -185,10 +190,10 @@ __global__ void lstm_bwd_kernel(RnnBwdArgs a) {
       const float dh = dyv + dhs[r * H + u];
       const float tc = tanhf_(c);
       const float dc = fmaf(dh * og, 1.f - tc * tc, dc_next);
-      const float dpi = dc * gg * ig * (1.f - ig);
-      const float dpf = dc * cprev * fg * (1.f - fg);
+      const float dpi = dc * gg * gate_der(ig, a.hard);
+      const float dpf = dc * cprev * gate_der(fg, a.hard);
       const float dpg = dc * ig * (1.f - gg * gg);
-      const float dpo = dh * tc * og * (1.f - og);
+      const float dpo = dh * tc * gate_der(og, a.hard);
       dc_next = dc * fg;
       float* d = dgs + r * NC;
       d[u] = dpi; d[H + u] = dpf; d[2 * H + u] = dpg; d[3 * H + u] = dpo;
@@ -280,8 +285,8 @@ __global__ void gru_fwd_kernel(RnnArgs a) {
     if (own) {
       const float* rr = rs + r2 * NC;
       const float* xx = xs + r2 * NC;
-      const float rg = sigmoidf_(xx[u2] + rr[u2]);
-      const float zg = sigmoidf_(xx[H + u2] + rr[H + u2]);
+      const float rg = gate_act(xx[u2] + rr[u2], a.hard);
+      const float zg = gate_act(xx[H + u2] + rr[H + u2], a.hard);
       const float hn = rr[2 * H + u2] + bhn;
       const float ng = tanhf_(fmaf(rg, hn, xx[2 * H + u2]));
       const float hp = hs[r2 * Hp + u2];
@@ -327,9 +332,9 @@ __global__ void gru_bwd_kernel(RnnBwdArgs a) {
     if (own) {
       const float dh = dyv + dhs[r * H + u];
       const float dn = dh * (1.f - zg);
-      const float dpz = dh * (hprev - ng) * zg * (1.f - zg);
+      const float dpz = dh * (hprev - ng) * gate_der(zg, a.hard);
       const float dpn = dn * (1.f - ng * ng);
-      const float dpr = dpn * hn * rg * (1.f - rg);
+      const float dpr = dpn * hn * gate_der(rg, a.hard);
       const float dhn = dpn * rg;
       dh_direct = dh * zg;
       float* d = dgs + r * NC;
@@ -390,11 +395,11 @@ int check_shape(int B, int T, int H) {
 ZOO_API int zoo_rnn_supported(int H) { return H > 0 && H <= 128; }
 
 ZOO_API int zoo_lstm_forward(float* gates, const float* whh, const float* h0, const float* c0, float* hout, float* cout,
-                             float* hT, float* cT, int B, int T, int H, int save, void* stream) {
+                             float* hT, float* cT, int B, int T, int H, int save, int hard, void* stream) {
   int rc = check_shape(B, T, H);
   if (rc) return rc;
   if (!gates || !whh || !hout) { zoo_set_last_error("lstm_forward: null pointer", __FILE__, __LINE__); return ZOO_ERR_ARG; }
-  RnnArgs a{gates, nullptr, whh, nullptr, h0, c0, hout, cout, hT, cT, B, T, H, save};
+  RnnArgs a{gates, nullptr, whh, nullptr, h0, c0, hout, cout, hT, cT, B, T, H, save, hard};
   const int Hp = (H + 3) & ~3, NC = 4 * H;
   const int tiles = kRnnRows * Hp + kRnnRows * NC;
   const unsigned grid = (B + kRnnRows - 1) / kRnnRows, block = (NC + 31) / 32 * 32;
@@ -414,11 +419,11 @@ ZOO_API int zoo_lstm_forward(float* gates, const float* whh, const float* h0, co
 
 ZOO_API int zoo_lstm_backward(float* gates, const float* whh, const float* hout, const float* cout, const float* h0,
                               const float* c0, const float* dy, long long dy_sb, long long dy_st, const float* dhT,
-                              const float* dcT, float* dh0, float* dc0, int B, int T, int H, void* stream) {
+                              const float* dcT, float* dh0, float* dc0, int B, int T, int H, int hard, void* stream) {
   int rc = check_shape(B, T, H);
   if (rc) return rc;
   if (!gates || !whh || !cout) { zoo_set_last_error("lstm_backward: null pointer", __FILE__, __LINE__); return ZOO_ERR_ARG; }
-  RnnBwdArgs a{gates, whh, hout, cout, h0, c0, dy, dy_sb, dy_st, dhT, dcT, dh0, dc0, B, T, H};
+  RnnBwdArgs a{gates, whh, hout, cout, h0, c0, dy, dy_sb, dy_st, dhT, dcT, dh0, dc0, B, T, H, hard};
   const int NC = 4 * H;
   const int tiles = kRnnRows * NC + kRnnRows * H;
   const unsigned grid = (B + kRnnRows - 1) / kRnnRows, block = (NC + 31) / 32 * 32;
@@ -437,11 +442,11 @@ ZOO_API int zoo_lstm_backward(float* gates, const float* whh, const float* hout,
 }
 
 ZOO_API int zoo_gru_forward(const float* gx, float* saved, const float* whh, const float* bhn, const float* h0,
-                            float* hout, float* hT, int B, int T, int H, void* stream) {
+                            float* hout, float* hT, int B, int T, int H, int hard, void* stream) {
   int rc = check_shape(B, T, H);
   if (rc) return rc;
   if (!gx || !whh || !hout) { zoo_set_last_error("gru_forward: null pointer", __FILE__, __LINE__); return ZOO_ERR_ARG; }
-  RnnArgs a{const_cast<float*>(gx), saved, whh, bhn, h0, nullptr, hout, nullptr, hT, nullptr, B, T, H, 0};
+  RnnArgs a{const_cast<float*>(gx), saved, whh, bhn, h0, nullptr, hout, nullptr, hT, nullptr, B, T, H, 0, hard};
   const int Hp = (H + 3) & ~3, NC = 3 * H;
   const int tiles = kRnnRows * Hp + 2 * kRnnRows * NC;
   const unsigned grid = (B + kRnnRows - 1) / kRnnRows, block = (4 * H + 31) / 32 * 32;
@@ -461,11 +466,11 @@ ZOO_API int zoo_gru_forward(const float* gx, float* saved, const float* whh, con
 
 ZOO_API int zoo_gru_backward(float* saved, const float* whh, const float* hout, const float* h0, const float* dy,
                              long long dy_sb, long long dy_st, const float* dhT, float* dh0, int B, int T, int H,
-                             void* stream) {
+                             int hard, void* stream) {
   int rc = check_shape(B, T, H);
   if (rc) return rc;
   if (!saved || !whh || !hout) { zoo_set_last_error("gru_backward: null pointer", __FILE__, __LINE__); return ZOO_ERR_ARG; }
-  RnnBwdArgs a{saved, whh, hout, nullptr, h0, nullptr, dy, dy_sb, dy_st, dhT, nullptr, dh0, nullptr, B, T, H};
+  RnnBwdArgs a{saved, whh, hout, nullptr, h0, nullptr, dy, dy_sb, dy_st, dhT, nullptr, dh0, nullptr, B, T, H, hard};
   const int NC = 3 * H;
   const int tiles = kRnnRows * NC + kRnnRows * H;
   const unsigned grid = (B + kRnnRows - 1) / kRnnRows, block = (4 * H + 31) / 32 * 32;

@@ -112,15 +112,15 @@ int zoo_p2p_barrier(void* const* flags, void* const* epoch, int world, int rank,
  * backward overwrites it with the pre-activation gate gradients. */
 int zoo_rnn_supported(int H);
 int zoo_lstm_forward(float* gates, const float* whh, const float* h0, const float* c0, float* hout, float* cout,
-                     float* hT, float* cT, int B, int T, int H, int save, void* stream);
+                     float* hT, float* cT, int B, int T, int H, int save, int hard_sigmoid, void* stream);
 int zoo_lstm_backward(float* gates, const float* whh, const float* hout, const float* cout, const float* h0,
                       const float* c0, const float* dy, long long dy_sb, long long dy_st, const float* dhT,
-                      const float* dcT, float* dh0, float* dc0, int B, int T, int H, void* stream);
+                      const float* dcT, float* dh0, float* dc0, int B, int T, int H, int hard_sigmoid, void* stream);
 int zoo_gru_forward(const float* gx, float* saved, const float* whh, const float* bhn, const float* h0,
-                    float* hout, float* hT, int B, int T, int H, void* stream);
+                    float* hout, float* hT, int B, int T, int H, int hard_sigmoid, void* stream);
 int zoo_gru_backward(float* saved, const float* whh, const float* hout, const float* h0, const float* dy,
                      long long dy_sb, long long dy_st, const float* dhT, float* dh0, int B, int T, int H,
-                     void* stream);
+                     int hard_sigmoid, void* stream);
 
 /* ---- K7: dilated causal conv1d with fused bias/ReLU/dropout/residual epilogue (csrc/ops/tcn.cu) -
  * North-star TCN forecaster (no TCN in the reference); also MTNet's CNN front-end

@@ -94,3 +94,28 @@ def test_rnn_inference_no_grad():
         y = m(x, return_sequences=True)
         y2, _ = m.rnn(x)
     torch.testing.assert_close(y, y2, atol=2e-4, rtol=2e-3)
+
+
+@pytest.mark.parametrize("kind", ["lstm", "gru"])
+def test_rnn_hard_sigmoid_gates(kind):
+    """zoo keras default inner_activation: kernel vs the explicit torch cell loop on CPU."""
+    from zoo.ops import lstm_persistent as lp
+    from zoo.ops.rnn import cell_loop
+
+    torch.manual_seed(0)
+    cls = nn.LSTM if kind == "lstm" else nn.GRU
+    ref = cls(5, 12, num_layers=2, batch_first=True)
+    for p in ref.parameters():
+        p.data.mul_(3.0)                      # push gates into the clipped region too
+    dev = copy.deepcopy(ref).cuda()
+    x = torch.randn(11, 9, 5)
+    xr = x.clone().requires_grad_(True)
+    o_ref, _ = cell_loop(ref, xr, None, True)
+    o_ref.pow(2).sum().backward()
+    xd = x.cuda().requires_grad_(True)
+    o_dev, _ = lp.maybe_run(dev, xd, None, True)
+    o_dev.pow(2).sum().backward()
+    torch.testing.assert_close(o_dev.detach().cpu(), o_ref.detach(), atol=2e-4, rtol=2e-3)
+    torch.testing.assert_close(xd.grad.cpu(), xr.grad, atol=2e-3, rtol=5e-3)
+    for p, q in zip(dev.parameters(), ref.parameters()):
+        torch.testing.assert_close(p.grad.cpu(), q.grad, atol=5e-3, rtol=5e-3)

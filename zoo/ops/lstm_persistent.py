@@ -23,10 +23,10 @@ from ..native import lib as _nl
 _V, _I, _L = C.c_void_p, C.c_int, C.c_longlong
 _nl.register_cuda_sigs({
     "zoo_rnn_supported": [_I],
-    "zoo_lstm_forward": [_V, _V, _V, _V, _V, _V, _V, _V, _I, _I, _I, _I, _V],
-    "zoo_lstm_backward": [_V, _V, _V, _V, _V, _V, _V, _L, _L, _V, _V, _V, _V, _I, _I, _I, _V],
-    "zoo_gru_forward": [_V, _V, _V, _V, _V, _V, _V, _I, _I, _I, _V],
-    "zoo_gru_backward": [_V, _V, _V, _V, _V, _L, _L, _V, _V, _I, _I, _I, _V],
+    "zoo_lstm_forward": [_V, _V, _V, _V, _V, _V, _V, _V, _I, _I, _I, _I, _I, _V],
+    "zoo_lstm_backward": [_V, _V, _V, _V, _V, _V, _V, _L, _L, _V, _V, _V, _V, _I, _I, _I, _I, _V],
+    "zoo_gru_forward": [_V, _V, _V, _V, _V, _V, _V, _I, _I, _I, _I, _V],
+    "zoo_gru_backward": [_V, _V, _V, _V, _V, _L, _L, _V, _V, _I, _I, _I, _I, _V],
 })
 
 MAX_HIDDEN = 128
@@ -47,7 +47,7 @@ def _dy_arg(dy):
 
 class _LSTMLayerFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w_ih, w_hh, b_ih, b_hh, h0, c0):
+    def forward(ctx, x, w_ih, w_hh, b_ih, b_hh, h0, c0, hard=False):
         B, T, Fin = x.shape
         H = w_hh.shape[1]
         x2 = x.reshape(B * T, Fin)
@@ -60,11 +60,12 @@ class _LSTMLayerFn(torch.autograd.Function):
         cT = torch.empty_like(hT)
         whh = w_hh.contiguous()
         _nl.check(_nl.cuda_lib().zoo_lstm_forward(gates.data_ptr(), whh.data_ptr(), _p(h0), _p(c0), hout.data_ptr(), _p(cout),
-                                                  hT.data_ptr(), cT.data_ptr(), B, T, H, int(need), _nl.stream_ptr()),
+                                                  hT.data_ptr(), cT.data_ptr(), B, T, H, int(need), int(hard), _nl.stream_ptr()),
                   "zoo_lstm_forward")
         if need:
             ctx.save_for_backward(x, w_ih, whh, gates, hout, cout, h0, c0)
             ctx.has_bias = (b_ih is not None, b_hh is not None)
+            ctx.hard = int(hard)
         return hout, hT, cT
 
     @staticmethod
@@ -79,7 +80,7 @@ class _LSTMLayerFn(torch.autograd.Function):
         dc0 = torch.empty((B, H), dtype=torch.float32, device=x.device) if ctx.needs_input_grad[6] else None
         _nl.check(_nl.cuda_lib().zoo_lstm_backward(gates.data_ptr(), whh.data_ptr(), hout.data_ptr(), cout.data_ptr(), _p(h0),
                                                    _p(c0), dy_ptr, sb, st, _p(dhT), _p(dcT), _p(dh0), _p(dc0), B, T, H,
-                                                   _nl.stream_ptr()), "zoo_lstm_backward")
+                                                   ctx.hard, _nl.stream_ptr()), "zoo_lstm_backward")
         dG = gates.view(B * T, 4 * H)           # now holds the pre-activation gate gradients
         x2 = x.reshape(B * T, Fin)
         first = h0.unsqueeze(1) if h0 is not None else torch.zeros((B, 1, H), dtype=torch.float32, device=x.device)
@@ -88,12 +89,12 @@ class _LSTMLayerFn(torch.autograd.Function):
         dw_hh = dG.t() @ hprev if ctx.needs_input_grad[2] else None
         db = dG.sum(0) if (ctx.needs_input_grad[3] or ctx.needs_input_grad[4]) else None
         dx = (dG @ w_ih).view(B, T, Fin) if ctx.needs_input_grad[0] else None
-        return dx, dw_ih, dw_hh, (db if ctx.has_bias[0] else None), (db if ctx.has_bias[1] else None), dh0, dc0
+        return dx, dw_ih, dw_hh, (db if ctx.has_bias[0] else None), (db if ctx.has_bias[1] else None), dh0, dc0, None
 
 
 class _GRULayerFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w_ih, w_hh, b_ih, b_hh, h0):
+    def forward(ctx, x, w_ih, w_hh, b_ih, b_hh, h0, hard=False):
         B, T, Fin = x.shape
         H = w_hh.shape[1]
         x2 = x.reshape(B * T, Fin)
@@ -110,10 +111,11 @@ class _GRULayerFn(torch.autograd.Function):
         whh = w_hh.contiguous()
         bhn = None if b_hh is None else b_hh[2 * H:].contiguous()
         _nl.check(_nl.cuda_lib().zoo_gru_forward(gx.data_ptr(), _p(saved), whh.data_ptr(), _p(bhn), _p(h0), hout.data_ptr(),
-                                                 hT.data_ptr(), B, T, H, _nl.stream_ptr()), "zoo_gru_forward")
+                                                 hT.data_ptr(), B, T, H, int(hard), _nl.stream_ptr()), "zoo_gru_forward")
         if need:
             ctx.save_for_backward(x, w_ih, whh, saved, hout, h0)
             ctx.has_bias = (b_ih is not None, b_hh is not None)
+            ctx.hard = int(hard)
         return hout, hT
 
     @staticmethod
@@ -125,7 +127,7 @@ class _GRULayerFn(torch.autograd.Function):
         dhT = None if dhT is None else dhT.float().contiguous()
         dh0 = torch.empty((B, H), dtype=torch.float32, device=x.device) if ctx.needs_input_grad[5] else None
         _nl.check(_nl.cuda_lib().zoo_gru_backward(saved.data_ptr(), whh.data_ptr(), hout.data_ptr(), _p(h0), dy_ptr, sb, st,
-                                                  _p(dhT), _p(dh0), B, T, H, _nl.stream_ptr()), "zoo_gru_backward")
+                                                  _p(dhT), _p(dh0), B, T, H, ctx.hard, _nl.stream_ptr()), "zoo_gru_backward")
         S = saved.view(B * T, 4 * H)            # dpr, dpz, dpn, dhn
         dGx = S[:, :3 * H]
         dRec = torch.cat([S[:, :2 * H], S[:, 3 * H:]], dim=1)
@@ -137,7 +139,7 @@ class _GRULayerFn(torch.autograd.Function):
         db_ih = dGx.sum(0) if (ctx.has_bias[0] and ctx.needs_input_grad[3]) else None
         db_hh = dRec.sum(0) if (ctx.has_bias[1] and ctx.needs_input_grad[4]) else None
         dx = (dGx @ w_ih).view(B, T, Fin) if ctx.needs_input_grad[0] else None
-        return dx, dw_ih, dw_hh, db_ih, db_hh, dh0
+        return dx, dw_ih, dw_hh, db_ih, db_hh, dh0, None
 
 
 def supported(rnn: torch.nn.Module, x: torch.Tensor) -> bool:
@@ -145,17 +147,20 @@ def supported(rnn: torch.nn.Module, x: torch.Tensor) -> bool:
             and not rnn.bidirectional and getattr(rnn, "proj_size", 0) == 0 and rnn.hidden_size <= MAX_HIDDEN)
 
 
-def lstm_layer(x, w_ih, w_hh, b_ih=None, b_hh=None, h0=None, c0=None):
-    """One LSTM layer over a [B,T,F] fp32 sequence -> (outputs [B,T,H], h_T, c_T)."""
+def lstm_layer(x, w_ih, w_hh, b_ih=None, b_hh=None, h0=None, c0=None, hard_sigmoid=False):
+    """One LSTM layer over a [B,T,F] fp32 sequence -> (outputs [B,T,H], h_T, c_T).
+    `hard_sigmoid` selects the zoo keras default gate activation clip(0.2x+0.5, 0, 1)."""
     return _LSTMLayerFn.apply(x.float().contiguous(), w_ih, w_hh, b_ih, b_hh,
-                              None if h0 is None else h0.float().contiguous(), None if c0 is None else c0.float().contiguous())
+                              None if h0 is None else h0.float().contiguous(), None if c0 is None else c0.float().contiguous(),
+                              bool(hard_sigmoid))
 
 
-def gru_layer(x, w_ih, w_hh, b_ih=None, b_hh=None, h0=None):
-    return _GRULayerFn.apply(x.float().contiguous(), w_ih, w_hh, b_ih, b_hh, None if h0 is None else h0.float().contiguous())
+def gru_layer(x, w_ih, w_hh, b_ih=None, b_hh=None, h0=None, hard_sigmoid=False):
+    return _GRULayerFn.apply(x.float().contiguous(), w_ih, w_hh, b_ih, b_hh, None if h0 is None else h0.float().contiguous(),
+                             bool(hard_sigmoid))
 
 
-def maybe_run(rnn, x, state=None):
+def maybe_run(rnn, x, state=None, hard_sigmoid=False):
     """Run `rnn` (nn.LSTM / nn.GRU) on the persistent kernels; None when the module/shape is not covered."""
     if not supported(rnn, x):
         return None
@@ -169,10 +174,10 @@ def maybe_run(rnn, x, state=None):
         w_ih, w_hh, b_ih, b_hh = g("weight_ih"), g("weight_hh"), g("bias_ih"), g("bias_hh")
         h0 = None if h0s is None else h0s[l]
         if is_lstm:
-            out, hT, cT = lstm_layer(out, w_ih, w_hh, b_ih, b_hh, h0, None if c0s is None else c0s[l])
+            out, hT, cT = lstm_layer(out, w_ih, w_hh, b_ih, b_hh, h0, None if c0s is None else c0s[l], hard_sigmoid)
             cs.append(cT)
         else:
-            out, hT = gru_layer(out, w_ih, w_hh, b_ih, b_hh, h0)
+            out, hT = gru_layer(out, w_ih, w_hh, b_ih, b_hh, h0, hard_sigmoid)
         hs.append(hT)
         if rnn.dropout > 0 and l + 1 < rnn.num_layers and rnn.training:
             out = F.dropout(out, rnn.dropout, True)

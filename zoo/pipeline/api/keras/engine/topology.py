@@ -183,32 +183,67 @@ class KerasNet(nn.Module):
 
 
 class Sequential(KerasNet):
-    """Linear stack of layers: `model.add(layer)`."""
+    """Linear stack of layers: `model.add(layer)`.  The first layer needs `input_shape=`; every later
+    layer is built from the previous layer's output shape (Topology.scala:827-961)."""
 
     def __init__(self, layers=None, name=None):
         super().__init__()
         self.seq = nn.ModuleList()
         self.zoo_name = name
+        self._out_shape = None
+        self._shape_known = True
         for l in layers or []:
             self.add(l)
 
     def add(self, layer):
-        if hasattr(layer, "build_from") and len(self.seq):
-            layer.build_from(self.get_output_shape())
+        from ..layers.base import ZooKerasLayer
+
+        if isinstance(layer, ZooKerasLayer):
+            shp = self._out_shape if len(self.seq) else layer._declared_input_shape
+            if len(self.seq) == 0 and shp is None and not layer.built:
+                raise ValueError(f"{layer.zoo_name}: the first layer of a Sequential model needs input_shape=")
+            if self._shape_known and shp is not None:
+                self._out_shape = layer.ensure_built(shp)
+            elif layer.built:
+                self._out_shape, self._shape_known = layer.output_shape_, layer.output_shape_ is not None
+        elif isinstance(layer, Sequential) and layer._shape_known:
+            self._out_shape = layer._out_shape
+        else:
+            self._out_shape, self._shape_known = None, False      # plain torch module: shapes resolve at the first call
         self.seq.append(layer)
         return self
 
     def get_output_shape(self):
-        shp = None
-        for l in self.seq:
-            if hasattr(l, "compute_output_shape"):
-                shp = l.compute_output_shape(shp)
-        return shp
+        return None if self._out_shape is None else ((None,) + tuple(self._out_shape) if not isinstance(self._out_shape, list)
+                                                     else [(None,) + tuple(s) for s in self._out_shape])
+
+    def get_input_shape(self):
+        first = self.seq[0] if len(self.seq) else None
+        return first.get_input_shape() if hasattr(first, "get_input_shape") else None
+
+    # a Sequential can itself be used as a layer of another model / called on Variables
+    _declared_input_shape = None
+    built = True
+
+    @property
+    def output_shape_(self):
+        return self._out_shape
+
+    def ensure_built(self, input_shape):
+        return self._out_shape
+
+    def __call__(self, *args, **kwargs):
+        from ...autograd import Variable
+
+        flat = args[0] if (len(args) == 1 and isinstance(args[0], (list, tuple))) else args
+        if flat and all(isinstance(a, Variable) for a in flat):
+            return Variable.from_layer(self, list(flat))
+        return super().__call__(*args, **kwargs)
 
     def forward(self, *xs):
-        x = xs[0] if len(xs) == 1 else xs
+        x = xs[0] if len(xs) == 1 else list(xs)
         for l in self.seq:
-            x = l(*x) if isinstance(x, tuple) and getattr(l, "multi_input", False) else l(x)
+            x = l(*x) if isinstance(x, (list, tuple)) and getattr(l, "multi_input", False) else l(x)
         return x
 
     def logits_kind(self):
@@ -219,17 +254,19 @@ class Sequential(KerasNet):
         """Everything but a trailing softmax/sigmoid activation (enables the fused loss kernels)."""
         last = self.seq[-1] if len(self.seq) else None
         strip = getattr(last, "strip_final_activation", None)
-        x = xs[0] if len(xs) == 1 else xs
+        x = xs[0] if len(xs) == 1 else list(xs)
         for l in list(self.seq)[:-1]:
-            x = l(x)
+            x = l(*x) if isinstance(x, (list, tuple)) and getattr(l, "multi_input", False) else l(x)
         if last is None:
             return x
+        if not getattr(last, "built", True):
+            return last(x)
         return strip(x) if strip is not None else last(x)
 
 
 class Model(KerasNet):
     """Functional graph container: `Model(input, output)` over symbolic `Variable`s
-    (zoo.pipeline.api.autograd) or a plain callable."""
+    (zoo.pipeline.api.autograd), or `Model(fn=callable)`."""
 
     def __init__(self, input=None, output=None, name=None, fn=None):
         super().__init__()
@@ -247,3 +284,49 @@ class Model(KerasNet):
         if self.graph is not None:
             return self.graph(*xs)
         return self.fn(*xs)
+
+    def get_input_shape(self):
+        s = [v.get_output_shape() for v in self.graph.inputs]
+        return s[0] if len(s) == 1 else s
+
+    def get_output_shape(self):
+        s = [v.get_output_shape() for v in self.graph.outputs]
+        return s[0] if self.graph.single_output else s
+
+    def __call__(self, *args, **kwargs):
+        from ...autograd import Variable
+
+        flat = args[0] if (len(args) == 1 and isinstance(args[0], (list, tuple))) else args
+        if flat and all(isinstance(a, Variable) for a in flat):
+            return Variable.from_layer(self, list(flat))
+        return super().__call__(*args, **kwargs)
+
+    def new_graph(self, outputs):
+        """Sub-graph ending at the named layers (Net.scala `newGraph`)."""
+        from ...autograd import GraphModule
+
+        names = [outputs] if isinstance(outputs, str) else list(outputs)
+        sel = []
+        for n in names:
+            vs = [v for v in self.graph.order if v.module is not None and getattr(v.module, "zoo_name", None) == n]
+            if not vs:
+                raise KeyError(f"no layer named {n!r}")
+            sel.append(vs[-1])
+        m = Model.__new__(Model)
+        KerasNet.__init__(m)
+        m.zoo_name, m.fn = None, None
+        m.graph = GraphModule(self.graph.inputs, sel[0] if len(sel) == 1 else sel)
+        return m
+
+    def freeze_up_to(self, names):
+        """Stop training every layer up to (and including) the named ones (Net.scala `freezeUpTo`)."""
+        names = [names] if isinstance(names, str) else list(names)
+        sub = self.new_graph(names)
+        for p in sub.parameters():
+            p.requires_grad_(False)
+        return self
+
+    def unfreeze(self):
+        for p in self.parameters():
+            p.requires_grad_(True)
+        return self
