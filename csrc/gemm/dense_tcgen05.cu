@@ -337,8 +337,20 @@ static int make_tmap(CUtensorMap* m, const void* base, long long rows, long long
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // A thread that has issued no CUDA runtime call yet (e.g. an autograd worker whose first backward node is
+    // one of our kernels) has no context bound; the runtime binds the primary context of its current device
+    // on the first real call.  Do that and encode again.
+    cudaFree(0);
+    r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   if (r != CUDA_SUCCESS) {
-    zoo_set_last_error("cuTensorMapEncodeTiled failed", __FILE__, __LINE__);
+    char msg[256];
+    snprintf(msg, sizeof(msg), "cuTensorMapEncodeTiled failed (CUresult %d): base %p rows %lld cols %lld ld %lld box %dx%d -- "
+             "base must be 16-byte aligned and ld a multiple of 8 elements", (int)r, base, rows, cols, ld, box_rows, box_cols);
+    zoo_set_last_error(msg, __FILE__, __LINE__);
     return ZOO_ERR_CUDA;
   }
   return ZOO_OK;

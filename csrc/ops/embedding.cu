@@ -158,16 +158,38 @@ embedding_gather_kernel(const long long* __restrict__ ids, int id_stride, int id
 // Entry e of a table's backward = (row id, gradient row).  The gradient row is
 //   dOut[b, 0:D] (bf16, leading dim ldg)           optionally times
 //   mul[b, 0:D]  (bf16, leading dim ldmul)         (the other factor saved by the GMF forward).
+// With nsrc > 1 the entries of `nsrc` GPUs are visited as one list (entry e belongs to source
+// e / E_local): ids, gradient rows and multiplier rows of the peers are read in place over NVLink,
+// so routing gradient rows to the owner (the backward all-to-all) happens inside these kernels.
 struct BwdEntries {
-  const long long* ids; int id_stride; int id_col; int bag;  // E = B * bag entries
-  const __nv_bfloat16* dout; long long ldg;
-  const __nv_bfloat16* mul; long long ldmul;                 // optional elementwise multiplier rows
-  float grad_scale;                                          // e.g. 1/bag for mean pooling
+  const long long* ids[kMaxPeers]; int id_stride; int id_col; int bag;  // E_local = B * bag entries per source
+  const __nv_bfloat16* dout[kMaxPeers]; long long ldg;
+  const __nv_bfloat16* mul[kMaxPeers]; long long ldmul;                 // optional elementwise multiplier rows
+  float grad_scale;                                                     // e.g. 1/bag for mean pooling
+  int nsrc; int E_local;
 };
 
+__device__ __forceinline__ void entry_split(const BwdEntries& en, int e, int& s, int& b, int& j) {
+  s = 0;
+  int el = e;
+  if (en.nsrc > 1) { s = e / en.E_local; el = e - s * en.E_local; }
+  b = el / en.bag;
+  j = el - b * en.bag;
+}
+
+template <typename P>
+__device__ __forceinline__ P pick(P const (&arr)[kMaxPeers], int s) {
+  // a switch keeps the pointer table in the constant bank (no local-memory copy of the kernel parameters)
+  switch (s) {
+    case 0: return arr[0]; case 1: return arr[1]; case 2: return arr[2]; case 3: return arr[3];
+    case 4: return arr[4]; case 5: return arr[5]; case 6: return arr[6]; default: return arr[7];
+  }
+}
+
 __device__ __forceinline__ long long entry_row(const BwdEntries& en, int e) {
-  const int b = e / en.bag, j = e - b * en.bag;
-  return en.ids[(long long)b * en.id_stride + en.id_col + j];
+  int s, b, j;
+  entry_split(en, e, s, b, j);
+  return pick(en.ids, s)[(long long)b * en.id_stride + en.id_col + j];
 }
 
 // Pass 1: elect, per touched row, the smallest entry index as its representative.
@@ -184,8 +206,9 @@ emb_mark_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* 
 
 template <bool VEC>
 __device__ __forceinline__ void entry_grad(const BwdEntries& en, int e, int c, float (&g)[4]) {
-  const int b = e / en.bag;
-  const __nv_bfloat16* gp = en.dout + (long long)b * en.ldg + c;
+  int s, b, j;
+  entry_split(en, e, s, b, j);
+  const __nv_bfloat16* gp = pick(en.dout, s) + (long long)b * en.ldg + c;
   if (VEC) {
     const uint2 u = *reinterpret_cast<const uint2*>(gp);
     const float2 a = unpack_bf16(u.x), d = unpack_bf16(u.y);
@@ -193,8 +216,8 @@ __device__ __forceinline__ void entry_grad(const BwdEntries& en, int e, int c, f
   } else {
     g[0] = __bfloat162float(gp[0]); g[1] = g[2] = g[3] = 0.f;
   }
-  if (en.mul) {
-    const __nv_bfloat16* mp = en.mul + (long long)b * en.ldmul + c;
+  if (en.mul[0]) {
+    const __nv_bfloat16* mp = pick(en.mul, s) + (long long)b * en.ldmul + c;
     if (VEC) {
       const uint2 u = *reinterpret_cast<const uint2*>(mp);
       const float2 a = unpack_bf16(u.x), d = unpack_bf16(u.y);
@@ -371,6 +394,16 @@ __global__ void fill_i32_kernel(int* p, long long n, int v) {
   for (; i < n; i += stride) p[i] = v;
 }
 
+static BwdEntries single_source(const long long* ids, int id_stride, int id_col, int bag, const void* dout, long long ldg,
+                                const void* mul, long long ldmul, float grad_scale, int E) {
+  BwdEntries en{};
+  en.ids[0] = ids; en.id_stride = id_stride; en.id_col = id_col; en.bag = bag;
+  en.dout[0] = (const __nv_bfloat16*)dout; en.ldg = ldg;
+  en.mul[0] = (const __nv_bfloat16*)mul; en.ldmul = ldmul;
+  en.grad_scale = grad_scale; en.nsrc = 1; en.E_local = E;
+  return en;
+}
+
 static ShardPtrs make_ptrs(const void* const* tabs, int world) {
   ShardPtrs s{};
   for (int i = 0; i < kMaxPeers; ++i) s.p[i] = (tabs && i < world) ? tabs[i] : nullptr;
@@ -461,7 +494,7 @@ ZOO_API int zoo_embedding_sparse_update(const long long* ids, int id_stride, int
   }
   const int E = B * bag;
   if (E == 0) return ZOO_OK;
-  BwdEntries en{ids, id_stride, id_col, bag, (const __nv_bfloat16*)dout, ldg, (const __nv_bfloat16*)mul, ldmul, grad_scale};
+  BwdEntries en = single_source(ids, id_stride, id_col, bag, dout, ldg, mul, ldmul, grad_scale, E);
   SparseState st{w, (__nv_bfloat16*)w16, opt == SOPT_SGD ? nullptr : m, opt == SOPT_ADAM ? v : nullptr};
   const bool vec = (D % 4 == 0) && (ldg % 4 == 0) && (((uintptr_t)dout & 7) == 0) && (((uintptr_t)w & 15) == 0) &&
                    (((uintptr_t)accum & 15) == 0) && (!m || ((uintptr_t)m & 15) == 0) &&
@@ -472,6 +505,62 @@ ZOO_API int zoo_embedding_sparse_update(const long long* ids, int id_stride, int
   emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row);
   const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
   const unsigned ab = (unsigned)((E + threads - 1) / threads);  // accum: one lane per entry
+  if (vec) {
+    emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
+    emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
+  } else {
+    emb_accum_kernel<false><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
+    emb_apply_kernel<false><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
+  }
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
+}
+
+// Multi-GPU form of zoo_embedding_sparse_update: the backward of a row-sharded table.
+//   ids_src / dout_src / mul_src : HOST arrays of `world` device pointers -- every rank's id matrix,
+//   gradient-row window and (optional) multiplier rows, all living in the symmetric heap so this GPU
+//   can read them in place.  B, id_stride, ldg, ldmul are the same on every rank.
+// The owner PULLS what it needs: all world*B*bag entries are scanned (ids are tiny), and only the
+// gradient rows of entries whose row lives here cross NVLink -- the all-to-all of a classic
+// dispatch/combine design without a separate collective or a staging copy on the receiver.
+// Callers bracket this with zoo_p2p_barrier (peers' buffers complete before / untouched until after).
+//   accum : fp32 [world*B*bag, D], dup_flag : int32 [world*B*bag] (zero on entry, restored on exit).
+ZOO_API int zoo_embedding_sparse_update_multi(const long long* const* ids_src, int id_stride, int id_col, int B, int bag,
+                                              const void* const* dout_src, long long ldg, const void* const* mul_src,
+                                              long long ldmul, float grad_scale, long long rows, int world, int rank,
+                                              int D, float* w, void* w16, float* m, float* v, int opt, const float* hyper,
+                                              int* rep_of_row, float* accum, int* dup_flag, void* stream) {
+  if (!ids_src || !dout_src || !w || !hyper || !rep_of_row || !accum || !dup_flag || D <= 0 || bag < 1 || world < 1 ||
+      world > kMaxPeers || rank < 0 || rank >= world) {
+    zoo_set_last_error("embedding_sparse_update_multi: bad arguments", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  if ((opt == SOPT_ADAM && (!m || !v)) || (opt == SOPT_ADAGRAD && !m)) {
+    zoo_set_last_error("embedding_sparse_update_multi: optimizer state missing", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  const long long E64 = (long long)world * B * bag;
+  if (E64 == 0) return ZOO_OK;
+  if (E64 > INT_MAX / 32) { zoo_set_last_error("embedding_sparse_update_multi: too many entries", __FILE__, __LINE__); return ZOO_ERR_TOO_LARGE; }
+  const int E = (int)E64;
+  BwdEntries en{};
+  bool vec = (D % 4 == 0) && (ldg % 4 == 0) && (((uintptr_t)w & 15) == 0) && (((uintptr_t)accum & 15) == 0) &&
+             (!m || ((uintptr_t)m & 15) == 0) && (!v || ((uintptr_t)v & 15) == 0) && (!w16 || ((uintptr_t)w16 & 7) == 0);
+  for (int s = 0; s < world; ++s) {
+    if (!ids_src[s] || !dout_src[s]) { zoo_set_last_error("embedding_sparse_update_multi: null source pointer", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+    en.ids[s] = ids_src[s];
+    en.dout[s] = (const __nv_bfloat16*)dout_src[s];
+    en.mul[s] = mul_src ? (const __nv_bfloat16*)mul_src[s] : nullptr;
+    vec = vec && (((uintptr_t)dout_src[s] & 7) == 0) && (!en.mul[s] || ((ldmul % 4 == 0) && ((uintptr_t)en.mul[s] & 7) == 0));
+  }
+  en.id_stride = id_stride; en.id_col = id_col; en.bag = bag; en.ldg = ldg; en.ldmul = ldmul;
+  en.grad_scale = grad_scale; en.nsrc = world; en.E_local = B * bag;
+  SparseState st{w, (__nv_bfloat16*)w16, opt == SOPT_SGD ? nullptr : m, opt == SOPT_ADAM ? v : nullptr};
+  cudaStream_t s = (cudaStream_t)stream;
+  const int threads = 256;
+  emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row);
+  const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
+  const unsigned ab = (unsigned)((E + threads - 1) / threads);
   if (vec) {
     emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
     emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
@@ -494,7 +583,7 @@ ZOO_API int zoo_embedding_dense_grad(const long long* ids, int id_stride, int id
   }
   const int E = B * bag;
   if (E == 0) return ZOO_OK;
-  BwdEntries en{ids, id_stride, id_col, bag, (const __nv_bfloat16*)dout, ldg, (const __nv_bfloat16*)mul, ldmul, grad_scale};
+  BwdEntries en = single_source(ids, id_stride, id_col, bag, dout, ldg, mul, ldmul, grad_scale, E);
   const bool vec = (D % 4 == 0) && (ldg % 4 == 0) && (((uintptr_t)dout & 7) == 0) && (((uintptr_t)dtable & 15) == 0) &&
                    (!mul || ((ldmul % 4 == 0) && ((uintptr_t)mul & 7) == 0));
   const int threads = 256;

@@ -80,3 +80,56 @@ def test_dp_p2p_matches_nccl_multi_gpu():
            "--master-port", "29533", os.path.join(root, "tests", "mgpu_dp_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "MGPU_DP_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_sharded_embedding_matches_single_gpu():
+    n = 2
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", "29534", os.path.join(root, "tests", "mgpu_sharded_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "MGPU_SHARDED_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("with_mul", [False, True])
+def test_sparse_update_multi_source_on_one_gpu(world, with_mul):
+    """The pull-based sharded backward, with all 'ranks' on one GPU (their launches do not wait on each other):
+    every rank scans all ranks' entries and updates the rows it owns; the union must equal one un-sharded update."""
+    import zoo.ops.embedding as E
+    from zoo.native import lib as nl
+
+    lib = nl.cuda_lib()
+    torch.manual_seed(0)
+    rows, D, B = 101, 16, 64
+    ids = [torch.randint(0, rows, (B, 2), device="cuda") for _ in range(world)]
+    dout = [torch.randn(B, D, device="cuda").to(torch.bfloat16) for _ in range(world)]
+    mul = [torch.randn(B, D, device="cuda").to(torch.bfloat16) for _ in range(world)] if with_mul else None
+    w_full = torch.randn(rows, D, device="cuda")
+    hyper = torch.zeros(16, device="cuda"); hyper[0], hyper[1], hyper[2], hyper[3], hyper[5] = 0.1, 0.9, 0.999, 1e-8, 1.0
+    # reference: dense gradient + one Adam step on touched rows
+    g = torch.zeros(rows, D, device="cuda")
+    for s in range(world):
+        gr = dout[s].float() * (mul[s].float() if with_mul else 1.0)
+        g.index_add_(0, ids[s][:, 1], gr)
+    touched = g.abs().sum(1) > 0
+    m = 0.1 * g; v = 0.001 * g * g
+    ref = w_full - 0.1 * (m / 0.1) / ((v / 0.001).sqrt() + 1e-8)
+    ref = torch.where(touched[:, None], ref, w_full)
+    st = torch.cuda.current_stream().cuda_stream
+    arr = lambda ts: (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+    for r in range(world):
+        rl = (rows + world - 1) // world
+        w = torch.zeros(rl, D, device="cuda")
+        w[: w_full[r::world].shape[0]] = w_full[r::world]
+        ea, es = torch.zeros_like(w), torch.zeros_like(w)
+        rep = torch.full((rl,), 2**31 - 1, dtype=torch.int32, device="cuda")
+        accum = torch.zeros(world * B, D, device="cuda"); dup = torch.zeros(world * B, dtype=torch.int32, device="cuda")
+        nl.check(lib.zoo_embedding_sparse_update_multi(arr(ids), 2, 1, B, 1, arr(dout), D, arr(mul) if with_mul else None, D, 1.0, rows, world, r, D,
+                                                       w.data_ptr(), None, ea.data_ptr(), es.data_ptr(), 1, hyper.data_ptr(), rep.data_ptr(),
+                                                       accum.data_ptr(), dup.data_ptr(), st), "multi")
+        torch.cuda.synchronize()
+        want = ref[r::world]
+        torch.testing.assert_close(w[: want.shape[0]], want, atol=2e-3, rtol=2e-3)
+        assert int(rep.min()) == 2**31 - 1 and float(accum.abs().sum()) == 0 and int(dup.sum()) == 0     # scratch restored

@@ -25,6 +25,69 @@ from ..native import lib as _nl
 SPARSE_OPTS = {"sgd": 0, "adam": 1, "adagrad": 2}
 INT_MAX = 2**31 - 1
 
+_V, _I, _L, _F = C.c_void_p, C.c_int, C.c_longlong, C.c_float
+_nl.register_cuda_sigs({
+    "zoo_embedding_sparse_update_multi": [_V, _I, _I, _I, _I, _V, _L, _V, _L, _F, _L, _I, _I, _I, _V, _V, _V, _V, _I, _V, _V, _V, _V, _V],
+})
+
+
+class ShardRuntime:
+    """Per-process state of row-sharded tables: the symmetric heap, a device-side barrier, staging buffers
+    every peer can read (ids, gradient rows, GMF factors) and the duplicate scratch shared by all tables."""
+    _inst = None
+
+    @classmethod
+    def get(cls):
+        from ..common.nncontext import get_context
+
+        ctx = get_context()
+        if cls._inst is None or cls._inst.ctx is not ctx:
+            cls._inst = cls(ctx)
+        return cls._inst
+
+    def __init__(self, ctx):
+        from ..parallel.symm import get_heap, ptr_array
+
+        if not ctx.is_gpu:
+            raise _nl.NativeError("row-sharded embedding tables (world > 1) need CUDA devices")
+        self.ctx, self.heap, self._ptr_array = ctx, get_heap(ctx), ptr_array
+        W, r = ctx.world_size, ctx.rank
+        self.flags = self.heap.alloc(4 * W)
+        self.flags.tensor(torch.int32, W).zero_()
+        self.epoch = torch.zeros(1, dtype=torch.int32, device=ctx.device)
+        self._bflags = ptr_array(self.flags.ptrs)
+        self._bepoch = ptr_array([self.epoch.data_ptr() if i == r else None for i in range(W)])
+        self.stages = {}
+        self.accum, self.dup = None, None
+        torch.cuda.synchronize()
+        ctx.barrier()
+
+    def barrier(self):
+        """All ranks' work queued so far on this stream is complete before anyone goes on (no host sync)."""
+        _nl.check(_nl.cuda_lib().zoo_p2p_barrier(self._bflags, self._bepoch, self.ctx.world_size, self.ctx.rank, 0,
+                                                 _nl.stream_ptr()), "zoo_p2p_barrier")
+
+    def stage(self, key, shape, dtype):
+        """A symmetric buffer (same key -> same buffer on every rank, allocated collectively on first use)."""
+        b = self.stages.get(key)
+        if b is None:
+            if torch.cuda.is_current_stream_capturing():
+                raise _nl.NativeError("sharded-embedding staging buffers must be created before CUDA-graph capture (run one eager step first)")
+            n = 1
+            for d in shape:
+                n *= int(d)
+            buf = self.heap.alloc(max(n, 1) * torch.empty(0, dtype=dtype).element_size())
+            b = self.stages[key] = (buf, buf.tensor(dtype, n).view(*shape))
+        return b
+
+    def scratch(self, E, D):
+        if self.accum is None or self.accum.shape[0] < E or self.accum.shape[1] < D:
+            E2 = max(E, 0 if self.accum is None else self.accum.shape[0])
+            D2 = max(D, 0 if self.accum is None else self.accum.shape[1])
+            self.accum = torch.zeros((E2, D2), dtype=torch.float32, device=self.ctx.device)
+            self.dup = torch.zeros((E2,), dtype=torch.int32, device=self.ctx.device)
+        return self.accum, self.dup
+
 
 class EmbeddingTable(nn.Module):
     def __init__(self, num_embeddings, embedding_dim, init="uniform", init_scale=0.05, sparse=True,
@@ -38,7 +101,19 @@ class EmbeddingTable(nn.Module):
         self.opt_cfg = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         self.padding_idx = padding_idx
         self.rows_local = (self.num_embeddings + self.world - 1) // self.world
-        w = torch.empty(self.rows_local, self.embedding_dim, device=device)  # big tables: initialise on the GPU
+        self._sym = None
+        if self.world > 1:
+            # the shard lives in the symmetric heap so every peer can gather rows from it over NVLink
+            rt = ShardRuntime.get()
+            if rt.ctx.world_size != self.world or rt.ctx.rank != self.rank:
+                raise ValueError(f"EmbeddingTable(world={self.world}, rank={self.rank}) does not match the context "
+                                 f"(world_size={rt.ctx.world_size}, rank={rt.ctx.rank})")
+            self._sym = rt.heap.alloc(self.rows_local * self.embedding_dim * 4)
+            w = self._sym.tensor(torch.float32, self.rows_local * self.embedding_dim).view(self.rows_local, self.embedding_dim)
+            if shadow_bf16:
+                raise NotImplementedError("shadow_bf16 with world > 1")
+        else:
+            w = torch.empty(self.rows_local, self.embedding_dim, device=device)  # big tables: initialise on the GPU
         if init == "uniform":
             w.uniform_(-init_scale, init_scale)
         elif init == "normal":
@@ -54,13 +129,20 @@ class EmbeddingTable(nn.Module):
         # lookup in the autograd graph (its own gradient is always None).
         self.anchor = nn.Parameter(torch.zeros(1))
         self.shadow_bf16 = shadow_bf16
-        self._peer_ptrs = None       # list[int] of device pointers (one per rank) when world > 1
+        self._peer_ptrs = None if self._sym is None else list(self._sym.ptrs)   # one device pointer per rank when world > 1
         self._peer_ptrs16 = None
+        if self._sym is not None:
+            torch.cuda.synchronize()      # the shard is initialised before any peer may read it
+            ShardRuntime.get().ctx.barrier()
         self._state_ready = False
         self._ptr_arr = None
 
     def _apply(self, fn, *a, **kw):
+        if self._sym is not None:
+            before = self.weight.data_ptr()
         super()._apply(fn, *a, **kw)
+        if self._sym is not None and self.weight.data_ptr() != before:
+            raise _nl.NativeError("a row-sharded EmbeddingTable cannot be moved or cast: its shard lives in the symmetric heap")
         # On a GPU a sparse table leaves the dense optimizer: its rows are updated in backward.
         self.weight.requires_grad_(not (self.sparse and self.weight.is_cuda))
         self._state_ready = False
@@ -92,6 +174,10 @@ class EmbeddingTable(nn.Module):
         self._state_ready = True
 
     def _ensure_scratch(self, E):
+        if self.world > 1:
+            self.accum, self.dup_flag = ShardRuntime.get().scratch(E * self.world, self.embedding_dim)
+            self._scratch_E = E
+            return
         if self._scratch_E < E:
             dev = self.weight.device
             self.accum = torch.zeros((E, self.embedding_dim), dtype=torch.float32, device=dev)
@@ -154,6 +240,27 @@ def _gather_into(ids, spec, out_window, save_a=None, save_b=None):
                                        _nl.ptr(save_b), _nl.stream_ptr()), "zoo_embedding_gather")
 
 
+def _sparse_update_sharded(table, ids_buf, ids, col, bag, dout_buf, dout_off, ldg, mul_buf, grad_scale):
+    """Backward of a row-sharded table: this rank pulls, from every peer's staged ids / gradient rows, the
+    entries whose rows it owns (the all-to-all happens inside the kernels)."""
+    lib, rt = _nl.cuda_lib(), ShardRuntime.get()
+    table._ensure_state()
+    B = ids.shape[0]
+    table._ensure_scratch(B * bag)
+    _nl.check(lib.zoo_hyper_step(table.hyper.data_ptr(), None, _nl.stream_ptr()), "zoo_hyper_step")
+    pa = rt._ptr_array
+    ids_p = pa(ids_buf.ptrs)
+    dout_p = pa([p + dout_off * 2 for p in dout_buf.ptrs])
+    mul_p = pa(mul_buf.ptrs) if mul_buf is not None else None
+    D = table.embedding_dim
+    accum = table.accum if table.accum.shape[1] == D else table.accum.view(-1)[: B * bag * table.world * D].view(-1, D)
+    _nl.check(lib.zoo_embedding_sparse_update_multi(
+        ids_p, ids.stride(0), col, B, bag, dout_p, ldg, mul_p, D if mul_buf is not None else 0, float(grad_scale),
+        table.num_embeddings, table.world, table.rank, D, table.weight.data_ptr(), None, _nl.ptr(table.exp_avg),
+        _nl.ptr(table.exp_avg_sq), SPARSE_OPTS[table.optimizer], table.hyper.data_ptr(), table.rep_of_row.data_ptr(),
+        accum.data_ptr(), table.dup_flag.data_ptr(), _nl.stream_ptr()), "zoo_embedding_sparse_update")
+
+
 def _sparse_update(table, ids, col, bag, dout_window, mul, grad_scale):
     lib = _nl.cuda_lib()
     table._ensure_state()
@@ -193,19 +300,39 @@ class _MultiLookupFn(torch.autograd.Function):
         out = torch.empty((B, ld), dtype=torch.bfloat16, device=ids.device)
         if ld != total:
             out[:, total:].zero_()
-        saves, off = [], 0
-        for s in specs:
+        sharded = any(t.world > 1 for t in _flat_tables(specs))
+        ctx.sharded = sharded
+        key = None
+        if sharded:
+            # ids (and GMF factors below) are staged in symmetric buffers: peers read them in backward
+            rt = ShardRuntime.get()
+            key = ("lookup", tuple((id(s.table), s.col, s.bag, id(s.mul_table), s.mul_col) for s in specs), B, ids.shape[1])
+            ids_buf, ids_st = rt.stage(key + ("ids",), ids.shape, torch.int64)
+            ids_st.copy_(ids)
+            ids = ids_st
+            ctx.ids_buf = ids_buf
+        saves, off, ctx.mul_bufs = [], 0, []
+        for k, s in enumerate(specs):
             s.table._ensure_state()
             sa = sb = None
             if s.mul_table is not None:
                 s.mul_table._ensure_state()
-                sa = torch.empty((B, s.dim), dtype=torch.bfloat16, device=ids.device)
-                sb = torch.empty((B, s.dim), dtype=torch.bfloat16, device=ids.device)
+                if sharded:
+                    ba, sa = rt.stage(key + ("sa", k), (B, s.dim), torch.bfloat16)
+                    bb, sb = rt.stage(key + ("sb", k), (B, s.dim), torch.bfloat16)
+                    ctx.mul_bufs.append((ba, bb))
+                else:
+                    sa = torch.empty((B, s.dim), dtype=torch.bfloat16, device=ids.device)
+                    sb = torch.empty((B, s.dim), dtype=torch.bfloat16, device=ids.device)
+                    ctx.mul_bufs.append(None)
+            else:
+                ctx.mul_bufs.append(None)
             _gather_into(ids, s, out[:, off:off + s.dim], sa, sb)
             saves += [sa, sb]
             off += s.dim
         ctx.specs = specs
         ctx.total = total
+        ctx.key = key
         ctx.save_for_backward(ids, *[t for t in saves if t is not None])
         ctx.has_save = [t is not None for t in saves]
         return out[:, :total]
@@ -218,6 +345,16 @@ class _MultiLookupFn(torch.autograd.Function):
         d16 = dout if dout.dtype == torch.bfloat16 else dout.to(torch.bfloat16)
         if d16.stride(-1) != 1:
             d16 = d16.contiguous()
+        rt = dbuf = None
+        if ctx.sharded:
+            # stage the gradient rows where peers can read them; the barrier makes every rank's staging
+            # (and every rank's forward gathers of the old weights) complete before rows are updated
+            rt = ShardRuntime.get()
+            B = ids.shape[0]
+            ld = (ctx.total + 7) // 8 * 8
+            dbuf, dst = rt.stage(ctx.key + ("dout",), (B, ld), torch.bfloat16)
+            dst[:, :ctx.total].copy_(d16)
+            rt.barrier()
         grads, off, si = [], 0, 0
         for k, s in enumerate(specs):
             win = d16[:, off:off + s.dim]
@@ -226,16 +363,25 @@ class _MultiLookupFn(torch.autograd.Function):
                 sa, sb = saved[si], saved[si + 1]
                 si += 2
             scale = 1.0 / s.bag if (s.mean and s.bag > 1) else 1.0
-            pairs = [(s.table, s.col, sb)]
+            pairs = [(s.table, s.col, sb, 1)]
             if s.mul_table is not None:
-                pairs.append((s.mul_table, s.mul_col, sa))
-            for table, col, mul in pairs:
-                if table.sparse:
+                pairs.append((s.mul_table, s.mul_col, sa, 0))
+            for table, col, mul, which in pairs:
+                if table.world > 1:
+                    if not table.sparse:
+                        raise _nl.NativeError("row-sharded tables are trained with the sparse optimizer (sparse=True)")
+                    mb = ctx.mul_bufs[k][which] if (mul is not None and ctx.mul_bufs[k] is not None) else None
+                    # 1/world: the loss is a mean over the GLOBAL batch, like the data-parallel dense part
+                    _sparse_update_sharded(table, ctx.ids_buf, ids, col, s.bag, dbuf, off, (ctx.total + 7) // 8 * 8, mb, scale / table.world)
+                    grads.append(None)
+                elif table.sparse:
                     _sparse_update(table, ids, col, s.bag, win, mul, scale)
                     grads.append(None)
                 else:
                     grads.append(_dense_grad(table, ids, col, s.bag, win, mul, scale))
             off += s.dim
+        if ctx.sharded:
+            rt.barrier()     # nobody overwrites its staging buffers / gathers new rows before all owners are done
         return (None, None, *grads)
 
 

@@ -21,6 +21,10 @@ _nl.register_cuda_sigs({
     "zoo_symm_free": [C.c_void_p],
     "zoo_rs_opt_ag": [C.c_void_p] * 8 + [C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p],
     "zoo_p2p_barrier": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p],
+    "zoo_vmm_alloc": [C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p],
+    "zoo_vmm_import": [C.c_int, C.c_longlong, C.c_void_p],
+    "zoo_vmm_free": [C.c_void_p, C.c_longlong],
+    "zoo_close_fd": [C.c_int],
 })
 
 _TYPESTR = {torch.float32: "<f4", torch.int32: "<i4", torch.int64: "<i8", torch.uint8: "|u1", torch.int16: "<i2"}
@@ -45,8 +49,9 @@ def ptr_array(ptrs):
 class SymmBuffer:
     """One slab per rank; `ptrs[r]` is rank r's slab as seen from this process."""
 
-    def __init__(self, ptrs, nbytes, rank, device, owner):
+    def __init__(self, ptrs, nbytes, rank, device, owner, kind="ipc", mapped=None):
         self.ptrs, self.nbytes, self.rank, self.device, self._owner = list(ptrs), nbytes, rank, device, owner
+        self.kind, self.mapped = kind, mapped or [nbytes] * len(self.ptrs)
 
     @property
     def local_ptr(self):
@@ -61,17 +66,101 @@ class SymmBuffer:
         return [p + offset_bytes for p in self.ptrs]
 
 
-class SymmetricHeap:
+class _FdExchange:
+    """Pass file descriptors between the ranks of one box (SCM_RIGHTS over abstract unix sockets)."""
+
     def __init__(self, ctx):
+        import os
+        import socket
+
+        self.ctx, self.socket = ctx, socket
+        self.tag = f"zoo-symm-{os.environ.get('MASTER_PORT', '0')}-{os.getppid() if os.environ.get('TORCHELASTIC_RUN_ID') else 0}"
+        self.listener = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        self.listener.bind("\0" + self._name(ctx.rank))
+        self.listener.listen(64)
+
+    def _name(self, rank):
+        return f"{self.tag}-{rank}"
+
+    def exchange(self, fd, payload: bytes):
+        """Send (fd, payload) to every peer; returns {rank: (fd, payload)} received from the peers."""
+        import torch.distributed as dist
+
+        W, r, socket = self.ctx.world_size, self.ctx.rank, self.socket
+        dist.barrier()            # every listener exists
+        for p in range(W):
+            if p == r:
+                continue
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect("\0" + self._name(p))
+            socket.send_fds(c, [r.to_bytes(4, "little") + payload], [fd])
+            c.close()
+        got = {}
+        while len(got) < W - 1:
+            conn, _ = self.listener.accept()
+            msg, fds, _, _ = socket.recv_fds(conn, 4096, 1)
+            conn.close()
+            got[int.from_bytes(msg[:4], "little")] = (fds[0], msg[4:])
+        dist.barrier()
+        return got
+
+    def close(self):
+        self.listener.close()
+
+
+class SymmetricHeap:
+    """`alloc` is collective: every rank calls it with the same size, in the same order.
+
+    Two transports: ``vmm`` (cuMemCreate + file-descriptor export, mapped by peers with large pages -- the
+    default; needed for random access into multi-GB peer buffers, see csrc/comm/symm_vmm.cu) and ``ipc``
+    (cudaMalloc + cudaIpc handles; fallback, select with ZOO_SYMM=ipc)."""
+
+    def __init__(self, ctx):
+        import os
+
         self.ctx = ctx
         self.buffers = []
         self.lib = _nl.cuda_lib()
         _nl._bind(self.lib, _nl._CUDA_SIGS)
+        self.mode = os.environ.get("ZOO_SYMM", "vmm")
+        self._fdx = None
+
+    def _alloc_vmm(self, nbytes):
+        ctx = self.ctx
+        ptr, fd, mapped = C.c_void_p(), C.c_int(-1), C.c_longlong(0)
+        _nl.check(self.lib.zoo_vmm_alloc(nbytes, C.byref(ptr), C.byref(fd), C.byref(mapped)), "zoo_vmm_alloc")
+        if ctx.world_size == 1:
+            self.lib.zoo_close_fd(fd.value)
+            return SymmBuffer([ptr.value], nbytes, 0, ctx.device, self, "vmm", [mapped.value])
+        if self._fdx is None:
+            self._fdx = _FdExchange(ctx)
+        got = self._fdx.exchange(fd.value, mapped.value.to_bytes(8, "little"))
+        self.lib.zoo_close_fd(fd.value)
+        ptrs, sizes = [None] * ctx.world_size, [0] * ctx.world_size
+        ptrs[ctx.rank], sizes[ctx.rank] = ptr.value, mapped.value
+        for r, (pfd, payload) in got.items():
+            p, sz = C.c_void_p(), int.from_bytes(payload[:8], "little")
+            _nl.check(self.lib.zoo_vmm_import(pfd, sz, C.byref(p)), "zoo_vmm_import")
+            self.lib.zoo_close_fd(pfd)
+            ptrs[r], sizes[r] = p.value, sz
+        return SymmBuffer(ptrs, nbytes, ctx.rank, ctx.device, self, "vmm", sizes)
 
     def alloc(self, nbytes) -> SymmBuffer:
         import torch.distributed as dist
 
         nbytes = (int(nbytes) + 255) // 256 * 256
+        if self.mode == "vmm":
+            try:
+                buf = self._alloc_vmm(nbytes)
+                self.buffers.append(buf)
+                return buf
+            except _nl.NativeError as e:
+                if self.buffers or self.ctx.world_size > 1:
+                    raise
+                import logging
+
+                logging.getLogger("zoo").warning("VMM symmetric memory unavailable (%s); using CUDA IPC", e)
+                self.mode = "ipc"
         ptr = C.c_void_p()
         handle = (C.c_ubyte * 64)()
         _nl.check(self.lib.zoo_symm_alloc(nbytes, C.byref(ptr), handle), "zoo_symm_alloc")
@@ -97,9 +186,18 @@ class SymmetricHeap:
 
     def close(self):
         torch.cuda.synchronize()
+        if self.ctx.world_size > 1:
+            import torch.distributed as dist
+
+            if dist.is_initialized():
+                dist.barrier()
         for b in self.buffers:
             for r, p in enumerate(b.ptrs):
-                if r != b.rank and p:
+                if not p:
+                    continue
+                if b.kind == "vmm":
+                    self.lib.zoo_vmm_free(C.c_void_p(p), b.mapped[r])
+                elif r != b.rank:
                     self.lib.zoo_symm_close(C.c_void_p(p))
         if self.ctx.world_size > 1:
             import torch.distributed as dist
@@ -107,8 +205,12 @@ class SymmetricHeap:
             if dist.is_initialized():
                 dist.barrier()
         for b in self.buffers:
-            self.lib.zoo_symm_free(C.c_void_p(b.local_ptr))
+            if b.kind != "vmm":
+                self.lib.zoo_symm_free(C.c_void_p(b.local_ptr))
         self.buffers = []
+        if self._fdx is not None:
+            self._fdx.close()
+            self._fdx = None
 
 
 _HEAP = None
