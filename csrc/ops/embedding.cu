@@ -194,8 +194,10 @@ __device__ __forceinline__ long long entry_row(const BwdEntries& en, int e) {
 
 // Pass 1: elect, per touched row, the smallest entry index as its representative.
 __global__ void __launch_bounds__(256)
-emb_mark_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* __restrict__ rep_of_row) {
+emb_mark_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* __restrict__ rep_of_row,
+                int* __restrict__ win_count) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e == 0 && win_count) *win_count = 0;     // the winner list is rebuilt by pass 2
   if (e >= E) return;
   const long long id = entry_row(en, e);
   if (id < 0 || id >= rows) return;
@@ -236,17 +238,33 @@ __device__ __forceinline__ void entry_grad(const BwdEntries& en, int e, int c, f
 template <bool VEC>
 __global__ void __launch_bounds__(256)
 emb_accum_kernel(BwdEntries en, int E, long long rows, int world, int rank, const int* __restrict__ rep_of_row,
-                 int D, float* __restrict__ accum, int* __restrict__ dup_flag) {
+                 int D, float* __restrict__ accum, int* __restrict__ dup_flag, int2* __restrict__ win_list,
+                 int* __restrict__ win_count) {
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   const int e_mine = warp_global * 32 + lane;
   int rep_mine = -1;
+  bool win = false;
+  int local_mine = 0;
   if (e_mine < E) {
     const long long id = entry_row(en, e_mine);
     if (id >= 0 && id < rows && !(world > 1 && (int)(id % world) != rank)) {
       const long long local = world > 1 ? id / world : id;
       const int rep = rep_of_row[local];
       if (rep != e_mine) rep_mine = rep;
+      else { win = true; local_mine = (int)local; }
+    }
+  }
+  if (win_list) {
+    // Representatives are appended to a compact (entry, local row) list so that pass 3 launches work only for
+    // them and never re-reads ids (which may sit on a peer) or the row map.
+    const unsigned wmask = __ballot_sync(0xffffffffu, win);
+    if (wmask) {
+      const int leader = __ffs(wmask) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(win_count, __popc(wmask));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (win) win_list[base + __popc(wmask & ((1u << lane) - 1u))] = make_int2(e_mine, local_mine);
     }
   }
   unsigned losers = __ballot_sync(0xffffffffu, rep_mine >= 0);
@@ -288,15 +306,23 @@ template <bool VEC>
 __global__ void __launch_bounds__(256)
 emb_apply_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* __restrict__ rep_of_row,
                  int D, float* __restrict__ accum, int* __restrict__ dup_flag, SparseState st, int opt,
-                 const float* __restrict__ hyper) {
-  const int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+                 const float* __restrict__ hyper, const int2* __restrict__ win_list, const int* __restrict__ win_count) {
+  int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (e >= E) return;
-  const long long id = entry_row(en, e);
-  if (id < 0 || id >= rows) return;
-  if (world > 1 && (int)(id % world) != rank) return;
-  const long long local = world > 1 ? id / world : id;
-  if (rep_of_row[local] != e) return;
+  long long local;
+  if (win_list) {                                  // compact list of representatives from pass 2
+    if (e >= *win_count) return;
+    const int2 wl = win_list[e];
+    e = wl.x;
+    local = wl.y;
+  } else {
+    const long long id = entry_row(en, e);
+    if (id < 0 || id >= rows) return;
+    if (world > 1 && (int)(id % world) != rank) return;
+    local = world > 1 ? id / world : id;
+    if (rep_of_row[local] != e) return;
+  }
   const bool dup = dup_flag[e] != 0;
   const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5];
   float bc1 = 1.f, bc2 = 1.f;
@@ -410,6 +436,27 @@ static ShardPtrs make_ptrs(const void* const* tabs, int world) {
   return s;
 }
 
+// The three passes.  win_list (optional, int32 [2*E + 4]): [0..2E) = (entry, local row) pairs, [2E] = count.
+static int launch_sparse_update(const BwdEntries& en, int E, long long rows, int world, int rank, int D, int* rep_of_row,
+                                float* accum, int* dup_flag, const SparseState& st, int opt, const float* hyper, bool vec,
+                                int* win_list, cudaStream_t s) {
+  const int threads = 256;
+  int2* wl = reinterpret_cast<int2*>(win_list);
+  int* wc = win_list ? win_list + 2 * (size_t)E : nullptr;
+  emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, wc);
+  const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
+  const unsigned ab = (unsigned)((E + threads - 1) / threads);  // accum: one lane per entry
+  if (vec) {
+    emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, wl, wc);
+    emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper, wl, wc);
+  } else {
+    emb_accum_kernel<false><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, wl, wc);
+    emb_apply_kernel<false><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper, wl, wc);
+  }
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
+}
+
 }  // namespace zoo
 
 using namespace zoo;
@@ -501,19 +548,34 @@ ZOO_API int zoo_embedding_sparse_update(const long long* ids, int id_stride, int
                    (!v || ((uintptr_t)v & 15) == 0) && (!w16 || ((uintptr_t)w16 & 7) == 0) &&
                    (!mul || ((ldmul % 4 == 0) && ((uintptr_t)mul & 7) == 0));
   cudaStream_t s = (cudaStream_t)stream;
-  const int threads = 256;
-  emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row);
-  const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
-  const unsigned ab = (unsigned)((E + threads - 1) / threads);  // accum: one lane per entry
-  if (vec) {
-    emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
-    emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
-  } else {
-    emb_accum_kernel<false><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
-    emb_apply_kernel<false><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
+  return launch_sparse_update(en, E, rows, world, rank, D, rep_of_row, accum, dup_flag, st, opt, hyper, vec, nullptr, s);
+}
+
+// zoo_embedding_sparse_update with one more caller-owned scratch buffer, `win_list` (int32 [2*E + 4], any
+// contents): pass 2 compacts the representative entries into it and pass 3 runs only over that list.
+ZOO_API int zoo_embedding_sparse_update_w(const long long* ids, int id_stride, int id_col, int B, int bag,
+                                          const void* dout, long long ldg, const void* mul, long long ldmul,
+                                          float grad_scale, long long rows, int world, int rank, int D,
+                                          float* w, void* w16, float* m, float* v, int opt, const float* hyper,
+                                          int* rep_of_row, float* accum, int* dup_flag, int* win_list, void* stream) {
+  if (!ids || !dout || !w || !hyper || !rep_of_row || !accum || !dup_flag || !win_list || D <= 0 || bag < 1 || world < 1 ||
+      world > kMaxPeers || rank < 0 || rank >= world || (rows + world - 1) / world > INT_MAX) {
+    zoo_set_last_error("embedding_sparse_update_w: bad arguments", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
   }
-  ZOO_CUDA_CHECK(cudaGetLastError());
-  return ZOO_OK;
+  if ((opt == SOPT_ADAM && (!m || !v)) || (opt == SOPT_ADAGRAD && !m)) {
+    zoo_set_last_error("embedding_sparse_update_w: optimizer state missing", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  const int E = B * bag;
+  if (E == 0) return ZOO_OK;
+  BwdEntries en = single_source(ids, id_stride, id_col, bag, dout, ldg, mul, ldmul, grad_scale, E);
+  SparseState st{w, (__nv_bfloat16*)w16, opt == SOPT_SGD ? nullptr : m, opt == SOPT_ADAM ? v : nullptr};
+  const bool vec = (D % 4 == 0) && (ldg % 4 == 0) && (((uintptr_t)dout & 7) == 0) && (((uintptr_t)w & 15) == 0) &&
+                   (((uintptr_t)accum & 15) == 0) && (!m || ((uintptr_t)m & 15) == 0) &&
+                   (!v || ((uintptr_t)v & 15) == 0) && (!w16 || ((uintptr_t)w16 & 7) == 0) &&
+                   (!mul || ((ldmul % 4 == 0) && ((uintptr_t)mul & 7) == 0));
+  return launch_sparse_update(en, E, rows, world, rank, D, rep_of_row, accum, dup_flag, st, opt, hyper, vec, win_list, (cudaStream_t)stream);
 }
 
 // Multi-GPU form of zoo_embedding_sparse_update: the backward of a row-sharded table.
@@ -529,7 +591,8 @@ ZOO_API int zoo_embedding_sparse_update_multi(const long long* const* ids_src, i
                                               const void* const* dout_src, long long ldg, const void* const* mul_src,
                                               long long ldmul, float grad_scale, long long rows, int world, int rank,
                                               int D, float* w, void* w16, float* m, float* v, int opt, const float* hyper,
-                                              int* rep_of_row, float* accum, int* dup_flag, void* stream) {
+                                              int* rep_of_row, float* accum, int* dup_flag, int* win_list, void* stream) {
+  if ((rows + world - 1) / (world > 0 ? world : 1) > INT_MAX) { zoo_set_last_error("embedding_sparse_update_multi: shard too large", __FILE__, __LINE__); return ZOO_ERR_TOO_LARGE; }
   if (!ids_src || !dout_src || !w || !hyper || !rep_of_row || !accum || !dup_flag || D <= 0 || bag < 1 || world < 1 ||
       world > kMaxPeers || rank < 0 || rank >= world) {
     zoo_set_last_error("embedding_sparse_update_multi: bad arguments", __FILE__, __LINE__);
@@ -557,19 +620,7 @@ ZOO_API int zoo_embedding_sparse_update_multi(const long long* const* ids_src, i
   en.grad_scale = grad_scale; en.nsrc = world; en.E_local = B * bag;
   SparseState st{w, (__nv_bfloat16*)w16, opt == SOPT_SGD ? nullptr : m, opt == SOPT_ADAM ? v : nullptr};
   cudaStream_t s = (cudaStream_t)stream;
-  const int threads = 256;
-  emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row);
-  const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
-  const unsigned ab = (unsigned)((E + threads - 1) / threads);
-  if (vec) {
-    emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
-    emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
-  } else {
-    emb_accum_kernel<false><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag);
-    emb_apply_kernel<false><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper);
-  }
-  ZOO_CUDA_CHECK(cudaGetLastError());
-  return ZOO_OK;
+  return launch_sparse_update(en, E, rows, world, rank, D, rep_of_row, accum, dup_flag, st, opt, hyper, vec, win_list, s);
 }
 
 // Dense gradient: dtable[ids] += dout rows (fp32 atomics); used when the table is trained as a

@@ -29,6 +29,9 @@ _CUDA_SIGS = {
     "zoo_embedding_sparse_update": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_ll, c_void_p, c_ll, c_float, c_ll,
                                     c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p],
+    "zoo_embedding_sparse_update_w": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_ll, c_void_p, c_ll, c_float, c_ll,
+                                      c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     "zoo_embedding_dense_grad": [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_ll, c_void_p, c_ll, c_float, c_ll,
                                  c_int, c_void_p, c_void_p],
     "zoo_dense_opt_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_void_p, c_int, c_void_p],
@@ -96,7 +99,7 @@ def register_cuda_sigs(sigs: dict):
 
 
 LAUNCH_COUNT = {"n": 0}
-_KERNELS_PER_CALL = {"zoo_embedding_sparse_update": 3, "zoo_sumsq": 1}
+_KERNELS_PER_CALL = {"zoo_embedding_sparse_update": 3, "zoo_embedding_sparse_update_w": 3, "zoo_sumsq": 1}
 
 
 def check(rc: int, what: str = ""):

@@ -27,7 +27,7 @@ INT_MAX = 2**31 - 1
 
 _V, _I, _L, _F = C.c_void_p, C.c_int, C.c_longlong, C.c_float
 _nl.register_cuda_sigs({
-    "zoo_embedding_sparse_update_multi": [_V, _I, _I, _I, _I, _V, _L, _V, _L, _F, _L, _I, _I, _I, _V, _V, _V, _V, _I, _V, _V, _V, _V, _V],
+    "zoo_embedding_sparse_update_multi": [_V, _I, _I, _I, _I, _V, _L, _V, _L, _F, _L, _I, _I, _I, _V, _V, _V, _V, _I, _V, _V, _V, _V, _V, _V],
 })
 
 
@@ -86,7 +86,8 @@ class ShardRuntime:
             D2 = max(D, 0 if self.accum is None else self.accum.shape[1])
             self.accum = torch.zeros((E2, D2), dtype=torch.float32, device=self.ctx.device)
             self.dup = torch.zeros((E2,), dtype=torch.int32, device=self.ctx.device)
-        return self.accum, self.dup
+            self.win = torch.zeros((2 * E2 + 4,), dtype=torch.int32, device=self.ctx.device)
+        return self.accum, self.dup, self.win
 
 
 class EmbeddingTable(nn.Module):
@@ -175,13 +176,14 @@ class EmbeddingTable(nn.Module):
 
     def _ensure_scratch(self, E):
         if self.world > 1:
-            self.accum, self.dup_flag = ShardRuntime.get().scratch(E * self.world, self.embedding_dim)
+            self.accum, self.dup_flag, self.win_list = ShardRuntime.get().scratch(E * self.world, self.embedding_dim)
             self._scratch_E = E
             return
         if self._scratch_E < E:
             dev = self.weight.device
             self.accum = torch.zeros((E, self.embedding_dim), dtype=torch.float32, device=dev)
             self.dup_flag = torch.zeros((E,), dtype=torch.int32, device=dev)
+            self.win_list = torch.zeros((2 * E + 4,), dtype=torch.int32, device=dev)
             self._scratch_E = E
 
     def set_lr(self, lr):
@@ -258,7 +260,7 @@ def _sparse_update_sharded(table, ids_buf, ids, col, bag, dout_buf, dout_off, ld
         ids_p, ids.stride(0), col, B, bag, dout_p, ldg, mul_p, D if mul_buf is not None else 0, float(grad_scale),
         table.num_embeddings, table.world, table.rank, D, table.weight.data_ptr(), None, _nl.ptr(table.exp_avg),
         _nl.ptr(table.exp_avg_sq), SPARSE_OPTS[table.optimizer], table.hyper.data_ptr(), table.rep_of_row.data_ptr(),
-        accum.data_ptr(), table.dup_flag.data_ptr(), _nl.stream_ptr()), "zoo_embedding_sparse_update")
+        accum.data_ptr(), table.dup_flag.data_ptr(), table.win_list.data_ptr(), _nl.stream_ptr()), "zoo_embedding_sparse_update")
 
 
 def _sparse_update(table, ids, col, bag, dout_window, mul, grad_scale):
@@ -267,13 +269,13 @@ def _sparse_update(table, ids, col, bag, dout_window, mul, grad_scale):
     E = ids.shape[0] * bag
     table._ensure_scratch(E)
     _nl.check(lib.zoo_hyper_step(table.hyper.data_ptr(), None, _nl.stream_ptr()), "zoo_hyper_step")
-    _nl.check(lib.zoo_embedding_sparse_update(
+    _nl.check(lib.zoo_embedding_sparse_update_w(
         ids.data_ptr(), ids.stride(0), col, ids.shape[0], bag, dout_window.data_ptr(), dout_window.stride(0),
         _nl.ptr(mul), mul.stride(0) if mul is not None else 0, float(grad_scale), table.num_embeddings, table.world,
         table.rank, table.embedding_dim, table.weight.data_ptr(), _nl.ptr(getattr(table, "weight16", None)),
         _nl.ptr(table.exp_avg), _nl.ptr(table.exp_avg_sq), SPARSE_OPTS[table.optimizer], table.hyper.data_ptr(),
-        table.rep_of_row.data_ptr(), table.accum.data_ptr(), table.dup_flag.data_ptr(), _nl.stream_ptr()),
-        "zoo_embedding_sparse_update")
+        table.rep_of_row.data_ptr(), table.accum.data_ptr(), table.dup_flag.data_ptr(), table.win_list.data_ptr(),
+        _nl.stream_ptr()), "zoo_embedding_sparse_update_w")
 
 
 def _dense_grad(table, ids, col, bag, dout_window, mul, grad_scale):
