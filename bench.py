@@ -147,10 +147,12 @@ def main():
     if cfg.get("custom_run"):
         return cfg["custom_run"](args, ctx)
 
-    opt = torch.optim.Adam([p for p in cfg["model"].parameters() if p.requires_grad] or [torch.zeros(1, requires_grad=True)],
-                           lr=cfg["extra"].get("lr", 1e-3))
+    opt = cfg.get("optimizer") or torch.optim.Adam([p for p in cfg["model"].parameters() if p.requires_grad] or [torch.zeros(1, requires_grad=True)],
+                                                   lr=cfg["extra"].get("lr", 1e-3))
     est = Estimator.from_torch(model=cfg["model"], optimizer=opt, loss=cfg["loss"], ctx=ctx)
     eng = est.engine
+    for k, v in cfg.get("engine_opts", {}).items():
+        setattr(eng, k, v)
     eng.prepare()
     crit = cfg["loss"].to(dev)
     K, Wm = args.steps, max(args.warmup, 3)
@@ -187,8 +189,12 @@ def main():
     if not args.no_e2e:
         from zoo.feature.common import FeatureSet
 
-        host = cfg["make_batches"](min(K + Wm, 48), torch.device("cpu"))
-        X = torch.cat([b[0] for b in host]); Y = torch.cat([b[1] for b in host])
+        host = cfg["make_batches"](min(K + Wm, cfg.get("e2e_pool", 48)), torch.device("cpu"))
+        if isinstance(host[0][0], (tuple, list)):
+            X = [torch.cat([b[0][i] for b in host]) for i in range(len(host[0][0]))]
+        else:
+            X = torch.cat([b[0] for b in host])
+        Y = torch.cat([b[1] for b in host])
         fs = FeatureSet(features=X, labels=Y, memory_type="DRAM", shuffle=False)  # pinned host cache
         marks = {}
 
@@ -209,20 +215,21 @@ def main():
         if ctx.world_size > 1:
             torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
         win2 = (marks["t0"], marks["t1"])
-        bi = cfg["batch"] * (X.shape[1] * X.element_size() + Y.element_size())
-        e2e = {"value": K * cfg["batch"] * ctx.world_size / float(dt), "unit": "samples/s", "h2d_bytes_per_step": bi,
+        xs_ = X if isinstance(X, list) else [X]
+        bi = cfg["batch"] * (sum(t[0].numel() * t.element_size() for t in xs_) + Y[0].numel() * Y.element_size())
+        e2e = {"value": K * cfg["batch"] * ctx.world_size / float(dt), "unit": cfg.get("unit", "samples/s"), "h2d_bytes_per_step": bi,
                "d2h_bytes_per_step": 4, "ms_per_step": float(dt) * 1e3 / K}
     clocks = sampler.stop([(t0, t1)] + ([win2] if win2 else []))
 
     if ctx.rank == 0:
         value = K * cfg["batch"] * ctx.world_size / (ms_total / 1e3)
         out = {"metric": "NCF training samples/sec" if args.config.startswith("ncf") else cfg.get("metric", "samples/sec"),
-               "value": value, "unit": "samples/s", "n_gpus": ctx.world_size, "steps": K, "warmup": Wm,
+               "value": value, "unit": cfg.get("unit", "samples/s"), "n_gpus": ctx.world_size, "steps": K, "warmup": Wm,
                "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                "dtype": "bf16", "data": "synthetic", "impl": "zoo-b200",
                "config": {"model": cfg["model_name"], "global_batch": cfg["batch"] * ctx.world_size, "seq_len": None,
                           "parallelism": cfg["parallelism"],
-                          "l2_policy": "embedding working set >> L2 (tables GBs); a distinct random batch every step",
+                          "l2_policy": cfg.get("l2_policy", "embedding working set >> L2 (tables GBs); a distinct random batch every step"),
                           **cfg["extra"]},
                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": loss_val,
                "invalid_debug_scale": args.scale if args.scale != 1.0 else None}

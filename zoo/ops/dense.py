@@ -80,6 +80,15 @@ def dense_wgrad(dy16, x16, dw32):
     M, N = dy16.shape
     K = x16.shape[1]
     lib = _nl.cuda_lib()
+    if dw32.stride(0) % 4 != 0 or dw32.data_ptr() % 16 != 0:
+        # the kernel reduces with 16-byte vector atomics: a weight whose row length is not a multiple of 4 floats
+        # (e.g. in_features 75) is accumulated in a padded scratch and folded in
+        ld = (K + 3) // 4 * 4
+        tmp = torch.zeros((N, ld), dtype=torch.float32, device=dw32.device)
+        _nl.check(lib.zoo_dense_wgrad_bf16(dy16.data_ptr(), dy16.stride(0), x16.data_ptr(), x16.stride(0),
+                                           tmp.data_ptr(), tmp.stride(0), M, N, K, _nl.stream_ptr()), "zoo_dense_wgrad_bf16")
+        dw32.add_(tmp[:, :K])
+        return dw32
     _nl.check(lib.zoo_dense_wgrad_bf16(dy16.data_ptr(), dy16.stride(0), x16.data_ptr(), x16.stride(0),
                                        dw32.data_ptr(), dw32.stride(0), M, N, K, _nl.stream_ptr()),
               "zoo_dense_wgrad_bf16")

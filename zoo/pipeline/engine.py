@@ -145,6 +145,8 @@ class TrainingEngine:
         self._graph = None
         self._loss_ring = None
         self._last_criterion = None
+        self.autocast_dtype = None   # e.g. torch.bfloat16: run generic torch models' forward under autocast (masters stay fp32)
+        self.channels_last = False
 
     # ----------------------------------------------------------------- set-up --
     @property
@@ -180,6 +182,8 @@ class TrainingEngine:
         if self.fopt is not None:
             return self
         self.model.to(self.device)
+        if self.channels_last and self.device.type == "cuda":
+            self.model.to(memory_format=torch.channels_last)
         self._prepare_tables_for_dp()
         self._sync_sparse_optimizers()
         default, per = self._default_cfg_and_map()
@@ -194,6 +198,11 @@ class TrainingEngine:
             self._apply_clip()
         if self.ctx.world_size > 1:
             self._dp.broadcast_parameters()
+            import torch.distributed as dist
+
+            for b in self.model.buffers():        # e.g. BatchNorm statistics start identical on every rank
+                if b.is_floating_point() or b.dtype in (torch.int64, torch.int32):
+                    dist.broadcast(b, src=0)
         return self
 
     def _sync_sparse_optimizers(self):
@@ -349,6 +358,13 @@ class TrainingEngine:
         if kind is not None and kind == getattr(criterion, "logits_kind", None):
             logits = m.forward_logits(*x) if isinstance(x, tuple) else m.forward_logits(x)
             return criterion.from_logits(logits, y), logits
+        if self.autocast_dtype is not None and self.device.type == "cuda":
+            if self.channels_last and torch.is_tensor(x) and x.dim() == 4:
+                x = x.contiguous(memory_format=torch.channels_last)
+            with torch.autocast("cuda", dtype=self.autocast_dtype):
+                out = m(*x) if isinstance(x, tuple) else m(x)
+            out = out.float() if torch.is_tensor(out) else out
+            return criterion(out, y), out
         out = m(*x) if isinstance(x, tuple) else m(x)
         return criterion(out, y), out
 
