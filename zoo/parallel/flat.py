@@ -118,9 +118,15 @@ class FlatParamArena:
         with torch.no_grad():
             for p, o in zip(self.params, self.offsets):
                 n = p.numel()
-                self.flat_p[o:o + n].copy_(p.detach().reshape(-1).to(self.device, torch.float32))
-                p.data = self.flat_p[o:o + n].view(p.shape)
-                g = self.flat_g[o:o + n].view(p.shape)
+                # A channels_last conv weight keeps its physical NHWC order inside the arena (the optimizer is
+                # elementwise, so order is irrelevant to it, while cuDNN gets the layout it was promised).
+                cl = p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last) and not p.is_contiguous()
+                src = p.detach().permute(0, 2, 3, 1) if cl else p.detach()
+                self.flat_p[o:o + n].copy_(src.reshape(-1).to(self.device, torch.float32))
+                view = (lambda f: f[o:o + n].view(p.shape[0], p.shape[2], p.shape[3], p.shape[1]).permute(0, 3, 1, 2)) if cl \
+                    else (lambda f: f[o:o + n].view(p.shape))
+                p.data = view(self.flat_p)
+                g = view(self.flat_g)
                 p.grad = g
                 p._zoo_grad = g
             if self.flat_p16 is not None:
@@ -140,7 +146,7 @@ class FlatParamArena:
         """Restore .grad views if user code dropped them (e.g. zero_grad(set_to_none=True))."""
         for p, o in zip(self.params, self.offsets):
             if p.grad is None or p.grad.data_ptr() != self.flat_g.data_ptr() + 4 * o:
-                p.grad = self.flat_g[o:o + p.numel()].view(p.shape)
+                p.grad = p._zoo_grad
 
 
 def _torch_opt_update(cfg: OptConfig, p, g, m, v, lr, step, gscale):
