@@ -1,0 +1,144 @@
+"""TFPark facade (TFDataset constructors, KerasModel fit/evaluate/predict/save_weights), LocalEstimator and the
+ONNX graph interpreter on hand-built GraphProto-shaped objects (reference tests: pyzoo/test/zoo/tfpark/*,
+pyzoo/test/zoo/pipeline/onnx/*)."""
+from types import SimpleNamespace as NS
+
+import numpy as np
+import pandas as pd
+import pytest
+import torch
+import torch.nn as nn
+
+
+@pytest.fixture(autouse=True)
+def _cpu_ctx(monkeypatch):
+    import zoo.common.nncontext as nc
+
+    monkeypatch.setenv("ZOO_FORCE_CPU", "1")
+    nc._CONTEXT = None
+    yield
+    nc._CONTEXT = None
+
+
+def _xy(n=600):
+    rng = np.random.RandomState(0)
+    x = rng.randn(n, 6).astype(np.float32)
+    return x, (x[:, :3].sum(1) > x[:, 3:].sum(1)).astype(np.int64)
+
+
+def test_tfdataset_and_keras_model(tmp_path):
+    from zoo.pipeline.api.keras.engine.topology import Sequential
+    from zoo.pipeline.api.keras.layers import Dense
+    from zoo.tfpark import KerasModel, TFDataset, TFEstimator, TFNet, TFOptimizer, ZooOptimizer
+
+    x, y = _xy()
+    with pytest.raises(ValueError):
+        TFDataset.from_ndarrays((x, y), batch_size=8, batch_per_thread=8)
+    ds = TFDataset.from_ndarrays((x, y), batch_size=60, val_tensors=(x[:100], y[:100]))
+    assert len(ds) == 600 and ds.get_validation_data().size() == 100
+    rdd = TFDataset.from_rdd([(x[i], y[i]) for i in range(50)], batch_size=10)
+    assert rdd.get_training_data().size() == 50
+    df = pd.DataFrame({"f": list(x[:40]), "l": y[:40]})
+    assert len(TFDataset.from_dataframe(df, ["f"], ["l"], batch_size=8)) == 40
+    with pytest.raises(NotImplementedError):
+        TFDataset.from_tfrecord_file("x")
+    net = Sequential([Dense(16, activation="relu", input_shape=(6,)), Dense(2, activation="softmax")])
+    net.compile(optimizer="adam", loss="sparse_categorical_crossentropy", metrics=["accuracy"])
+    km = KerasModel(net)
+    km.fit(ds, epochs=25)
+    loss, acc = km.evaluate(ds)
+    assert acc > 0.9 and km.metrics_names == ["loss", "Top1Accuracy"]
+    p = km.predict(TFDataset.from_ndarrays(x[:9], batch_per_thread=4))
+    assert p.shape == (9, 2)
+    km.save_weights(str(tmp_path / "w.pt"))
+    net2 = Sequential([Dense(16, activation="relu", input_shape=(6,)), Dense(2, activation="softmax")])
+    km2 = KerasModel(net2, optimizer="sgd", loss="sparse_categorical_crossentropy")
+    km2.load_weights(str(tmp_path / "w.pt"))
+    np.testing.assert_allclose(km2.predict(x[:9]), p, atol=1e-6)
+    plain = KerasModel(nn.Sequential(nn.Linear(6, 2), nn.Softmax(-1)), optimizer="adam", loss="sparse_categorical_crossentropy")
+    plain.fit(x, y, batch_size=100, epochs=1, distributed=True)
+    for cls in (TFOptimizer, TFEstimator, TFNet):
+        with pytest.raises(NotImplementedError):
+            cls()
+    with pytest.raises(NotImplementedError):
+        TFOptimizer.from_loss(None, None)
+    assert ZooOptimizer(torch.optim.SGD([torch.zeros(1, requires_grad=True)], lr=0.5)).defaults["lr"] == 0.5
+
+
+def test_local_estimator():
+    from zoo.pipeline.api.keras.optimizers import Adam
+    from zoo.pipeline.estimator import LocalEstimator
+
+    x, y = _xy(400)
+    data = [(x[i], y[i]) for i in range(400)]
+    est = LocalEstimator(nn.Sequential(nn.Linear(6, 16), nn.ReLU(), nn.Linear(16, 2), nn.Softmax(-1)), "sparse_categorical_crossentropy", Adam(lr=1e-2), ["accuracy"], thread_num=4)
+    est.fit(data, data[:100], batch_size=40, epoch=15)
+    assert est.validate(data, batch_size=100)[0].value > 0.9
+
+
+def _t(name, arr):
+    return NS(name=name, numpy_value=np.asarray(arr))
+
+
+def _node(op, ins, outs, **attrs):
+    return NS(op_type=op, input=ins, output=outs, attribute=list(attrs.items()))
+
+
+def test_onnx_graph_mlp_and_convnet():
+    from zoo.pipeline.api.onnx import OnnxLoader
+
+    rng = np.random.RandomState(0)
+    w1, b1, w2, b2 = rng.randn(8, 5).astype(np.float32), rng.randn(8).astype(np.float32), rng.randn(8, 3).astype(np.float32), rng.randn(3).astype(np.float32)
+    g = NS(initializer=[_t("w1", w1), _t("b1", b1), _t("w2", w2), _t("b2", b2)], input=[NS(name="x"), NS(name="w1"), NS(name="b1"), NS(name="w2"), NS(name="b2")],
+           output=[NS(name="y")],
+           node=[_node("Gemm", ["x", "w1", "b1"], ["h"], transB=1), _node("Relu", ["h"], ["r"]), _node("MatMul", ["r", "w2"], ["m"]),
+                 _node("Add", ["m", "b2"], ["a"]), _node("Softmax", ["a"], ["y"], axis=1)])
+    model = OnnxLoader(NS(graph=g)).to_keras()
+    x = torch.randn(4, 5)
+    ref = torch.softmax(torch.relu(x @ torch.from_numpy(w1).t() + torch.from_numpy(b1)) @ torch.from_numpy(w2) + torch.from_numpy(b2), 1)
+    torch.testing.assert_close(model(x), ref)
+    assert len(list(model.parameters())) == 4                            # initializers are trainable
+    model(x).sum().backward()
+    cw, cb = rng.randn(4, 3, 3, 3).astype(np.float32), rng.randn(4).astype(np.float32)
+    sc, bi, mu, va = np.ones(4, np.float32), np.zeros(4, np.float32), rng.randn(4).astype(np.float32), np.abs(rng.randn(4)).astype(np.float32) + 0.5
+    g2 = NS(initializer=[_t("cw", cw), _t("cb", cb), _t("sc", sc), _t("bi", bi), _t("mu", mu), _t("va", va), _t("shape", np.array([0, -1], np.int64))],
+            input=[NS(name="img")], output=[NS(name="out")],
+            node=[_node("Conv", ["img", "cw", "cb"], ["c"], kernel_shape=[3, 3], pads=[1, 1, 1, 1], strides=[1, 1]),
+                  _node("BatchNormalization", ["c", "sc", "bi", "mu", "va"], ["bn"], epsilon=1e-5), _node("LeakyRelu", ["bn"], ["l"], alpha=0.1),
+                  _node("MaxPool", ["l"], ["p"], kernel_shape=[2, 2], strides=[2, 2]), _node("GlobalAveragePool", ["p"], ["gap"]),
+                  _node("Reshape", ["gap", "shape"], ["out"])])
+    m2 = OnnxLoader(g2).to_keras()
+    img = torch.randn(2, 3, 8, 8)
+    c = torch.nn.functional.conv2d(img, torch.from_numpy(cw), torch.from_numpy(cb), padding=1)
+    bn = (c - torch.from_numpy(mu).view(1, -1, 1, 1)) / torch.sqrt(torch.from_numpy(va).view(1, -1, 1, 1) + 1e-5)
+    want = torch.nn.functional.max_pool2d(torch.nn.functional.leaky_relu(bn, 0.1), 2).mean((2, 3))
+    torch.testing.assert_close(m2(img), want, atol=1e-5, rtol=1e-4)
+    with pytest.raises(NotImplementedError):
+        OnnxLoader(NS(initializer=[], input=[NS(name="x")], output=[NS(name="y")], node=[_node("NonMaxSuppression", ["x"], ["y"])])).to_keras()
+    with pytest.raises(ImportError):
+        OnnxLoader.from_path("model.onnx")
+
+
+@pytest.mark.parametrize("op,ins,attrs,ref", [
+    ("Abs", [np.array([-1.0, 2.0])], {}, lambda a: np.abs(a)),
+    ("Clip", [np.array([-2.0, 0.5, 3.0])], {"min": -1.0, "max": 1.0}, lambda a: np.clip(a, -1, 1)),
+    ("Concat", [np.ones((2, 2)), np.zeros((2, 3))], {"axis": 1}, lambda a, b: np.concatenate([a, b], 1)),
+    ("Transpose", [np.arange(6.0).reshape(2, 3)], {"perm": [1, 0]}, lambda a: a.T),
+    ("Unsqueeze", [np.arange(3.0)], {"axes": [0]}, lambda a: a[None]),
+    ("Squeeze", [np.zeros((1, 3, 1))], {"axes": [0, 2]}, lambda a: a.reshape(3)),
+    ("Gather", [np.arange(12.0).reshape(4, 3), np.array([3, 0])], {"axis": 0}, lambda a, i: a[i]),
+    ("Slice", [np.arange(20.0).reshape(4, 5)], {"starts": [1, 0], "ends": [3, 4], "axes": [0, 1]}, lambda a: a[1:3, 0:4]),
+    ("ReduceMean", [np.arange(6.0).reshape(2, 3)], {"axes": [1], "keepdims": 0}, lambda a: a.mean(1)),
+    ("ReduceSum", [np.arange(6.0).reshape(2, 3)], {"axes": [0], "keepdims": 1}, lambda a: a.sum(0, keepdims=True)),
+    ("HardSigmoid", [np.array([-5.0, 0.0, 5.0])], {"alpha": 0.2, "beta": 0.5}, lambda a: np.clip(0.2 * a + 0.5, 0, 1)),
+    ("Flatten", [np.zeros((2, 3, 4))], {"axis": 1}, lambda a: a.reshape(2, 12)),
+    ("Pow", [np.array([2.0, 3.0]), np.array([2.0, 2.0])], {}, lambda a, b: a ** b),
+    ("AveragePool", [np.arange(16.0).reshape(1, 1, 4, 4)], {"kernel_shape": [2, 2], "strides": [2, 2]}, lambda a: a.reshape(1, 1, 2, 2, 2, 2).mean((3, 5))),
+    ("Shape", [np.zeros((2, 5))], {}, lambda a: np.array([2, 5])),
+    ("LogSoftmax", [np.array([[1.0, 2.0, 3.0]])], {"axis": 1}, lambda a: a - np.log(np.exp(a).sum(1, keepdims=True))),
+])
+def test_onnx_run_node(op, ins, attrs, ref):
+    from zoo.pipeline.api.onnx import OnnxLoader
+
+    out = OnnxLoader.run_node(_node(op, [f"i{k}" for k in range(len(ins))], ["o"], **attrs), ins)[0]
+    np.testing.assert_allclose(out, ref(*ins), atol=1e-6)
