@@ -135,20 +135,28 @@ class TorchEstimator:
         return {"epoch": st["epoch"] - 1, "iterations": st["neval"] - 1, "loss": st["Loss"],
                 "throughput": self.engine.last_throughput}
 
-    def _to_set(self, data, feature_cols=None, label_cols=None):
+    def _to_set(self, data, feature_cols=None, label_cols=None, batch_size=32):
         if data is None or isinstance(data, FeatureSet):
             return data
+        if callable(data) and not isinstance(data, torch.utils.data.DataLoader) and not hasattr(data, "collect"):
+            data = data(self.config, batch_size)          # a data_creator(config, batch_size)
+            if isinstance(data, FeatureSet):
+                return data
         if hasattr(data, "collect") and hasattr(data, "num_partitions"):
             return FeatureSet.xshards(data, feature_cols, label_cols)
         return self.engine._make_set(data)
 
     def evaluate(self, data, batch_size=32, feature_cols=None, label_cols=None):
-        res = self.engine.evaluate(self._to_set(data, feature_cols, label_cols), self.metrics or ["loss"], batch_size, self.loss)
+        res = self.engine.evaluate(self._to_set(data, feature_cols, label_cols, batch_size), self.metrics or ["loss"], batch_size, self.loss)
         return {r.name: r.value for r in res}
 
     def predict(self, data, batch_size=32, feature_cols=None):
         if hasattr(data, "collect") and hasattr(data, "num_partitions"):
             data = FeatureSet.xshards(data, feature_cols, None)
+        elif callable(data) and not isinstance(data, (FeatureSet, torch.utils.data.DataLoader)):
+            data = data(self.config, batch_size)
+            if isinstance(data, (tuple, list)) and len(data) == 2:
+                data = data[0]
         return self.engine.predict(data, batch_size)
 
     def get_model(self):
