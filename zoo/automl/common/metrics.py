@@ -78,3 +78,10 @@ class Evaluator:
     @staticmethod
     def get_metric_mode(metric):
         return "max" if metric.lower() in Evaluator.max_mode else "min"
+
+
+def check_input(y_true, y_pred, multioutput="raw_values"):
+    t, p = _prep(y_true, y_pred)
+    if multioutput not in ("raw_values", "uniform_average"):
+        raise ValueError("multioutput must be 'raw_values' or 'uniform_average'")
+    return t, p, t[0].shape

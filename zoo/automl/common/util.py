@@ -88,3 +88,26 @@ def split_input_df(input_df, val_split_ratio=0, test_split_ratio=0.1, ts_col="da
     val = df.iloc[max(n_train - overlap, 0):n_train + n_val]
     test = df.iloc[max(n_train + n_val - overlap, 0):]
     return train.reset_index(drop=True), val.reset_index(drop=True), test.reset_index(drop=True)
+
+
+def convert_bayes_configs(config):
+    from ..config.recipe import convert_bayes_configs as _c
+
+    return _c(config)
+
+
+# reference names (util.py): save/restore are the zip helpers above; HDFS variants need a client that is not here
+save, restore = save_zip, restore_zip
+
+
+def process(command, fail_fast=False, timeout=120):
+    from ...ray.process import session_execute
+
+    return session_execute(command, fail_fast=fail_fast, timeout=timeout)
+
+
+def get_remote_list(dir_in):
+    raise NotImplementedError("remote file systems (hdfs://) need clients that are not on this box")
+
+
+upload_ppl_hdfs = restore_hdfs = get_remote_list

@@ -17,3 +17,14 @@ class SearchEngine(ABC):
     @abstractmethod
     def get_best_trials(self, k):
         pass
+
+
+from ..config.recipe import GridSearch, RandomSample  # noqa: E402,F401
+
+
+class GoodError(Exception):
+    pass
+
+
+class BayersianOpt:
+    """Marker for a Bayesian-optimisation search (see BayesRecipe / RayTuneSearchEngine)."""

@@ -173,3 +173,19 @@ def stop_orca_context():
 
 def getOrCreateSparkContext(conf=None, appName=None):
     return init_nncontext(conf, appName or "zoo-b200")
+
+
+def get_analytics_zoo_conf():
+    """The framework's default configuration (reference: reads spark-analytics-zoo.conf from the jar)."""
+    return dict(ZOO_CONF_DEFAULTS)
+
+
+def load_conf(conf_str):
+    """`key value` lines -> dict (nncontext.py `load_conf`)."""
+    out = {}
+    for line in conf_str.split("\n"):
+        line = line.strip()
+        if line and not line.startswith("#"):
+            k, _, v = line.partition(" ")
+            out[k] = v.strip()
+    return out

@@ -111,3 +111,38 @@ register_zoo_func("setCoreNumber", set_core_number)
 register_zoo_func("getRemoteFileToLocal", get_remote_file_to_local)
 register_zoo_func("putLocalFileToRemote", put_local_file_to_remote)
 register_zoo_func("listPaths", get_file_list)
+
+
+def is_local_path(path):
+    return "://" not in path or path.startswith("file://")
+
+
+def append_suffix(prefix, path):
+    """`prefix` + the file extension of `path`."""
+    return prefix + os.path.splitext(path)[1]
+
+
+def convert_to_safe_path(input_path, follow_symlinks=True):
+    return os.path.realpath(input_path) if follow_symlinks else os.path.abspath(input_path)
+
+
+def to_list_of_numpy(elements):
+    if isinstance(elements, np.ndarray):
+        return [elements]
+    if np.isscalar(elements):
+        return [np.array(elements)]
+    if not isinstance(elements, list):
+        raise ValueError(f"Wrong type: {type(elements)}")
+    return [e if isinstance(e, np.ndarray) else np.array(e) for e in elements]
+
+
+def save_file(save_func, path, **kwargs):
+    if not is_local_path(path):
+        raise NotImplementedError("remote file systems need clients that are not on this box")
+    save_func(path[len("file://"):] if path.startswith("file://") else path, **kwargs)
+
+
+def load_from_file(load_func, path):
+    if not is_local_path(path):
+        raise NotImplementedError("remote file systems need clients that are not on this box")
+    return load_func(path[len("file://"):] if path.startswith("file://") else path)

@@ -79,3 +79,6 @@ class ZooModel(KerasNet):
 
 class KerasZooModel(ZooModel):
     """Keras-style built-in model (all KerasNet methods are inherited)."""
+
+
+ZooModelCreator = ZooModel

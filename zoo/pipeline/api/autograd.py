@@ -416,3 +416,6 @@ class CustomLoss(LossFunction):
         yp = torch.as_tensor(np.asarray(y_pred), dtype=torch.float32).requires_grad_(True)
         self.forward(yp, torch.as_tensor(np.asarray(y_true), dtype=torch.float32)).backward()
         return yp.grad.numpy()
+
+
+VariableOperator = Variable

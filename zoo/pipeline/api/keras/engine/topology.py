@@ -90,6 +90,15 @@ class KerasNet(nn.Module):
         self.eval()
         return self
 
+    def regularization_loss(self):
+        """Sum of the layers' weight regularizers (`W_regularizer=l2(...)`), or None when no layer has one."""
+        total = None
+        for m in self.modules():
+            for reg, t in getattr(m, "_zoo_regularizers", ()):
+                v = reg(t.float())
+                total = v if total is None else total + v
+        return total
+
     # -- fit / evaluate / predict ------------------------------------------------------
     @staticmethod
     def _as_set(x, y=None):

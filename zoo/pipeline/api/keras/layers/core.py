@@ -130,6 +130,8 @@ class Dense(ZooKerasLayer):
         self.dense = FusedDense(input_shape[-1], self.output_dim, activation=fused, bias=self.use_bias)
         init_weight(self.dense.weight, self.init)
         self._post = None if fused == self.activation or self.activation in (None, "linear") else get_activation(self.activation)
+        self._zoo_regularizers = [(r, t) for r, t in ((self.W_regularizer, self.dense.weight), (self.b_regularizer, self.dense.bias))
+                                  if r is not None and t is not None]
 
     def strip_final_activation(self, x):
         return self.dense(x)

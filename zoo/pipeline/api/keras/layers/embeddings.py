@@ -122,3 +122,9 @@ class SparseEmbedding(ZooKerasLayer):
         elif self.combiner == "sqrtn":
             out = out / cnt.sqrt()
         return out
+
+
+def prepare_embedding(embedding_file, word_index=None, randomize_unknown=False, normalize=False):
+    from .....models.textmatching.knrm import prepare_embedding as _p
+
+    return _p(embedding_file, word_index, randomize_unknown, normalize)

@@ -195,3 +195,12 @@ class BERT(TransformerLayer):
             b.hidden_drop, b.attn_drop = m.hidden_drop, m.attn_drop
         m.output_all_block = output_all_block
         return m
+
+
+def layer_norm(x, w, b, e=1e-5):
+    """Variable-level layer norm over the last dimension (self_attention.py `layer_norm`)."""
+    from ... import autograd as A
+
+    u = A.mean(x, axis=len(x.get_output_shape()) - 1, keepDims=True)
+    s = A.mean(A.square(x - u), axis=len(x.get_output_shape()) - 1, keepDims=True)
+    return (x - u) / A.sqrt(s + e) * w + b

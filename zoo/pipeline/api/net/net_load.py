@@ -57,3 +57,13 @@ class Net:
     @staticmethod
     def load_tf(path, inputs=None, outputs=None, byte_order="little_endian", bin_file=None, bigdl_type="float"):
         _unsupported("Net.load_tf")
+
+
+class JavaToPython:
+    """py4j class-name mapping of the reference (net_load.py:30-66); there is no JVM here, kept as a name."""
+
+    def __init__(self, jvalue=None, bigdl_type="float"):
+        self.jvalue = jvalue
+
+    def get_python_class(self):
+        return type(self.jvalue)

@@ -274,3 +274,8 @@ class OnnxLoader:
 
     def to_keras(self):
         return OnnxModel(self.graph)
+
+
+class OnnxInput:
+    def __init__(self, name, zvalue, data=None):
+        self.name, self.zvalue, self.data = name, zvalue, data

@@ -372,6 +372,9 @@ class TrainingEngine:
         from ..ops import loss as _fused_loss
 
         loss, _ = self.forward_loss(criterion, inputs, targets)
+        reg = self.model.regularization_loss() if hasattr(self.model, "regularization_loss") else None
+        if reg is not None:
+            loss = loss + reg
         _fused_loss.UNIT_UPSTREAM["on"] = True   # we seed backward with exactly 1.0
         try:
             loss.backward()

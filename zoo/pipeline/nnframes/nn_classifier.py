@@ -380,3 +380,16 @@ class NNClassifier(NNEstimator):
 
     def _label_array(self, col):
         return np.asarray([float(np.asarray(v).reshape(-1)[0]) for v in col], dtype=np.float32)
+
+
+# Spark-ML param mixin names of the reference (nn_classifier.py:29-132); here one mixin carries them all
+HasBatchSize = HasSamplePreprocessing = HasOptimMethod = _Params
+
+
+class HasThreshold:
+    def setThreshold(self, v):
+        self.threshold = float(v)
+        return self
+
+    def getThreshold(self):
+        return self.threshold

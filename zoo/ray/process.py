@@ -42,3 +42,32 @@ class ProcessMonitor:
 
 
 JVMGuard = ProcessMonitor
+
+
+def pids_from_gpid(gpid):
+    """PIDs whose process group is `gpid` (reads /proc)."""
+    out = []
+    for d in os.listdir("/proc"):
+        if d.isdigit():
+            try:
+                if os.getpgid(int(d)) == int(gpid):
+                    out.append(int(d))
+            except (ProcessLookupError, PermissionError):
+                pass
+    return out
+
+
+def session_execute(command, env=None, tag=None, fail_fast=False, timeout=120):
+    """Run a shell command in its own session; returns a ProcessInfo (process.py:60-88)."""
+    import subprocess
+
+    p = subprocess.Popen(command, shell=True, env=env, cwd=None, stdout=subprocess.PIPE, stderr=subprocess.PIPE, start_new_session=True)
+    try:
+        out, err = p.communicate(timeout=timeout)
+    except subprocess.TimeoutExpired:
+        p.kill()
+        out, err = p.communicate()
+    info = ProcessInfo(out.decode(errors="replace"), err.decode(errors="replace"), p.returncode, p.pid, tag or "default", os.getpgid(os.getpid()))
+    if fail_fast and p.returncode != 0:
+        raise Exception(f"command failed ({p.returncode}): {command}\n{info.err}")
+    return info

@@ -168,3 +168,16 @@ class RayContext:
 
     def purge(self):
         self.stop()
+
+
+JVMGuard = ProcessMonitor
+
+
+class RayServiceFuncGenerator:
+    """In the reference: builds the `ray start` shell commands run inside Spark barrier tasks (raycontext.py:51-187).
+    Workers here are local processes started by `RayContext.init()`, so this only records the settings."""
+
+    def __init__(self, python_loc=None, redis_port=None, ray_node_cpu_cores=None, password=None, object_store_memory=None,
+                 verbose=False, env=None, extra_params=None):
+        self.python_loc, self.redis_port, self.ray_node_cpu_cores = python_loc, redis_port, ray_node_cpu_cores
+        self.password, self.object_store_memory, self.verbose, self.env, self.extra_params = password, object_store_memory, verbose, env, extra_params

@@ -115,3 +115,20 @@ class TFDataset:
 
     def __len__(self):
         return self.feature_set.size()
+
+
+# concrete dataset class names of the reference (tf_dataset.py:600-1179); all are TFDataset here
+TFNdarrayDataset = TFFeatureDataset = TFBytesDataset = TFTextDataset = TFImageDataset = DataFrameDataset = TFDataDataset = TFDataset
+
+
+class TensorMeta:
+    def __init__(self, dtype, name=None, shape=None):
+        self.dtype, self.name, self.shape = dtype, name, shape
+
+
+class MergeFeatureLabelImagePreprocessing:
+    def __call__(self, f):
+        return f
+
+
+MergeFeatureLabelFeatureTransformer = MergeFeatureLabelImagePreprocessing

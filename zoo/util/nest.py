@@ -43,3 +43,7 @@ def ptensor_to_numpy(seq):
     import torch
 
     return pack_sequence_as(seq, [t.detach().cpu().numpy() if torch.is_tensor(t) else t for t in flatten(seq)])
+
+
+def is_sequence(s):
+    return isinstance(s, (list, tuple, dict))

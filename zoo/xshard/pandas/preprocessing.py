@@ -58,3 +58,25 @@ def read_json(file_path, context=None, **kwargs):
 
 def read_parquet(file_path, context=None, **kwargs):
     return read_file(context, file_path, "parquet", **kwargs)
+
+
+def read_file_ray(context, file_path, file_type, **kwargs):
+    return read_file(context, file_path, file_type, **kwargs)
+
+
+class RayPandasShard:
+    """One shard holding a pandas DataFrame (an actor in the reference; a plain object here, or a `RayContext.actor`)."""
+
+    def __init__(self, data=None):
+        self.data = data
+
+    def read_file_partitions(self, paths, file_type, **kwargs):
+        self.data = _load(list(paths), file_type, kwargs)
+        return 0
+
+    def apply(self, func, *args):
+        self.data = func(self.data, *args)
+        return 0
+
+    def get_data(self):
+        return self.data
