@@ -1,0 +1,6 @@
+# Source me: environment of a zoo-b200 checkout (reference: scripts/analytics-zoo-env.sh).
+export ZOO_HOME="$(cd "$(dirname "${BASH_SOURCE[0]}")/.." && pwd)"
+export PYTHONPATH="$ZOO_HOME:$PYTHONPATH"
+export PATH="$ZOO_HOME/scripts:$ZOO_HOME/scripts/cluster-serving:$PATH"
+# knobs the framework reads (zoo/common/nncontext.py): ZOO_NUM_MKLTHREADS / OMP_NUM_THREADS, ZOO_FORCE_CPU=1,
+# ZOO_SYMM=vmm|ipc, ZOO_COMM_BACKEND=auto|p2p|nccl|gloo, ZOO_FAULT_INJECT=rank:iteration
