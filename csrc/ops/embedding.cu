@@ -19,6 +19,7 @@
 // pass the reference performs for embedding gradients (Topology.scala:1187-1206).
 #include "../common/zoo_common.cuh"
 #include <limits.h>
+#include <stdlib.h>
 
 namespace zoo {
 
@@ -51,30 +52,44 @@ __device__ __forceinline__ void load_vec<__nv_bfloat16>(const __nv_bfloat16* p, 
 __device__ __forceinline__ float to_f(float x) { return x; }
 __device__ __forceinline__ float to_f(__nv_bfloat16 x) { return __bfloat162float(x); }
 
+// Select entry `i` of a small pointer table that lives in kernel-parameter space.  A switch keeps the table in the
+// constant bank; indexing it with a run-time value would make the compiler copy it to local memory first.
+template <typename P>
+__device__ __forceinline__ P pick8(P const (&arr)[kMaxPeers], int i) {
+  switch (i) {
+    case 0: return arr[0]; case 1: return arr[1]; case 2: return arr[2]; case 3: return arr[3];
+    case 4: return arr[4]; case 5: return arr[5]; case 6: return arr[6]; default: return arr[7];
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ const T* row_ptr(const ShardPtrs& s, long long id, int world, int D) {
-  const int owner = world > 1 ? (int)(id % world) : 0;
-  const long long local = world > 1 ? id / world : id;
-  return reinterpret_cast<const T*>(s.p[owner]) + local * (long long)D;
+  if (world == 1) return reinterpret_cast<const T*>(s.p[0]) + id * (long long)D;
+  const int owner = (int)(id % world);
+  const long long local = id / world;
+  return reinterpret_cast<const T*>(pick8(s.p, owner)) + local * (long long)D;
 }
 
 // One warp per (sample, slot). ids: [B, id_stride] int64, column id_col (and id_col2 for the
 // second table when MUL).  Rows whose id is out of [0, total_rows) produce zeros.
 // bag > 1: ids[b, id_col .. id_col+bag) are pooled (sum, or mean when mean != 0), negative ids skipped.
+// G lanes serve one sample (G = 32 unless the row is narrower than a warp's worth of 16-byte vectors), so narrow rows put
+// several samples in one warp and keep every lane loading.
 template <typename T, bool MUL, bool VEC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, MUL ? 4 : 6)
 embedding_gather_kernel(const long long* __restrict__ ids, int id_stride, int id_col, int id_col2,
                         int B, int bag, int mean, ShardPtrs ta, long long rows_a, ShardPtrs tb,
                         long long rows_b, int world, int D, __nv_bfloat16* __restrict__ out,
-                        long long ldo, __nv_bfloat16* __restrict__ save_a, __nv_bfloat16* __restrict__ save_b) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
+                        long long ldo, __nv_bfloat16* __restrict__ save_a, __nv_bfloat16* __restrict__ save_b, int G) {
+  const int gl = threadIdx.x & 31;
+  const int warp = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / G) + gl / G;   // = sample index
+  const int lane = gl - (gl / G) * G;
   if (warp >= B) return;
   const long long* idr = ids + (long long)warp * id_stride;
   __nv_bfloat16* o = out + (long long)warp * ldo;
   constexpr int VN = Vec<T>::N;
   if (VEC) {
-    for (int c = lane * VN; c < D; c += 32 * VN) {
+    for (int c = lane * VN; c < D; c += G * VN) {
       float acc[VN];
 #pragma unroll
       for (int t = 0; t < VN; ++t) acc[t] = 0.f;
@@ -129,7 +144,7 @@ embedding_gather_kernel(const long long* __restrict__ ids, int id_stride, int id
       }
     }
   } else {
-    for (int c = lane; c < D; c += 32) {
+    for (int c = lane; c < D; c += G) {
       float acc = 0.f;
       int cnt = 0;
       for (int j = 0; j < bag; ++j) {
@@ -389,6 +404,85 @@ emb_apply_kernel(BwdEntries en, int E, long long rows, int world, int rank, int*
   }
 }
 
+// Pass 3, fast path (winner list, D % 4 == 0, D <= 128): the update is latency-bound -- a row is a handful of 16-byte
+// loads (gradient row, possibly from a peer over NVLink, plus w / m / v) followed by a little math -- so the kernel is
+// organised for loads in flight rather than for arithmetic: a row uses only as many lanes as it has float4 columns
+// (G = 8 / 16 / 32), a warp therefore covers 32/G rows per pass, and every warp issues the loads of R passes before it
+// computes anything.
+template <int R>
+__global__ void __launch_bounds__(256)
+emb_apply_fast_kernel(BwdEntries en, int D, int G, float* __restrict__ accum, int* __restrict__ dup_flag, int* __restrict__ rep_of_row,
+                      SparseState st, int opt, const float* __restrict__ hyper, const int2* __restrict__ win_list,
+                      const int* __restrict__ win_count) {
+  const int count = *win_count;
+  const int lane = threadIdx.x & 31;
+  const int P = 32 / G;                                   // rows per warp pass
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int base = warp * P * R;
+  if (base >= count) return;
+  const int slot = lane / G, c = (lane - slot * G) * 4;
+  const bool col_ok = c < D;
+  const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5];
+  float bc1 = 1.f, bc2 = 1.f;
+  if (opt == SOPT_ADAM) { bc1 = 1.f - powf(b1, step); bc2 = 1.f - powf(b2, step); }
+  int e[R]; long long local[R]; bool ok[R], dup[R];
+  float g[R][4]; float4 w4[R], m4[R], v4[R], a4[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {                            // ---- issue every load first
+    const int idx = base + r * P + slot;
+    ok[r] = idx < count && col_ok;
+    e[r] = 0; local[r] = 0; dup[r] = false;
+    if (idx < count) { const int2 wl = win_list[idx]; e[r] = wl.x; local[r] = wl.y; }
+    if (ok[r]) {
+      dup[r] = dup_flag[e[r]] != 0;
+      entry_grad<true>(en, e[r], c, g[r]);
+      const long long o = local[r] * (long long)D + c;
+      w4[r] = *reinterpret_cast<const float4*>(st.w + o);
+      if (st.m) m4[r] = *reinterpret_cast<const float4*>(st.m + o);
+      if (st.v) v4[r] = *reinterpret_cast<const float4*>(st.v + o);
+      if (dup[r]) a4[r] = *reinterpret_cast<const float4*>(accum + (long long)e[r] * D + c);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {                            // ---- then compute and store
+    if (!ok[r]) continue;
+    float w[4] = {w4[r].x, w4[r].y, w4[r].z, w4[r].w};
+    float m[4] = {0, 0, 0, 0}, v[4] = {0, 0, 0, 0};
+    if (st.m) { m[0] = m4[r].x; m[1] = m4[r].y; m[2] = m4[r].z; m[3] = m4[r].w; }
+    if (st.v) { v[0] = v4[r].x; v[1] = v4[r].y; v[2] = v4[r].z; v[3] = v4[r].w; }
+    if (dup[r]) {
+      g[r][0] += a4[r].x; g[r][1] += a4[r].y; g[r][2] += a4[r].z; g[r][3] += a4[r].w;
+      *reinterpret_cast<float4*>(accum + (long long)e[r] * D + c) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const float gg = g[r][t] + wd * w[t];
+      if (opt == SOPT_ADAM) {
+        m[t] = b1 * m[t] + (1.f - b1) * gg;
+        v[t] = b2 * v[t] + (1.f - b2) * gg * gg;
+        w[t] -= lr * (m[t] / bc1) / (sqrtf(v[t] / bc2) + eps);
+      } else if (opt == SOPT_ADAGRAD) {
+        m[t] += gg * gg;
+        w[t] -= lr * gg / (sqrtf(m[t]) + eps);
+      } else {
+        w[t] -= lr * gg;
+      }
+    }
+    const long long o = local[r] * (long long)D + c;
+    *reinterpret_cast<float4*>(st.w + o) = make_float4(w[0], w[1], w[2], w[3]);
+    if (st.m) *reinterpret_cast<float4*>(st.m + o) = make_float4(m[0], m[1], m[2], m[3]);
+    if (st.v) *reinterpret_cast<float4*>(st.v + o) = make_float4(v[0], v[1], v[2], v[3]);
+    if (st.w16) {
+      uint2 pk; pk.x = pack_bf16(w[0], w[1]); pk.y = pack_bf16(w[2], w[3]);
+      *reinterpret_cast<uint2*>(st.w16 + o) = pk;
+    }
+    if (c == 0) {                                          // one lane per row restores the scratch
+      rep_of_row[local[r]] = INT_MAX;
+      if (dup[r]) dup_flag[e[r]] = 0;
+    }
+  }
+}
+
 // Dense-gradient mode (exact reference semantics for small tables): dTable[id] += dOut rows.
 template <bool VEC>
 __global__ void __launch_bounds__(256)
@@ -446,7 +540,18 @@ static int launch_sparse_update(const BwdEntries& en, int E, long long rows, int
   emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, wc);
   const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
   const unsigned ab = (unsigned)((E + threads - 1) / threads);  // accum: one lane per entry
-  if (vec) {
+  if (vec && win_list && D <= 128) {
+    emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, wl, wc);
+    const int G = D <= 32 ? 8 : (D <= 64 ? 16 : 32);
+    static int R = -1;
+    if (R < 0) { const char* ev = getenv("ZOO_APPLY_R"); R = ev ? atoi(ev) : 1; if (R != 1 && R != 2 && R != 4) R = 1; }
+    const int rows_per_warp = (32 / G) * R;
+    const long long warps = ((long long)E + rows_per_warp - 1) / rows_per_warp;
+    const unsigned grid = (unsigned)((warps * 32 + threads - 1) / threads);
+    if (R == 1) emb_apply_fast_kernel<1><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
+    else if (R == 2) emb_apply_fast_kernel<2><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
+    else emb_apply_fast_kernel<4><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
+  } else if (vec) {
     emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, wl, wc);
     emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper, wl, wc);
   } else {
@@ -487,14 +592,19 @@ ZOO_API int zoo_embedding_gather(const long long* ids, int id_stride, int id_col
     if (mul && ((uintptr_t)tb.p[i] & 15)) vec = false;
   }
   const int threads = 256;
-  const long long blocks = ((long long)B * 32 + threads - 1) / threads;
+  // lanes per sample: enough 16-byte vectors (or scalars) to cover one row, rounded up to a power of two
+  const int units = vec ? (D + vn - 1) / vn : D;
+  int G = 32;
+  while (G > 1 && G / 2 >= units) G /= 2;
+  const long long warps = ((long long)B + (32 / G) - 1) / (32 / G);
+  const long long blocks = (warps * 32 + threads - 1) / threads;
   cudaStream_t s = (cudaStream_t)stream;
   __nv_bfloat16* o = (__nv_bfloat16*)out;
   __nv_bfloat16* sa = (__nv_bfloat16*)save_a;
   __nv_bfloat16* sb = (__nv_bfloat16*)save_b;
 #define ZOO_GATHER(T, MUL, VEC)                                                                     \
   embedding_gather_kernel<T, MUL, VEC><<<(unsigned)blocks, threads, 0, s>>>(                        \
-      ids, id_stride, id_col, id_col2, B, bag, mean, ta, rows_a, tb, rows_b, world, D, o, ldo, sa, sb)
+      ids, id_stride, id_col, id_col2, B, bag, mean, ta, rows_a, tb, rows_b, world, D, o, ldo, sa, sb, G)
   if (table_dtype == 0) {
     if (mul) { if (vec) ZOO_GATHER(float, true, true); else ZOO_GATHER(float, true, false); }
     else     { if (vec) ZOO_GATHER(float, false, true); else ZOO_GATHER(float, false, false); }
