@@ -106,6 +106,60 @@ __global__ void __launch_bounds__(256) tcn_prep_grad_kernel(const float* __restr
   }
 }
 
+// Weight gradient: dW[o][i][j] = sum over (b, t) of g[b][o][t] * x[b][i][t - (K-1-j)*dil].
+// A small-output, huge-reduction GEMM (M = Cout, N = Cin per tap, reduction = B*T): each CTA owns a 64 x 64 block of
+// (o, i), walks a strided share of the (b, t-tile) work items with a 4 x 4 register tile per thread, and adds its partial
+// sum into dW with fp32 reductions at the end.  Taps are the outer loop (the g tile is re-read from L2, which is cheap
+// next to one pass over x per tap).
+constexpr int kWgTile = 64, kWgTT = 32;
+
+__global__ void __launch_bounds__(256) tcn_wgrad_kernel(const float* __restrict__ g, const float* __restrict__ x, float* __restrict__ dw,
+                                                        int B, int Cin, int Cout, int T, int K, int dil) {
+  __shared__ __align__(16) float gs[kWgTT][kWgTile + 4];
+  __shared__ __align__(16) float xs[kWgTT][kWgTile + 4];
+  const int o0 = blockIdx.y * kWgTile, i0 = blockIdx.z * kWgTile;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;          // thread tile: o = ty*4.., i = tx*4..
+  const int ttiles = (T + kWgTT - 1) / kWgTT;
+  const long long items = (long long)B * ttiles;
+  for (int j = 0; j < K; ++j) {
+    const int shift = (K - 1 - j) * dil;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[a][c] = 0.f;
+    for (long long it = blockIdx.x; it < items; it += gridDim.x) {
+      const int b = (int)(it / ttiles), t0 = (int)(it - (long long)b * ttiles) * kWgTT;
+      // load g[b][o0..o0+63][t0..t0+31] and x[b][i0..i0+63][t0-shift ..] transposed into [t][channel]
+      for (int l = tid; l < kWgTile * kWgTT; l += 256) {
+        const int ch = l / kWgTT, tt = l - ch * kWgTT, t = t0 + tt;
+        const int o = o0 + ch, i = i0 + ch, ts = t - shift;
+        gs[tt][ch] = (o < Cout && t < T) ? __ldg(g + ((size_t)b * Cout + o) * T + t) : 0.f;
+        xs[tt][ch] = (i < Cin && t < T && ts >= 0) ? __ldg(x + ((size_t)b * Cin + i) * T + ts) : 0.f;
+      }
+      __syncthreads();
+#pragma unroll 8
+      for (int tt = 0; tt < kWgTT; ++tt) {
+        const float4 a4 = *reinterpret_cast<const float4*>(&gs[tt][ty * 4]);
+        const float4 b4 = *reinterpret_cast<const float4*>(&xs[tt][tx * 4]);
+        const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) acc[a][c] = fmaf(av[a], bv[c], acc[a][c]);
+      }
+      __syncthreads();
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int o = o0 + ty * 4 + a, i = i0 + tx * 4 + c;
+        if (o < Cout && i < Cin && acc[a][c] != 0.f) atomicAdd(dw + ((size_t)o * Cin + i) * K + j, acc[a][c]);
+      }
+  }
+}
+
 }  // namespace zoo
 
 using namespace zoo;
@@ -158,6 +212,23 @@ ZOO_API int zoo_tcn_prep_grad(const float* dout, const float* out, const float* 
   const long long blocks = (n + 255) / 256;
   tcn_prep_grad_kernel<<<(unsigned)(blocks > 148 * 8 ? 148 * 8 : blocks), 256, 0, (cudaStream_t)stream>>>(
       dout, out, res, g, dres, n, relu, drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f);
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
+}
+
+/* dw[Cout,Cin,K] += sum_{b,t} g[b,o,t] * x[b,i,t-(K-1-j)*dilation]   (dw must be zero-initialised by the caller) */
+ZOO_API int zoo_tcn_conv_wgrad(const float* g, const float* x, float* dw, int B, int Cin, int Cout, int T, int K, int dilation,
+                               void* stream) {
+  if (!g || !x || !dw || B <= 0 || Cin <= 0 || Cout <= 0 || T <= 0 || K <= 0 || dilation <= 0) {
+    zoo_set_last_error("tcn_conv_wgrad: bad arguments", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  const long long items = (long long)B * ((T + kWgTT - 1) / kWgTT);
+  const unsigned ob = (Cout + kWgTile - 1) / kWgTile, ib = (Cin + kWgTile - 1) / kWgTile;
+  long long gx = (148LL * 2) / (ob * ib);
+  if (gx < 1) gx = 1;
+  if (gx > items) gx = items;
+  tcn_wgrad_kernel<<<dim3((unsigned)gx, ob, ib), 256, 0, (cudaStream_t)stream>>>(g, x, dw, B, Cin, Cout, T, K, dilation);
   ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;
 }

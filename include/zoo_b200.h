@@ -67,6 +67,22 @@ int zoo_embedding_sparse_update_noalloc(const long long* ids, int id_stride, int
                                         float grad_scale, long long rows, int world, int rank, int D,
                                         float* w, void* w16, float* m, float* v, int opt,
                                         const float* hyper, void* stream);
+/* Same as zoo_embedding_sparse_update plus win_list (int32 [2*B*bag + 4], any contents): pass 2 compacts the
+ * representative entries into it and pass 3 runs only over that list. */
+int zoo_embedding_sparse_update_w(const long long* ids, int id_stride, int id_col, int B, int bag,
+                                  const void* dout, long long ldg, const void* mul, long long ldmul,
+                                  float grad_scale, long long rows, int world, int rank, int D,
+                                  float* w, void* w16, float* m, float* v, int opt, const float* hyper,
+                                  int* rep_of_row, float* accum, int* dup_flag, int* win_list, void* stream);
+/* Backward of a row-sharded table: ids_src / dout_src / mul_src are HOST arrays of `world` device pointers into the
+ * symmetric heap (every rank's ids, gradient-row window, optional multiplier rows); the owner pulls the rows it needs over
+ * NVLink.  accum fp32 [world*B*bag, D], dup_flag int32 [world*B*bag], win_list int32 [2*world*B*bag + 4].
+ * Bracket with zoo_p2p_barrier. */
+int zoo_embedding_sparse_update_multi(const long long* const* ids_src, int id_stride, int id_col, int B, int bag,
+                                      const void* const* dout_src, long long ldg, const void* const* mul_src,
+                                      long long ldmul, float grad_scale, long long rows, int world, int rank,
+                                      int D, float* w, void* w16, float* m, float* v, int opt, const float* hyper,
+                                      int* rep_of_row, float* accum, int* dup_flag, int* win_list, void* stream);
 int zoo_embedding_dense_grad(const long long* ids, int id_stride, int id_col, int B, int bag,
                              const void* dout, long long ldg, const void* mul, long long ldmul,
                              float grad_scale, long long rows, int D, float* dtable, void* stream);
@@ -100,6 +116,11 @@ int zoo_symm_alloc(long long nbytes, void** ptr, void* ipc_handle64);
 int zoo_symm_open(const void* ipc_handle64, void** ptr);
 int zoo_symm_close(void* ptr);
 int zoo_symm_free(void* ptr);
+/* Large-page symmetric memory (cuMemCreate + POSIX fd export / cuMemMap on the peer), csrc/comm/symm_vmm.cu */
+int zoo_vmm_alloc(long long bytes, void** ptr, int* fd, long long* mapped_bytes);
+int zoo_vmm_import(int fd, long long mapped_bytes, void** ptr);
+int zoo_vmm_free(void* ptr, long long mapped_bytes);
+int zoo_close_fd(int fd);
 int zoo_rs_opt_ag(void* const* g, void* const* p, void* const* p16, void* const* m, void* const* v,
                   void* const* flags, void* const* epoch, void* const* hyper, long long start, long long end,
                   int world, int rank, int device_slot, int opt, int zero_grad, int grid, void* stream);
@@ -130,6 +151,8 @@ int zoo_tcn_conv_forward(const float* x, const float* w, const float* bias, cons
                          unsigned long long seed, void* stream);
 int zoo_tcn_conv_dgrad(const float* g, const float* w, float* dx, int B, int Cin, int Cout, int T, int K,
                        int dilation, void* stream);
+int zoo_tcn_conv_wgrad(const float* g, const float* x, float* dw, int B, int Cin, int Cout, int T, int K, int dilation,
+                       void* stream);
 int zoo_tcn_prep_grad(const float* dout, const float* out, const float* res, float* g, float* dres, long long n,
                       int relu, float drop_p, void* stream);
 

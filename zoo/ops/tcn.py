@@ -2,7 +2,7 @@
 
 `causal_conv1d` = dilated causal conv + bias + ReLU + dropout (+ residual add + ReLU) in ONE kernel;
 backward recovers the ReLU/dropout masks from the saved output (no mask tensor), runs the same tap
-kernel mirrored for d(x), and forms d(w) as K small GEMMs over (B*T).  `TemporalBlock` /
+kernel mirrored for d(x), and a register-tiled reduction kernel for d(w).  `TemporalBlock` /
 `TemporalConvNet` follow Bai et al.'s TCN (two weight-normalised dilated causal convs per block,
 1x1 down-sample on the residual when channels change) -- the forecaster the north-star adds next to
 the reference's LSTM / Seq2Seq / MTNet models.  CPU uses the same math in torch.
@@ -22,6 +22,7 @@ _nl.register_cuda_sigs({
     "zoo_tcn_conv_forward": [_V, _V, _V, _V, _V, _I, _I, _I, _I, _I, _I, _I, _F, C.c_ulonglong, _V],
     "zoo_tcn_conv_dgrad": [_V, _V, _V, _I, _I, _I, _I, _I, _I, _V],
     "zoo_tcn_prep_grad": [_V, _V, _V, _V, _V, _L, _I, _F, _V],
+    "zoo_tcn_conv_wgrad": [_V, _V, _V, _I, _I, _I, _I, _I, _I, _V],
 })
 
 
@@ -66,8 +67,8 @@ class _CausalConvFn(torch.autograd.Function):
                       "zoo_tcn_conv_dgrad")
         dw = None
         if ctx.needs_input_grad[1]:
-            xp = F.pad(x, ((K - 1) * dilation, 0))
-            dw = torch.stack([torch.einsum("bot,bit->oi", g, xp[:, :, j * dilation:j * dilation + T]) for j in range(K)], dim=-1)
+            dw = torch.zeros_like(w)
+            _nl.check(lib.zoo_tcn_conv_wgrad(g.data_ptr(), x.data_ptr(), dw.data_ptr(), B, Cin, Cout, T, K, dilation, st), "zoo_tcn_conv_wgrad")
         db = g.sum((0, 2)) if (has_bias and ctx.needs_input_grad[2]) else None
         return dx, dw, db, dres, None, None, None, None
 
