@@ -17,6 +17,7 @@
 // Pipelines: 4-stage smem ring (TMA <-> MMA) and a 2-stage TMEM accumulator ring
 // (MMA <-> epilogue) so the epilogue of tile i overlaps the main loop of tile i+1.
 #include "../common/zoo_common.cuh"
+#include <stdlib.h>
 
 namespace zoo {
 
@@ -47,6 +48,7 @@ struct GemmArgs {
   int a_mn, b_mn;           // 1 = MN-major operand
   int m_blocks, n_blocks, k_splits, kb_per_split;
   int epilogue, act;
+  int b_resident;           // 1: the whole B operand (<= 4 k-blocks) is loaded once per CTA and stays in shared memory
   long long ldd;            // leading dimension of out (elements)
   long long ldmask;         // leading dimension of mask (elements)
   int mask_cols;            // the mask applies to output columns [0, mask_cols) only
@@ -133,6 +135,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   __shared__ __align__(8) uint64_t empty_bar[kStages];
   __shared__ __align__(8) uint64_t tmem_full_bar[kAccStages];
   __shared__ __align__(8) uint64_t tmem_empty_bar[kAccStages];
+  __shared__ __align__(8) uint64_t b_full_bar;
   __shared__ uint32_t tmem_base_slot;
   __shared__ __align__(16) float s_bias[kMaxN];
 
@@ -149,6 +152,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < kAccStages; ++i) { mbar_init(&tmem_full_bar[i], 1); mbar_init(&tmem_empty_bar[i], kEpiWarps); }
+    mbar_init(&b_full_bar, 1);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(&tmem_base_slot, 512);
@@ -164,11 +168,28 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t a_stage_bytes = kABytes;
   const uint32_t b_boxes = g.b_mn ? (uint32_t)((g.block_n + 63) / 64) : 1u;
   const uint32_t b_stage_bytes = g.b_mn ? b_boxes * kMnBoxBytes : (uint32_t)g.block_n * 128u;
+  // Weight-stationary mode: the layers here are skinny (R <= 256), so B (the weights) is at most 4 k-blocks = 128 KiB.
+  // Streaming it through the ring again for every M tile makes the main loop L2-bandwidth bound (B is 2/3 of the
+  // bytes of a stage); instead it is loaded once and the ring carries only A.
+  const bool resident = g.b_resident != 0;
+  const uint32_t a_ring_stride = resident ? (uint32_t)kABytes : (uint32_t)kStageBytes;
+  const uint32_t b_res_base = kStages * kABytes;       // resident B lives behind the A ring (1024-byte aligned)
 
   if (warp == 0) {
     // ===================== TMA producer (one elected lane) =====================
     if (elect_one()) {
       uint32_t stage = 0, phase = 0;
+      if (resident && (int)blockIdx.x < total_work) {
+        mbar_arrive_expect_tx(&b_full_bar, (uint32_t)total_kb * b_stage_bytes);
+        for (int kb = 0; kb < total_kb; ++kb) {
+          uint8_t* sb = smem_al + b_res_base + kb * kBBytes;
+          if (!g.b_mn) {
+            tma_load_2d(sb, &tmap_b, &b_full_bar, kb * kBlockK, 0);
+          } else {
+            for (uint32_t bx = 0; bx < b_boxes; ++bx) tma_load_2d(sb + bx * kMnBoxBytes, &tmap_b, &b_full_bar, (int)bx * 64, kb * kBlockK);
+          }
+        }
+      }
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
         const int ks = w % g.k_splits;
         const int n_blk = (w / g.k_splits) % g.n_blocks;
@@ -177,9 +198,9 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const int kb1 = min(kb0 + g.kb_per_split, total_kb);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
-          uint8_t* sa = smem_al + stage * kStageBytes;
+          uint8_t* sa = smem_al + stage * a_ring_stride;
           uint8_t* sb = sa + kABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], a_stage_bytes + b_stage_bytes);
+          mbar_arrive_expect_tx(&full_bar[stage], resident ? a_stage_bytes : a_stage_bytes + b_stage_bytes);
           const int r0 = kb * kBlockK;
           if (!g.a_mn) {
             tma_load_2d(sa, &tmap_a, &full_bar[stage], r0, m_blk * kBlockM);
@@ -187,7 +208,9 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             tma_load_2d(sa, &tmap_a, &full_bar[stage], m_blk * kBlockM, r0);
             tma_load_2d(sa + kMnBoxBytes, &tmap_a, &full_bar[stage], m_blk * kBlockM + 64, r0);
           }
-          if (!g.b_mn) {
+          if (resident) {
+            // B is already in shared memory
+          } else if (!g.b_mn) {
             tma_load_2d(sb, &tmap_b, &full_bar[stage], r0, n_blk * g.block_n);
           } else {
             for (uint32_t bx = 0; bx < b_boxes; ++bx)
@@ -203,6 +226,10 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(kBlockM, (uint32_t)g.block_n, (uint32_t)g.a_mn, (uint32_t)g.b_mn);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+      if (resident && (int)blockIdx.x < total_work) {
+        mbar_wait(&b_full_bar, 0);
+        tc_fence_after();
+      }
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
         const int ks = w % g.k_splits;
         const int kb0 = ks * g.kb_per_split;
@@ -213,8 +240,8 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_base + stage * kStageBytes;
-          const uint32_t sb = sa + kABytes;
+          const uint32_t sa = smem_base + stage * a_ring_stride;
+          const uint32_t sb = resident ? smem_base + b_res_base + (uint32_t)kb * kBBytes : sa + kABytes;
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             // K-major: step 16 elements (32 B) inside the swizzled 128 B row.
@@ -394,6 +421,11 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
     g.k_splits = 1;
     g.kb_per_split = total_kb;
   }
+  // weight-stationary B: one N block, no split, and all of B's k-blocks fit behind the A ring
+  static int allow_resident = -1;
+  if (allow_resident < 0) { const char* ev = getenv("ZOO_DENSE_RESIDENT"); allow_resident = ev ? atoi(ev) : 1; }
+  g.b_resident = (allow_resident && g.k_splits == 1 && g.n_blocks == 1 && g.m_blocks > 1 &&
+                  kStages * kABytes + total_kb * kBBytes + 1024 <= kSmemBytes) ? 1 : 0;
   CUtensorMap ta, tb;
   int rc;
   if (!a_mn) rc = make_tmap(&ta, A, g.Mo, g.R, lda, kBlockK, kBlockM);

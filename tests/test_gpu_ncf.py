@@ -74,7 +74,9 @@ def test_cuda_graph_step_matches_eager():
     results = []
     for use_graph in (False, True):
         m = copy.deepcopy(base)
-        est = Estimator.from_torch(model=m, optimizer=torch.optim.Adam(m.parameters(), lr=1e-2),
+        # SGD: the update is linear in the gradient, so the fp32-atomic rounding noise of two runs stays at rounding size
+        # (Adam would turn a sign flip of a ~0 gradient into a 2*lr step and make the comparison flaky)
+        est = Estimator.from_torch(model=m, optimizer=torch.optim.SGD(m.parameters(), lr=0.1),
                                    loss=SparseCategoricalCrossEntropy(zero_based_label=False, padding_value=None), ctx=ctx)
         est.engine.use_cuda_graph = use_graph
         est.engine.prepare()
@@ -86,9 +88,6 @@ def test_cuda_graph_step_matches_eager():
         results.append((losses, m.linear_last.weight.detach().clone(), m.mlp_user_embed.weight.detach().clone()))
     (l0, w0, e0), (l1, w1, e1) = results
     torch.testing.assert_close(torch.tensor(l0), torch.tensor(l1), atol=2e-3, rtol=2e-3)
-    # fp32 atomics in wgrad make the two runs differ in rounding; Adam turns a sign flip of a ~0 gradient into a
-    # 2*lr step, so compare in bulk: no large difference anywhere, almost no element off by more than 1e-3
-    dw = (w0 - w1).abs()
-    assert dw.max() < 2e-2 and (dw > 1e-3).float().mean() < 2e-2, (dw.max().item(), (dw > 1e-3).float().mean().item(), l0, l1)
-    de = (e0 - e1).abs()
-    assert de.max() < 2e-2 and (de > 1e-3).float().mean() < 5e-3, (de.max().item(), (de > 1e-3).float().mean().item())
+    # fp32 atomics in wgrad / duplicate accumulation make the two runs differ only in rounding
+    torch.testing.assert_close(w0, w1, atol=2e-3, rtol=2e-2)
+    torch.testing.assert_close(e0, e1, atol=2e-3, rtol=2e-2)
