@@ -129,11 +129,17 @@ def _serving(args, ctx, torch):
         jpgs = [q.base64_encode_image(cv2.imencode(".jpg", rng.randint(0, 256, (224, 224, 3), dtype=np.uint8))[1]) for _ in range(64)]
 
     def feed():
-        for i in range(total):
-            if kind == "resnet50":
+        if kind == "resnet50":
+            for i in range(total):
                 srv.db.xadd("image_stream", {"uri": f"r{i}", "image": jpgs[i % 64]})
-            else:
-                q.enqueue_tensor(f"r{i}", np.array([rng.randint(1, 1_000_001), rng.randint(1, 100_001)], dtype=np.int64))
+            return
+        q.enqueue_tensor("r0", np.array([1, 1], dtype=np.int64))          # one record through the per-record path
+        chunk = 1024                                                        # then bulk producers (one native call per 1024 records)
+        for s0 in range(1, total, chunk):
+            n = min(chunk, total - s0)
+            ids = np.stack([rng.randint(1, 1_000_001, n), rng.randint(1, 100_001, n)], 1).astype(np.int64)
+            while q.enqueue_tensors([f"r{s0 + k}" for k in range(n)], ids) == 0:
+                pass
 
     t = threading.Thread(target=feed, daemon=True)
     t.start()

@@ -182,6 +182,93 @@ class Broker {
 
   long long used() { std::lock_guard<std::mutex> lk(mu_); return used_; }
 
+  // ---- batch paths for the in-process serving engine (no RESP encoding, one call per batch) ----------------
+  // Read up to `count` new entries of `key` for `group`, copying the bytes of `field` of each entry back to back into
+  // `data` (entries are taken while they have the same length as the first one and fit) and their `uri` fields,
+  // '\n'-separated, into `uris`.  Blocks up to block_ms for the first entry.  Returns the number of entries.
+  long long read_pack(const std::string& key, const std::string& group, long long count, long long block_ms, const std::string& field,
+                      char* data, long long data_cap, long long* rec_len, char* uris, long long uris_cap, long long* uris_len) {
+    std::unique_lock<std::mutex> lk(mu_);
+    ++ncmd_;
+    auto take = [&]() -> long long {
+      auto it = streams_.find(key);
+      if (it == streams_.end()) return 0;
+      Stream& s = it->second;
+      auto gi = s.groups.find(group);
+      if (gi == s.groups.end()) return -1;
+      Group& g = gi->second;
+      auto first = std::upper_bound(s.entries.begin(), s.entries.end(), g.last_delivered, [](const StreamId& v, const Entry& e) { return v < e.id; });
+      long long n = 0, doff = 0, uoff = 0, len = -1;
+      for (auto e = first; e != s.entries.end() && n < count; ++e) {
+        const std::string* val = nullptr; const std::string* uri = nullptr;
+        for (auto& f : e->fields) { if (f.first == field) val = &f.second; else if (f.first == "uri") uri = &f.second; }
+        if (!val || !uri) { if (n == 0) { g.last_delivered = e->id; continue; } break; }   // skip a malformed head entry
+        if (len < 0) len = (long long)val->size();
+        if ((long long)val->size() != len || doff + len > data_cap || uoff + (long long)uri->size() + 1 > uris_cap) break;
+        memcpy(data + doff, val->data(), (size_t)len); doff += len;
+        memcpy(uris + uoff, uri->data(), uri->size()); uoff += (long long)uri->size(); uris[uoff++] = '\n';
+        g.last_delivered = e->id;
+        ++n;
+      }
+      *rec_len = len < 0 ? 0 : len;
+      *uris_len = uoff;
+      return n;
+    };
+    long long n = take();
+    if (n != 0 || block_ms < 0) return n;
+    auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(block_ms == 0 ? 3600 * 1000 : block_ms);
+    while (true) {
+      if (cv_.wait_until(lk, deadline) == std::cv_status::timeout) return take();
+      n = take();
+      if (n != 0 || stopping_) return n;
+    }
+  }
+
+  // HSET <prefix><key_k> <field> <value_k> for k in [0, n); keys / values are blobs with n+1 offsets each.
+  long long hset_many(const std::string& prefix, const std::string& field, long long n, const char* keys, const long long* koff, const char* vals,
+                      const long long* voff) {
+    std::lock_guard<std::mutex> lk(mu_);
+    ++ncmd_;
+    long long bytes = 0;
+    for (long long k = 0; k < n; ++k) bytes += voff[k + 1] - voff[k] + (long long)field.size();
+    if (maxmemory_ > 0 && used_ + bytes > maxmemory_) return -1;
+    for (long long k = 0; k < n; ++k) {
+      std::string name = prefix;
+      name.append(keys + koff[k], (size_t)(koff[k + 1] - koff[k]));
+      auto& h = hashes_[name];
+      auto f = h.find(field);
+      std::string v(vals + voff[k], (size_t)(voff[k + 1] - voff[k]));
+      if (f == h.end()) { used_ += (long long)(field.size() + v.size()); h.emplace(field, std::move(v)); }
+      else { used_ += (long long)v.size() - (long long)f->second.size(); f->second = std::move(v); }
+    }
+    return n;
+  }
+
+  // XADD key * uri <uri_k> <field> <record_k> [extra fields...] for k in [0, n); records have a fixed length.
+  long long xadd_many(const std::string& key, long long n, const char* uris, const long long* uoff, const std::string& field, const char* recs,
+                      long long rec_len, const std::vector<std::pair<std::string, std::string>>& extra) {
+    std::lock_guard<std::mutex> lk(mu_);
+    ++ncmd_;
+    Stream& s = streams_[key];
+    long long added = 0;
+    for (long long k = 0; k < n; ++k) {
+      Entry e;
+      e.id = next_id(s);
+      e.fields.emplace_back("uri", std::string(uris + uoff[k], (size_t)(uoff[k + 1] - uoff[k])));
+      e.fields.emplace_back(field, std::string(recs + k * rec_len, (size_t)rec_len));
+      size_t bytes = 64 + e.fields[0].second.size() + (size_t)rec_len + field.size();
+      for (auto& x : extra) { e.fields.push_back(x); bytes += x.first.size() + x.second.size() + 16; }
+      if (maxmemory_ > 0 && used_ + (long long)bytes > maxmemory_) break;
+      e.bytes = bytes;
+      used_ += (long long)bytes;
+      s.last_id = e.id;
+      s.entries.push_back(std::move(e));
+      ++added;
+    }
+    if (added) cv_.notify_all();
+    return added;
+  }
+
  private:
   StreamId next_id(Stream& s) {
     using namespace std::chrono;
@@ -530,3 +617,19 @@ ZOO_RT_API int zoo_broker_command(void* b, int argc, const char* const* argv, co
   return 0;
 }
 ZOO_RT_API void zoo_broker_free(char* p) { free(p); }
+
+ZOO_RT_API long long zoo_broker_read_pack(void* b, const char* key, const char* group, long long count, long long block_ms, const char* field,
+                                          char* data, long long data_cap, long long* rec_len, char* uris, long long uris_cap, long long* uris_len) {
+  return static_cast<Broker*>(b)->read_pack(key, group, count, block_ms, field, data, data_cap, rec_len, uris, uris_cap, uris_len);
+}
+ZOO_RT_API long long zoo_broker_hset_many(void* b, const char* prefix, const char* field, long long n, const char* keys, const long long* koff,
+                                          const char* vals, const long long* voff) {
+  return static_cast<Broker*>(b)->hset_many(prefix, field, n, keys, koff, vals, voff);
+}
+ZOO_RT_API long long zoo_broker_xadd_many(void* b, const char* key, long long n, const char* uris, const long long* uoff, const char* field,
+                                          const char* recs, long long rec_len, int n_extra, const char* const* extra_names,
+                                          const char* const* extra_vals) {
+  std::vector<std::pair<std::string, std::string>> extra;
+  for (int i = 0; i < n_extra; ++i) extra.emplace_back(extra_names[i], extra_vals[i]);
+  return static_cast<Broker*>(b)->xadd_many(key, n, uris, uoff, field, recs, rec_len, extra);
+}

@@ -116,3 +116,31 @@ def test_client_backpressure():
     assert ok[0] and not ok[-1]                 # refused once 60 % of maxmemory is used
     assert b.info()["used_memory"] <= 0.6 * 20000 + 1200
     b.close()
+
+
+def test_serving_bulk_tensor_path():
+    """enqueue_tensors -> packed batch read -> hset_many: results equal the per-record path."""
+    from zoo.serving import ClusterServing, InputQueue, OutputQueue
+
+    class Score(nn.Module):
+        def forward(self, x):
+            x = x.float()
+            return torch.softmax(torch.stack([x[:, 0], x[:, 1], x[:, 0] - x[:, 1]], 1), -1)
+
+    conf = {"data": {"filter": "topN(1)"}, "params": {"batch_size": 64}}
+    srv = ClusterServing(conf, model=Score(), device="cpu").start()
+    q, o = InputQueue(conf, broker=srv.db), OutputQueue(conf, broker=srv.db)
+    rng = np.random.RandomState(0)
+    data = rng.randint(0, 5, (300, 2)).astype(np.int64)
+    assert q.enqueue_tensor("r0", data[0])
+    assert q.enqueue_tensors([f"r{i}" for i in range(1, 300)], data[1:]) == 299
+    assert srv.wait_until(300, 30)
+    time.sleep(0.05)
+    res = o.dequeue()
+    assert len(res) == 300
+    probs = torch.softmax(torch.tensor(np.stack([data[:, 0], data[:, 1], data[:, 0] - data[:, 1]], 1), dtype=torch.float32), -1)
+    for i in (0, 1, 57, 299):
+        idx, p = eval(res[f"r{i}"])[0]
+        assert abs(p - float(probs[i].max())) < 1e-5 and float(probs[i][idx]) == pytest.approx(float(probs[i].max()))
+    assert srv._tensor_meta is not None
+    srv.close()

@@ -22,6 +22,9 @@ def rt():
             "zoo_broker_stop_server": ([_V], None), "zoo_broker_used_memory": ([_V], _L),
             "zoo_broker_command": ([_V, _I, C.POINTER(C.c_char_p), C.POINTER(_L), C.POINTER(C.POINTER(C.c_char)), C.POINTER(_L)], _I),
             "zoo_broker_free": ([C.POINTER(C.c_char)], None),
+            "zoo_broker_read_pack": ([_V, C.c_char_p, C.c_char_p, _L, _L, C.c_char_p, _V, _L, C.POINTER(_L), _V, _L, C.POINTER(_L)], _L),
+            "zoo_broker_hset_many": ([_V, C.c_char_p, C.c_char_p, _L, C.c_char_p, _V, C.c_char_p, _V], _L),
+            "zoo_broker_xadd_many": ([_V, C.c_char_p, _L, C.c_char_p, _V, C.c_char_p, _V, _L, _I, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p)], _L),
             "zoo_arena_create": ([_I, _L, C.c_char_p], _V), "zoo_arena_destroy": ([_V], None), "zoo_arena_base": ([_V], _V),
             "zoo_arena_capacity": ([_V], _L), "zoo_arena_used": ([_V], _L), "zoo_arena_reset": ([_V], None),
             "zoo_arena_alloc": ([_V, _L, _I], _L), "zoo_arena_evict": ([_V, _L, _L], _I),
@@ -222,6 +225,45 @@ class Broker(_Commands):
 
     def used_memory(self):
         return self._lib.zoo_broker_used_memory(self._h)
+
+    # ---- batch paths (one native call per batch; used by the in-process serving engine and bulk producers) --------
+    def read_pack(self, stream, group, count, field, block_ms=5, buf=None, uri_buf=None):
+        """Up to `count` new entries whose `field` values have equal length -> (n, uint8 array [n, rec_len], list of uris)."""
+        if buf is None:
+            buf = np.empty(64 << 20, dtype=np.uint8)
+        if uri_buf is None:
+            uri_buf = np.empty(max(1 << 20, count * 64), dtype=np.uint8)
+        rec_len, uris_len = _L(0), _L(0)
+        n = self._lib.zoo_broker_read_pack(self._h, stream.encode(), group.encode(), int(count), int(block_ms), field.encode(), buf.ctypes.data,
+                                           buf.nbytes, C.byref(rec_len), uri_buf.ctypes.data, uri_buf.nbytes, C.byref(uris_len))
+        if n < 0:
+            raise RespError(f"NOGROUP No such consumer group '{group}' for key '{stream}'")
+        if n == 0:
+            return 0, None, []
+        uris = uri_buf[:uris_len.value].tobytes().decode().split("\n")[:-1]
+        return n, buf[:n * rec_len.value].reshape(n, rec_len.value), uris
+
+    def hset_many(self, prefix, field, keys, values):
+        kb = [k.encode() if isinstance(k, str) else k for k in keys]
+        vb = [v.encode() if isinstance(v, str) else v for v in values]
+        koff = np.zeros(len(kb) + 1, dtype=np.int64); np.cumsum([len(k) for k in kb], out=koff[1:])
+        voff = np.zeros(len(vb) + 1, dtype=np.int64); np.cumsum([len(v) for v in vb], out=voff[1:])
+        n = self._lib.zoo_broker_hset_many(self._h, prefix.encode(), field.encode(), len(kb), b"".join(kb), koff.ctypes.data, b"".join(vb), voff.ctypes.data)
+        if n < 0:
+            raise RespError("OOM command not allowed when used memory > 'maxmemory'.")
+        return n
+
+    def xadd_many(self, stream, uris, field, records: np.ndarray, extra=None):
+        """One entry per row of `records` ([n, ...] array; raw little-endian bytes), fields {uri, field, **extra}."""
+        recs = np.ascontiguousarray(records)
+        n = recs.shape[0]
+        ub = [u.encode() for u in uris]
+        uoff = np.zeros(n + 1, dtype=np.int64); np.cumsum([len(u) for u in ub], out=uoff[1:])
+        extra = extra or {}
+        names = (C.c_char_p * len(extra))(*[k.encode() for k in extra])
+        vals = (C.c_char_p * len(extra))(*[str(v).encode() for v in extra.values()])
+        return self._lib.zoo_broker_xadd_many(self._h, stream.encode(), n, b"".join(ub), uoff.ctypes.data, field.encode(), recs.ctypes.data,
+                                              recs.nbytes // max(n, 1), len(extra), names, vals)
 
     def close(self):
         if self._h:

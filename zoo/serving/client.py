@@ -108,6 +108,19 @@ class InputQueue(API):
         a = np.ascontiguousarray(arr)
         return self._guarded_xadd({"uri": uri, "tensor": a.tobytes(), "shape": ",".join(map(str, a.shape)), "dtype": a.dtype.str})
 
+    def enqueue_tensors(self, uris, arr):
+        """Bulk form of `enqueue_tensor`: one record per row of `arr`.  With an in-process broker this is a single native
+        call; over a socket it falls back to one XADD per record.  Returns the number of records written."""
+        a = np.ascontiguousarray(arr)
+        if hasattr(self.db, "xadd_many"):
+            inf = self.db.info()
+            if inf.get("maxmemory", 0) and inf["used_memory"] >= inf["maxmemory"] * self.input_threshold:
+                print("Redis queue is full, please wait for inference or delete the unprocessed records.")
+                time.sleep(self.interval_if_error)
+                return 0
+            return self.db.xadd_many(INPUT_STREAM, list(uris), "tensor", a, {"shape": ",".join(map(str, a.shape[1:])), "dtype": a.dtype.str})
+        return sum(bool(self.enqueue_tensor(u, a[k])) for k, u in enumerate(uris))
+
     @staticmethod
     def base64_encode_image(img):
         return base64.b64encode(img).decode("utf-8")

@@ -184,9 +184,42 @@ class ClusterServing:
             return "topn", (idx.cpu().numpy(), val.cpu().numpy())
         return "raw", out.float().cpu().numpy()
 
+    def _packed_batch(self):
+        """Tensor records through the broker's batch path: one native call returns the batch as one contiguous array."""
+        if self._pack_buf is None:
+            self._pack_buf = np.empty(max(16 << 20, self.conf.batch_size * 4096), dtype=np.uint8)
+            self._uri_buf = np.empty(max(1 << 20, self.conf.batch_size * 96), dtype=np.uint8)
+        n, data, uris = self.db.read_pack(INPUT_STREAM, GROUP, self.conf.batch_size, "tensor", 5, self._pack_buf, self._uri_buf)
+        if n == 0:
+            return None
+        shape, dtype = self._tensor_meta
+        return uris, data.view(dtype).reshape(n, *shape)
+
     def _engine_loop(self):
         idle = 0
+        self._pack_buf, self._tensor_meta = None, None
         while not self._stop.is_set():
+            if self._tensor_meta is not None and hasattr(self.db, "read_pack"):
+                got = self._packed_batch()
+                if got is None:
+                    continue
+                uris, batch = got
+                t0 = time.perf_counter()
+                try:
+                    out = self.model.predict_tensor(torch.from_numpy(batch))
+                    out = (out[0] if isinstance(out, (tuple, list)) else out)
+                    out = out.reshape(out.shape[0], -1)
+                    if self.conf.top_n is not None:
+                        from ..ops.serving_ops import topk
+
+                        idx, val = topk(out, min(self.conf.top_n, out.shape[1], 8), softmax=False)
+                        self._out_q.put((uris, "topn", (idx.cpu().numpy(), val.cpu().numpy()), t0))
+                    else:
+                        self._out_q.put((uris, "raw", out.float().cpu().numpy(), t0))
+                except Exception as e:
+                    log.exception("batch failed: %r", e)
+                    self._out_q.put((uris, "error", repr(e), t0))
+                continue
             entries = self._read_batch(5)
             if not entries:
                 idle += 1
@@ -195,6 +228,10 @@ class ClusterServing:
                 continue
             t0 = time.perf_counter()
             uris = [f["uri"].decode() for _, f in entries]
+            f0 = entries[0][1]
+            if "tensor" in f0 and self._tensor_meta is None and hasattr(self.db, "read_pack"):
+                # tensor records: from the next batch on use the packed batch path (homogeneous shape / dtype)
+                self._tensor_meta = ([int(v) for v in f0["shape"].decode().split(",") if v], np.dtype(f0["dtype"].decode()))
             try:
                 items = list(self.pool.map(self._decode_one, [f for _, f in entries]))
                 kind, payload = self._infer(items)
@@ -214,21 +251,27 @@ class ClusterServing:
             if item is None:
                 return
             uris, kind, payload, t0 = item
-            for k, uri in enumerate(uris):
-                if kind == "topn":
-                    value = format_topn(payload[0][k], payload[1][k])
-                elif kind == "raw":
-                    value = np.array2string(payload[k], separator=",", threshold=1 << 20, max_line_width=1 << 20)
+            if kind == "topn":
+                if payload[0].shape[1] == 1:
+                    values = [f"[[{i},{v}]]" for i, v in zip(payload[0][:, 0].tolist(), payload[1][:, 0].tolist())]
                 else:
-                    value = "NaN"
-                while True:      # retry forever on a full broker, every 3 s (ClusterServing.scala:276-310)
-                    try:
-                        self.db.hset("result:" + uri, "value", value)
+                    values = [format_topn(payload[0][k], payload[1][k]) for k in range(len(uris))]
+            elif kind == "raw":
+                values = [np.array2string(payload[k], separator=",", threshold=1 << 20, max_line_width=1 << 20) for k in range(len(uris))]
+            else:
+                values = ["NaN"] * len(uris)
+            while True:          # retry forever on a full broker, every 3 s (ClusterServing.scala:276-310)
+                try:
+                    if hasattr(self.db, "hset_many"):
+                        self.db.hset_many("result:", "value", uris, values)
+                    else:
+                        for uri, value in zip(uris, values):
+                            self.db.hset("result:" + uri, "value", value)
+                    break
+                except RespError as e:
+                    log.warning("result write failed (%s); retrying in 3 s", e)
+                    if self._stop.wait(3):
                         break
-                    except RespError as e:
-                        log.warning("result write failed (%s); retrying in 3 s", e)
-                        if self._stop.wait(3):
-                            break
             dt = time.perf_counter() - t0
             self.total_records += len(uris)
             self.latencies.append((len(uris), dt))
