@@ -28,7 +28,11 @@ for (K, N) in [(256, 256), (256, 128), (128, 64), (128, 5)]:
     dw = torch.zeros(N, K, device="cuda")
     y = torch.empty(M, ldn, device="cuda", dtype=torch.bfloat16)[:, :N]
     dx = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
+    bits = torch.zeros(M, (N + 31) // 32, dtype=torch.int32, device="cuda")
+    xbits = torch.full((M, (K + 31) // 32), 0x55555555, dtype=torch.int32, device="cuda")
     ops = {"fwd": (lambda: dense_forward(x, w, b, "relu", out=y), (M * K + M * N + N * K) * 2),
+           "fwd_bits": (lambda: dense_forward(x, w, b, "relu", out=y, relu_bits=bits), (M * K + M * N + N * K) * 2 + M * N // 8),
+           "dgrad_bits": (lambda: dense_dgrad(dy, w, out=dx, mask_bits=xbits), (M * N + M * K + N * K) * 2 + M * K // 8),
            "dgrad": (lambda: dense_dgrad(dy, w, x, out=dx), (M * N + 2 * M * K + N * K) * 2),
            "wgrad": (lambda: dense_wgrad(dy, x, dw), (M * N + M * K) * 2 + N * K * 4)}
     for name, (fn, nbytes) in ops.items():

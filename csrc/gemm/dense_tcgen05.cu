@@ -13,7 +13,10 @@
 //
 // Roles per CTA (384 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane),
 // warp 2 = TMEM allocator, warps 4-11 = epilogue (TMEM -> registers -> global; two warps per
-// TMEM lane quarter so every SM sub-partition has two epilogue warps to interleave).
+// TMEM lane quarter so every SM sub-partition has two epilogue warps to interleave).  The epilogue
+// stages each 32-row x 128-byte piece of the tile in swizzled shared memory and hands it to the TMA
+// engine (bulk tensor store; reduce-add for the split-K fp32 partial sums), so global writes are full
+// 128-byte lines issued asynchronously instead of 32 scattered 16-byte stores per instruction.
 // Pipelines: 4-stage smem ring (TMA <-> MMA) and a 2-stage TMEM accumulator ring
 // (MMA <-> epilogue) so the epilogue of tile i overlaps the main loop of tile i+1.
 #include "../common/zoo_common.cuh"
@@ -25,12 +28,15 @@ constexpr int kBlockM = 128;       // UMMA M
 constexpr int kBlockK = 64;        // 64 bf16 = 128 B = one swizzle-128B row
 constexpr int kUmmaK = 16;
 constexpr int kMaxN = 256;         // UMMA N upper bound
-constexpr int kStages = 4;
+constexpr int kStages = 4;          // ring depth when a stage carries A and B
+constexpr int kMaxStages = 12;      // ring depth limit when B is resident and the ring carries only A
 constexpr int kAccStages = 2;
 constexpr int kABytes = kBlockM * kBlockK * 2;   // 16 KiB
 constexpr int kBBytes = kMaxN * kBlockK * 2;     // 32 KiB
 constexpr int kStageBytes = kABytes + kBBytes;
-constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // + alignment slack
+constexpr int kEpiSlotBytes = 4096;               // per epilogue warp: 32 rows x 128 B staging box for the TMA store
+constexpr int kEpiStageOff = kStages * kStageBytes;
+constexpr int kSmemBytes = kStages * kStageBytes + 8 * kEpiSlotBytes + 1024;  // + alignment slack
 constexpr int kEpiWarps = 8;
 constexpr int kThreads = 128 + kEpiWarps * 32;  // 4 control warps + 8 epilogue warps
 constexpr int kMnBoxBytes = kBlockK * 128;       // one MN-major TMA box: 64 k-rows x 128 B
@@ -49,12 +55,17 @@ struct GemmArgs {
   int m_blocks, n_blocks, k_splits, kb_per_split;
   int epilogue, act;
   int b_resident;           // 1: the whole B operand (<= 4 k-blocks) is loaded once per CTA and stays in shared memory
+  int stages;               // ring depth of this launch
   long long ldd;            // leading dimension of out (elements)
   long long ldmask;         // leading dimension of mask (elements)
   int mask_cols;            // the mask applies to output columns [0, mask_cols) only
   void* out;
   const float* bias;                  // [No] fp32 or null
   const __nv_bfloat16* mask;          // [Mo, ldmask] or null
+  int tma_epi;                        // 1: epilogue through shared memory + TMA store / reduce-add
+  uint32_t* relu_bits;                // forward, optional: bit (n & 31) of word [m, n / 32] = (out[m, n] > 0)
+  const uint32_t* mask_bits;          // dgrad, optional: same layout, replaces `mask`
+  int bits_wpr;                       // words per row of relu_bits / mask_bits
 };
 
 template <int ACT>
@@ -129,10 +140,11 @@ template <int EPI, int ACT>
 __global__ void __launch_bounds__(kThreads, 1)
 dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                      const __grid_constant__ CUtensorMap tmap_b,
+                     const __grid_constant__ CUtensorMap tmap_out,
                      const GemmArgs g) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[kStages];
-  __shared__ __align__(8) uint64_t empty_bar[kStages];
+  __shared__ __align__(8) uint64_t full_bar[kMaxStages];
+  __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
   __shared__ __align__(8) uint64_t tmem_full_bar[kAccStages];
   __shared__ __align__(8) uint64_t tmem_empty_bar[kAccStages];
   __shared__ __align__(8) uint64_t b_full_bar;
@@ -148,9 +160,10 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    if (g.tma_epi) tma_prefetch_desc(&tmap_out);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < g.stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < kAccStages; ++i) { mbar_init(&tmem_full_bar[i], 1); mbar_init(&tmem_empty_bar[i], kEpiWarps); }
     mbar_init(&b_full_bar, 1);
     fence_mbar_init();
@@ -173,7 +186,8 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   // bytes of a stage); instead it is loaded once and the ring carries only A.
   const bool resident = g.b_resident != 0;
   const uint32_t a_ring_stride = resident ? (uint32_t)kABytes : (uint32_t)kStageBytes;
-  const uint32_t b_res_base = kStages * kABytes;       // resident B lives behind the A ring (1024-byte aligned)
+  const uint32_t b_res_base = (uint32_t)g.stages * kABytes;   // resident B lives behind the A ring (1024-byte aligned)
+  const int nstages = g.stages;
 
   if (warp == 0) {
     // ===================== TMA producer (one elected lane) =====================
@@ -182,7 +196,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       if (resident && (int)blockIdx.x < total_work) {
         mbar_arrive_expect_tx(&b_full_bar, (uint32_t)total_kb * b_stage_bytes);
         for (int kb = 0; kb < total_kb; ++kb) {
-          uint8_t* sb = smem_al + b_res_base + kb * kBBytes;
+          uint8_t* sb = smem_al + b_res_base + kb * b_stage_bytes;
           if (!g.b_mn) {
             tma_load_2d(sb, &tmap_b, &b_full_bar, kb * kBlockK, 0);
           } else {
@@ -217,7 +231,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
               tma_load_2d(sb + bx * kMnBoxBytes, &tmap_b, &full_bar[stage],
                           n_blk * g.block_n + (int)bx * 64, r0);
           }
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          if (++stage == (uint32_t)nstages) { stage = 0; phase ^= 1u; }
         }
       }
     }
@@ -241,7 +255,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_base + stage * a_ring_stride;
-          const uint32_t sb = resident ? smem_base + b_res_base + (uint32_t)kb * kBBytes : sa + kABytes;
+          const uint32_t sb = resident ? smem_base + b_res_base + (uint32_t)kb * b_stage_bytes : sa + kABytes;
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             // K-major: step 16 elements (32 B) inside the swizzled 128 B row.
@@ -254,7 +268,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
           umma_commit(&empty_bar[stage]);             // frees the smem slot when the MMAs retire
           if (kb == kb1 - 1) umma_commit(&tmem_full_bar[acc]);  // accumulator complete
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          if (++stage == (uint32_t)nstages) { stage = 0; phase ^= 1u; }
         }
         if (kb1 <= kb0) umma_commit(&tmem_full_bar[acc]);  // empty split: still hand the stage over
         if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
@@ -271,6 +285,127 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     const int c_end = half == 0 ? (nchunks + 1) / 2 : nchunks;
     uint32_t acc = 0, acc_phase = 0;
     int bias_blk = g.n_blocks == 1 ? 0 : -1;
+    if (g.tma_epi) {
+      // ---- staged epilogue: registers -> swizzled smem box (32 rows x 128 B) -> TMA store / reduce-add ----
+      const uint32_t slot = smem_base + kEpiStageOff + (warp - 4u) * kEpiSlotBytes;   // 1024-byte aligned
+      const uint32_t my_row = slot + lane * 128u;
+      const uint32_t swz = lane & 7u;
+      constexpr int UNIT = (EPI == EPI_RED_F32) ? 32 : 64;     // output columns per box (128 bytes)
+      const int nunits = (g.block_n + UNIT - 1) / UNIT;
+      const int u_begin = half == 0 ? 0 : (nunits + 1) / 2;
+      const int u_end = half == 0 ? (nunits + 1) / 2 : nunits;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int ks = w % g.k_splits;
+        const int n_blk = (w / g.k_splits) % g.n_blocks;
+        const int m_blk = w / (g.k_splits * g.n_blocks);
+        const bool has_work = (ks * g.kb_per_split) < total_kb;
+        if (EPI == EPI_BIAS_ACT && n_blk != bias_blk) {   // N > 256: reload this block's bias slice
+          named_bar_sync(1, kEpiWarps * 32);
+          const int t = threadIdx.x - 128;
+          const int n = n_blk * g.block_n + t;
+          if (t < kMaxN) s_bias[t] = (g.bias && t < g.block_n && n < g.No) ? g.bias[n] : 0.f;
+          named_bar_sync(1, kEpiWarps * 32);
+          bias_blk = n_blk;
+        }
+        mbar_wait(&tmem_full_bar[acc], acc_phase);
+        tc_fence_after();
+        const int row0 = m_blk * kBlockM + (int)q * 32;
+        const long long row = (long long)row0 + lane;
+        const bool row_ok = row < g.Mo;
+        const int col0 = n_blk * g.block_n;
+        const uint32_t taddr = tmem_base + acc * kMaxN + ((q * 32u) << 16);
+        for (int u = u_begin; u < u_end; ++u) {
+          const int col = col0 + u * UNIT;
+          if (EPI == EPI_RED_F32) {
+            uint32_t r[32];
+            tmem_ld_32x32(taddr + u * 32, r);
+            tmem_ld_wait();
+            if (lane == 0) bulk_wait_read0();              // the previous box has left shared memory
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) st_shared_u4(my_row + ((j ^ swz) << 4), r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && has_work && col < g.No && row0 < g.Mo) { tma_reduce_add_2d(&tmap_out, slot, col, row0); bulk_commit(); }
+          } else {
+            uint32_t r[2][32];
+            const bool second = u * 64 + 32 < g.block_n;
+            tmem_ld_32x32(taddr + u * 64, r[0]);
+            if (second) tmem_ld_32x32(taddr + u * 64 + 32, r[1]);
+            uint32_t mw[2] = {0xffffffffu, 0xffffffffu};
+            uint4 mk[2][4];
+            bool use_mk[2] = {false, false};
+            if (EPI == EPI_MASK) {                          // issue the mask loads under the TMEM latency
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                const int ch = col + h * 32;
+                if (ch >= g.mask_cols || ch >= g.No || !row_ok) continue;
+                if (g.mask_bits) {
+                  mw[h] = __ldg(g.mask_bits + row * g.bits_wpr + (ch >> 5));
+                } else if (g.mask) {
+                  use_mk[h] = true;
+                  if (ch + 32 <= g.No) {
+                    const uint4* mp = reinterpret_cast<const uint4*>(g.mask + row * g.ldmask + ch);
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) mk[h][t] = ld_nc_u4(mp + t);
+                  } else {
+                    __nv_bfloat16 tmp[32];
+                    for (int t = 0; t < 32; ++t) tmp[t] = (ch + t < g.No) ? g.mask[row * g.ldmask + ch + t] : __float2bfloat16(0.f);
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) mk[h][t] = reinterpret_cast<const uint4*>(tmp)[t];
+                  }
+                }
+              }
+            }
+            tmem_ld_wait();
+            uint32_t pk[2][16];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              uint32_t bits = 0;
+#pragma unroll
+              for (int j = 0; j < 32; j += 2) {
+                float v0 = __uint_as_float(r[h][j]), v1 = __uint_as_float(r[h][j + 1]);
+                if (EPI == EPI_BIAS_ACT) {
+                  v0 = act_fn<ACT>(v0 + s_bias[u * 64 + h * 32 + j]);
+                  v1 = act_fn<ACT>(v1 + s_bias[u * 64 + h * 32 + j + 1]);
+                  bits |= (v0 > 0.f ? 1u : 0u) << j;
+                  bits |= (v1 > 0.f ? 1u : 0u) << (j + 1);
+                } else {
+                  if (use_mk[h]) {
+                    const uint4 m4 = mk[h][j >> 3];
+                    const uint32_t m32 = ((j >> 1) & 3) == 0 ? m4.x : ((j >> 1) & 3) == 1 ? m4.y : ((j >> 1) & 3) == 2 ? m4.z : m4.w;
+                    const float2 f = unpack_bf16(m32);
+                    if (!(f.x > 0.f)) v0 = 0.f;
+                    if (!(f.y > 0.f)) v1 = 0.f;
+                  } else {
+                    if (!((mw[h] >> j) & 1u)) v0 = 0.f;
+                    if (!((mw[h] >> (j + 1)) & 1u)) v1 = 0.f;
+                  }
+                }
+                pk[h][j >> 1] = pack_bf16(v0, v1);
+              }
+              if (EPI == EPI_BIAS_ACT && g.relu_bits && row_ok && (h == 0 || second) && col + h * 32 < g.No)
+                g.relu_bits[row * g.bits_wpr + ((col + h * 32) >> 5)] = bits;
+            }
+            if (lane == 0) bulk_wait_read0();
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int h = j >> 2, o = (j & 3) * 4;
+              st_shared_u4(my_row + ((j ^ swz) << 4), pk[h][o], pk[h][o + 1], pk[h][o + 2], pk[h][o + 3]);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && has_work && col < g.No && row0 < g.Mo) { tma_store_2d(&tmap_out, slot, col, row0); bulk_commit(); }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+      }
+      if (lane == 0) bulk_wait_all();                      // all stores of this warp are complete before the CTA exits
+    } else
     for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
       const int ks = w % g.k_splits;
       const int n_blk = (w / g.k_splits) % g.n_blocks;
@@ -354,14 +489,15 @@ static PFN_encodeTiled get_encode() {
 
 // rows x cols bf16 matrix, row-major with leading dimension ld (elements).
 static int make_tmap(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld,
-                     int box_cols, int box_rows) {
+                     int box_cols, int box_rows, bool f32 = false) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) { zoo_set_last_error("cuTensorMapEncodeTiled unavailable", __FILE__, __LINE__); return ZOO_ERR_CUDA; }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * (f32 ? 4 : 2)};
+  const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r == CUDA_ERROR_INVALID_CONTEXT) {
@@ -369,7 +505,7 @@ static int make_tmap(CUtensorMap* m, const void* base, long long rows, long long
     // one of our kernels) has no context bound; the runtime binds the primary context of its current device
     // on the first real call.  Do that and encode again.
     cudaFree(0);
-    r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+    r = enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   }
@@ -424,8 +560,16 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
   // weight-stationary B: one N block, no split, and all of B's k-blocks fit behind the A ring
   static int allow_resident = -1;
   if (allow_resident < 0) { const char* ev = getenv("ZOO_DENSE_RESIDENT"); allow_resident = ev ? atoi(ev) : 1; }
+  const int b_stage = b_mn ? ((bn + 63) / 64) * kMnBoxBytes : bn * 128;
   g.b_resident = (allow_resident && g.k_splits == 1 && g.n_blocks == 1 && g.m_blocks > 1 &&
-                  kStages * kABytes + total_kb * kBBytes + 1024 <= kSmemBytes) ? 1 : 0;
+                  kStages * kABytes + total_kb * b_stage <= kEpiStageOff) ? 1 : 0;
+  g.stages = kStages;
+  if (g.b_resident) {
+    static int max_stages = -1;
+    if (max_stages < 0) { const char* ev = getenv("ZOO_DENSE_ASTAGES"); max_stages = ev ? atoi(ev) : kMaxStages; if (max_stages < 2 || max_stages > kMaxStages) max_stages = kMaxStages; }
+    g.stages = (kEpiStageOff - total_kb * b_stage) / kABytes;
+    if (g.stages > max_stages) g.stages = max_stages;
+  }
   CUtensorMap ta, tb;
   int rc;
   if (!a_mn) rc = make_tmap(&ta, A, g.Mo, g.R, lda, kBlockK, kBlockM);
@@ -434,6 +578,15 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
   if (!b_mn) rc = make_tmap(&tb, B, g.No, g.R, ldb, kBlockK, bn);
   else       rc = make_tmap(&tb, B, g.R, g.No, ldb, 64, kBlockK);
   if (rc) return rc;
+  static int allow_tma_epi = -1;
+  if (allow_tma_epi < 0) { const char* ev = getenv("ZOO_DENSE_TMA_EPI"); allow_tma_epi = ev ? atoi(ev) : 1; }
+  g.tma_epi = (allow_tma_epi || g.relu_bits || g.mask_bits) ? 1 : 0;   // the bit-mask forms exist only in the staged epilogue
+  CUtensorMap to = ta;
+  if (g.tma_epi) {
+    if (g.epilogue == EPI_RED_F32) rc = make_tmap(&to, g.out, g.Mo, g.No, g.ldd, 32, 32, true);
+    else                           rc = make_tmap(&to, g.out, g.Mo, g.No, g.ldd, 64, 32);
+    if (rc) return rc;
+  }
   const int total_work = g.m_blocks * g.n_blocks * g.k_splits;
   const int grid = total_work < max_ctas ? total_work : max_ctas;
 #define ZOO_LAUNCH(EPI, ACT)                                                                                   \
@@ -444,7 +597,7 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));          \
       attr_set = true;                                                                                         \
     }                                                                                                          \
-    dense_tcgen05_kernel<EPI, ACT><<<grid, kThreads, kSmemBytes, stream>>>(ta, tb, g);                         \
+    dense_tcgen05_kernel<EPI, ACT><<<grid, kThreads, kSmemBytes, stream>>>(ta, tb, to, g);                        \
   } while (0)
   if (g.epilogue == EPI_RED_F32) ZOO_LAUNCH(EPI_RED_F32, ACT_NONE);
   else if (g.epilogue == EPI_MASK) ZOO_LAUNCH(EPI_MASK, ACT_NONE);
@@ -470,6 +623,36 @@ ZOO_API int zoo_dense_fwd_bf16(const void* x, long long ldx, const void* w, long
   g.out = y; g.ldd = ldy; g.bias = bias; g.mask = nullptr; g.ldmask = 0;
   if (ldy % 8 || ((uintptr_t)y & 15)) { zoo_set_last_error("dense_fwd: ldy % 8 != 0", __FILE__, __LINE__); return ZOO_ERR_ARG; }
   return launch(x, ldx, 0, w, ldw, 0, g, num_sms(), (cudaStream_t)stream);
+}
+
+// Forward that also emits the sign bits of its output: bit (n & 31) of relu_bits[m * bits_wpr + n / 32] = (Y[m, n] > 0).
+// The next layer's dgrad reads them instead of re-reading Y as its ReLU mask (1/16 of the bytes).
+ZOO_API int zoo_dense_fwd_bf16_bits(const void* x, long long ldx, const void* w, long long ldw, const float* bias,
+                                    void* y, long long ldy, int M, int N, int K, int act, unsigned int* relu_bits,
+                                    int bits_wpr, void* stream) {
+  GemmArgs g{};
+  g.Mo = M; g.No = N; g.R = K; g.epilogue = EPI_BIAS_ACT; g.act = act;
+  g.out = y; g.ldd = ldy; g.bias = bias; g.mask = nullptr; g.ldmask = 0;
+  g.relu_bits = relu_bits; g.bits_wpr = bits_wpr;
+  if (ldy % 8 || ((uintptr_t)y & 15)) { zoo_set_last_error("dense_fwd: ldy % 8 != 0", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+  if (relu_bits && bits_wpr * 32 < N) { zoo_set_last_error("dense_fwd: bits_wpr too small", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+  return launch(x, ldx, 0, w, ldw, 0, g, num_sms(), (cudaStream_t)stream);
+}
+
+// dgrad whose ReLU mask is the bit matrix written by zoo_dense_fwd_bf16_bits (mask_cols must be a multiple of 32 or K).
+ZOO_API int zoo_dense_dgrad_bf16_bits(const void* dy, long long lddy, const void* w, long long ldw, const unsigned int* mask_bits,
+                                      int bits_wpr, int mask_cols, void* dx, long long lddx, int M, int N, int K, void* stream) {
+  GemmArgs g{};
+  g.Mo = M; g.No = K; g.R = N; g.epilogue = EPI_MASK; g.act = ACT_NONE;
+  g.out = dx; g.ldd = lddx; g.bias = nullptr; g.mask = nullptr; g.ldmask = 0;
+  g.mask_bits = mask_bits; g.bits_wpr = bits_wpr;
+  g.mask_cols = (mask_cols <= 0 || mask_cols > K) ? K : mask_cols;
+  if (!mask_bits || (g.mask_cols % 32 && g.mask_cols != K) || bits_wpr * 32 < g.mask_cols) {
+    zoo_set_last_error("dense_dgrad_bits: need mask_bits, mask_cols % 32 == 0 and bits_wpr * 32 >= mask_cols", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  if (lddx % 8 || ((uintptr_t)dx & 15)) { zoo_set_last_error("dense_dgrad: output rows must be 16-byte aligned", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+  return launch(dy, lddy, 0, w, ldw, 1, g, num_sms(), (cudaStream_t)stream);
 }
 
 // dX[M,K] (bf16, lddx) = (dY[M,N] (bf16, lddy) * W[N,K] (bf16, ldw)) * (mask[M,K] > 0)   (mask may be null)

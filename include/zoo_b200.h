@@ -33,6 +33,13 @@ int zoo_dense_fwd_bf16(const void* x, long long ldx, const void* w, long long ld
 int zoo_dense_dgrad_bf16(const void* dy, long long lddy, const void* w, long long ldw, const void* mask,
                          long long ldmask, int mask_cols, void* dx, long long lddx, int M, int N, int K,
                          void* stream);
+/* Forward that also writes the sign bits of Y (bit n%32 of relu_bits[m*bits_wpr + n/32] = Y[m,n] > 0), and the dgrad
+ * that takes them as its ReLU mask (mask_cols: multiple of 32, or <= 0 for all K columns). */
+int zoo_dense_fwd_bf16_bits(const void* x, long long ldx, const void* w, long long ldw, const float* bias,
+                            void* y, long long ldy, int M, int N, int K, int act, unsigned int* relu_bits,
+                            int bits_wpr, void* stream);
+int zoo_dense_dgrad_bf16_bits(const void* dy, long long lddy, const void* w, long long ldw, const unsigned int* mask_bits,
+                              int bits_wpr, int mask_cols, void* dx, long long lddx, int M, int N, int K, void* stream);
 int zoo_dense_wgrad_bf16(const void* dy, long long lddy, const void* x, long long ldx, float* dw,
                          long long lddw, int M, int N, int K, void* stream);
 int zoo_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* out, void* stream);

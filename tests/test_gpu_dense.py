@@ -92,6 +92,52 @@ def test_dense_dgrad_partial_mask():
     torch.testing.assert_close(dx.float(), ref, atol=3e-2, rtol=2e-2)
 
 
+def _unpack_bits(bits, n):
+    sh = torch.arange(32, device=bits.device, dtype=torch.int64)
+    b = ((bits.to(torch.int64).unsqueeze(-1) >> sh) & 1).reshape(bits.shape[0], -1)
+    return b[:, :n].bool()
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 256, 256), (65536, 128, 256), (4096, 64, 128), (333, 96, 72), (2048, 512, 64)])
+def test_dense_relu_bits_roundtrip(M, N, K):
+    """Forward writes the sign bits of its output; the next layer's dgrad takes them as its ReLU mask."""
+    from zoo.ops.dense import dense_dgrad, dense_forward
+
+    torch.manual_seed(11)
+    x = _bf(torch.randn(M, K, device="cuda"))
+    w = _bf(torch.randn(N, K, device="cuda") / K ** 0.5)
+    b = torch.randn(N, device="cuda")
+    bits = torch.zeros(M, (N + 31) // 32, dtype=torch.int32, device="cuda")
+    y = dense_forward(x, w, b, "relu", relu_bits=bits)
+    torch.cuda.synchronize()
+    assert torch.equal(_unpack_bits(bits, N), y > 0)
+    # consumer layer: N -> 40 features; its dgrad produces dY of width N masked by the bits
+    w2 = _bf(torch.randn(40, N, device="cuda") / N ** 0.5)
+    dz = _bf(torch.randn(M, 40, device="cuda"))
+    dy = dense_dgrad(dz, w2, mask_bits=bits)
+    ref = (dz.float() @ w2.float()) * (y > 0)
+    torch.testing.assert_close(dy.float(), ref, atol=3e-2, rtol=2e-2)
+    if N >= 64:
+        dy2 = dense_dgrad(dz, w2, mask_bits=bits, mask_cols=32)
+        ref2 = dz.float() @ w2.float()
+        ref2[:, :32] = ref2[:, :32] * (y[:, :32] > 0)
+        torch.testing.assert_close(dy2.float(), ref2, atol=3e-2, rtol=2e-2)
+
+
+def test_dense_fwd_into_column_window():
+    """`out` may be a column window of a wider buffer (fused concat): neighbouring columns stay untouched."""
+    from zoo.ops.dense import dense_forward
+
+    torch.manual_seed(12)
+    M, N, K = 777, 72, 64
+    x = _bf(torch.randn(M, K, device="cuda"))
+    w = _bf(torch.randn(N, K, device="cuda") / 8)
+    buf = torch.full((M, 160), 7.0, device="cuda", dtype=torch.bfloat16)
+    dense_forward(x, w, None, None, out=buf[:, 8:8 + N])
+    torch.testing.assert_close(buf[:, 8:8 + N].float(), x.float() @ w.float().t(), atol=3e-2, rtol=2e-2)
+    assert bool((buf[:, :8] == 7).all()) and bool((buf[:, 8 + N:] == 7).all())
+
+
 def test_colsum():
     from zoo.ops.dense import colsum
 

@@ -63,7 +63,10 @@ class NeuralCF(Recommender):
         h = self.mlp(h)
         if self.include_mf:
             mf = multi_lookup(ids, [LookupSpec(self.mf_user_embed, 0, mul_table=self.mf_item_embed, mul_col=1)])
+            bits = getattr(h, "_zoo_relu_bits", None)
             h = torch.cat([h, mf.to(h.dtype)], dim=1)
+            if bits is not None:            # sign bits of the MLP half travel with the concatenated activation
+                h._zoo_relu_bits = bits
         return self.linear_last(h)
 
     def forward(self, x):

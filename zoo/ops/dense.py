@@ -43,9 +43,11 @@ def _aligned(t: torch.Tensor) -> bool:
     return t.stride(-1) == 1 and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0
 
 
-def dense_forward(x16: torch.Tensor, w16: torch.Tensor, bias: torch.Tensor | None, act, out: torch.Tensor | None = None):
+def dense_forward(x16: torch.Tensor, w16: torch.Tensor, bias: torch.Tensor | None, act, out: torch.Tensor | None = None,
+                  relu_bits: torch.Tensor | None = None):
     """y = act(x16 @ w16.T + bias) with bf16 operands on the tcgen05 kernel.  `out` may be a
-    column window of a wider buffer (fused concat)."""
+    column window of a wider buffer (fused concat).  `relu_bits` (int32 [M, ceil(N/32)]) optionally receives the
+    sign bits of y for the consumer's dgrad (`dense_dgrad(mask_bits=...)`)."""
     M, K = x16.shape
     N = w16.shape[0]
     if out is None:
@@ -54,20 +56,31 @@ def dense_forward(x16: torch.Tensor, w16: torch.Tensor, bias: torch.Tensor | Non
     lib = _nl.cuda_lib()
     if not (_aligned(x16) and _aligned(w16) and _aligned(out)):
         raise _nl.NativeError("dense_forward: operands must have 16-byte aligned rows (pad K/N to a multiple of 8)")
+    if relu_bits is not None:
+        _nl.check(lib.zoo_dense_fwd_bf16_bits(x16.data_ptr(), x16.stride(0), w16.data_ptr(), w16.stride(0), _nl.ptr(bias),
+                                              out.data_ptr(), out.stride(0), M, N, K, ACT_IDS[act], relu_bits.data_ptr(),
+                                              relu_bits.stride(0), _nl.stream_ptr()), "zoo_dense_fwd_bf16_bits")
+        return out
     _nl.check(lib.zoo_dense_fwd_bf16(x16.data_ptr(), x16.stride(0), w16.data_ptr(), w16.stride(0), _nl.ptr(bias),
                                      out.data_ptr(), out.stride(0), M, N, K, ACT_IDS[act], _nl.stream_ptr()),
               "zoo_dense_fwd_bf16")
     return out
 
 
-def dense_dgrad(dy16, w16, mask16=None, out=None, mask_cols=0):
-    """dx = (dy16 @ w16) * (mask16 > 0); with mask_cols > 0 only columns [0, mask_cols) are masked."""
+def dense_dgrad(dy16, w16, mask16=None, out=None, mask_cols=0, mask_bits=None):
+    """dx = (dy16 @ w16) * (mask16 > 0); with mask_cols > 0 only columns [0, mask_cols) are masked.  `mask_bits` is the
+    bit-matrix form of the mask written by `dense_forward(relu_bits=...)`."""
     M, N = dy16.shape
     K = w16.shape[1]
     if out is None:
         ldk = (K + 7) // 8 * 8
         out = torch.empty((M, ldk), dtype=torch.bfloat16, device=dy16.device)[:, :K]
     lib = _nl.cuda_lib()
+    if mask_bits is not None:
+        _nl.check(lib.zoo_dense_dgrad_bf16_bits(dy16.data_ptr(), dy16.stride(0), w16.data_ptr(), w16.stride(0), mask_bits.data_ptr(),
+                                                mask_bits.stride(0), int(mask_cols), out.data_ptr(), out.stride(0), M, N, K,
+                                                _nl.stream_ptr()), "zoo_dense_dgrad_bf16_bits")
+        return out
     _nl.check(lib.zoo_dense_dgrad_bf16(dy16.data_ptr(), dy16.stride(0), w16.data_ptr(), w16.stride(0),
                                        _nl.ptr(mask16), mask16.stride(0) if mask16 is not None else 0, int(mask_cols),
                                        out.data_ptr(), out.stride(0), M, N, K, _nl.stream_ptr()),
@@ -108,21 +121,28 @@ class _FusedDenseFn(torch.autograd.Function):
     when the parameters carry ``_zoo_grad`` views (set by the flat-parameter arena)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False, relu_input_cols=0):
+    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False, relu_input_cols=0, x_bits=None, emit_bits=False):
         x16 = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
         if not _aligned(x16):
             x16 = _pad_cols(x16)
-        y = dense_forward(x16, w16, bias, act)
+        bits = None
+        if emit_bits:
+            bits = torch.empty((x16.shape[0], (w16.shape[0] + 31) // 32), dtype=torch.int32, device=x16.device)
+        y = dense_forward(x16, w16, bias, act, relu_bits=bits)
+        ctx.x_bits = x_bits
         ctx.act = act
         ctx.relu_input = relu_input
         ctx.skip_relu_bwd = skip_relu_bwd
         ctx.relu_input_cols = relu_input_cols
         ctx.in_dtype = x.dtype
-        ctx.save_for_backward(x16, w16, y if act == "relu" else None, weight, bias)
+        ctx.save_for_backward(x16, w16, y if act == "relu" and not skip_relu_bwd else None, weight, bias)
+        if emit_bits:
+            ctx.mark_non_differentiable(bits)
+            return y, bits
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *_unused):
         x16, w16, y, weight, bias = ctx.saved_tensors
         dy16 = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
         if ctx.act == "relu":
@@ -135,8 +155,11 @@ class _FusedDenseFn(torch.autograd.Function):
         K = weight.shape[1]
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = dense_dgrad(dy16, w16[:, :K] if w16.shape[1] != K else w16, x16[:, :K] if ctx.relu_input else None,
-                             mask_cols=ctx.relu_input_cols)
+            wk = w16[:, :K] if w16.shape[1] != K else w16
+            if ctx.relu_input and ctx.x_bits is not None:
+                dx = dense_dgrad(dy16, wk, mask_bits=ctx.x_bits, mask_cols=ctx.relu_input_cols)
+            else:
+                dx = dense_dgrad(dy16, wk, x16[:, :K] if ctx.relu_input else None, mask_cols=ctx.relu_input_cols)
             if dx.dtype != ctx.in_dtype:
                 dx = dx.to(ctx.in_dtype)
         gw = getattr(weight, "_zoo_grad", None)
@@ -154,7 +177,7 @@ class _FusedDenseFn(torch.autograd.Function):
             elif ctx.needs_input_grad[2]:
                 db_ret = torch.zeros_like(bias, dtype=torch.float32)
                 colsum(dy16, db_ret)
-        return dx, dw_ret, db_ret, None, None, None, None, None
+        return dx, dw_ret, db_ret, None, None, None, None, None, None, None
 
 
 def _pad_cols(t: torch.Tensor) -> torch.Tensor:
@@ -213,9 +236,22 @@ class FusedDense(nn.Module):
             lead = x.shape[:-1]
             x2 = x.reshape(-1, x.shape[-1])
             self.refresh_shadow()
+            # ReLU sign bits travel with the activation tensor: the producer writes them in its forward epilogue and
+            # this layer's dgrad reads them instead of the full activation
+            x_bits = getattr(x, "_zoo_relu_bits", None) if self.relu_input else None
+            if x_bits is not None and (x_bits.shape[0] != x2.shape[0] or (self.relu_input_cols or self.in_features) % 32
+                                       or x_bits.shape[1] * 32 < (self.relu_input_cols or self.in_features)):
+                x_bits = None
+            emit = self.activation == "relu" and self.skip_relu_bwd and torch.is_grad_enabled() and self.out_features % 32 == 0
             y = _FusedDenseFn.apply(x2, self.weight, self.bias, self.weight_bf16, self.activation, self.relu_input,
-                                    self.skip_relu_bwd, self.relu_input_cols)
-            return y.reshape(*lead, self.out_features)
+                                    self.skip_relu_bwd, self.relu_input_cols, x_bits, emit)
+            bits = None
+            if emit:
+                y, bits = y
+            out = y.reshape(*lead, self.out_features)
+            if bits is not None:
+                out._zoo_relu_bits = bits
+            return out
         y = F.linear(x.to(self.weight.dtype), self.weight, self.bias)
         return _act_torch(y, self.activation)
 
