@@ -203,6 +203,8 @@ def main():
             if k == Wm:
                 torch.cuda.synchronize(); barrier(); marks["t0"] = time.time()
             marks["n"] = k + 1
+            if os.environ.get("ZOO_BENCH_TRACE"):
+                marks.setdefault("ts", []).append(time.time())
 
         eng.on_step = on_step
         eng.async_loss = True
@@ -211,6 +213,10 @@ def main():
         torch.cuda.synchronize(); barrier()
         marks["t1"] = time.time()
         eng.on_step = None
+        if os.environ.get("ZOO_BENCH_TRACE") and ctx.rank == 0:
+            ts = marks["ts"]
+            d = [round((b - a) * 1e6) for a, b in zip(ts[:-1], ts[1:])]
+            print("e2e per-step host deltas (us):", d, "tail after last step (us):", round((marks["t1"] - ts[-1]) * 1e6), file=sys.stderr)
         dt = torch.tensor([marks["t1"] - marks["t0"]], device=dev, dtype=torch.float64)
         if ctx.world_size > 1:
             torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)

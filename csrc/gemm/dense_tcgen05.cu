@@ -66,6 +66,7 @@ struct GemmArgs {
   uint32_t* relu_bits;                // forward, optional: bit (n & 31) of word [m, n / 32] = (out[m, n] > 0)
   const uint32_t* mask_bits;          // dgrad, optional: same layout, replaces `mask`
   int bits_wpr;                       // words per row of relu_bits / mask_bits
+  float* colsum;                      // split-K mode, optional: colsum[m] += sum_r A(m, r)  (the bias gradient of a wgrad)
 };
 
 template <int ACT>
@@ -169,6 +170,13 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(&tmem_base_slot, 512);
+  if (EPI == EPI_RED_F32 && g.colsum && warp == 3) {
+    // B operand of the bias-gradient MMA: a 16 x 64 tile of ones (2 KiB; any swizzle of all-ones is all-ones).  It borrows
+    // the first epilogue staging slot, which is not written before every MMA of this CTA's only work item has retired.
+    uint32_t* ones = reinterpret_cast<uint32_t*>(smem_al + kEpiStageOff);
+    for (int i = lane; i < 512; i += 32) ones[i] = 0x3F803F80u;
+    fence_proxy_async_smem();
+  }
   if (EPI == EPI_BIAS_ACT && g.n_blocks == 1 && threadIdx.x < kMaxN)   // bias of the only N block, once
     s_bias[threadIdx.x] = (g.bias && (int)threadIdx.x < g.No) ? g.bias[threadIdx.x] : 0.f;
   tc_fence_before();
@@ -244,10 +252,13 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         mbar_wait(&b_full_bar, 0);
         tc_fence_after();
       }
+      const uint32_t idesc_ones = make_idesc_bf16(kBlockM, 16u, (uint32_t)g.a_mn, 0u);
+      const uint64_t d_ones = make_smem_desc_sw128(smem_base + kEpiStageOff, 16, 1024);
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
         const int ks = w % g.k_splits;
         const int kb0 = ks * g.kb_per_split;
         const int kb1 = min(kb0 + g.kb_per_split, total_kb);
+        const bool do_colsum = EPI == EPI_RED_F32 && g.colsum && ((w / g.k_splits) % g.n_blocks) == 0;
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * kMaxN;
@@ -265,6 +276,8 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             const uint64_t db = g.b_mn ? make_smem_desc_sw128(sb + k * 2048, kMnBoxBytes, 1024)
                                        : make_smem_desc_sw128(sb + k * 32, 16, 1024);
             umma_bf16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            // row sums of A ride along as a 16-column MMA against ones (accumulator: the unused second TMEM stage)
+            if (do_colsum) umma_bf16(tmem_base + kMaxN, da, d_ones, idesc_ones, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty_bar[stage]);             // frees the smem slot when the MMAs retire
           if (kb == kb1 - 1) umma_commit(&tmem_full_bar[acc]);  // accumulator complete
@@ -327,6 +340,12 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0 && has_work && col < g.No && row0 < g.Mo) { tma_reduce_add_2d(&tmap_out, slot, col, row0); bulk_commit(); }
+            if (g.colsum && n_blk == 0 && half == 0 && u == u_begin) {       // bias gradient: TMEM column 256 of this lane's row
+              uint32_t cs[32];
+              tmem_ld_32x32(tmem_base + kMaxN + ((q * 32u) << 16), cs);
+              tmem_ld_wait();
+              if (has_work && row_ok) atomicAdd(g.colsum + row, __uint_as_float(cs[0]));
+            }
           } else {
             uint32_t r[2][32];
             const bool second = u * 64 + 32 < g.block_n;
@@ -580,7 +599,7 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
   if (rc) return rc;
   static int allow_tma_epi = -1;
   if (allow_tma_epi < 0) { const char* ev = getenv("ZOO_DENSE_TMA_EPI"); allow_tma_epi = ev ? atoi(ev) : 1; }
-  g.tma_epi = (allow_tma_epi || g.relu_bits || g.mask_bits) ? 1 : 0;   // the bit-mask forms exist only in the staged epilogue
+  g.tma_epi = (allow_tma_epi || g.relu_bits || g.mask_bits || g.colsum) ? 1 : 0;   // the bit-mask forms exist only in the staged epilogue
   CUtensorMap to = ta;
   if (g.tma_epi) {
     if (g.epilogue == EPI_RED_F32) rc = make_tmap(&to, g.out, g.Mo, g.No, g.ldd, 32, 32, true);
@@ -670,6 +689,29 @@ ZOO_API int zoo_dense_dgrad_bf16(const void* dy, long long lddy, const void* w, 
     return ZOO_ERR_ARG;
   }
   return launch(dy, lddy, 0, w, ldw, 1, g, num_sms(), (cudaStream_t)stream);
+}
+
+extern "C" int zoo_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* out, void* stream);
+
+// zoo_dense_wgrad_bf16 that also accumulates the bias gradient db[N] += column sums of dY.  When every CTA owns a single
+// split (always the case for layers up to 256 x 256) the sums come out of the same kernel as one extra 16-column MMA per
+// k-step; otherwise a separate column-sum kernel runs.
+ZOO_API int zoo_dense_wgrad_bias_bf16(const void* dy, long long lddy, const void* x, long long ldx, float* dw,
+                                      long long lddw, float* db, int M, int N, int K, void* stream) {
+  GemmArgs g{};
+  g.Mo = N; g.No = K; g.R = M; g.epilogue = EPI_RED_F32; g.act = ACT_NONE;
+  g.out = dw; g.ldd = lddw; g.bias = nullptr; g.mask = nullptr; g.ldmask = 0;
+  if (lddw % 4 || ((uintptr_t)dw & 15)) { zoo_set_last_error("dense_wgrad: lddw % 4 != 0", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+  const int m_blocks = (N + kBlockM - 1) / kBlockM, n_blocks = (K + kMaxN - 1) / kMaxN;
+  static int allow_fused = -1;
+  if (allow_fused < 0) { const char* ev = getenv("ZOO_DENSE_FUSED_COLSUM"); allow_fused = ev ? atoi(ev) : 1; }
+  const bool fused = db && allow_fused && m_blocks * n_blocks <= num_sms();
+  if (db && !fused) {
+    int rc = zoo_colsum_bf16(dy, lddy, M, N, db, stream);
+    if (rc) return rc;
+  }
+  g.colsum = fused ? db : nullptr;
+  return launch(dy, lddy, 1, x, ldx, 1, g, num_sms(), (cudaStream_t)stream);
 }
 
 // dW[N,K] (fp32, lddw) += dY[M,N]^T (bf16, lddy) * X[M,K] (bf16, ldx); split over the batch dimension.

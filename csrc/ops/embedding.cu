@@ -210,9 +210,10 @@ __device__ __forceinline__ long long entry_row(const BwdEntries& en, int e) {
 // Pass 1: elect, per touched row, the smallest entry index as its representative.
 __global__ void __launch_bounds__(256)
 emb_mark_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* __restrict__ rep_of_row,
-                int* __restrict__ win_count) {
+                int* __restrict__ win_count, float* __restrict__ step_slot) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e == 0 && win_count) *win_count = 0;     // the winner list is rebuilt by pass 2
+  if (e == 0 && step_slot) *step_slot += 1.f;  // optimizer step counter (bias correction) kept on the device
   if (e >= E) return;
   const long long id = entry_row(en, e);
   if (id < 0 || id >= rows) return;
@@ -533,11 +534,12 @@ static ShardPtrs make_ptrs(const void* const* tabs, int world) {
 // The three passes.  win_list (optional, int32 [2*E + 4]): [0..2E) = (entry, local row) pairs, [2E] = count.
 static int launch_sparse_update(const BwdEntries& en, int E, long long rows, int world, int rank, int D, int* rep_of_row,
                                 float* accum, int* dup_flag, const SparseState& st, int opt, const float* hyper, bool vec,
-                                int* win_list, cudaStream_t s) {
+                                int* win_list, cudaStream_t s, bool bump_step = false) {
   const int threads = 256;
   int2* wl = reinterpret_cast<int2*>(win_list);
   int* wc = win_list ? win_list + 2 * (size_t)E : nullptr;
-  emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, wc);
+  emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, wc,
+                                                                  bump_step ? const_cast<float*>(hyper) + 5 : nullptr);
   const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
   const unsigned ab = (unsigned)((E + threads - 1) / threads);  // accum: one lane per entry
   if (vec && win_list && D <= 128) {
@@ -667,7 +669,7 @@ ZOO_API int zoo_embedding_sparse_update_w(const long long* ids, int id_stride, i
                                           const void* dout, long long ldg, const void* mul, long long ldmul,
                                           float grad_scale, long long rows, int world, int rank, int D,
                                           float* w, void* w16, float* m, float* v, int opt, const float* hyper,
-                                          int* rep_of_row, float* accum, int* dup_flag, int* win_list, void* stream) {
+                                          int* rep_of_row, float* accum, int* dup_flag, int* win_list, int bump_step, void* stream) {
   if (!ids || !dout || !w || !hyper || !rep_of_row || !accum || !dup_flag || !win_list || D <= 0 || bag < 1 || world < 1 ||
       world > kMaxPeers || rank < 0 || rank >= world || (rows + world - 1) / world > INT_MAX) {
     zoo_set_last_error("embedding_sparse_update_w: bad arguments", __FILE__, __LINE__);
@@ -685,7 +687,7 @@ ZOO_API int zoo_embedding_sparse_update_w(const long long* ids, int id_stride, i
                    (((uintptr_t)accum & 15) == 0) && (!m || ((uintptr_t)m & 15) == 0) &&
                    (!v || ((uintptr_t)v & 15) == 0) && (!w16 || ((uintptr_t)w16 & 7) == 0) &&
                    (!mul || ((ldmul % 4 == 0) && ((uintptr_t)mul & 7) == 0));
-  return launch_sparse_update(en, E, rows, world, rank, D, rep_of_row, accum, dup_flag, st, opt, hyper, vec, win_list, (cudaStream_t)stream);
+  return launch_sparse_update(en, E, rows, world, rank, D, rep_of_row, accum, dup_flag, st, opt, hyper, vec, win_list, (cudaStream_t)stream, bump_step != 0);
 }
 
 // Multi-GPU form of zoo_embedding_sparse_update: the backward of a row-sharded table.
@@ -697,11 +699,12 @@ ZOO_API int zoo_embedding_sparse_update_w(const long long* ids, int id_stride, i
 // dispatch/combine design without a separate collective or a staging copy on the receiver.
 // Callers bracket this with zoo_p2p_barrier (peers' buffers complete before / untouched until after).
 //   accum : fp32 [world*B*bag, D], dup_flag : int32 [world*B*bag] (zero on entry, restored on exit).
+//   bump_step : 1 = hyper[5] (the optimizer step) is incremented on the device before it is used.
 ZOO_API int zoo_embedding_sparse_update_multi(const long long* const* ids_src, int id_stride, int id_col, int B, int bag,
                                               const void* const* dout_src, long long ldg, const void* const* mul_src,
                                               long long ldmul, float grad_scale, long long rows, int world, int rank,
                                               int D, float* w, void* w16, float* m, float* v, int opt, const float* hyper,
-                                              int* rep_of_row, float* accum, int* dup_flag, int* win_list, void* stream) {
+                                              int* rep_of_row, float* accum, int* dup_flag, int* win_list, int bump_step, void* stream) {
   if ((rows + world - 1) / (world > 0 ? world : 1) > INT_MAX) { zoo_set_last_error("embedding_sparse_update_multi: shard too large", __FILE__, __LINE__); return ZOO_ERR_TOO_LARGE; }
   if (!ids_src || !dout_src || !w || !hyper || !rep_of_row || !accum || !dup_flag || D <= 0 || bag < 1 || world < 1 ||
       world > kMaxPeers || rank < 0 || rank >= world) {
@@ -730,7 +733,7 @@ ZOO_API int zoo_embedding_sparse_update_multi(const long long* const* ids_src, i
   en.grad_scale = grad_scale; en.nsrc = world; en.E_local = B * bag;
   SparseState st{w, (__nv_bfloat16*)w16, opt == SOPT_SGD ? nullptr : m, opt == SOPT_ADAM ? v : nullptr};
   cudaStream_t s = (cudaStream_t)stream;
-  return launch_sparse_update(en, E, rows, world, rank, D, rep_of_row, accum, dup_flag, st, opt, hyper, vec, win_list, s);
+  return launch_sparse_update(en, E, rows, world, rank, D, rep_of_row, accum, dup_flag, st, opt, hyper, vec, win_list, s, bump_step != 0);
 }
 
 // Dense gradient: dtable[ids] += dout rows (fp32 atomics); used when the table is trained as a

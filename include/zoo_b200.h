@@ -42,6 +42,9 @@ int zoo_dense_dgrad_bf16_bits(const void* dy, long long lddy, const void* w, lon
                               int bits_wpr, int mask_cols, void* dx, long long lddx, int M, int N, int K, void* stream);
 int zoo_dense_wgrad_bf16(const void* dy, long long lddy, const void* x, long long ldx, float* dw,
                          long long lddw, int M, int N, int K, void* stream);
+/* wgrad + bias gradient in one kernel: db[N] += column sums of dY (an extra 16-column MMA against a tile of ones). */
+int zoo_dense_wgrad_bias_bf16(const void* dy, long long lddy, const void* x, long long ldx, float* dw,
+                              long long lddw, float* db, int M, int N, int K, void* stream);
 int zoo_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* out, void* stream);
 
 /* ---- K2/K4: embedding gather and sparse optimizer (csrc/ops/embedding.cu) --------------------
@@ -80,7 +83,7 @@ int zoo_embedding_sparse_update_w(const long long* ids, int id_stride, int id_co
                                   const void* dout, long long ldg, const void* mul, long long ldmul,
                                   float grad_scale, long long rows, int world, int rank, int D,
                                   float* w, void* w16, float* m, float* v, int opt, const float* hyper,
-                                  int* rep_of_row, float* accum, int* dup_flag, int* win_list, void* stream);
+                                  int* rep_of_row, float* accum, int* dup_flag, int* win_list, int bump_step, void* stream);
 /* Backward of a row-sharded table: ids_src / dout_src / mul_src are HOST arrays of `world` device pointers into the
  * symmetric heap (every rank's ids, gradient-row window, optional multiplier rows); the owner pulls the rows it needs over
  * NVLink.  accum fp32 [world*B*bag, D], dup_flag int32 [world*B*bag], win_list int32 [2*world*B*bag + 4].
@@ -89,7 +92,7 @@ int zoo_embedding_sparse_update_multi(const long long* const* ids_src, int id_st
                                       const void* const* dout_src, long long ldg, const void* const* mul_src,
                                       long long ldmul, float grad_scale, long long rows, int world, int rank,
                                       int D, float* w, void* w16, float* m, float* v, int opt, const float* hyper,
-                                      int* rep_of_row, float* accum, int* dup_flag, int* win_list, void* stream);
+                                      int* rep_of_row, float* accum, int* dup_flag, int* win_list, int bump_step, void* stream);
 int zoo_embedding_dense_grad(const long long* ids, int id_stride, int id_col, int B, int bag,
                              const void* dout, long long ldg, const void* mul, long long ldmul,
                              float grad_scale, long long rows, int D, float* dtable, void* stream);

@@ -129,7 +129,7 @@ def test_sparse_update_multi_source_on_one_gpu(world, with_mul):
         win = torch.full((2 * world * B + 4,), -7, dtype=torch.int32, device="cuda")
         nl.check(lib.zoo_embedding_sparse_update_multi(arr(ids), 2, 1, B, 1, arr(dout), D, arr(mul) if with_mul else None, D, 1.0, rows, world, r, D,
                                                        w.data_ptr(), None, ea.data_ptr(), es.data_ptr(), 1, hyper.data_ptr(), rep.data_ptr(),
-                                                       accum.data_ptr(), dup.data_ptr(), win.data_ptr(), st), "multi")
+                                                       accum.data_ptr(), dup.data_ptr(), win.data_ptr(), 0, st), "multi")
         torch.cuda.synchronize()
         want = ref[r::world]
         torch.testing.assert_close(w[: want.shape[0]], want, atol=2e-3, rtol=2e-3)

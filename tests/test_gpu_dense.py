@@ -78,6 +78,24 @@ def test_dense_wgrad(M, N, K):
     torch.testing.assert_close(dw / scale, ref / scale, atol=2e-2, rtol=2e-2)
 
 
+@pytest.mark.parametrize("M,N,K", [(1000, 128, 256), (65536, 256, 256), (4096, 64, 128), (333, 40, 72), (512, 5, 128), (3000, 300, 264)])
+def test_dense_wgrad_with_bias_grad(M, N, K):
+    from zoo.ops.dense import dense_wgrad
+
+    torch.manual_seed(4)
+    ldn = (N + 7) // 8 * 8
+    dy = torch.zeros(M, ldn, device="cuda", dtype=torch.bfloat16)
+    dy[:, :N] = _bf(torch.randn(M, N, device="cuda"))
+    dy = dy[:, :N]
+    x = _bf(torch.randn(M, K, device="cuda"))
+    dw = torch.ones(N, K, device="cuda")
+    db = torch.full((N,), 2.0, device="cuda")
+    dense_wgrad(dy, x, dw, db)
+    scale = max(1.0, M ** 0.5)
+    torch.testing.assert_close(dw / scale, (dy.float().t() @ x.float() + 1.0) / scale, atol=2e-2, rtol=2e-2)
+    torch.testing.assert_close(db / scale, (dy.float().sum(0) + 2.0) / scale, atol=2e-2, rtol=2e-2)
+
+
 def test_dense_dgrad_partial_mask():
     from zoo.ops.dense import dense_dgrad
 

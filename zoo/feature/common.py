@@ -69,10 +69,11 @@ class Sample:
 class MiniBatch:
     """(inputs, targets) of one step; inputs/targets are tensors or tuples of tensors."""
 
-    __slots__ = ("inputs", "targets", "size")
+    __slots__ = ("inputs", "targets", "size", "_h2d_done")
 
     def __init__(self, inputs, targets, size):
         self.inputs, self.targets, self.size = inputs, targets, size
+        self._h2d_done = None     # CUDA event recorded by the prefetcher once the batch has been copied to the device
 
     def to(self, device, non_blocking=True):
         mv = lambda t: None if t is None else (tuple(x.to(device, non_blocking=non_blocking) for x in t)
@@ -513,6 +514,39 @@ class FeatureSet:
         l = None if self.labels is None else tuple(sel(t) for t in self.labels)
         return MiniBatch(f[0] if self.single_feature else f, None if l is None else (l[0] if self.single_label else l), len(idx))
 
+    def _window(self, lo, n):
+        """Contiguous batch: zero-copy views (of pinned memory for the DRAM tier, so the H2D copy is one async DMA)."""
+        f = tuple(t.narrow(0, lo, n) for t in self.features)
+        l = None if self.labels is None else tuple(t.narrow(0, lo, n) for t in self.labels)
+        return MiniBatch(f[0] if self.single_feature else f, None if l is None else (l[0] if self.single_label else l), n)
+
+    def _gather_pinned(self, idx):
+        """Shuffled batch from host memory: gathered into a small ring of pinned staging buffers so the H2D copy stays
+        asynchronous.  A slot is reused only after the copy that read it has finished (`_h2d_done`, set by the prefetcher)."""
+        ring = self.__dict__.setdefault("_stage_ring", {"slots": [None] * 4, "i": 0})
+        k = ring["i"]
+        ring["i"] = (k + 1) % len(ring["slots"])
+        slot = ring["slots"][k]
+        n = len(idx)
+        tensors = list(self.features) + (list(self.labels) if self.labels is not None else [])
+        if slot is None or slot["n"] < n:
+            slot = ring["slots"][k] = {"n": n, "bufs": [torch.empty((n,) + tuple(t.shape[1:]), dtype=t.dtype).pin_memory() for t in tensors],
+                                       "batch": None}
+        old = slot["batch"]
+        ev = getattr(old, "_h2d_done", None) if old is not None else None
+        if ev is not None:
+            ev.synchronize()
+        outs = []
+        for t, buf in zip(tensors, slot["bufs"]):
+            o = buf.narrow(0, 0, n)
+            torch.index_select(t, 0, idx, out=o)
+            outs.append(o)
+        nf = len(self.features)
+        f, l = tuple(outs[:nf]), (None if self.labels is None else tuple(outs[nf:]))
+        b = MiniBatch(f[0] if self.single_feature else f, None if l is None else (l[0] if self.single_label else l), n)
+        slot["batch"] = b
+        return b
+
     def _slice_offset(self):
         if self.num_slice <= 1:
             return 0, self.size()
@@ -535,15 +569,17 @@ class FeatureSet:
             for _ in range(epochs):
                 lo, hi = self._slice_offset()
                 n = hi - lo
-                if train and self.do_shuffle and not self.sequential_order:
-                    perm = self._rng.permutation(n) + lo
-                else:
-                    perm = np.arange(lo, hi)
-                dev = self.features[0].device
-                perm_t = torch.from_numpy(perm).to(dev)
                 stop = n - (n % batch_size) if drop_last else n
-                for s in range(0, stop, batch_size):
-                    yield self._gather(perm_t[s:s + batch_size])
+                dev = self.features[0].device
+                if not (train and self.do_shuffle and not self.sequential_order):
+                    for s in range(0, stop, batch_size):
+                        yield self._window(lo + s, min(batch_size, n - s))
+                else:
+                    perm_t = torch.from_numpy(self._rng.permutation(n) + lo).to(dev)
+                    host_pinned = dev.type == "cpu" and self.features[0].is_pinned()
+                    for s in range(0, stop, batch_size):
+                        idx = perm_t[s:s + batch_size]
+                        yield self._gather_pinned(idx) if host_pinned else self._gather(idx)
                 if self.num_slice > 1:
                     self.current_slice += 1
             return

@@ -88,11 +88,18 @@ def dense_dgrad(dy16, w16, mask16=None, out=None, mask_cols=0, mask_bits=None):
     return out
 
 
-def dense_wgrad(dy16, x16, dw32):
-    """dw32 += dy16.T @ x16  (fp32 accumulation straight into the gradient arena)."""
+def dense_wgrad(dy16, x16, dw32, db32=None):
+    """dw32 += dy16.T @ x16  (fp32 accumulation straight into the gradient arena); with `db32` also db32 += dy16.sum(0),
+    computed by the same kernel as one extra 16-column MMA against a tile of ones."""
     M, N = dy16.shape
     K = x16.shape[1]
     lib = _nl.cuda_lib()
+    if db32 is not None and dw32.stride(0) % 4 == 0 and dw32.data_ptr() % 16 == 0:
+        _nl.check(lib.zoo_dense_wgrad_bias_bf16(dy16.data_ptr(), dy16.stride(0), x16.data_ptr(), x16.stride(0), dw32.data_ptr(),
+                                                dw32.stride(0), db32.data_ptr(), M, N, K, _nl.stream_ptr()), "zoo_dense_wgrad_bias_bf16")
+        return dw32
+    if db32 is not None:
+        colsum(dy16, db32)
     if dw32.stride(0) % 4 != 0 or dw32.data_ptr() % 16 != 0:
         # the kernel reduces with 16-byte vector atomics: a weight whose row length is not a multiple of 4 floats
         # (e.g. in_features 75) is accumulated in a padded scratch and folded in
@@ -138,12 +145,15 @@ class _FusedDenseFn(torch.autograd.Function):
         ctx.save_for_backward(x16, w16, y if act == "relu" and not skip_relu_bwd else None, weight, bias)
         if emit_bits:
             ctx.mark_non_differentiable(bits)
+            ctx.set_materialize_grads(False)      # no zero tensor for the bits output's "gradient"
             return y, bits
         return y
 
     @staticmethod
     def backward(ctx, dy, *_unused):
         x16, w16, y, weight, bias = ctx.saved_tensors
+        if dy is None:
+            return (None,) * 10
         dy16 = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
         if ctx.act == "relu":
             if not ctx.skip_relu_bwd:  # otherwise the consumer's dgrad epilogue already applied the mask
@@ -163,20 +173,17 @@ class _FusedDenseFn(torch.autograd.Function):
             if dx.dtype != ctx.in_dtype:
                 dx = dx.to(ctx.in_dtype)
         gw = getattr(weight, "_zoo_grad", None)
-        dw_ret = None
+        gb = getattr(bias, "_zoo_grad", None) if bias is not None else None
+        dw_ret, db_ret = None, None
+        if bias is not None and gb is None and ctx.needs_input_grad[2]:
+            gb = db_ret = torch.zeros_like(bias, dtype=torch.float32)
         if gw is not None:
-            dense_wgrad(dy16, x16[:, :K], gw)
+            dense_wgrad(dy16, x16[:, :K], gw, gb)          # bias gradient rides along in the same kernel
         elif ctx.needs_input_grad[1]:
             dw_ret = torch.zeros_like(weight, dtype=torch.float32)
-            dense_wgrad(dy16, x16[:, :K], dw_ret)
-        db_ret = None
-        if bias is not None:
-            gb = getattr(bias, "_zoo_grad", None)
-            if gb is not None:
-                colsum(dy16, gb)
-            elif ctx.needs_input_grad[2]:
-                db_ret = torch.zeros_like(bias, dtype=torch.float32)
-                colsum(dy16, db_ret)
+            dense_wgrad(dy16, x16[:, :K], dw_ret, gb)
+        elif gb is not None:
+            colsum(dy16, gb)
         return dx, dw_ret, db_ret, None, None, None, None, None, None, None
 
 

@@ -27,7 +27,7 @@ INT_MAX = 2**31 - 1
 
 _V, _I, _L, _F = C.c_void_p, C.c_int, C.c_longlong, C.c_float
 _nl.register_cuda_sigs({
-    "zoo_embedding_sparse_update_multi": [_V, _I, _I, _I, _I, _V, _L, _V, _L, _F, _L, _I, _I, _I, _V, _V, _V, _V, _I, _V, _V, _V, _V, _V, _V],
+    "zoo_embedding_sparse_update_multi": [_V, _I, _I, _I, _I, _V, _L, _V, _L, _F, _L, _I, _I, _I, _V, _V, _V, _V, _I, _V, _V, _V, _V, _V, _I, _V],
 })
 
 
@@ -249,7 +249,6 @@ def _sparse_update_sharded(table, ids_buf, ids, col, bag, dout_buf, dout_off, ld
     table._ensure_state()
     B = ids.shape[0]
     table._ensure_scratch(B * bag)
-    _nl.check(lib.zoo_hyper_step(table.hyper.data_ptr(), None, _nl.stream_ptr()), "zoo_hyper_step")
     pa = rt._ptr_array
     ids_p = pa(ids_buf.ptrs)
     dout_p = pa([p + dout_off * 2 for p in dout_buf.ptrs])
@@ -260,7 +259,7 @@ def _sparse_update_sharded(table, ids_buf, ids, col, bag, dout_buf, dout_off, ld
         ids_p, ids.stride(0), col, B, bag, dout_p, ldg, mul_p, D if mul_buf is not None else 0, float(grad_scale),
         table.num_embeddings, table.world, table.rank, D, table.weight.data_ptr(), None, _nl.ptr(table.exp_avg),
         _nl.ptr(table.exp_avg_sq), SPARSE_OPTS[table.optimizer], table.hyper.data_ptr(), table.rep_of_row.data_ptr(),
-        accum.data_ptr(), table.dup_flag.data_ptr(), table.win_list.data_ptr(), _nl.stream_ptr()), "zoo_embedding_sparse_update")
+        accum.data_ptr(), table.dup_flag.data_ptr(), table.win_list.data_ptr(), 1, _nl.stream_ptr()), "zoo_embedding_sparse_update")
 
 
 def _sparse_update(table, ids, col, bag, dout_window, mul, grad_scale):
@@ -268,13 +267,12 @@ def _sparse_update(table, ids, col, bag, dout_window, mul, grad_scale):
     table._ensure_state()
     E = ids.shape[0] * bag
     table._ensure_scratch(E)
-    _nl.check(lib.zoo_hyper_step(table.hyper.data_ptr(), None, _nl.stream_ptr()), "zoo_hyper_step")
     _nl.check(lib.zoo_embedding_sparse_update_w(
         ids.data_ptr(), ids.stride(0), col, ids.shape[0], bag, dout_window.data_ptr(), dout_window.stride(0),
         _nl.ptr(mul), mul.stride(0) if mul is not None else 0, float(grad_scale), table.num_embeddings, table.world,
         table.rank, table.embedding_dim, table.weight.data_ptr(), _nl.ptr(getattr(table, "weight16", None)),
         _nl.ptr(table.exp_avg), _nl.ptr(table.exp_avg_sq), SPARSE_OPTS[table.optimizer], table.hyper.data_ptr(),
-        table.rep_of_row.data_ptr(), table.accum.data_ptr(), table.dup_flag.data_ptr(), table.win_list.data_ptr(),
+        table.rep_of_row.data_ptr(), table.accum.data_ptr(), table.dup_flag.data_ptr(), table.win_list.data_ptr(), 1,
         _nl.stream_ptr()), "zoo_embedding_sparse_update_w")
 
 

@@ -89,6 +89,9 @@ class Prefetcher:
         self.h2d_bytes = _nbytes(b.inputs) + _nbytes(b.targets)
         with torch.cuda.stream(self.stream):
             self._next = MiniBatch(_to_device(b.inputs, self.device), _to_device(b.targets, self.device), b.size)
+            if self.h2d_bytes:
+                b._h2d_done = torch.cuda.Event()      # lets the producer of `b` recycle its pinned staging buffer
+                b._h2d_done.record(self.stream)
 
     def __iter__(self):
         return self
@@ -489,6 +492,9 @@ class TrainingEngine:
                     raise
                 log.warning("training failed with %r; retry %d/%d from %s", e, failures, retry_budget, self.latest_checkpoint())
                 self.load_checkpoint()
+        if self.async_loss and getattr(self, "_final_loss_dev", None) is not None:
+            self.state["Loss"] = float(self._final_loss_dev)
+            self._final_loss_dev = None
         if self.train_summary is not None:
             self.train_summary.writer.flush()
         return self
@@ -538,7 +544,9 @@ class TrainingEngine:
                 if end_trigger(st) and not isinstance(end_trigger, MaxEpoch):
                     break
             if loss_dev is not None:
-                st["Loss"] = float(loss_dev)
+                self._final_loss_dev = loss_dev
+                if not self.async_loss:
+                    st["Loss"] = float(loss_dev)    # (async_loss: read once when fit returns -- no pipeline drain per pass)
             # one pass over the (slice of the) data is done
             if fs.num_of_slice() > 1:
                 st["currentSlice"] = fs.current_slice
