@@ -46,6 +46,7 @@ struct RsArgs {
   const float* hyper[kMaxRanks];     // device hyper-parameter vectors (same values on every rank)
   long long start, end;              // arena range of this launch; (end - start) % (4 * world) == 0
   int world, rank, emulate, opt, zero_grad;
+  int replicated;                    // 1: every rank reduces and updates the WHOLE range locally (no publish stores)
 };
 
 __device__ __forceinline__ float4 ld_f4(const float* p) { return *reinterpret_cast<const float4*>(p); }
@@ -73,11 +74,15 @@ rs_opt_ag_kernel(const RsArgs a) {
 
   // ---- reduce-scatter + optimizer + all-gather on the owned shard --------------------------
   const long long units = (a.end - a.start) >> 2;       // float4 units in the range
-  const long long shard_units = units / W;
-  const long long u0 = (long long)rank * shard_units;    // first unit of my shard
   const OptHyper h = load_hyper(a.hyper[rank], a.opt);
   float* m_loc = a.m[rank];
   float* v_loc = a.v[rank];
+  // Small ranges (the dense part of a recommender is a few hundred KB): the two extra NVLink round trips of the
+  // owner-computes schedule cost more than the math, so every rank reads all `world` gradient copies of the whole
+  // range, sums them in the same order and applies the same update to its own replica -- bitwise identical
+  // parameters everywhere, no publish stores, and phase B only has to say "done reading".
+  const long long shard_units = a.replicated ? units : units / W;
+  const long long u0 = a.replicated ? 0 : (long long)rank * shard_units;    // first unit of my shard
   for (long long u = u0 + b * (long long)kRsThreads + threadIdx.x; u < u0 + shard_units; u += (long long)G * kRsThreads) {
     const long long off = a.start + (u << 2);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -99,11 +104,16 @@ rs_opt_ag_kernel(const RsArgs a) {
     if (v_loc) *reinterpret_cast<float4*>(v_loc + off) = vv;
     uint2 pk;
     pk.x = pack_bf16(pp.x, pp.y); pk.y = pack_bf16(pp.z, pp.w);
+    if (a.replicated) {
+      *reinterpret_cast<float4*>(a.p[rank] + off) = pp;
+      if (a.p16[rank]) *reinterpret_cast<uint2*>(a.p16[rank] + off) = pk;
+    } else {
 #pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r) {
-      if (r < W) {
-        *reinterpret_cast<float4*>(a.p[r] + off) = pp;
-        if (a.p16[r]) *reinterpret_cast<uint2*>(a.p16[r] + off) = pk;
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < W) {
+          *reinterpret_cast<float4*>(a.p[r] + off) = pp;
+          if (a.p16[r]) *reinterpret_cast<uint2*>(a.p16[r] + off) = pk;
+        }
       }
     }
   }
@@ -125,7 +135,7 @@ rs_opt_ag_kernel(const RsArgs a) {
     // unit u of MY gradient arena was read only by CTA (u - shard start) % G ... of its owner; all
     // owners' CTAs with my index have signalled, so zero exactly the units those CTAs read.
     float* gl = a.g[rank];
-    for (int s = 0; s < W; ++s) {
+    for (int s = 0; s < (a.replicated ? 1 : W); ++s) {
       const long long s0 = (long long)s * shard_units;
       for (long long u = s0 + b * (long long)kRsThreads + threadIdx.x; u < s0 + shard_units; u += (long long)G * kRsThreads)
         *reinterpret_cast<float4*>(gl + a.start + (u << 2)) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -216,7 +226,8 @@ ZOO_API int zoo_rs_opt_ag(void* const* g, void* const* p, void* const* p16, void
   }
   if (!opt_needs_m(opt) && opt != OPT_SGD) for (int r = 0; r < world; ++r) a.m[r] = nullptr;
   if (!opt_needs_v(opt)) for (int r = 0; r < world; ++r) a.v[r] = nullptr;
-  a.start = start; a.end = end; a.world = world; a.rank = rank; a.emulate = emulate; a.opt = opt; a.zero_grad = zero_grad;
+  a.start = start; a.end = end; a.world = world; a.rank = rank; a.emulate = emulate; a.opt = opt;
+  a.zero_grad = zero_grad & 1; a.replicated = (zero_grad >> 1) & 1;     // bit 0: zero the gradient range afterwards, bit 1: replicated update
   cudaStream_t s = (cudaStream_t)stream;
   if (emulate) {
     void* args[] = {(void*)&a};
@@ -225,6 +236,42 @@ ZOO_API int zoo_rs_opt_ag(void* const* g, void* const* p, void* const* p16, void
     rs_opt_ag_kernel<<<dim3(grid, 1), kRsThreads, 0, s>>>(a);
     ZOO_CUDA_CHECK(cudaGetLastError());
   }
+  return ZOO_OK;
+}
+
+// One-to-all push over peer memory: dst[p][dst_off ...] = src[0 .. bytes) for every rank p (own slab included).  Used to
+// replicate small per-step metadata (the id matrix of a sharded lookup) so later kernels scan it from local memory.
+struct BcastArgs { unsigned char* dst[kMaxRanks]; const unsigned char* src; long long bytes; int world; };
+__global__ void __launch_bounds__(256) symm_bcast_kernel(const BcastArgs a) {
+  const long long n16 = a.bytes >> 4;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+    const uint4 v = reinterpret_cast<const uint4*>(a.src)[i];
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < a.world) reinterpret_cast<uint4*>(a.dst[p])[i] = v;
+  }
+  for (long long i = (n16 << 4) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.bytes; i += stride)
+    for (int p = 0; p < a.world; ++p) a.dst[p][i] = a.src[i];
+}
+
+ZOO_API int zoo_symm_bcast(void* const* dst, long long dst_off, const void* src, long long bytes, int world, void* stream) {
+  if (!dst || !src || bytes < 0 || world < 1 || world > kMaxRanks || (dst_off & 15) || ((uintptr_t)src & 15)) {
+    zoo_set_last_error("symm_bcast: bad arguments (offset and source must be 16-byte aligned)", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  if (bytes == 0) return ZOO_OK;
+  BcastArgs a{};
+  for (int p = 0; p < world; ++p) {
+    if (!dst[p] || ((uintptr_t)dst[p] & 15)) { zoo_set_last_error("symm_bcast: null or unaligned destination", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+    a.dst[p] = (unsigned char*)dst[p] + dst_off;
+  }
+  a.src = (const unsigned char*)src; a.bytes = bytes; a.world = world;
+  long long blocks = ((bytes >> 4) + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > 296) blocks = 296;
+  symm_bcast_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;
 }
 

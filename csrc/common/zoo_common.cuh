@@ -97,6 +97,14 @@ __device__ __forceinline__ void fence_sys() {
   asm volatile("fence.acq_rel.sys;" ::: "memory");
 }
 
+// ------------------------------------------- programmatic dependent launch --
+// Kernels of one step run back to back on one stream.  Launched through zoo_launch_pdl they may be scheduled while
+// their predecessor drains, so their launch latency and prologue (barrier init, TMEM allocation, descriptor prefetch)
+// overlap its tail; pdl_wait() then blocks until the predecessor has completed and its writes are visible, and MUST
+// precede the kernel's first global-memory access.  Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // -------------------------------------------------------------- mbarrier --
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
@@ -246,3 +254,22 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t m, uint32_t n, u
 }
 
 }  // namespace zoo
+
+// ---------------------------------------------------------------- host: PDL launch --
+#include <stdlib.h>
+#include <utility>
+inline bool zoo_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("ZOO_PDL"); v = e ? atoi(e) : 0; }   // measured: no gain inside CUDA graphs (launches are pre-staged), so off by default
+  return v != 0;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t zoo_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = zoo_pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}

@@ -177,11 +177,13 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     for (int i = lane; i < 512; i += 32) ones[i] = 0x3F803F80u;
     fence_proxy_async_smem();
   }
+  pdl_wait();        // everything above overlapped the previous kernel's tail; global memory is touched from here on
   if (EPI == EPI_BIAS_ACT && g.n_blocks == 1 && threadIdx.x < kMaxN)   // bias of the only N block, once
     s_bias[threadIdx.x] = (g.bias && (int)threadIdx.x < g.No) ? g.bias[threadIdx.x] : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_launch_dependents();
   const uint32_t tmem_base = tmem_base_slot;
 
   const int total_work = g.m_blocks * g.n_blocks * g.k_splits;
@@ -616,7 +618,7 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));          \
       attr_set = true;                                                                                         \
     }                                                                                                          \
-    dense_tcgen05_kernel<EPI, ACT><<<grid, kThreads, kSmemBytes, stream>>>(ta, tb, to, g);                        \
+    ZOO_CUDA_CHECK(zoo_launch_pdl(dense_tcgen05_kernel<EPI, ACT>, dim3(grid), dim3(kThreads), kSmemBytes, stream, ta, tb, to, g));                        \
   } while (0)
   if (g.epilogue == EPI_RED_F32) ZOO_LAUNCH(EPI_RED_F32, ACT_NONE);
   else if (g.epilogue == EPI_MASK) ZOO_LAUNCH(EPI_MASK, ACT_NONE);

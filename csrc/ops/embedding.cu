@@ -81,6 +81,8 @@ embedding_gather_kernel(const long long* __restrict__ ids, int id_stride, int id
                         int B, int bag, int mean, ShardPtrs ta, long long rows_a, ShardPtrs tb,
                         long long rows_b, int world, int D, __nv_bfloat16* __restrict__ out,
                         long long ldo, __nv_bfloat16* __restrict__ save_a, __nv_bfloat16* __restrict__ save_b, int G) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int gl = threadIdx.x & 31;
   const int warp = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / G) + gl / G;   // = sample index
   const int lane = gl - (gl / G) * G;
@@ -211,6 +213,8 @@ __device__ __forceinline__ long long entry_row(const BwdEntries& en, int e) {
 __global__ void __launch_bounds__(256)
 emb_mark_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* __restrict__ rep_of_row,
                 int* __restrict__ win_count, float* __restrict__ step_slot) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e == 0 && win_count) *win_count = 0;     // the winner list is rebuilt by pass 2
   if (e == 0 && step_slot) *step_slot += 1.f;  // optimizer step counter (bias correction) kept on the device
@@ -256,6 +260,8 @@ __global__ void __launch_bounds__(256)
 emb_accum_kernel(BwdEntries en, int E, long long rows, int world, int rank, const int* __restrict__ rep_of_row,
                  int D, float* __restrict__ accum, int* __restrict__ dup_flag, int2* __restrict__ win_list,
                  int* __restrict__ win_count) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   const int e_mine = warp_global * 32 + lane;
@@ -273,15 +279,22 @@ emb_accum_kernel(BwdEntries en, int E, long long rows, int world, int rank, cons
   }
   if (win_list) {
     // Representatives are appended to a compact (entry, local row) list so that pass 3 launches work only for
-    // them and never re-reads ids (which may sit on a peer) or the row map.
+    // them and never re-reads ids (which may sit on a peer) or the row map.  One atomic per CTA on the list counter:
+    // thousands of warps hitting a single address serialise in L2 and used to dominate this kernel.
+    __shared__ int s_wcount[8];
+    __shared__ int s_base;
     const unsigned wmask = __ballot_sync(0xffffffffu, win);
-    if (wmask) {
-      const int leader = __ffs(wmask) - 1;
-      int base = 0;
-      if (lane == leader) base = atomicAdd(win_count, __popc(wmask));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (win) win_list[base + __popc(wmask & ((1u << lane) - 1u))] = make_int2(e_mine, local_mine);
+    const int wib = threadIdx.x >> 5;
+    if (lane == 0) s_wcount[wib] = __popc(wmask);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int tot = 0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { const int c = s_wcount[i]; s_wcount[i] = tot; tot += c; }
+      s_base = tot ? atomicAdd(win_count, tot) : 0;
     }
+    __syncthreads();
+    if (win) win_list[s_base + s_wcount[wib] + __popc(wmask & ((1u << lane) - 1u))] = make_int2(e_mine, local_mine);
   }
   unsigned losers = __ballot_sync(0xffffffffu, rep_mine >= 0);
   while (losers) {
@@ -323,6 +336,8 @@ __global__ void __launch_bounds__(256)
 emb_apply_kernel(BwdEntries en, int E, long long rows, int world, int rank, int* __restrict__ rep_of_row,
                  int D, float* __restrict__ accum, int* __restrict__ dup_flag, SparseState st, int opt,
                  const float* __restrict__ hyper, const int2* __restrict__ win_list, const int* __restrict__ win_count) {
+  pdl_wait();
+  pdl_launch_dependents();
   int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (e >= E) return;
@@ -411,21 +426,25 @@ emb_apply_kernel(BwdEntries en, int E, long long rows, int world, int rank, int*
 // (G = 8 / 16 / 32), a warp therefore covers 32/G rows per pass, and every warp issues the loads of R passes before it
 // computes anything.
 template <int R>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, R == 1 ? 5 : 1)
 emb_apply_fast_kernel(BwdEntries en, int D, int G, float* __restrict__ accum, int* __restrict__ dup_flag, int* __restrict__ rep_of_row,
                       SparseState st, int opt, const float* __restrict__ hyper, const int2* __restrict__ win_list,
                       const int* __restrict__ win_count) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int count = *win_count;
   const int lane = threadIdx.x & 31;
   const int P = 32 / G;                                   // rows per warp pass
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int base = warp * P * R;
-  if (base >= count) return;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
   const int slot = lane / G, c = (lane - slot * G) * 4;
   const bool col_ok = c < D;
   const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], step = hyper[5];
   float bc1 = 1.f, bc2 = 1.f;
   if (opt == SOPT_ADAM) { bc1 = 1.f - powf(b1, step); bc2 = 1.f - powf(b2, step); }
+  // The grid is sized for full occupancy, not for the entry count: the winner count is only known on the device, and a grid
+  // of one warp per POSSIBLE entry (world x batch of them for a sharded table) spent most of its time launching empty CTAs.
+  for (int base = warp * P * R; base < count; base += nwarps * P * R) {
   int e[R]; long long local[R]; bool ok[R], dup[R];
   float g[R][4]; float4 w4[R], m4[R], v4[R], a4[R];
 #pragma unroll
@@ -481,6 +500,7 @@ emb_apply_fast_kernel(BwdEntries en, int D, int G, float* __restrict__ accum, in
       rep_of_row[local[r]] = INT_MAX;
       if (dup[r]) dup_flag[e[r]] = 0;
     }
+  }
   }
 }
 
@@ -538,19 +558,23 @@ static int launch_sparse_update(const BwdEntries& en, int E, long long rows, int
   const int threads = 256;
   int2* wl = reinterpret_cast<int2*>(win_list);
   int* wc = win_list ? win_list + 2 * (size_t)E : nullptr;
-  emb_mark_kernel<<<(E + threads - 1) / threads, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, wc,
-                                                                  bump_step ? const_cast<float*>(hyper) + 5 : nullptr);
+  ZOO_CUDA_CHECK(zoo_launch_pdl(emb_mark_kernel, dim3((E + threads - 1) / threads), dim3(threads), 0, s, en, E, rows, world, rank, rep_of_row, wc,
+                                bump_step ? const_cast<float*>(hyper) + 5 : (float*)nullptr));
   const unsigned wb = (unsigned)(((long long)E * 32 + threads - 1) / threads);
   const unsigned ab = (unsigned)((E + threads - 1) / threads);  // accum: one lane per entry
   if (vec && win_list && D <= 128) {
-    emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, wl, wc);
+    ZOO_CUDA_CHECK(zoo_launch_pdl(emb_accum_kernel<true>, dim3(ab), dim3(threads), 0, s, en, E, rows, world, rank, (const int*)rep_of_row, D, accum, dup_flag, wl, wc));
     const int G = D <= 32 ? 8 : (D <= 64 ? 16 : 32);
     static int R = -1;
     if (R < 0) { const char* ev = getenv("ZOO_APPLY_R"); R = ev ? atoi(ev) : 1; if (R != 1 && R != 2 && R != 4) R = 1; }
     const int rows_per_warp = (32 / G) * R;
     const long long warps = ((long long)E + rows_per_warp - 1) / rows_per_warp;
-    const unsigned grid = (unsigned)((warps * 32 + threads - 1) / threads);
-    if (R == 1) emb_apply_fast_kernel<1><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
+    long long grid_ll = (warps * 32 + threads - 1) / threads;
+    static int sm_count = 0;
+    if (!sm_count) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev); if (sm_count <= 0) sm_count = 148; }
+    if (grid_ll > (long long)sm_count * 16) grid_ll = (long long)sm_count * 16;     // a few waves; the kernel strides over the winner list
+    const unsigned grid = (unsigned)grid_ll;
+    if (R == 1) ZOO_CUDA_CHECK(zoo_launch_pdl(emb_apply_fast_kernel<1>, dim3(grid), dim3(threads), 0, s, en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, (const int2*)wl, (const int*)wc));
     else if (R == 2) emb_apply_fast_kernel<2><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
     else emb_apply_fast_kernel<4><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
   } else if (vec) {
@@ -605,8 +629,8 @@ ZOO_API int zoo_embedding_gather(const long long* ids, int id_stride, int id_col
   __nv_bfloat16* sa = (__nv_bfloat16*)save_a;
   __nv_bfloat16* sb = (__nv_bfloat16*)save_b;
 #define ZOO_GATHER(T, MUL, VEC)                                                                     \
-  embedding_gather_kernel<T, MUL, VEC><<<(unsigned)blocks, threads, 0, s>>>(                        \
-      ids, id_stride, id_col, id_col2, B, bag, mean, ta, rows_a, tb, rows_b, world, D, o, ldo, sa, sb, G)
+  ZOO_CUDA_CHECK(zoo_launch_pdl(embedding_gather_kernel<T, MUL, VEC>, dim3((unsigned)blocks), dim3(threads), 0, s, \
+      ids, id_stride, id_col, id_col2, B, bag, mean, ta, rows_a, tb, rows_b, world, D, o, ldo, sa, sb, G))
   if (table_dtype == 0) {
     if (mul) { if (vec) ZOO_GATHER(float, true, true); else ZOO_GATHER(float, true, false); }
     else     { if (vec) ZOO_GATHER(float, false, true); else ZOO_GATHER(float, false, false); }
@@ -734,6 +758,140 @@ ZOO_API int zoo_embedding_sparse_update_multi(const long long* const* ids_src, i
   SparseState st{w, (__nv_bfloat16*)w16, opt == SOPT_SGD ? nullptr : m, opt == SOPT_ADAM ? v : nullptr};
   cudaStream_t s = (cudaStream_t)stream;
   return launch_sparse_update(en, E, rows, world, rank, D, rep_of_row, accum, dup_flag, st, opt, hyper, vec, win_list, s, bump_step != 0);
+}
+
+// K4b: backward DISPATCH of a row-sharded table.  Every source GPU pushes the gradient row of each of its entries into the
+// receive buffer of the GPU that owns the row (row r lives on rank r % world): posted NVLink writes of whole 16-byte
+// vectors, issued by the side that already has the data, instead of latency-bound remote reads by the owner.  Slot
+// `rank * cap + pos` of the owner's buffers receives (local row index, gradient row); `pos` comes from a per-destination
+// counter on the source (one global atomic per destination per CTA).  After a barrier the owner runs the ordinary
+// single-GPU sparse update over its receive buffer, whose unused slots hold the id -1.
+//   recv_ids  : HOST array of `world` device pointers, int64 [world * cap]  (peer memory, pre-filled with -1)
+//   recv_grad : HOST array of `world` device pointers, bf16  [world * cap, D]
+//   counters  : int32 [world] on this GPU (zeroed here)
+// The multiplier rows (GMF factor) and grad_scale are applied at the source, so only the final gradient row travels.
+namespace zoo {
+struct DispatchArgs {
+  long long* recv_ids[kMaxPeers];
+  __nv_bfloat16* recv_grad[kMaxPeers];
+};
+
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+emb_dispatch_kernel(const long long* __restrict__ ids, int id_stride, int id_col, int E, int bag,
+                    const __nv_bfloat16* __restrict__ dout, long long ldg, const __nv_bfloat16* __restrict__ mul, long long ldmul,
+                    float grad_scale, long long rows, int world, int rank, int D, int G, DispatchArgs a,
+                    int* __restrict__ counters, int cap) {
+  __shared__ int s_cnt[kMaxPeers];     // entries of this CTA per destination, then the CTA's base position there
+  __shared__ int s_dest[256];          // destination rank of entry t of this CTA (-1: skipped)
+  __shared__ int s_slot[256];          // slot in the destination's receive buffers
+  const int t = threadIdx.x;
+  if (t < kMaxPeers) s_cnt[t] = 0;
+  __syncthreads();
+  // ---- phase 1: one thread per entry picks destination and position
+  const int e = blockIdx.x * 256 + t;
+  int o = -1, mypos = 0;
+  long long local = 0;
+  if (e < E) {
+    const int b = e / bag, j = e - b * bag;
+    const long long id = ids[(long long)b * id_stride + id_col + j];
+    if (id >= 0 && id < rows) {
+      o = (int)(id % world);
+      local = id / world;
+      mypos = atomicAdd(&s_cnt[o], 1);
+    }
+  }
+  __syncthreads();
+  if (t < world) {
+    const int c = s_cnt[t];
+    s_cnt[t] = c ? atomicAdd(counters + t, c) : 0;
+  }
+  __syncthreads();
+  int slot = 0;
+  if (o >= 0) {
+    const int pos = s_cnt[o] + mypos;
+    if (pos >= cap) { printf("zoo emb_dispatch: receive buffer overflow (rank %d -> %d)\n", rank, o); __trap(); }
+    slot = rank * cap + pos;
+    pick8(a.recv_ids, o)[slot] = local;
+  }
+  s_dest[t] = o;
+  s_slot[t] = slot;
+  __syncthreads();
+  // ---- phase 2: G lanes move one gradient row (16-byte vectors), 32 / G rows per warp pass
+  const int lane = t & 31, warp = t >> 5, P = 32 / G, sub = lane / G, l = lane - sub * G;
+  for (int base = warp * P; base < 256; base += 8 * P) {
+    const int k = base + sub;
+    const int dst = s_dest[k];
+    if (dst < 0) continue;
+    const int ek = blockIdx.x * 256 + k;
+    const int b = ek / bag;
+    const __nv_bfloat16* src = dout + (long long)b * ldg;
+    const __nv_bfloat16* mrow = mul ? mul + (long long)b * ldmul : nullptr;
+    __nv_bfloat16* out = pick8(a.recv_grad, dst) + (long long)s_slot[k] * D;
+    if (VEC) {
+      for (int c = l * 8; c < D; c += G * 8) {
+        uint4 v = *reinterpret_cast<const uint4*>(src + c);
+        if (mrow || grad_scale != 1.f) {
+          uint32_t w[4] = {v.x, v.y, v.z, v.w};
+          uint4 m4 = make_uint4(0, 0, 0, 0);
+          if (mrow) m4 = *reinterpret_cast<const uint4*>(mrow + c);
+          const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float2 f = unpack_bf16(w[q]);
+            if (mrow) { const float2 g = unpack_bf16(mw[q]); f.x *= g.x; f.y *= g.y; }
+            w[q] = pack_bf16(f.x * grad_scale, f.y * grad_scale);
+          }
+          v = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        *reinterpret_cast<uint4*>(out + c) = v;
+      }
+    } else {
+      for (int c = l; c < D; c += G) {
+        float f = __bfloat162float(src[c]);
+        if (mrow) f *= __bfloat162float(mrow[c]);
+        out[c] = __float2bfloat16(f * grad_scale);
+      }
+    }
+  }
+  __threadfence_system();     // pushed rows are ordered before the flag stores of the barrier kernel that follows
+}
+
+}  // namespace zoo
+using namespace zoo;
+
+ZOO_API int zoo_embedding_dispatch(const long long* ids, int id_stride, int id_col, int B, int bag, const void* dout, long long ldg,
+                                   const void* mul, long long ldmul, float grad_scale, long long rows, int world, int rank, int D,
+                                   void* const* recv_ids, void* const* recv_grad, int* counters, int cap, void* stream) {
+  if (!ids || !dout || !recv_ids || !recv_grad || !counters || B < 0 || bag < 1 || D <= 0 || world < 1 || world > kMaxPeers ||
+      rank < 0 || rank >= world || cap < 1) {
+    zoo_set_last_error("embedding_dispatch: bad arguments", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  const long long E64 = (long long)B * bag;
+  if (E64 > INT_MAX) { zoo_set_last_error("embedding_dispatch: too many entries", __FILE__, __LINE__); return ZOO_ERR_TOO_LARGE; }
+  const int E = (int)E64;
+  cudaStream_t s = (cudaStream_t)stream;
+  ZOO_CUDA_CHECK(cudaMemsetAsync(counters, 0, sizeof(int) * world, s));
+  if (E == 0) return ZOO_OK;
+  DispatchArgs a{};
+  bool vec = (D % 8 == 0) && (ldg % 8 == 0) && (((uintptr_t)dout & 15) == 0) && (!mul || ((ldmul % 8 == 0) && ((uintptr_t)mul & 15) == 0));
+  for (int p = 0; p < world; ++p) {
+    if (!recv_ids[p] || !recv_grad[p]) { zoo_set_last_error("embedding_dispatch: null receive buffer", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+    a.recv_ids[p] = (long long*)recv_ids[p];
+    a.recv_grad[p] = (__nv_bfloat16*)recv_grad[p];
+    vec = vec && (((uintptr_t)recv_grad[p] & 15) == 0);
+  }
+  const int units = vec ? (D + 7) / 8 : D;
+  int G = 32;
+  while (G > 1 && G / 2 >= units) G /= 2;
+  const unsigned blocks = (unsigned)((E + 255) / 256);
+  if (vec) emb_dispatch_kernel<true><<<blocks, 256, 0, s>>>(ids, id_stride, id_col, E, bag, (const __nv_bfloat16*)dout, ldg, (const __nv_bfloat16*)mul,
+                                                           ldmul, grad_scale, rows, world, rank, D, G, a, counters, cap);
+  else     emb_dispatch_kernel<false><<<blocks, 256, 0, s>>>(ids, id_stride, id_col, E, bag, (const __nv_bfloat16*)dout, ldg, (const __nv_bfloat16*)mul,
+                                                            ldmul, grad_scale, rows, world, rank, D, G, a, counters, cap);
+  ZOO_CUDA_CHECK(cudaGetLastError());
+  return ZOO_OK;
 }
 
 // Dense gradient: dtable[ids] += dout rows (fp32 atomics); used when the table is trained as a

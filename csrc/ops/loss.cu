@@ -87,6 +87,8 @@ softmax_nll_small_kernel(const T* __restrict__ logits, long long ldl, const long
                          float eps, float loss_scale, float grad_scale, float* __restrict__ loss_out,
                          float* __restrict__ row_loss, T* __restrict__ dlogits, long long ldd, float* __restrict__ probs,
                          long long ldp) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   __shared__ float blk_loss[8];
   __shared__ float blk_cnt[8];

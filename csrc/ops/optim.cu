@@ -18,6 +18,8 @@ __global__ void __launch_bounds__(256)
 dense_opt_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                  __nv_bfloat16* __restrict__ p16, long long n, int opt, const float* __restrict__ hyper,
                  int zero_grad, float* __restrict__ gmut) {
+  pdl_wait();
+  pdl_launch_dependents();
   const OptHyper h = load_hyper(hyper, opt);
   const long long stride = (long long)gridDim.x * blockDim.x;
   if (VEC) {
@@ -197,7 +199,7 @@ ZOO_API int zoo_dense_opt_step(float* p, float* g, float* m, float* v, void* p16
   if (!opt_needs_v(opt)) v = nullptr;
   const bool vec = !(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) && !((uintptr_t)p16 & 7);
   cudaStream_t s = (cudaStream_t)stream;
-  if (vec) dense_opt_kernel<true><<<grid_for(n, 4), 256, 0, s>>>(p, g, m, v, (__nv_bfloat16*)p16, n, opt, hyper, zero_grad, g);
+  if (vec) ZOO_CUDA_CHECK(zoo_launch_pdl(dense_opt_kernel<true>, dim3(grid_for(n, 4)), dim3(256), 0, s, p, g, m, v, (__nv_bfloat16*)p16, n, opt, hyper, zero_grad, g));
   else     dense_opt_kernel<false><<<grid_for(n, 1), 256, 0, s>>>(p, g, m, v, (__nv_bfloat16*)p16, n, opt, hyper, zero_grad, g);
   ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;

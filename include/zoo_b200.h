@@ -93,6 +93,13 @@ int zoo_embedding_sparse_update_multi(const long long* const* ids_src, int id_st
                                       long long ldmul, float grad_scale, long long rows, int world, int rank,
                                       int D, float* w, void* w16, float* m, float* v, int opt, const float* hyper,
                                       int* rep_of_row, float* accum, int* dup_flag, int* win_list, int bump_step, void* stream);
+/* Backward dispatch of a row-sharded table: every source GPU pushes (local row index, final gradient row) of each entry
+ * into the owner's receive buffers (recv_ids: int64 [world*cap], -1 = empty; recv_grad: bf16 [world*cap, D]; both HOST
+ * arrays of `world` device pointers into the symmetric heap).  counters: int32 [world] on this GPU.  After a barrier the
+ * owner runs zoo_embedding_sparse_update_w over its receive buffer with world = 1. */
+int zoo_embedding_dispatch(const long long* ids, int id_stride, int id_col, int B, int bag, const void* dout, long long ldg,
+                           const void* mul, long long ldmul, float grad_scale, long long rows, int world, int rank, int D,
+                           void* const* recv_ids, void* const* recv_grad, int* counters, int cap, void* stream);
 int zoo_embedding_dense_grad(const long long* ids, int id_stride, int id_col, int B, int bag,
                              const void* dout, long long ldg, const void* mul, long long ldmul,
                              float grad_scale, long long rows, int D, float* dtable, void* stream);
@@ -131,9 +138,14 @@ int zoo_vmm_alloc(long long bytes, void** ptr, int* fd, long long* mapped_bytes)
 int zoo_vmm_import(int fd, long long mapped_bytes, void** ptr);
 int zoo_vmm_free(void* ptr, long long mapped_bytes);
 int zoo_close_fd(int fd);
+/* zero_grad: bit 0 = zero the gradient range afterwards; bit 1 = replicated update (every rank reduces and updates the
+ * whole range on its own replica: one NVLink round trip less, for ranges of a few MB). */
 int zoo_rs_opt_ag(void* const* g, void* const* p, void* const* p16, void* const* m, void* const* v,
                   void* const* flags, void* const* epoch, void* const* hyper, long long start, long long end,
                   int world, int rank, int device_slot, int opt, int zero_grad, int grid, void* stream);
+/* One-to-all push over peer memory: dst[p] + dst_off <- src[0..bytes) for every rank p (dst: HOST array of `world` device
+ * pointers into the symmetric heap).  Offsets and source must be 16-byte aligned. */
+int zoo_symm_bcast(void* const* dst, long long dst_off, const void* src, long long bytes, int world, void* stream);
 int zoo_p2p_barrier(void* const* flags, void* const* epoch, int world, int rank, int slot, void* stream);
 
 /* ---- K6: persistent LSTM / GRU, forward and backward-through-time (csrc/ops/rnn.cu) -----------

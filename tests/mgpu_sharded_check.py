@@ -70,15 +70,18 @@ if r == 0:
     torch.cuda.synchronize()
     rl = torch.stack(rl)
     dl = (rl - lt).abs().max().item()
-    worst = 0.0
+    worst, mean = 0.0, 0.0
     for n, t in sh.named_modules():
         if hasattr(t, "rows_local"):
             want = dict(ref.named_modules())[n].weight.detach()[r::W]
             got = t.weight.detach()[: want.shape[0]]
             worst = max(worst, (want - got).abs().max().item())
+            mean = max(mean, (want - got).abs().mean().item())
     dw = max((p.detach() - dict(ref.named_parameters())[n].detach()).abs().max().item() for n, p in sh.named_parameters() if n in dense0)
-    print(f"loss diff {dl:.2e}, table diff {worst:.2e}, dense diff {dw:.2e}")
-    ok = dl < 5e-3 and worst < 2e-2 and dw < 2e-2
+    print(f"loss diff {dl:.2e}, table diff max {worst:.2e} mean {mean:.2e}, dense diff {dw:.2e}")
+    # Adam at lr 1e-2 turns rounding noise on near-zero gradients into +-lr steps: single elements may drift by a few lr,
+    # a missed or doubled update would show in the loss and in the mean
+    ok = dl < 1e-3 and worst < 4e-2 and mean < 1e-3 and dw < 3e-2
 flag = torch.tensor([1 if ok else 0], device=ctx.device)
 dist.broadcast(flag, src=0)
 dist.barrier()

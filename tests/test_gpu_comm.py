@@ -21,7 +21,8 @@ def _arr(ts):
 
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("opt", ["adam", "sgd"])
-def test_rs_opt_ag_emulated_matches_torch(world, opt):
+@pytest.mark.parametrize("replicated", [0, 1])
+def test_rs_opt_ag_emulated_matches_torch(world, opt, replicated):
     import zoo.parallel.symm  # registers signatures
     from zoo.native import lib as nl
     from zoo.parallel.flat import OPT_IDS, OptConfig
@@ -46,7 +47,7 @@ def test_rs_opt_ag_emulated_matches_torch(world, opt):
         hy = [hv] * world
         gsum = sum(gs) / world
         nl.check(lib.zoo_rs_opt_ag(_arr(gs), _arr(ps), _arr(p16), _arr(ms), _arr(vs), _arr(flags), _arr(epochs), _arr(hy),
-                                   0, n, world, 0, 1, OPT_IDS[cfg.name], 1, 8, st), "zoo_rs_opt_ag")
+                                   0, n, world, 0, 1, OPT_IDS[cfg.name], 1 | (2 * replicated), 8, st), "zoo_rs_opt_ag")
         ref_p.grad = gsum.clone()
         ref_opt.step()
         torch.cuda.synchronize()
@@ -134,3 +135,61 @@ def test_sparse_update_multi_source_on_one_gpu(world, with_mul):
         want = ref[r::world]
         torch.testing.assert_close(w[: want.shape[0]], want, atol=2e-3, rtol=2e-3)
         assert int(rep.min()) == 2**31 - 1 and float(accum.abs().sum()) == 0 and int(dup.sum()) == 0     # scratch restored
+
+
+@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("with_mul", [False, True])
+def test_dispatch_then_owner_update_on_one_gpu(world, with_mul):
+    """Push-based backward of a sharded table, all ranks emulated on one GPU: every source dispatches its gradient rows
+    into the owners' receive buffers, then each owner runs the single-GPU sparse update over what it received."""
+    import ctypes as C
+
+    import zoo.ops.embedding  # registers signatures
+    from zoo.native import lib as nl
+
+    lib = nl.cuda_lib()
+    torch.manual_seed(5)
+    rows, D, B = 1003, 64, 700
+    arr = lambda ts: (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+    w_full = torch.randn(rows, D, device="cuda")
+    ids = [torch.stack([torch.zeros(B, dtype=torch.int64), torch.randint(0, rows, (B,))], 1).cuda() for _ in range(world)]
+    dout = [torch.randn(B, D, device="cuda").to(torch.bfloat16) for _ in range(world)]
+    mul = [torch.randn(B, D, device="cuda").to(torch.bfloat16) for _ in range(world)]
+    # reference: dense gradient (bf16-rounded rows like the transfer), one Adam step on touched rows
+    g = torch.zeros(rows, D, device="cuda")
+    for s in range(world):
+        row = dout[s].float() * (mul[s].float() if with_mul else 1.0) * 0.5
+        g.index_add_(0, ids[s][:, 1], row.to(torch.bfloat16).float())
+    touched = torch.zeros(rows, dtype=torch.bool, device="cuda")
+    for s in range(world):
+        touched[ids[s][:, 1]] = True
+    m = 0.1 * g
+    v = 0.001 * g * g
+    ref = w_full - 1e-2 * (m / 0.1) / ((v / 0.001).sqrt() + 1e-8) * touched.unsqueeze(1)
+    cap = B
+    recv_ids = [torch.full((world * cap,), -1, dtype=torch.int64, device="cuda") for _ in range(world)]
+    recv_grad = [torch.zeros(world * cap, D, dtype=torch.bfloat16, device="cuda") for _ in range(world)]
+    st = torch.cuda.current_stream().cuda_stream
+    for s in range(world):          # every source pushes
+        counters = torch.zeros(8, dtype=torch.int32, device="cuda")
+        nl.check(lib.zoo_embedding_dispatch(ids[s].data_ptr(), 2, 1, B, 1, dout[s].data_ptr(), D, mul[s].data_ptr() if with_mul else None, D, 0.5,
+                                            rows, world, s, D, arr(recv_ids), arr(recv_grad), counters.data_ptr(), cap, st), "dispatch")
+        torch.cuda.synchronize()
+        assert int(counters[:world].sum()) == B
+    for r in range(world):          # every owner updates its shard from what it received
+        hyper = torch.tensor([1e-2, 0.9, 0.999, 1e-8, 0.0, 0.0, 1.0] + [0.0] * 9, device="cuda")   # step 0 -> bumped to 1
+        rl = (rows + world - 1) // world
+        w = torch.zeros(rl, D, device="cuda")
+        w[: w_full[r::world].shape[0]] = w_full[r::world]
+        ea, es = torch.zeros_like(w), torch.zeros_like(w)
+        rep = torch.full((rl,), 2**31 - 1, dtype=torch.int32, device="cuda")
+        n = world * cap
+        accum = torch.zeros(n, D, device="cuda"); dup = torch.zeros(n, dtype=torch.int32, device="cuda")
+        win = torch.zeros(2 * n + 4, dtype=torch.int32, device="cuda")
+        nl.check(lib.zoo_embedding_sparse_update_w(recv_ids[r].data_ptr(), 1, 0, n, 1, recv_grad[r].data_ptr(), D, None, 0, 1.0, rl, 1, 0, D,
+                                                   w.data_ptr(), None, ea.data_ptr(), es.data_ptr(), 1, hyper.data_ptr(), rep.data_ptr(),
+                                                   accum.data_ptr(), dup.data_ptr(), win.data_ptr(), 1, st), "update")
+        torch.cuda.synchronize()
+        want = ref[r::world]
+        torch.testing.assert_close(w[: want.shape[0]], want, atol=2e-3, rtol=2e-3)
+        assert int(rep.min()) == 2**31 - 1 and float(accum.abs().sum()) == 0 and int(dup.sum()) == 0

@@ -24,7 +24,7 @@ from .recommender import Recommender
 
 class NeuralCF(Recommender):
     def __init__(self, user_count, item_count, class_num, user_embed=20, item_embed=20, hidden_layers=(40, 20, 10),
-                 include_mf=True, mf_embed=20, bigdl_type="float", sparse=True, world=1, rank=0, shadow_bf16=False,
+                 include_mf=True, mf_embed=20, bigdl_type="float", sparse=True, world=1, rank=0, shadow_bf16=None,
                  device=None):
         super().__init__()
         self.user_count, self.item_count, self.class_num = int(user_count), int(item_count), int(class_num)

@@ -128,7 +128,7 @@ class _FusedDenseFn(torch.autograd.Function):
     when the parameters carry ``_zoo_grad`` views (set by the flat-parameter arena)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False, relu_input_cols=0, x_bits=None, emit_bits=False):
+    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False, relu_input_cols=0, x_bits=None, emit_bits=False, dx_out=None):
         x16 = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
         if not _aligned(x16):
             x16 = _pad_cols(x16)
@@ -137,6 +137,7 @@ class _FusedDenseFn(torch.autograd.Function):
             bits = torch.empty((x16.shape[0], (w16.shape[0] + 31) // 32), dtype=torch.int32, device=x16.device)
         y = dense_forward(x16, w16, bias, act, relu_bits=bits)
         ctx.x_bits = x_bits
+        ctx.dx_out = dx_out
         ctx.act = act
         ctx.relu_input = relu_input
         ctx.skip_relu_bwd = skip_relu_bwd
@@ -153,7 +154,7 @@ class _FusedDenseFn(torch.autograd.Function):
     def backward(ctx, dy, *_unused):
         x16, w16, y, weight, bias = ctx.saved_tensors
         if dy is None:
-            return (None,) * 10
+            return (None,) * 11
         dy16 = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
         if ctx.act == "relu":
             if not ctx.skip_relu_bwd:  # otherwise the consumer's dgrad epilogue already applied the mask
@@ -166,10 +167,13 @@ class _FusedDenseFn(torch.autograd.Function):
         dx = None
         if ctx.needs_input_grad[0]:
             wk = w16[:, :K] if w16.shape[1] != K else w16
+            dxo = ctx.dx_out       # a buffer the producer of x wants its gradient in (e.g. peer-readable staging memory)
+            if dxo is not None and (tuple(dxo.shape) != (dy16.shape[0], K) or dxo.dtype != torch.bfloat16 or ctx.in_dtype != torch.bfloat16):
+                dxo = None
             if ctx.relu_input and ctx.x_bits is not None:
-                dx = dense_dgrad(dy16, wk, mask_bits=ctx.x_bits, mask_cols=ctx.relu_input_cols)
+                dx = dense_dgrad(dy16, wk, out=dxo, mask_bits=ctx.x_bits, mask_cols=ctx.relu_input_cols)
             else:
-                dx = dense_dgrad(dy16, wk, x16[:, :K] if ctx.relu_input else None, mask_cols=ctx.relu_input_cols)
+                dx = dense_dgrad(dy16, wk, x16[:, :K] if ctx.relu_input else None, out=dxo, mask_cols=ctx.relu_input_cols)
             if dx.dtype != ctx.in_dtype:
                 dx = dx.to(ctx.in_dtype)
         gw = getattr(weight, "_zoo_grad", None)
@@ -184,7 +188,7 @@ class _FusedDenseFn(torch.autograd.Function):
             dense_wgrad(dy16, x16[:, :K], dw_ret, gb)
         elif gb is not None:
             colsum(dy16, gb)
-        return dx, dw_ret, db_ret, None, None, None, None, None, None, None
+        return dx, dw_ret, db_ret, None, None, None, None, None, None, None, None
 
 
 def _pad_cols(t: torch.Tensor) -> torch.Tensor:
@@ -251,7 +255,7 @@ class FusedDense(nn.Module):
                 x_bits = None
             emit = self.activation == "relu" and self.skip_relu_bwd and torch.is_grad_enabled() and self.out_features % 32 == 0
             y = _FusedDenseFn.apply(x2, self.weight, self.bias, self.weight_bf16, self.activation, self.relu_input,
-                                    self.skip_relu_bwd, self.relu_input_cols, x_bits, emit)
+                                    self.skip_relu_bwd, self.relu_input_cols, x_bits, emit, getattr(x, "_zoo_dx_out", None))
             bits = None
             if emit:
                 y, bits = y

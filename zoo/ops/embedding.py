@@ -15,6 +15,7 @@ semantics of the reference, which treats ``Embedding`` as a dense ``LookupTable`
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.nn as nn
@@ -27,6 +28,7 @@ INT_MAX = 2**31 - 1
 
 _V, _I, _L, _F = C.c_void_p, C.c_int, C.c_longlong, C.c_float
 _nl.register_cuda_sigs({
+    "zoo_embedding_dispatch": [_V, _I, _I, _I, _I, _V, _L, _V, _L, _F, _L, _I, _I, _I, _V, _V, _V, _I, _V],
     "zoo_embedding_sparse_update_multi": [_V, _I, _I, _I, _I, _V, _L, _V, _L, _F, _L, _I, _I, _I, _V, _V, _V, _V, _I, _V, _V, _V, _V, _V, _I, _V],
 })
 
@@ -59,6 +61,7 @@ class ShardRuntime:
         self._bepoch = ptr_array([self.epoch.data_ptr() if i == r else None for i in range(W)])
         self.stages = {}
         self.accum, self.dup = None, None
+        self.pending_post = False
         torch.cuda.synchronize()
         ctx.barrier()
 
@@ -66,6 +69,13 @@ class ShardRuntime:
         """All ranks' work queued so far on this stream is complete before anyone goes on (no host sync)."""
         _nl.check(_nl.cuda_lib().zoo_p2p_barrier(self._bflags, self._bepoch, self.ctx.world_size, self.ctx.rank, 0,
                                                  _nl.stream_ptr()), "zoo_p2p_barrier")
+
+    def settle(self):
+        """The barrier that ends a sharded backward ("every owner has finished reading my staged ids / gradient rows") is
+        deferred to the next point where staged data is overwritten, so a step with several sharded lookups pays it once."""
+        if self.pending_post:
+            self.barrier()
+            self.pending_post = False
 
     def stage(self, key, shape, dtype):
         """A symmetric buffer (same key -> same buffer on every rank, allocated collectively on first use)."""
@@ -80,6 +90,23 @@ class ShardRuntime:
             b = self.stages[key] = (buf, buf.tensor(dtype, n).view(*shape))
         return b
 
+    def recv_buffers(self, key, n, D):
+        """Receive side of the backward dispatch for one table: ids int64 [n] (-1 = empty slot) and gradient rows bf16 [n, D]
+        in the symmetric heap (peers push into them), plus this rank's per-destination counters."""
+        rb = self.stages.get(("recv",) + tuple(key))
+        if rb is None:
+            if torch.cuda.is_current_stream_capturing():
+                raise _nl.NativeError("sharded-embedding receive buffers must be created before CUDA-graph capture (run one eager step first)")
+            ib, gb = self.heap.alloc(n * 8), self.heap.alloc(n * D * 2)
+            rb = {"n": n, "D": D, "ids": ib.tensor(torch.int64, n), "grad": gb.tensor(torch.bfloat16, n * D).view(n, D),
+                  "ids_ptrs": self._ptr_array(ib.ptrs), "grad_ptrs": self._ptr_array(gb.ptrs), "bufs": (ib, gb),
+                  "counters": torch.zeros(8, dtype=torch.int32, device=self.ctx.device)}
+            rb["ids"].fill_(-1)
+            torch.cuda.synchronize()      # every rank's buffers are empty before any peer may push into them
+            self.ctx.barrier()
+            self.stages[("recv",) + tuple(key)] = rb
+        return rb
+
     def scratch(self, E, D):
         if self.accum is None or self.accum.shape[0] < E or self.accum.shape[1] < D:
             E2 = max(E, 0 if self.accum is None else self.accum.shape[0])
@@ -93,7 +120,7 @@ class ShardRuntime:
 class EmbeddingTable(nn.Module):
     def __init__(self, num_embeddings, embedding_dim, init="uniform", init_scale=0.05, sparse=True,
                  optimizer="adam", lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
-                 world=1, rank=0, shadow_bf16=False, padding_idx=None, device=None):
+                 world=1, rank=0, shadow_bf16=None, padding_idx=None, device=None):
         super().__init__()
         self.num_embeddings, self.embedding_dim = int(num_embeddings), int(embedding_dim)
         self.world, self.rank = int(world), int(rank)
@@ -111,8 +138,11 @@ class EmbeddingTable(nn.Module):
                                  f"(world_size={rt.ctx.world_size}, rank={rt.ctx.rank})")
             self._sym = rt.heap.alloc(self.rows_local * self.embedding_dim * 4)
             w = self._sym.tensor(torch.float32, self.rows_local * self.embedding_dim).view(self.rows_local, self.embedding_dim)
-            if shadow_bf16:
-                raise NotImplementedError("shadow_bf16 with world > 1")
+            if shadow_bf16 is None:
+                # Remote gathers are NVLink-bandwidth bound and the forward rounds rows to bf16 anyway: peers read a
+                # bf16 shadow of the shard (written by the sparse optimizer together with the fp32 master row).
+                shadow_bf16 = os.environ.get("ZOO_EMB_SHADOW", "1") != "0"
+            self._sym16 = rt.heap.alloc(self.rows_local * self.embedding_dim * 2) if shadow_bf16 else None
         else:
             w = torch.empty(self.rows_local, self.embedding_dim, device=device)  # big tables: initialise on the GPU
         if init == "uniform":
@@ -125,6 +155,8 @@ class EmbeddingTable(nn.Module):
             nn.init.xavier_uniform_(w)
         if padding_idx is not None and self.world == 1:
             w[padding_idx].zero_()
+        if shadow_bf16 is None:
+            shadow_bf16 = os.environ.get("ZOO_EMB_SHADOW", "0") == "1"
         self.weight = nn.Parameter(w)
         # Sparse mode updates rows inside backward; this 1-element parameter only anchors the
         # lookup in the autograd graph (its own gradient is always None).
@@ -132,11 +164,30 @@ class EmbeddingTable(nn.Module):
         self.shadow_bf16 = shadow_bf16
         self._peer_ptrs = None if self._sym is None else list(self._sym.ptrs)   # one device pointer per rank when world > 1
         self._peer_ptrs16 = None
+        if self._sym is not None and self.shadow_bf16:
+            self.weight16 = self._sym16.tensor(torch.bfloat16, self.rows_local * self.embedding_dim).view(self.rows_local, self.embedding_dim)
+            self.weight16.copy_(w)
+            self._peer_ptrs16 = list(self._sym16.ptrs)
+            self._shadow_version = self.weight._version
         if self._sym is not None:
             torch.cuda.synchronize()      # the shard is initialised before any peer may read it
             ShardRuntime.get().ctx.barrier()
         self._state_ready = False
         self._ptr_arr = None
+        self.register_load_state_dict_post_hook(lambda mod, _keys: mod.refresh_shadow())
+
+    def refresh_shadow(self):
+        """Re-derive the bf16 shadow from the fp32 master rows (after a checkpoint load / in-place weight edit).  The
+        sparse optimizer keeps both in step by itself; an edit through torch bumps `weight._version`, which the next
+        lookup notices.  Collective for a sharded table (peers must not gather a half-refreshed shard)."""
+        w16 = getattr(self, "weight16", None)
+        if w16 is not None:
+            with torch.no_grad():
+                w16.copy_(self.weight.data)
+            if self._sym is not None:
+                torch.cuda.synchronize()
+                ShardRuntime.get().ctx.barrier()
+        self._shadow_version = self.weight._version
 
     def _apply(self, fn, *a, **kw):
         if self._sym is not None:
@@ -162,7 +213,9 @@ class EmbeddingTable(nn.Module):
         z = lambda: torch.zeros_like(self.weight.data, dtype=torch.float32)
         self.exp_avg = z() if self.optimizer in ("adam", "adagrad") else None
         self.exp_avg_sq = z() if self.optimizer == "adam" else None
-        self.weight16 = self.weight.data.to(torch.bfloat16) if self.shadow_bf16 else None
+        if self._sym is None:
+            self.weight16 = self.weight.data.to(torch.bfloat16) if self.shadow_bf16 else None
+            self._shadow_version = self.weight._version
         c = self.opt_cfg
         h = torch.zeros(16, dtype=torch.float32)
         h[0], h[1], h[2], h[3], h[4], h[5], h[6] = c["lr"], c["betas"][0], c["betas"][1], c["eps"], c["weight_decay"], 0.0, 1.0
@@ -198,6 +251,8 @@ class EmbeddingTable(nn.Module):
     def table_ptrs(self):
         """(ctypes void*[world], dtype id) for the gather kernel."""
         use16 = self.shadow_bf16 and getattr(self, "weight16", None) is not None
+        if use16 and getattr(self, "_shadow_version", None) != self.weight._version:
+            self.refresh_shadow()
         if self.world == 1:
             p = [self.weight16.data_ptr() if use16 else self.weight.data_ptr()]
         else:
@@ -250,16 +305,49 @@ def _sparse_update_sharded(table, ids_buf, ids, col, bag, dout_buf, dout_off, ld
     B = ids.shape[0]
     table._ensure_scratch(B * bag)
     pa = rt._ptr_array
-    ids_p = pa(ids_buf.ptrs)
+    slot = ids.numel() * 8
+    ids_p = pa([ids_buf.local_ptr + s * slot for s in range(table.world)])     # every rank's ids, replicated locally in forward
     dout_p = pa([p + dout_off * 2 for p in dout_buf.ptrs])
     mul_p = pa(mul_buf.ptrs) if mul_buf is not None else None
     D = table.embedding_dim
     accum = table.accum if table.accum.shape[1] == D else table.accum.view(-1)[: B * bag * table.world * D].view(-1, D)
     _nl.check(lib.zoo_embedding_sparse_update_multi(
         ids_p, ids.stride(0), col, B, bag, dout_p, ldg, mul_p, D if mul_buf is not None else 0, float(grad_scale),
-        table.num_embeddings, table.world, table.rank, D, table.weight.data_ptr(), None, _nl.ptr(table.exp_avg),
+        table.num_embeddings, table.world, table.rank, D, table.weight.data_ptr(), _nl.ptr(getattr(table, "weight16", None)), _nl.ptr(table.exp_avg),
         _nl.ptr(table.exp_avg_sq), SPARSE_OPTS[table.optimizer], table.hyper.data_ptr(), table.rep_of_row.data_ptr(),
         accum.data_ptr(), table.dup_flag.data_ptr(), table.win_list.data_ptr(), 1, _nl.stream_ptr()), "zoo_embedding_sparse_update")
+
+
+def _push_mode():
+    """Backward of row-sharded tables: "pull" (default; owners read ids / gradient rows of their entries from the peers'
+    staging buffers inside the update kernels) or "push" (sources dispatch gradient rows into the owners' receive buffers,
+    owners then update from local memory).  Measured on 4 / 8 B200s: within 2-3 % of each other (profiles/README.md)."""
+    return os.environ.get("ZOO_SHARD_BWD", "pull") == "push"
+
+
+def _dispatch(table, rb, ids, col, bag, dout_window, mul, grad_scale):
+    """Push this rank's gradient rows for `table` into the owners' receive buffers (zoo_embedding_dispatch)."""
+    B = ids.shape[0]
+    _nl.check(_nl.cuda_lib().zoo_embedding_dispatch(
+        ids.data_ptr(), ids.stride(0), col, B, bag, dout_window.data_ptr(), dout_window.stride(0), _nl.ptr(mul),
+        mul.stride(0) if mul is not None else 0, float(grad_scale), table.num_embeddings, table.world, table.rank,
+        table.embedding_dim, rb["ids_ptrs"], rb["grad_ptrs"], rb["counters"].data_ptr(), B * bag, _nl.stream_ptr()), "zoo_embedding_dispatch")
+
+
+def _sparse_update_received(table, rb):
+    """Owner side of the dispatch: the ordinary single-GPU sparse update over the receive buffer (local row ids, final
+    gradient rows), then the buffer's id slots are emptied for the next step."""
+    lib = _nl.cuda_lib()
+    table._ensure_state()
+    n, D = rb["n"], table.embedding_dim
+    table._ensure_scratch(n // table.world)
+    accum = table.accum if table.accum.shape[1] == D else table.accum.view(-1)[: n * D].view(-1, D)
+    _nl.check(lib.zoo_embedding_sparse_update_w(
+        rb["ids"].data_ptr(), 1, 0, n, 1, rb["grad"].data_ptr(), D, None, 0, 1.0, table.rows_local, 1, 0, D,
+        table.weight.data_ptr(), _nl.ptr(getattr(table, "weight16", None)), _nl.ptr(table.exp_avg), _nl.ptr(table.exp_avg_sq),
+        SPARSE_OPTS[table.optimizer], table.hyper.data_ptr(), table.rep_of_row.data_ptr(), accum.data_ptr(),
+        table.dup_flag.data_ptr(), table.win_list.data_ptr(), 1, _nl.stream_ptr()), "zoo_embedding_sparse_update_w")
+    rb["ids"].fill_(-1)
 
 
 def _sparse_update(table, ids, col, bag, dout_window, mul, grad_scale):
@@ -291,6 +379,7 @@ def _dense_grad(table, ids, col, bag, dout_window, mul, grad_scale):
 
 class _MultiLookupFn(torch.autograd.Function):
     """Gather every spec into its column window of one [B, sum(D)] bf16 buffer."""
+    offered_dx_out = None
 
     @staticmethod
     def forward(ctx, ids, specs, *weights):
@@ -302,14 +391,31 @@ class _MultiLookupFn(torch.autograd.Function):
             out[:, total:].zero_()
         sharded = any(t.world > 1 for t in _flat_tables(specs))
         ctx.sharded = sharded
+        ctx.push = sharded and _push_mode()
         key = None
-        if sharded:
+        if ctx.push:
+            # backward DISPATCHES gradient rows to their owners (zoo_embedding_dispatch): forward stages nothing
+            rt = ShardRuntime.get()
+            rt.settle()
+            key = ("lookup", tuple((id(s.table), s.col, s.bag, id(s.mul_table), s.mul_col) for s in specs), B, ids.shape[1])
+            if torch.is_grad_enabled():
+                for k, s in enumerate(specs):      # receive buffers exist (collectively allocated) before the first backward
+                    for which, t in enumerate([s.table] + ([s.mul_table] if s.mul_table is not None else [])):
+                        if t.world > 1:
+                            rt.recv_buffers((key, k, which), t.world * B * s.bag, t.embedding_dim)
+        elif sharded:
             # ids (and GMF factors below) are staged in symmetric buffers: peers read them in backward
             rt = ShardRuntime.get()
+            rt.settle()        # peers are done with what the previous backward staged before anything is staged again
             key = ("lookup", tuple((id(s.table), s.col, s.bag, id(s.mul_table), s.mul_col) for s in specs), B, ids.shape[1])
-            ids_buf, ids_st = rt.stage(key + ("ids",), ids.shape, torch.int64)
-            ids_st.copy_(ids)
-            ids = ids_st
+            # every rank PUSHES its id matrix into slot [rank] of every peer's copy, so the owner-side passes of backward
+            # (election, duplicate accumulation) scan all world * B entries from local memory
+            W, r = rt.ctx.world_size, rt.ctx.rank
+            ids_buf, ids_all = rt.stage(key + ("ids",), (W,) + tuple(ids.shape), torch.int64)
+            src = ids.contiguous()
+            _nl.check(_nl.cuda_lib().zoo_symm_bcast(rt._ptr_array(ids_buf.ptrs), r * src.numel() * 8, src.data_ptr(), src.numel() * 8, W,
+                                                    _nl.stream_ptr()), "zoo_symm_bcast")
+            ids = ids_all[r]
             ctx.ids_buf = ids_buf
         saves, off, ctx.mul_bufs = [], 0, []
         for k, s in enumerate(specs):
@@ -317,7 +423,7 @@ class _MultiLookupFn(torch.autograd.Function):
             sa = sb = None
             if s.mul_table is not None:
                 s.mul_table._ensure_state()
-                if sharded:
+                if sharded and not ctx.push:
                     ba, sa = rt.stage(key + ("sa", k), (B, s.dim), torch.bfloat16)
                     bb, sb = rt.stage(key + ("sb", k), (B, s.dim), torch.bfloat16)
                     ctx.mul_bufs.append((ba, bb))
@@ -335,7 +441,13 @@ class _MultiLookupFn(torch.autograd.Function):
         ctx.key = key
         ctx.save_for_backward(ids, *[t for t in saves if t is not None])
         ctx.has_save = [t is not None for t in saves]
-        return out[:, :total]
+        res = out[:, :total]
+        if sharded and not ctx.push and torch.is_grad_enabled():
+            # the gradient rows of this lookup must sit where peers can read them: offer the staging buffer to the consumer
+            # (FusedDense writes its input gradient straight into it), which saves the copy in backward
+            dbuf, dst = rt.stage(key + ("dout",), (B, ld), torch.bfloat16)
+            _MultiLookupFn.offered_dx_out = dst[:, :total]      # attached to the result by multi_lookup()
+        return res
 
     @staticmethod
     def backward(ctx, dout):
@@ -346,14 +458,18 @@ class _MultiLookupFn(torch.autograd.Function):
         if d16.stride(-1) != 1:
             d16 = d16.contiguous()
         rt = dbuf = None
-        if ctx.sharded:
+        jobs = []
+        if ctx.push:
+            rt = ShardRuntime.get()
+        elif ctx.sharded:
             # stage the gradient rows where peers can read them; the barrier makes every rank's staging
             # (and every rank's forward gathers of the old weights) complete before rows are updated
             rt = ShardRuntime.get()
             B = ids.shape[0]
             ld = (ctx.total + 7) // 8 * 8
             dbuf, dst = rt.stage(ctx.key + ("dout",), (B, ld), torch.bfloat16)
-            dst[:, :ctx.total].copy_(d16)
+            if d16.data_ptr() != dst.data_ptr() or d16.stride(0) != dst.stride(0):
+                dst[:, :ctx.total].copy_(d16)
             rt.barrier()
         grads, off, si = [], 0, 0
         for k, s in enumerate(specs):
@@ -367,7 +483,15 @@ class _MultiLookupFn(torch.autograd.Function):
             if s.mul_table is not None:
                 pairs.append((s.mul_table, s.mul_col, sa, 0))
             for table, col, mul, which in pairs:
-                if table.world > 1:
+                if table.world > 1 and ctx.push:
+                    if not table.sparse:
+                        raise _nl.NativeError("row-sharded tables are trained with the sparse optimizer (sparse=True)")
+                    rb = rt.recv_buffers((ctx.key, k, 0 if which == 1 else 1), table.world * ids.shape[0] * s.bag, table.embedding_dim)
+                    # 1/world: the loss is a mean over the GLOBAL batch, like the data-parallel dense part
+                    _dispatch(table, rb, ids, col, s.bag, win, mul, scale / table.world)
+                    jobs.append((table, rb))
+                    grads.append(None)
+                elif table.world > 1:
                     if not table.sparse:
                         raise _nl.NativeError("row-sharded tables are trained with the sparse optimizer (sparse=True)")
                     mb = ctx.mul_bufs[k][which] if (mul is not None and ctx.mul_bufs[k] is not None) else None
@@ -380,8 +504,13 @@ class _MultiLookupFn(torch.autograd.Function):
                 else:
                     grads.append(_dense_grad(table, ids, col, s.bag, win, mul, scale))
             off += s.dim
+        if jobs:
+            # every rank's pushes have landed (and every rank's forward gathers of the old rows are done) before owners update
+            rt.barrier()
+            for table, rb in jobs:
+                _sparse_update_received(table, rb)
         if ctx.sharded:
-            rt.barrier()     # nobody overwrites its staging buffers / gathers new rows before all owners are done
+            rt.pending_post = True     # nobody overwrites staging buffers / gathers new rows before all owners are done: see settle()
         return (None, None, *grads)
 
 
@@ -402,7 +531,12 @@ def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None):
         if ids.dtype != torch.int64:
             ids = ids.long()
         weights = [t.anchor if t.sparse else t.weight for t in _flat_tables(specs)]
-        return _MultiLookupFn.apply(ids, specs, *weights)
+        _MultiLookupFn.offered_dx_out = None
+        res = _MultiLookupFn.apply(ids, specs, *weights)
+        if _MultiLookupFn.offered_dx_out is not None:
+            res._zoo_dx_out = _MultiLookupFn.offered_dx_out
+            _MultiLookupFn.offered_dx_out = None
+        return res
     outs = []
     for s in specs:
         idc = ids[:, s.col:s.col + s.bag].long()

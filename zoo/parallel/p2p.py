@@ -8,6 +8,8 @@ handles and to broadcast the initial weights.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from ..native import lib as _nl
@@ -81,9 +83,18 @@ class P2PFusedSync:
         _nl.check(_nl.cuda_lib().zoo_p2p_barrier(self._bflags, self._bepoch, self.ctx.world_size, self.ctx.rank, 0,
                                                  _nl.stream_ptr()), "zoo_p2p_barrier")
 
-    def _grid_for(self, n):
-        per_rank_units = n // (4 * self.ctx.world_size)
-        return int(min(self.max_grid, max(4, (per_rank_units + 2047) // 2048)))
+    def _grid_for(self, n, replicated=False):
+        # every thread's loads cross NVLink (~2-3 us each): a range of a few hundred KB wants ONE float4 per thread so all
+        # of them are in flight at once; large ranges settle at the CTA cap and stream
+        per_rank_units = n // 4 if replicated else n // (4 * self.ctx.world_size)
+        return int(min(self.max_grid, max(4, (per_rank_units + 255) // 256)))
+
+    def _replicated(self, n):
+        """Small ranges: every rank sums all gradient copies and updates its own replica (one NVLink round trip less)."""
+        mode = os.environ.get("ZOO_K1_REPLICATED", "auto")
+        if mode in ("0", "1"):
+            return mode == "1"
+        return n * 4 * self.ctx.world_size <= (32 << 20)
 
     def step(self):
         f = self.fopt
@@ -97,9 +108,10 @@ class P2PFusedSync:
             hp = f.hyper_dev[i].data_ptr()
             _nl.check(lib.zoo_hyper_step(hp, f.hyper_stage[i].data_ptr() if refresh else None, st), "zoo_hyper_step")
             hy = ptr_array([hp if k == r else None for k in range(W)])
+            rep = self._replicated(g.end - g.start)
             _nl.check(lib.zoo_rs_opt_ag(self._g, self._p, self._p16, self._m, self._v, self._flags, self._epoch, hy,
-                                        g.start, g.end, W, r, 0, OPT_IDS[g.cfg.name], 1, self._grid_for(g.end - g.start),
-                                        st), "zoo_rs_opt_ag")
+                                        g.start, g.end, W, r, 0, OPT_IDS[g.cfg.name], 1 | (2 if rep else 0),
+                                        self._grid_for(g.end - g.start, rep), st), "zoo_rs_opt_ag")
 
     def close(self):
         pass

@@ -21,6 +21,7 @@ _nl.register_cuda_sigs({
     "zoo_symm_free": [C.c_void_p],
     "zoo_rs_opt_ag": [C.c_void_p] * 8 + [C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p],
     "zoo_p2p_barrier": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p],
+    "zoo_symm_bcast": [C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p],
     "zoo_vmm_alloc": [C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p],
     "zoo_vmm_import": [C.c_int, C.c_longlong, C.c_void_p],
     "zoo_vmm_free": [C.c_void_p, C.c_longlong],
