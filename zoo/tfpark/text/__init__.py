@@ -1,11 +1,4 @@
-"""TFPark text estimators (reference: pyzoo/zoo/tfpark/text/**: BERT classifier / NER / SQuAD estimators and the
-NLP-architect keras models NER, SequenceTagger, IntentEntity).  They are TensorFlow model functions; the torch
-counterparts are `zoo.pipeline.api.keras.layers.BERT` / `TransformerLayer` with a task head trained by `Estimator`."""
-from ..unsupported import _stub
-
-BERTClassifier = _stub("BERTClassifier")
-BERTNER = _stub("BERTNER")
-BERTSQuAD = _stub("BERTSQuAD")
-NER = _stub("NER")
-SequenceTagger = _stub("SequenceTagger")
-IntentEntity = _stub("IntentEntity")
+"""TFPark text models (reference: pyzoo/zoo/tfpark/text/**): the BERT estimators and the Keras-style NER / SequenceTagger /
+IntentEntity models, as torch networks with the reference's constructor arguments and train / evaluate / predict surface."""
+from .estimator import BERTNER, BERTBaseEstimator, BERTClassifier, BERTSQuAD, BertEncoder, bert_input_fn  # noqa: F401
+from .keras import CRF, NER, IntentEntity, SequenceTagger, TextKerasModel  # noqa: F401

@@ -20,7 +20,6 @@ TFOptimizer = _stub("TFOptimizer", ("from_loss", "from_keras", "from_train_op"))
 TFEstimator = _stub("TFEstimator", ("from_model_fn",))
 TFNet = _stub("TFNet", ("from_export_folder", "from_session", "from_saved_model"))
 TFPredictor = _stub("TFPredictor", ("from_outputs", "from_keras"))
-GANEstimator = _stub("GANEstimator")
 
 
 class ZooOptimizer:
