@@ -189,3 +189,43 @@ def test_bert_ner_and_squad_heads():
     assert sq.evaluate(fn, ["loss"])["loss"] < l0
     p = sq.predict(bert_input_fn([r[0] for r in sq_recs], L, 8))
     assert set(p[0]) == {"start_logits", "end_logits"} and p[0]["start_logits"].shape == (L,)
+
+
+def test_reference_module_names_resolve():
+    """Every public name of every module of the reference's python package resolves here (dev/api_parity.py)."""
+    import subprocess
+    import sys
+
+    out = subprocess.run([sys.executable, "dev/api_parity.py"], capture_output=True, text=True, cwd=__import__("os").path.dirname(__import__("os").path.dirname(__file__)))
+    last = [l for l in out.stdout.splitlines() if "names present" in l][-1]
+    assert "(100.0 %)" in last, out.stdout[-2000:]
+
+
+def test_compat_helpers():
+    from zoo.automl.model.MTNet_keras import AttentionRNNWrapper
+    from zoo.pipeline.api.utils import remove_batch, toMultiShape
+    from zoo.ray.mxnet.mxnet_runner import MXNetRunner
+    from zoo.ray.mxnet.utils import create_trainer_config, find_free_port
+    from zoo.tfpark.gan.common import GanOptimMethod
+    from zoo.tfpark.tfnet import to_sample_rdd
+    from zoo.util.engine import compare_version
+    from zoo.util.tf import export_tf
+
+    assert toMultiShape((2, 3)) == [[2, 3]] and remove_batch([(None, 4), (None, 5, 6)]) == [[4], [5, 6]]
+    assert create_trainer_config(8, seed=3, extra_config={"a": 1}) == {"batch_size": 8, "optimizer": "sgd", "optimizer_params": {"learning_rate": 0.01},
+                                                                      "log_interval": 10, "seed": 3, "a": 1}
+    assert 1024 < find_free_port() < 65536
+    assert compare_version("2.4.3", "2.2") == 1 and compare_version("1.6", "1.6.0") == 0 and compare_version("2.1", "2.2") == -1
+    assert [GanOptimMethod(None, None, 2, 1).phase(i) for i in range(4)] == ["D", "D", "G", "D"]
+    s = to_sample_rdd(np.zeros((3, 2)), np.arange(3))
+    assert len(s) == 3
+    with pytest.raises(NotImplementedError):
+        export_tf(None, "/tmp/x", [], [])
+    a = AttentionRNNWrapper(nn.LSTM(5, 7, batch_first=True))
+    a.return_sequences = True
+    assert a(torch.randn(2, 6, 5)).shape == (2, 6, 7)
+    r = MXNetRunner().setup_distributed({"DMLC_ROLE": "worker"}, create_trainer_config(4), lambda c, e: [(torch.randn(4, 3), torch.randint(0, 2, (4,)))] * 3,
+                                        lambda c: nn.Linear(3, 2))
+    st = r.train(2)
+    assert st["epoch"] == 2 and st["train_loss"] > 0
+    assert MXNetRunner().setup_distributed({"DMLC_ROLE": "server"}, {}, None, None).train() == {}

@@ -339,3 +339,8 @@ class Model(KerasNet):
         for p in self.parameters():
             p.requires_grad_(True)
         return self
+
+
+# names the reference defines in this module (engine/topology.py: Input, InputLayer, Merge, merge)
+from ..layers.base import Input, InputLayer  # noqa: E402,F401
+from ..layers.core import Merge, merge  # noqa: E402,F401

@@ -27,3 +27,18 @@ def modified_generator_loss(fake_d_outputs):
 
 
 modified_discriminator_loss = minimax_discriminator_loss
+
+
+class GanOptimMethod:
+    """(reference: gan/common.py:21-60) one OptimMethod that applies the discriminator optimizer for `d_steps` iterations, then
+    the generator optimizer for `g_steps`, over disjoint parameter slices.  The torch GANEstimator keeps two optimizers and
+    the same phase arithmetic; this class exposes that arithmetic."""
+
+    def __init__(self, d_optim, g_optim, d_steps, g_steps, g_param_size=None):
+        self.d_optim, self.g_optim, self.d_steps, self.g_steps, self.g_param_size = d_optim, g_optim, int(d_steps), int(g_steps), g_param_size
+
+    def phase(self, counter):
+        return "D" if counter % (self.d_steps + self.g_steps) < self.d_steps else "G"
+
+    def optimizer_for(self, counter):
+        return self.d_optim if self.phase(counter) == "D" else self.g_optim
