@@ -58,6 +58,8 @@ class Variable:
     @classmethod
     def from_layer(cls, layer, parents):
         shapes = [p.shape_ for p in parents]
+        if len(shapes) == 1 and isinstance(shapes[0], list):      # one multi-output variable (a table) feeding a table layer
+            shapes = shapes[0]
         if isinstance(layer, ZooKerasLayer):
             out = layer.ensure_built(shapes if (len(shapes) > 1 or layer.multi_input) else shapes[0])
         else:

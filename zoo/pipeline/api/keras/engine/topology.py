@@ -28,6 +28,19 @@ class KerasNet(nn.Module):
         self._compiled = None
         self._pending = {}
 
+    # -- weights (KerasNet.get_weights / set_weights of the reference: a flat list of ndarrays) ----------------------
+    def get_weights(self):
+        return [p.detach().cpu().numpy() for p in self.parameters()]
+
+    def set_weights(self, weights):
+        ps = list(self.parameters())
+        if len(ps) != len(weights):
+            raise ValueError(f"expected {len(ps)} weight arrays, got {len(weights)}")
+        with torch.no_grad():
+            for p, w in zip(ps, weights):
+                p.copy_(torch.as_tensor(w).reshape(p.shape))
+        return self
+
     # -- engine plumbing -------------------------------------------------------------
     def _get_engine(self, optimizer=None):
         from ....engine import TrainingEngine

@@ -71,6 +71,7 @@ class ActorHandle:
             self._exec = ProcessPoolExecutor(1, mp_context=mp.get_context("spawn"))
             self._exec.submit(_actor_new, self._id, cloudpickle.dumps((cls, args, kwargs))).result()
             ProcessMonitor.register_pids(list(self._exec._processes.keys()))
+            ctx._actors.append(self)
 
     def __getattr__(self, name):
         if name.startswith("_"):
@@ -90,8 +91,11 @@ class ActorHandle:
         return remote
 
     def kill(self):
-        if self._local is None:
-            self._exec.shutdown(wait=False, cancel_futures=True)
+        if self._local is None and self._exec is not None:
+            pids = list(self._exec._processes.keys())
+            self._exec.shutdown(wait=True, cancel_futures=True)
+            ProcessMonitor.unregister(pids)
+            self._exec = None
 
 
 class RayContext:
@@ -108,6 +112,7 @@ class RayContext:
         self._pool = None
         self._ids = itertools.count()
         self._lock = threading.Lock()
+        self._actors = []
 
     @classmethod
     def get(cls, initialize=True):
@@ -157,6 +162,9 @@ class RayContext:
         return [r.get(timeout) for r in refs] if isinstance(refs, (list, tuple)) else refs.get(timeout)
 
     def stop(self):
+        for a in self._actors:          # actor processes end with the context (the reference kills raylets and their actors)
+            a.kill()
+        self._actors = []
         if self._pool is not None:
             pids = list(self._pool._processes.keys())
             self._pool.shutdown(wait=True, cancel_futures=True)
