@@ -1,0 +1,100 @@
+"""Auxiliary subsystems: tracing helpers and the rank watchdog."""
+import logging
+import os
+import subprocess
+import sys
+import time
+
+import torch
+
+from zoo.utils.profiler import PhaseTimer, nvtx_range, throughputing, time_it
+from zoo.utils.watchdog import HeartbeatBoard, RankWatchdog
+
+
+def test_time_it_and_throughputing_log_lines(caplog):
+    with caplog.at_level(logging.INFO, logger="zoo.profiler"):
+        with time_it("load model"):
+            time.sleep(0.01)
+        with throughputing("batch", 100, loss=lambda: 0.5):
+            time.sleep(0.01)
+        with nvtx_range("noop"):
+            pass
+    text = caplog.text
+    assert "load model time elapsed [0 s," in text
+    assert "records/second. Loss is 0.500000." in text
+
+
+def test_phase_timer_cpu():
+    pt = PhaseTimer("cpu")
+    for _ in range(3):
+        with pt.phase("a"):
+            time.sleep(0.004)
+        with pt.phase("b"):
+            time.sleep(0.001)
+        pt.step()
+    s = pt.summary()
+    assert list(s) == ["a", "b"] and s["a"]["count"] == 3 and s["a"]["mean_ms"] > s["b"]["mean_ms"] > 0.5
+    assert pt.steps == 3
+    pt.reset()
+    assert pt.summary() == {}
+
+
+def test_heartbeat_board_roundtrip(tmp_path):
+    p = str(tmp_path / "hb")
+    b0, b1 = HeartbeatBoard(2, 0, p), HeartbeatBoard(2, 1, p)
+    b1.beat(7)
+    assert b0.read(1)["step"] == 7 and b0.read(1)["pid"] == os.getpid() and b0.read(0)["step"] == 0
+    b1.close()
+    assert b0.read(1)["state"] == 1
+    b0.close(unlink=True)
+    assert not os.path.exists(p)
+
+
+def test_watchdog_detects_stalled_peer_and_own_hang(tmp_path):
+    p = str(tmp_path / "hb")
+    seen = []
+    w0 = RankWatchdog(2, 0, timeout=0.3, interval=0.05, on_failure=seen.append, path=p).start()
+    peer = HeartbeatBoard(2, 1, p)
+    peer.beat(1)
+    for i in range(8):              # rank 0 keeps stepping, rank 1 went silent after its first beat
+        w0.beat(i)
+        time.sleep(0.08)
+    assert seen and seen[0]["kind"] == "stalled" and seen[0]["rank"] == 1
+    w0.stop(unlink=False)
+    # own hang: a rank that stops beating notices it itself
+    seen2 = []
+    w = RankWatchdog(1, 0, timeout=0.2, interval=0.05, on_failure=seen2.append, path=str(tmp_path / "hb2")).start()
+    w.beat(1)
+    time.sleep(0.6)
+    assert seen2 and seen2[0]["kind"] == "hang"
+    w.stop()
+
+
+def test_watchdog_detects_dead_process(tmp_path):
+    p = str(tmp_path / "hb")
+    w0 = RankWatchdog(2, 0, timeout=60, interval=0.05, on_failure=lambda f: None, path=p)
+    code = ("import sys; sys.path.insert(0, %r); from zoo.utils.watchdog import HeartbeatBoard; b = HeartbeatBoard(2, 1, %r, create=False); b.beat(3)"
+            % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), p))
+    subprocess.run([sys.executable, "-c", code], check=True, timeout=120)     # the peer beats once and exits without closing
+    w0.beat(1)
+    f = w0.check()
+    assert f is not None and f["kind"] == "dead" and f["rank"] == 1 and f["step"] == 3
+    w0.stop()
+
+
+def test_engine_beats_the_watchdog(tmp_path, monkeypatch):
+    import numpy as np
+    import torch.nn as nn
+
+    from zoo.common.triggers import MaxIteration
+    from zoo.feature.common import FeatureSet
+    from zoo.pipeline.estimator import Estimator
+
+    monkeypatch.setenv("ZOO_WATCHDOG_TIMEOUT", "120")
+    est = Estimator(nn.Linear(4, 2), optim_methods=torch.optim.SGD)
+    x, y = np.random.randn(64, 4).astype(np.float32), np.random.randint(0, 2, 64)
+    est.train(FeatureSet.numpy(x, y), nn.CrossEntropyLoss(), end_trigger=MaxIteration(5), batch_size=16)
+    wd = est.engine.watchdog
+    assert wd is not None and wd.board.read(0)["step"] >= 5 and wd.failed is None
+    est.close()
+    assert est.engine.watchdog is None

@@ -144,6 +144,7 @@ class TrainingEngine:
         self.last_throughput = 0.0
         self.on_step = None          # optional callback(iteration, loss_tensor) after every step
         self.async_loss = False      # read the loss back with a one-step lag (no pipeline stall)
+        self.watchdog = None         # RankWatchdog when ZOO_WATCHDOG_TIMEOUT / zoo.watchdog.timeout is set
         self.use_cuda_graph = None   # None = auto (models that declare `graph_safe = True`)
         self._graph = None
         self._loss_ring = None
@@ -474,6 +475,11 @@ class TrainingEngine:
         retry_budget, retry_window = int(conf.get("zoo.failure.retryTimes", 5)), float(conf.get("zoo.failure.retryTimeInterval", 120))
         failures, window_start = 0, time.time()
         self.state["numSlice"] = fs.num_of_slice()
+        wd_timeout = float(os.environ.get("ZOO_WATCHDOG_TIMEOUT", conf.get("zoo.watchdog.timeout", 0)) or 0)
+        if wd_timeout > 0 and self.watchdog is None:      # heartbeats + hang detection across the ranks of the box
+            from ..utils.watchdog import RankWatchdog
+
+            self.watchdog = RankWatchdog(ctx.world_size, ctx.rank, timeout=wd_timeout).start()
         while True:
             try:
                 self._train_loop(fs, criterion, end_trigger, checkpoint_trigger, validation_set, metrics, local_bs,
@@ -520,6 +526,8 @@ class TrainingEngine:
                 self._maybe_inject_fault()
                 self.fopt.epoch = st["epoch"]
                 loss_dev = self.train_step(criterion, batch)
+                if self.watchdog is not None:
+                    self.watchdog.beat(st["neval"])
                 if self.on_step is not None:
                     self.on_step(st["neval"], loss_dev)
                 st["neval"] += 1
@@ -652,3 +660,6 @@ class TrainingEngine:
                 s.close()
         if self._dp is not None:
             self._dp.close()
+        if self.watchdog is not None:
+            self.watchdog.stop()
+            self.watchdog = None
