@@ -31,7 +31,8 @@ for rows in (4_000_000, 25_000_000):
             src = buf.ptrs[ctx.rank if where == "local" else 1 - ctx.rank]
             arr = (C.c_void_p * 1)(src)
             st = torch.cuda.current_stream().cuda_stream
-            run = lambda: nl.check(lib.zoo_embedding_gather(ids.data_ptr(), 1, 0, 0, B, 1, 0, arr, rows, None, 0, 1, D, 0, out.data_ptr(), D, None, None, st), "g")
+            run = lambda: nl.check(lib.zoo_embedding_gather(ids.data_ptr(), 1, 0, 0, B, 1, 0, arr, rows, None, 0, 1, D, 0,
+                                                            out.data_ptr(), D, None, None, st), "g")
             for only in ((0,), (0, 1)):          # one direction, then both ranks at once
                 dist.barrier()
                 if ctx.rank in only:

@@ -90,7 +90,8 @@ fa = lambda v: (C.c_float * 4)(*(list(v) + [1.0])[:4])
 
 
 def ours_pre():
-    nl.check(nl.cuda_lib().zoo_serving_preproc(bat.dev.data_ptr(), bat.meta_dev.data_ptr(), bat.meta_dev[Bn:].data_ptr(), out.data_ptr(), 64, 3, 224, 224, 224, 224,
+    nl.check(nl.cuda_lib().zoo_serving_preproc(bat.dev.data_ptr(), bat.meta_dev.data_ptr(), bat.meta_dev[Bn:].data_ptr(), out.data_ptr(),
+                                               64, 3, 224, 224, 224, 224,
                                                C.cast(fa(mean), C.c_void_p), C.cast(fa(std), C.c_void_p), 1, 1, 1, nl.stream_ptr()), "pre")
 
 

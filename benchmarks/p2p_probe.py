@@ -27,7 +27,9 @@ print(f"peer copy 0->1: {5 * a.numel() * 4 / e0.elapsed_time(e1) / 1e6:.1f} GB/s
 
 lib = nl.cuda_lib()
 D, B = 128, 65536 * 4
-for rows, dt_name, dt, code in ((4_000_000, "fp32", torch.float32, 0), (12_500_000, "fp32", torch.float32, 0), (25_000_000, "fp32", torch.float32, 0), (25_000_000, "bf16", torch.bfloat16, 1)):
+CASES = ((4_000_000, "fp32", torch.float32, 0), (12_500_000, "fp32", torch.float32, 0), (25_000_000, "fp32", torch.float32, 0),
+         (25_000_000, "bf16", torch.bfloat16, 1))
+for rows, dt_name, dt, code in CASES:
     local = torch.empty(rows, D, device="cuda:0", dtype=dt).normal_()
     peer = torch.empty(rows, D, device="cuda:1", dtype=dt).normal_()
     out = torch.empty(B, D, dtype=torch.bfloat16, device="cuda:0")

@@ -3,7 +3,9 @@ import torch, torch.nn.functional as F
 from torch.profiler import profile, ProfilerActivity
 from zoo.ops.tcn import causal_conv1d
 B,C,T,K,d = 1024,30,64,3,4
-x = torch.randn(B, C, T, device="cuda", requires_grad=True); w = (torch.randn(C, C, K, device="cuda")*0.1).requires_grad_(True); b = torch.zeros(C, device="cuda", requires_grad=True)
+x = torch.randn(B, C, T, device="cuda", requires_grad=True)
+w = (torch.randn(C, C, K, device="cuda")*0.1).requires_grad_(True)
+b = torch.zeros(C, device="cuda", requires_grad=True)
 def ours(): causal_conv1d(x, w, b, d, True).sum().backward()
 def lib(): torch.relu(F.conv1d(F.pad(x, ((K-1)*d, 0)), w, b, dilation=d)).sum().backward()
 for fn in (ours, lib):

@@ -20,5 +20,6 @@ setup(name="zoo-b200", version="0.8.0.dev0", description="Blackwell-native frame
       install_requires=["torch>=2.6", "numpy", "pandas", "pyyaml", "cloudpickle", "scipy"],
       extras_require={"image": ["opencv-python", "torchvision"], "automl": ["scikit-learn"]},
       scripts=[os.path.join("scripts", s) for s in ("zoo-submit", "jupyter-with-zoo.sh")] +
-              [os.path.join("scripts", "cluster-serving", s) for s in os.listdir(os.path.join(HERE, "scripts", "cluster-serving")) if s.startswith("cluster-serving-")],
+              [os.path.join("scripts", "cluster-serving", s) for s in os.listdir(os.path.join(HERE, "scripts", "cluster-serving"))
+               if s.startswith("cluster-serving-")],
       cmdclass={"build_py": BuildWithNative})

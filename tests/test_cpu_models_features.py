@@ -247,7 +247,8 @@ def test_image_models_and_detection_utils(tmp_path):
     lo = LabelOutput({0: "a", 1: "b"})({"predict": np.array([0.2, 0.8])})
     assert lo["clses"] == ["b", "a"]
     assert nms(np.array([[0, 0, 10, 10], [1, 1, 10, 10], [20, 20, 30, 30]], np.float32), np.array([0.9, 0.8, 0.7]), 0.5) == [0, 2]
-    feat = {"mat": np.zeros((100, 200, 3), np.uint8), "originalSize": (100, 200, 3), "predict": np.array([2, 15, 0.9, 0.1, 0.2, 0.5, 0.6, 7, 0.2, 0, 0, 1, 1], np.float32)}
+    feat = {"mat": np.zeros((100, 200, 3), np.uint8), "originalSize": (100, 200, 3),
+            "predict": np.array([2, 15, 0.9, 0.1, 0.2, 0.5, 0.6, 7, 0.2, 0, 0, 1, 1], np.float32)}
     DecodeOutput()(feat)
     assert feat["predict"].shape == (2, 6)
     ScaleDetection()(feat)

@@ -24,7 +24,8 @@ def test_config_and_filter_parsing(tmp_path):
     from zoo.serving.server import ServingConfig
 
     p = tmp_path / "config.yaml"
-    p.write_text("model:\n  path: /m\ndata:\n  src: 10.0.0.1:7000\n  image_shape: 3, 32,48\n  filter: topN(3)\nparams:\n  batch_size: 16\nredis:\n  maxmem: 2g\n")
+    p.write_text("model:\n  path: /m\ndata:\n  src: 10.0.0.1:7000\n  image_shape: 3, 32,48\n  filter: topN(3)\n"
+                 "params:\n  batch_size: 16\nredis:\n  maxmem: 2g\n")
     c = ServingConfig(str(p))
     assert (c.host, c.port, c.C, c.H, c.W, c.top_n, c.batch_size, c.maxmem, c.chw) == ("10.0.0.1", 7000, 3, 32, 48, 3, 16, 2 << 30, True)
     d = ServingConfig({})

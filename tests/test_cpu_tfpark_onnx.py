@@ -71,7 +71,8 @@ def test_local_estimator():
 
     x, y = _xy(400)
     data = [(x[i], y[i]) for i in range(400)]
-    est = LocalEstimator(nn.Sequential(nn.Linear(6, 16), nn.ReLU(), nn.Linear(16, 2), nn.Softmax(-1)), "sparse_categorical_crossentropy", Adam(lr=1e-2), ["accuracy"], thread_num=4)
+    est = LocalEstimator(nn.Sequential(nn.Linear(6, 16), nn.ReLU(), nn.Linear(16, 2), nn.Softmax(-1)), "sparse_categorical_crossentropy",
+                         Adam(lr=1e-2), ["accuracy"], thread_num=4)
     est.fit(data, data[:100], batch_size=40, epoch=15)
     assert est.validate(data, batch_size=100)[0].value > 0.9
 
@@ -89,7 +90,8 @@ def test_onnx_graph_mlp_and_convnet():
 
     rng = np.random.RandomState(0)
     w1, b1, w2, b2 = rng.randn(8, 5).astype(np.float32), rng.randn(8).astype(np.float32), rng.randn(8, 3).astype(np.float32), rng.randn(3).astype(np.float32)
-    g = NS(initializer=[_t("w1", w1), _t("b1", b1), _t("w2", w2), _t("b2", b2)], input=[NS(name="x"), NS(name="w1"), NS(name="b1"), NS(name="w2"), NS(name="b2")],
+    g = NS(initializer=[_t("w1", w1), _t("b1", b1), _t("w2", w2), _t("b2", b2)],
+           input=[NS(name="x"), NS(name="w1"), NS(name="b1"), NS(name="w2"), NS(name="b2")],
            output=[NS(name="y")],
            node=[_node("Gemm", ["x", "w1", "b1"], ["h"], transB=1), _node("Relu", ["h"], ["r"]), _node("MatMul", ["r", "w2"], ["m"]),
                  _node("Add", ["m", "b2"], ["a"]), _node("Softmax", ["a"], ["y"], axis=1)])

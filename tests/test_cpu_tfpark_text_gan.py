@@ -196,7 +196,10 @@ def test_reference_module_names_resolve():
     import subprocess
     import sys
 
-    out = subprocess.run([sys.executable, "dev/api_parity.py"], capture_output=True, text=True, cwd=__import__("os").path.dirname(__import__("os").path.dirname(__file__)))
+    import os
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "dev/api_parity.py"], capture_output=True, text=True, cwd=root)
     last = [l for l in out.stdout.splitlines() if "names present" in l][-1]
     assert "(100.0 %)" in last, out.stdout[-2000:]
 

@@ -24,7 +24,8 @@ def prepare_embedding(embedding_file, word_index=None, randomize_unknown=False, 
                 dim = len(p) - 1
     index = word_index or {w: i + 1 for i, w in enumerate(vecs)}
     rng = np.random.RandomState(0)
-    w = rng.uniform(-0.05, 0.05, (max(index.values()) + 1, dim)).astype(np.float32) if randomize_unknown else np.zeros((max(index.values()) + 1, dim), np.float32)
+    n_rows = max(index.values()) + 1
+    w = rng.uniform(-0.05, 0.05, (n_rows, dim)).astype(np.float32) if randomize_unknown else np.zeros((n_rows, dim), np.float32)
     w[0] = 0
     for word, i in index.items():
         if word in vecs:

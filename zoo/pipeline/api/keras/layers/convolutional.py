@@ -82,7 +82,8 @@ class AtrousConvolution2D(_ConvND):
                  atrous_rate=(1, 1), dim_ordering="th", W_regularizer=None, b_regularizer=None, bias=True, input_shape=None, **kw):
         if border_mode != "valid":
             raise ValueError("For AtrousConvolution2D, only border_mode='valid' is supported for now")
-        super().__init__(nb_filter, (int(nb_row), int(nb_col)), init, activation, border_mode, tuple(subsample), tuple(atrous_rate), dim_ordering, bias, input_shape, **kw)
+        super().__init__(nb_filter, (int(nb_row), int(nb_col)), init, activation, border_mode, tuple(subsample), tuple(atrous_rate), dim_ordering,
+                         bias, input_shape, **kw)
 
 
 class Convolution3D(_ConvND):
@@ -90,7 +91,8 @@ class Convolution3D(_ConvND):
 
     def __init__(self, nb_filter, kernel_dim1, kernel_dim2, kernel_dim3, init="glorot_uniform", activation=None, border_mode="valid",
                  subsample=(1, 1, 1), dim_ordering="th", W_regularizer=None, b_regularizer=None, bias=True, input_shape=None, **kw):
-        super().__init__(nb_filter, (int(kernel_dim1), int(kernel_dim2), int(kernel_dim3)), init, activation, border_mode, tuple(subsample), (1, 1, 1), dim_ordering, bias, input_shape, **kw)
+        super().__init__(nb_filter, (int(kernel_dim1), int(kernel_dim2), int(kernel_dim3)), init, activation, border_mode, tuple(subsample),
+                         (1, 1, 1), dim_ordering, bias, input_shape, **kw)
 
 
 class Deconvolution2D(ZooKerasLayer):

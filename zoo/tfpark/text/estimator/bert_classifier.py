@@ -6,7 +6,7 @@ def make_bert_classifier_model_fn(optimizer):
     """The reference returns a TF model_fn closed over the optimizer; here: a factory `(params) -> (network, optimizer)`
     for the same head, usable with `BERTBaseEstimator`."""
     def model_fn(params):
-        args = [params.get("bert_config_file")] + ([params["num_classes"]] if "classifier" == "classifier" else [params["num_entities"]] if "classifier" == "ner" else [])
+        args = [params.get("bert_config_file")] + [params["num_classes"]]
         return _ClassifierNet(*args), optimizer
 
     return model_fn
