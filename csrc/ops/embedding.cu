@@ -425,8 +425,10 @@ emb_apply_kernel(BwdEntries en, int E, long long rows, int world, int rank, int*
 // organised for loads in flight rather than for arithmetic: a row uses only as many lanes as it has float4 columns
 // (G = 8 / 16 / 32), a warp therefore covers 32/G rows per pass, and every warp issues the loads of R passes before it
 // computes anything.
-template <int R>
-__global__ void __launch_bounds__(256, R == 1 ? 5 : 1)
+// LOOP == false: one pass per warp over a grid sized for the entries (small entry counts: no register cost of the loop, full
+// occupancy); LOOP == true: a grid of a few waves strides over the winner list (entry counts far above the winner count).
+template <int R, bool LOOP>
+__global__ void __launch_bounds__(256, R == 1 ? (LOOP ? 5 : 6) : 1)
 emb_apply_fast_kernel(BwdEntries en, int D, int G, float* __restrict__ accum, int* __restrict__ dup_flag, int* __restrict__ rep_of_row,
                       SparseState st, int opt, const float* __restrict__ hyper, const int2* __restrict__ win_list,
                       const int* __restrict__ win_count) {
@@ -444,7 +446,9 @@ emb_apply_fast_kernel(BwdEntries en, int D, int G, float* __restrict__ accum, in
   if (opt == SOPT_ADAM) { bc1 = 1.f - powf(b1, step); bc2 = 1.f - powf(b2, step); }
   // The grid is sized for full occupancy, not for the entry count: the winner count is only known on the device, and a grid
   // of one warp per POSSIBLE entry (world x batch of them for a sharded table) spent most of its time launching empty CTAs.
-  for (int base = warp * P * R; base < count; base += nwarps * P * R) {
+  int base = warp * P * R;
+  if (base >= count) return;
+  do {                                                     // LOOP == false: exactly one pass (the grid covers every possible entry)
   int e[R]; long long local[R]; bool ok[R], dup[R];
   float g[R][4]; float4 w4[R], m4[R], v4[R], a4[R];
 #pragma unroll
@@ -501,7 +505,8 @@ emb_apply_fast_kernel(BwdEntries en, int D, int G, float* __restrict__ accum, in
       if (dup[r]) dup_flag[e[r]] = 0;
     }
   }
-  }
+  base += nwarps * P * R;
+  } while (LOOP && base < count);
 }
 
 // Dense-gradient mode (exact reference semantics for small tables): dTable[id] += dOut rows.
@@ -572,11 +577,15 @@ static int launch_sparse_update(const BwdEntries& en, int E, long long rows, int
     long long grid_ll = (warps * 32 + threads - 1) / threads;
     static int sm_count = 0;
     if (!sm_count) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev); if (sm_count <= 0) sm_count = 148; }
-    if (grid_ll > (long long)sm_count * 16) grid_ll = (long long)sm_count * 16;     // a few waves; the kernel strides over the winner list
+    // up to 64 CTAs per SM worth of entries (one GPU's own batch): one pass, no loop; beyond that (world x batch possible entries
+    // of a sharded table, most of them not owned here) a few waves stride over the winner list
+    const bool loop = grid_ll > (long long)sm_count * 64;
+    if (loop) grid_ll = (long long)sm_count * 16;
     const unsigned grid = (unsigned)grid_ll;
-    if (R == 1) ZOO_CUDA_CHECK(zoo_launch_pdl(emb_apply_fast_kernel<1>, dim3(grid), dim3(threads), 0, s, en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, (const int2*)wl, (const int*)wc));
-    else if (R == 2) emb_apply_fast_kernel<2><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
-    else emb_apply_fast_kernel<4><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
+    if (R == 1 && !loop) ZOO_CUDA_CHECK(zoo_launch_pdl(emb_apply_fast_kernel<1, false>, dim3(grid), dim3(threads), 0, s, en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, (const int2*)wl, (const int*)wc));
+    else if (R == 1) ZOO_CUDA_CHECK(zoo_launch_pdl(emb_apply_fast_kernel<1, true>, dim3(grid), dim3(threads), 0, s, en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, (const int2*)wl, (const int*)wc));
+    else if (R == 2) emb_apply_fast_kernel<2, true><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
+    else emb_apply_fast_kernel<4, true><<<grid, threads, 0, s>>>(en, D, G, accum, dup_flag, rep_of_row, st, opt, hyper, wl, wc);
   } else if (vec) {
     emb_accum_kernel<true><<<ab, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, wl, wc);
     emb_apply_kernel<true><<<wb, threads, 0, s>>>(en, E, rows, world, rank, rep_of_row, D, accum, dup_flag, st, opt, hyper, wl, wc);

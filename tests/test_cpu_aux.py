@@ -98,3 +98,37 @@ def test_engine_beats_the_watchdog(tmp_path, monkeypatch):
     assert wd is not None and wd.board.read(0)["step"] >= 5 and wd.failed is None
     est.close()
     assert est.engine.watchdog is None
+
+
+def test_native_arrays_over_the_arena(tmp_path):
+    import numpy as np
+    import pytest
+
+    from zoo.feature.pmem import FixLenBytesArray, FloatArray, MemoryType, VarLenBytesArray, VarLenFloatsArray
+
+    assert MemoryType.DISK_AND_DRAM(4) == "DISK_AND_DRAM(4)"
+    v = VarLenBytesArray(3, 64, MemoryType.DIRECT)
+    for i, b in enumerate([b"abc", b"", b"0123456789"]):
+        v.set(i, b)
+    assert len(v) == 3 and v.get(0) == b"abc" and v.get(1) == b"" and v.get(2) == b"0123456789"
+    with pytest.raises(ValueError):
+        v.set(7, b"x")
+    v.free()
+    with pytest.raises(RuntimeError):
+        v.get(0)
+    f = FloatArray(100, 4, MemoryType.PMEM, path=str(tmp_path / "pmem.bin")).pin()       # file-backed: the "pmem mount"
+    for i in range(100):
+        f.set(i, [i, i + 0.5, -i, 1.0])
+    np.testing.assert_allclose(f.get(7), [7, 7.5, -7, 1.0])
+    assert f.batch([1, 3]).shape == (2, 4) and float(f.batch([1, 3])[1, 1]) == 3.5
+    f.free()
+    fx = FixLenBytesArray(4, 8)
+    fx.set(2, b"12345678")
+    assert fx.get(2) == b"12345678"
+    with pytest.raises(ValueError):
+        fx.set(0, b"short")
+    vf = VarLenFloatsArray(2, 10)
+    vf.set(0, [1.0, 2.0, 3.0]); vf.set(1, [4.0])
+    np.testing.assert_allclose(vf.get(0), [1, 2, 3]); np.testing.assert_allclose(vf.get(1), [4])
+    with pytest.raises(ValueError):
+        FloatArray(1, memory_type="TAPE")
