@@ -33,7 +33,7 @@ namespace zoo {
 
 constexpr int kMaxRanks = 8;
 constexpr int kRsThreads = 256;
-constexpr int kFlagStride = 64;   // flag slots per (phase, rank): fixed so launches with different grids never alias
+constexpr int kFlagStride = 1024; // flag slots per (phase, rank): fixed so launches with different grids never alias; also the CTA cap
 
 struct RsArgs {
   float* g[kMaxRanks];               // gradient arenas (index = rank; peers via IPC)

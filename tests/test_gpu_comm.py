@@ -36,8 +36,8 @@ def test_rs_opt_ag_emulated_matches_torch(world, opt, replicated):
     gs = [torch.randn(n, device="cuda") for _ in range(world)]
     ms = [torch.zeros(n, device="cuda") for _ in range(world)]
     vs = [torch.zeros(n, device="cuda") for _ in range(world)]
-    flags = [torch.zeros(2 * world * 64, dtype=torch.int32, device="cuda") for _ in range(world)]
-    epochs = [torch.zeros(64, dtype=torch.int32, device="cuda") for _ in range(world)]
+    flags = [torch.zeros(2 * world * 1024, dtype=torch.int32, device="cuda") for _ in range(world)]
+    epochs = [torch.zeros(1024, dtype=torch.int32, device="cuda") for _ in range(world)]
     cfg = OptConfig("adam", lr=1e-2) if opt == "adam" else OptConfig("sgd", lr=1e-2, b1=0.9)
     ref_p = p0.clone().requires_grad_(True)
     ref_opt = torch.optim.Adam([ref_p], lr=1e-2) if opt == "adam" else torch.optim.SGD([ref_p], lr=1e-2, momentum=0.9)

@@ -27,7 +27,8 @@ class P2PFusedSync:
         self.heap = get_heap(ctx)
         self.fopt = None
         self._bufs = []
-        self.max_grid = 64
+        self.flag_stride = 1024      # kFlagStride of csrc/comm/rs_opt_ag.cu
+        self.max_grid = 592          # 4 CTAs per SM: a ResNet-sized arena needs the whole GPU to fill NVLink (64 CTAs reached 11 % of it)
 
     # -- arena allocation in the symmetric heap -------------------------------------------
     def allocator(self):
@@ -53,10 +54,15 @@ class P2PFusedSync:
         by_ptr = {b.local_ptr: b for b in self._bufs}
         self.buf_p, self.buf_g = by_ptr[a.flat_p.data_ptr()], by_ptr[a.flat_g.data_ptr()]
         self.buf_p16 = by_ptr[a.flat_p16.data_ptr()] if a.flat_p16 is not None else None
-        self.flag_buf = self.heap.alloc(4 * 2 * W * self.max_grid)
-        self.epoch = torch.zeros(self.max_grid, dtype=torch.int32, device=self.ctx.device)
+        self.flag_buf = self.heap.alloc(4 * 2 * W * self.flag_stride)
+        self.epoch = torch.zeros(self.flag_stride, dtype=torch.int32, device=self.ctx.device)
         self.bar_flags = self.heap.alloc(4 * W)
         self.bar_epoch = torch.zeros(1, dtype=torch.int32, device=self.ctx.device)
+        # flags count epochs from zero: clear them on every rank before any peer can signal
+        self.flag_buf.tensor(torch.int32, 2 * W * self.flag_stride).zero_()
+        self.bar_flags.tensor(torch.int32, W).zero_()
+        torch.cuda.synchronize()
+        self.ctx.barrier()
         r = self.ctx.rank
         self._g = ptr_array(self.buf_g.ptrs)
         self._p = ptr_array(self.buf_p.ptrs)
