@@ -282,3 +282,25 @@ def test_sequential_fit_and_keras2(tmp_path):
     a, b = L.Input(shape=(4,)), L.Input(shape=(4,))
     mm = Model([a, b], K2.maximum([a, b]))
     torch.testing.assert_close(mm(torch.zeros(2, 4), torch.ones(2, 4)), torch.ones(2, 4))
+
+
+@pytest.mark.parametrize("idx", range(len(CASES)))
+def test_layer_serializer_roundtrip(idx, tmp_path):
+    """Every layer survives saveModel -> Net.load with identical outputs (reference: the serializer specs, one per layer)."""
+    from zoo.pipeline.api.net import Net
+
+    make, in_shape, _ = CASES[idx]
+    torch.manual_seed(100 + idx)
+    m = Sequential().add(make())
+    m.eval()
+    x = torch.rand(3, *in_shape) + 0.1
+    with torch.no_grad():
+        want = m(x)
+    path = str(tmp_path / "layer.model")
+    m.saveModel(path, over_write=True)
+    m2 = Net.load(path)
+    m2.eval()
+    with torch.no_grad():
+        got = m2(x)
+    torch.testing.assert_close(got, want)
+    assert [tuple(p.shape) for p in m2.parameters()] == [tuple(p.shape) for p in m.parameters()]

@@ -39,11 +39,28 @@ def hard_sigmoid(x):
     return torch.clamp(0.2 * x + 0.5, 0.0, 1.0)
 
 
+# module-level functions (not lambdas): layers keep a reference to their activation and must stay picklable for saveModel
+def linear(x):
+    return x
+
+
+def softmax_last(x):
+    return torch.softmax(x, -1)
+
+
+def softmin_last(x):
+    return F.softmin(x, -1)
+
+
+def log_softmax_last(x):
+    return F.log_softmax(x, -1)
+
+
 ACTIVATIONS = {
-    None: lambda x: x, "linear": lambda x: x, "relu": torch.relu, "tanh": torch.tanh, "sigmoid": torch.sigmoid,
-    "hard_sigmoid": hard_sigmoid, "softmax": lambda x: torch.softmax(x, -1), "softplus": F.softplus, "softsign": F.softsign,
-    "relu6": F.relu6, "tanh_shrink": F.tanhshrink, "softmin": lambda x: F.softmin(x, -1), "log_sigmoid": F.logsigmoid,
-    "log_softmax": lambda x: F.log_softmax(x, -1), "gelu": F.gelu, "elu": F.elu, "selu": F.selu, "exp": torch.exp,
+    None: linear, "linear": linear, "relu": torch.relu, "tanh": torch.tanh, "sigmoid": torch.sigmoid,
+    "hard_sigmoid": hard_sigmoid, "softmax": softmax_last, "softplus": F.softplus, "softsign": F.softsign,
+    "relu6": F.relu6, "tanh_shrink": F.tanhshrink, "softmin": softmin_last, "log_sigmoid": F.logsigmoid,
+    "log_softmax": log_softmax_last, "gelu": F.gelu, "elu": F.elu, "selu": F.selu, "exp": torch.exp,
 }
 
 
