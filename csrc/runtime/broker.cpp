@@ -19,6 +19,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <charconv>
 #include <chrono>
 #include <condition_variable>
 #include <cstring>
@@ -242,6 +243,52 @@ class Broker {
       else { used_ += (long long)v.size() - (long long)f->second.size(); f->second = std::move(v); }
     }
     return n;
+  }
+
+  // Results of one batch: HSET <prefix><uri_k> <field> "[[idx,prob],...]" for the n records whose uris are the '\n'-separated
+  // blob `uris` (as returned by read_pack); idx / val are row-major [n, k].  The result string is the reference's
+  // (PostProcessing.scala:83-92) with shortest round-trip floats, formatted here instead of once per record in Python.
+  long long hset_topn(const std::string& prefix, const std::string& field, long long n, const char* uris, long long uris_len, int k,
+                      const int* idx, const float* val) {
+    std::vector<std::string> vals((size_t)n);
+    char num[64];
+    for (long long r = 0; r < n; ++r) {                      // format outside the lock
+      std::string& v = vals[(size_t)r];
+      v.reserve(16 * (size_t)k + 4);
+      v.push_back('[');
+      for (int j = 0; j < k; ++j) {
+        if (j) v.push_back(',');
+        v.push_back('[');
+        auto r1 = std::to_chars(num, num + sizeof(num), idx[r * k + j]);
+        v.append(num, r1.ptr);
+        v.push_back(',');
+        auto r2 = std::to_chars(num, num + sizeof(num), val[r * k + j]);
+        v.append(num, r2.ptr);
+        v.push_back(']');
+      }
+      v.push_back(']');
+    }
+    std::lock_guard<std::mutex> lk(mu_);
+    ++ncmd_;
+    long long bytes = 0;
+    for (auto& v : vals) bytes += (long long)(v.size() + field.size());
+    if (maxmemory_ > 0 && used_ + bytes > maxmemory_) return -1;
+    const char* p = uris;
+    const char* end = uris + uris_len;
+    long long done = 0;
+    for (; done < n && p < end; ++done) {
+      const char* q = (const char*)memchr(p, '\n', (size_t)(end - p));
+      if (!q) q = end;
+      std::string name = prefix;
+      name.append(p, (size_t)(q - p));
+      auto& h = hashes_[name];
+      auto f = h.find(field);
+      std::string& v = vals[(size_t)done];
+      if (f == h.end()) { used_ += (long long)(field.size() + v.size()); h.emplace(field, std::move(v)); }
+      else { used_ += (long long)v.size() - (long long)f->second.size(); f->second = std::move(v); }
+      p = q + 1;
+    }
+    return done;
   }
 
   // XADD key * uri <uri_k> <field> <record_k> [extra fields...] for k in [0, n); records have a fixed length.
@@ -625,6 +672,10 @@ ZOO_RT_API long long zoo_broker_read_pack(void* b, const char* key, const char* 
 ZOO_RT_API long long zoo_broker_hset_many(void* b, const char* prefix, const char* field, long long n, const char* keys, const long long* koff,
                                           const char* vals, const long long* voff) {
   return static_cast<Broker*>(b)->hset_many(prefix, field, n, keys, koff, vals, voff);
+}
+ZOO_RT_API long long zoo_broker_hset_topn(void* b, const char* prefix, const char* field, long long n, const char* uris, long long uris_len,
+                                          int k, const int* idx, const float* val) {
+  return static_cast<Broker*>(b)->hset_topn(prefix, field, n, uris, uris_len, k, idx, val);
 }
 ZOO_RT_API long long zoo_broker_xadd_many(void* b, const char* key, long long n, const char* uris, const long long* uoff, const char* field,
                                           const char* recs, long long rec_len, int n_extra, const char* const* extra_names,

@@ -133,3 +133,32 @@ def test_crc_and_tfrecord_match_python_writer():
         assert rt.masked_crc32c(data) == w.masked_crc(data)
         assert rt.tfrecord_frame(data) == w.frame_record(data)
     assert rt.crc32c(b"123456789") == 0xE3069283
+
+
+def test_broker_native_topn_results_match_python_format():
+    import ast
+
+    import numpy as np
+
+    from zoo.native.rt import Broker
+    from zoo.ops.serving_ops import format_topn
+
+    b = Broker()
+    idx = np.array([[3, 1], [0, 2], [7, 7]], np.int32)
+    val = np.array([[0.75, 0.125], [1e-8, 0.3], [0.99999994, 123456.79]], np.float32)
+    assert b.hset_topn("result:", "value", b"a\nb/c\nlast\n", idx, val) == 3
+    for k, uri in enumerate(["a", "b/c", "last"]):
+        got = b.hgetall("result:" + uri)
+        got = {(k2.decode() if isinstance(k2, bytes) else k2): (v.decode() if isinstance(v, bytes) else v) for k2, v in got.items()}["value"]
+        parsed, want = ast.literal_eval(got), ast.literal_eval(format_topn(idx[k], val[k]))
+        assert [p[0] for p in parsed] == [w[0] for w in want]
+        np.testing.assert_allclose([p[1] for p in parsed], [w[1] for w in want], rtol=1e-7)     # shortest round-trip float32 digits
+        assert np.float32(parsed[0][1]) == val[k, 0]
+    b.config_set("maxmemory", 1)
+    import pytest
+
+    from zoo.native.rt import RespError
+
+    with pytest.raises(RespError):
+        b.hset_topn("result:", "value", b"zzz\n", idx[:1], val[:1])
+    b.close()

@@ -23,6 +23,7 @@ def rt():
             "zoo_broker_command": ([_V, _I, C.POINTER(C.c_char_p), C.POINTER(_L), C.POINTER(C.POINTER(C.c_char)), C.POINTER(_L)], _I),
             "zoo_broker_free": ([C.POINTER(C.c_char)], None),
             "zoo_broker_read_pack": ([_V, C.c_char_p, C.c_char_p, _L, _L, C.c_char_p, _V, _L, C.POINTER(_L), _V, _L, C.POINTER(_L)], _L),
+            "zoo_broker_hset_topn": ([_V, C.c_char_p, C.c_char_p, _L, _V, _L, _I, _V, _V], _L),
             "zoo_broker_hset_many": ([_V, C.c_char_p, C.c_char_p, _L, C.c_char_p, _V, C.c_char_p, _V], _L),
             "zoo_broker_xadd_many": ([_V, C.c_char_p, _L, C.c_char_p, _V, C.c_char_p, _V, _L, _I, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p)], _L),
             "zoo_arena_create": ([_I, _L, C.c_char_p], _V), "zoo_arena_destroy": ([_V], None), "zoo_arena_base": ([_V], _V),
@@ -227,7 +228,7 @@ class Broker(_Commands):
         return self._lib.zoo_broker_used_memory(self._h)
 
     # ---- batch paths (one native call per batch; used by the in-process serving engine and bulk producers) --------
-    def read_pack(self, stream, group, count, field, block_ms=5, buf=None, uri_buf=None):
+    def read_pack(self, stream, group, count, field, block_ms=5, buf=None, uri_buf=None, raw_uris=False):
         """Up to `count` new entries whose `field` values have equal length -> (n, uint8 array [n, rec_len], list of uris)."""
         if buf is None:
             buf = np.empty(64 << 20, dtype=np.uint8)
@@ -240,8 +241,20 @@ class Broker(_Commands):
             raise RespError(f"NOGROUP No such consumer group '{group}' for key '{stream}'")
         if n == 0:
             return 0, None, []
-        uris = uri_buf[:uris_len.value].tobytes().decode().split("\n")[:-1]
+        blob = uri_buf[:uris_len.value].tobytes()
+        uris = blob if raw_uris else blob.decode().split("\n")[:-1]
         return n, buf[:n * rec_len.value].reshape(n, rec_len.value), uris
+
+    def hset_topn(self, prefix, field, uris_blob: bytes, idx: np.ndarray, val: np.ndarray):
+        """Top-N results of a batch: `uris_blob` is the newline-separated uri blob of `read_pack(raw_uris=True)`, idx / val are
+        [n, k]; the "[[idx,prob],...]" strings are formatted natively."""
+        idx = np.ascontiguousarray(idx, dtype=np.int32)
+        val = np.ascontiguousarray(val, dtype=np.float32)
+        n, k = idx.shape
+        r = self._lib.zoo_broker_hset_topn(self._h, prefix.encode(), field.encode(), n, uris_blob, len(uris_blob), k, idx.ctypes.data, val.ctypes.data)
+        if r < 0:
+            raise RespError("OOM command not allowed when used memory > 'maxmemory'.")
+        return r
 
     def hset_many(self, prefix, field, keys, values):
         kb = [k.encode() if isinstance(k, str) else k for k in keys]

@@ -189,7 +189,8 @@ class ClusterServing:
         if self._pack_buf is None:
             self._pack_buf = np.empty(max(16 << 20, self.conf.batch_size * 4096), dtype=np.uint8)
             self._uri_buf = np.empty(max(1 << 20, self.conf.batch_size * 96), dtype=np.uint8)
-        n, data, uris = self.db.read_pack(INPUT_STREAM, GROUP, self.conf.batch_size, "tensor", 5, self._pack_buf, self._uri_buf)
+        n, data, uris = self.db.read_pack(INPUT_STREAM, GROUP, self.conf.batch_size, "tensor", 5, self._pack_buf, self._uri_buf,
+                                          raw_uris=True)          # the uri blob goes to the result writer undecoded
         if n == 0:
             return None
         shape, dtype = self._tensor_meta
@@ -215,10 +216,10 @@ class ClusterServing:
                         idx, val = topk(out, min(self.conf.top_n, out.shape[1], 8), softmax=False)
                         self._out_q.put((uris, "topn", (idx.cpu().numpy(), val.cpu().numpy()), t0))
                     else:
-                        self._out_q.put((uris, "raw", out.float().cpu().numpy(), t0))
+                        self._out_q.put((uris.decode().split("\n")[:-1], "raw", out.float().cpu().numpy(), t0))
                 except Exception as e:
                     log.exception("batch failed: %r", e)
-                    self._out_q.put((uris, "error", repr(e), t0))
+                    self._out_q.put((uris.decode().split("\n")[:-1], "error", repr(e), t0))
                 continue
             entries = self._read_batch(5)
             if not entries:
@@ -251,7 +252,12 @@ class ClusterServing:
             if item is None:
                 return
             uris, kind, payload, t0 = item
-            if kind == "topn":
+            packed = isinstance(uris, (bytes, bytearray))        # the undecoded uri blob of the packed batch path
+            count = uris.count(b"\n") if packed else len(uris)
+            values = None
+            if packed:
+                pass                                             # formatted natively by hset_topn
+            elif kind == "topn":
                 if payload[0].shape[1] == 1:
                     values = [f"[[{i},{v}]]" for i, v in zip(payload[0][:, 0].tolist(), payload[1][:, 0].tolist())]
                 else:
@@ -262,7 +268,9 @@ class ClusterServing:
                 values = ["NaN"] * len(uris)
             while True:          # retry forever on a full broker, every 3 s (ClusterServing.scala:276-310)
                 try:
-                    if hasattr(self.db, "hset_many"):
+                    if packed:
+                        self.db.hset_topn("result:", "value", bytes(uris), payload[0], payload[1])
+                    elif hasattr(self.db, "hset_many"):
                         self.db.hset_many("result:", "value", uris, values)
                     else:
                         for uri, value in zip(uris, values):
@@ -273,8 +281,8 @@ class ClusterServing:
                     if self._stop.wait(3):
                         break
             dt = time.perf_counter() - t0
-            self.total_records += len(uris)
-            self.latencies.append((len(uris), dt))
+            self.total_records += count
+            self.latencies.append((count, dt))
             if self.summary is not None:
                 el = max(time.perf_counter() - self._t_start, 1e-9)
                 self.summary.add_scalar("Serving Throughput", self.total_records / el, self.total_records)
