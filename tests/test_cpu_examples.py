@@ -19,6 +19,7 @@ CASES = [
     ("tfpark/gan_train.py", [], "generated radius"),
     ("tfpark/bert_classifier.py", [], "probabilities of 4 records"),
     ("ray/parameter_server.py", [], "weights after training: [1.0, 2.0, 3.0, 4.0]"),
+    ("ray/async_parameter_server.py", [], "updates applied: 180"),
     ("streaming/text_classification_stream.py", [], "200 lines classified"),
     ("imageclassification/predict.py", [], "predicted 6 images"),
     ("localestimator/lenet_local.py", [], "Top1Accuracy"),
