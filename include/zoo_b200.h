@@ -47,6 +47,13 @@ int zoo_dense_wgrad_bias_bf16(const void* dy, long long lddy, const void* x, lon
                               long long lddw, float* db, int M, int N, int K, void* stream);
 int zoo_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* out, void* stream);
 
+/* ---- K8: blockwise attention forward (csrc/ops/attention.cu) ---------------------------------
+ * out[B,H,L,64] = softmax(scale * q k^T + mask[b,key] (+causal)) v; q, k, v, out contiguous bf16 [B,H,L,64]; mask additive
+ * fp32 [B,L] or null.  Head dimension 64 only.  Not yet validated on hardware (see the file header); opt in with
+ * ZOO_ATTN_KERNEL=1 on the Python side. */
+int zoo_attention_fwd_bf16(const void* q, const void* k, const void* v, void* out, const float* mask, int B, int H, int L, int D,
+                           float scale, int causal, void* stream);
+
 /* ---- K2/K4: embedding gather and sparse optimizer (csrc/ops/embedding.cu) --------------------
  * Replaces LookupTable / LookupTableSparse inside zoo Embedding / SparseEmbedding
  * (zoo/.../pipeline/api/keras/layers/Embedding.scala:82-101, SparseEmbedding.scala:76-89).

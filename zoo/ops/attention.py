@@ -3,12 +3,15 @@
 Reference: TransformerLayer.scala:163-181 materialises `[batch, heads, L, L]` scores (`mm(q,k)` -> mask ->
 softmax -> dropout -> `mm(w,v)`).  Here one fused call is used: blockwise (flash-style) attention through
 torch's SDPA on the GPU, which never writes the L x L matrix; the explicit reference math is kept as
-`attention_reference` (CPU path and oracle).  A hand-written tcgen05 kernel for this op is the K8 stretch
-item of SURVEY section 8; until it lands this op counts as a library call.
+`attention_reference` (CPU path and oracle).  The hand-written tcgen05 kernel for this op (K8, csrc/ops/attention.cu: forward,
+head dimension 64, key-padding mask and causal) was written after round 1's GPU budget was spent and has not run on hardware
+yet: it is taken only with ZOO_ATTN_KERNEL=1 and only for inference calls; until it is validated this op counts as a library
+call.
 """
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 import torch.nn.functional as F
@@ -31,9 +34,36 @@ def attention_reference(q, k, v, additive_mask=None, causal=False, scale=True, d
     return torch.matmul(w, v)
 
 
+def attention_kernel(q, k, v, key_mask=None, causal=False, scale=True):
+    """K8 forward.  q, k, v: [B, H, L, 64] (any float dtype; computed in bf16); key_mask: additive [B, L] or None."""
+    from ..native import lib as _nl
+
+    B, H, L, D = q.shape
+    q16, k16, v16 = (t.to(torch.bfloat16).contiguous() for t in (q, k, v))
+    out = torch.empty_like(q16)
+    km = None if key_mask is None else key_mask.to(torch.float32).contiguous()
+    _nl.check(_nl.cuda_lib().zoo_attention_fwd_bf16(q16.data_ptr(), k16.data_ptr(), v16.data_ptr(), out.data_ptr(), _nl.ptr(km), B, H, L, D,
+                                                    (1.0 / math.sqrt(D)) if scale else 1.0, int(causal), _nl.stream_ptr()), "zoo_attention_fwd_bf16")
+    return out.to(q.dtype)
+
+
+def _kernel_eligible(q, additive_mask, dropout_p, training):
+    if os.environ.get("ZOO_ATTN_KERNEL", "0") != "1" or q.shape[-1] != 64 or (dropout_p > 0 and training):
+        return False
+    if torch.is_grad_enabled() and q.requires_grad:
+        return False                      # forward only: training goes through SDPA
+    if additive_mask is None:
+        return True
+    m = additive_mask                     # only key-padding masks [B, 1, 1, L] (or [B, L]) map onto the kernel
+    return (m.dim() == 4 and m.shape[1] == 1 and m.shape[2] == 1 and m.shape[0] == q.shape[0]) or (m.dim() == 2 and m.shape[0] == q.shape[0])
+
+
 def attention(q, k, v, additive_mask=None, causal=False, scale=True, dropout_p=0.0, training=False):
     if not q.is_cuda:
         return attention_reference(q, k, v, additive_mask, causal, scale, dropout_p, training)
+    if _kernel_eligible(q, additive_mask, dropout_p, training):
+        km = None if additive_mask is None else additive_mask.reshape(additive_mask.shape[0], -1)
+        return attention_kernel(q, k, v, km, causal, scale)
     mask = None
     if additive_mask is not None:
         mask = additive_mask.to(q.dtype)
