@@ -88,7 +88,7 @@ class ServingConfig:
 class ClusterServing:
     def __init__(self, config="config.yaml", model=None, broker=None, device=None, serve_socket=False, consumer=None,
                  decode_threads=None, **overrides):
-        self.conf = ServingConfig(config, **overrides)
+        self.conf = config if isinstance(config, ServingConfig) else ServingConfig(config, **overrides)
         self.device = torch.device(device) if device is not None else torch.device("cuda" if torch.cuda.is_available() else "cpu")
         self.owns_broker = broker is None
         self.db = broker if broker is not None else Broker(self.conf.maxmem)
@@ -351,9 +351,13 @@ def main(argv=None):
 
     ap = argparse.ArgumentParser()
     ap.add_argument("-c", "--config", default="config.yaml")
+    ap.add_argument("--port", type=int, default=None, help="RESP listener port (overrides data.src of the config; one per GPU process)")
     a = ap.parse_args(argv)
     logging.basicConfig(level=logging.INFO, filename="cluster-serving.log")
-    ClusterServing(a.config, serve_socket=True).serve_forever()
+    conf = ServingConfig(a.config)
+    if a.port is not None:
+        conf.port = a.port
+    ClusterServing(conf, serve_socket=True).serve_forever()
 
 
 if __name__ == "__main__":
