@@ -44,7 +44,8 @@ class P2PFusedSync:
         return max(8, 4 * self.ctx.world_size)
 
     def graph_safe(self):
-        return True
+        f = getattr(self, "fopt", None)
+        return f is None or (f.clip_l2 is None and f.clip_const is None)      # the clipping fallback calls NCCL: no capture
 
     def attach(self, fopt):
         self.fopt = fopt
@@ -105,7 +106,13 @@ class P2PFusedSync:
     def step(self):
         f = self.fopt
         if f.clip_l2 is not None or f.clip_const is not None:
-            raise NotImplementedError("gradient clipping with the fused P2P exchange: use grad_sync='nccl'")
+            # clipping needs the global gradient norm / clamp BEFORE the update, which the owner-computes kernel does not
+            # have: take the library all-reduce + local fused optimizer for this step (same arenas, same optimizer state)
+            import torch.distributed as dist
+
+            dist.all_reduce(f.arena.flat_g)
+            f.step()
+            return
         f.step_count += 1
         f._apply_schedules()
         refresh = f._sync_hyper()
