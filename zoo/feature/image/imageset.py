@@ -59,20 +59,32 @@ class ImageSet:
             files = sorted(f for f in glob.glob(os.path.join(path, "**", "*"), recursive=True) if f.lower().endswith(IMG_EXT))
         else:
             files = sorted(glob.glob(path))
-        feats = []
-        for i, f in enumerate(files):
+        codec = cv2.IMREAD_COLOR if image_codec in (-1, 1) else image_codec
+
+        def load(i):
+            f = files[i]
             with open(f, "rb") as fh:
                 raw = fh.read()
-            mat = cv2.imdecode(np.frombuffer(raw, np.uint8), cv2.IMREAD_COLOR if image_codec in (-1, 1) else image_codec)
+            mat = cv2.imdecode(np.frombuffer(raw, np.uint8), codec)
             if mat is None:
-                continue
+                return None
             feat = ImageFeature(uri=f, bytes=raw, originalSize=mat.shape)
             if resize_height > 0 and resize_width > 0:
                 mat = cv2.resize(mat, (resize_width, resize_height))
             feat["mat"] = mat
             if with_label:
                 feat["label"] = np.array([labels[i]], dtype=np.float32)
-            feats.append(feat)
+            return feat
+
+        # decode on a thread pool (cv2 releases the GIL): the reference parallelises over Spark partitions (`min_partitions`)
+        workers = max(1, min(16, os.cpu_count() or 1, len(files)))
+        if workers > 1 and len(files) >= 8:
+            from concurrent.futures import ThreadPoolExecutor
+
+            with ThreadPoolExecutor(workers) as pool:
+                feats = [f for f in pool.map(load, range(len(files))) if f is not None]
+        else:
+            feats = [f for f in map(load, range(len(files))) if f is not None]
         return cls(feats, label_map)
 
     @classmethod
