@@ -125,7 +125,8 @@ def build_ncf(args, ctx, torch):
 def main():
     args = parse()
     if args.impl == "reference":
-        print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
+        if int(os.environ.get("RANK", "0")) == 0:         # one line per job, also under torchrun
+            print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
         return 0
     import torch
 
