@@ -304,3 +304,20 @@ def test_layer_serializer_roundtrip(idx, tmp_path):
         got = m2(x)
     torch.testing.assert_close(got, want)
     assert [tuple(p.shape) for p in m2.parameters()] == [tuple(p.shape) for p in m.parameters()]
+
+
+@pytest.mark.parametrize("L,causal,masked", [(77, False, False), (300, True, False), (300, False, True), (130, True, True)])
+def test_blockwise_attention_restatement_matches_dense_attention(L, causal, masked):
+    """The algorithm of the K8 kernel (online softmax over key blocks, bf16 probabilities) against the reference's dense attention."""
+    from zoo.ops.attention import attention_blockwise_reference, attention_reference
+
+    torch.manual_seed(L)
+    q, k, v = (torch.randn(2, 2, L, 64).to(torch.bfloat16) for _ in range(3))
+    km = None
+    if masked:
+        keep = torch.rand(2, L) > 0.2
+        keep[:, 0] = True
+        km = (1.0 - keep.float()) * -10000.0
+    got = attention_blockwise_reference(q, k, v, km, causal)
+    want = attention_reference(q.float(), k.float(), v.float(), None if km is None else km[:, None, None, :], causal)
+    torch.testing.assert_close(got, want, atol=1e-2, rtol=1e-2)

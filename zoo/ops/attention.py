@@ -34,6 +34,45 @@ def attention_reference(q, k, v, additive_mask=None, causal=False, scale=True, d
     return torch.matmul(w, v)
 
 
+def attention_blockwise_reference(q, k, v, key_mask=None, causal=False, scale=True, block=128):
+    """The K8 kernel's algorithm restated in torch (CPU oracle for debugging it): 128-query tiles walk the keys in blocks of
+    `block`; scores in the log2 domain, running maximum m, running sum l, output rescaled by alpha = 2^(m_old - m_new); the
+    probabilities are rounded to bf16 before the second product, as the kernel feeds them to the tensor core; keys beyond L or
+    above the diagonal get probability 0; a row with no live key yields zeros."""
+    B, H, L, D = q.shape
+    log2e = 1.4426950408889634
+    sc = ((1.0 / math.sqrt(D)) if scale else 1.0) * log2e
+    out = torch.zeros(B, H, L, D, dtype=torch.float32, device=q.device)
+    qf, kf, vf = q.float(), k.float(), v.float()
+    for q0 in range(0, L, 128):
+        q1 = min(L, q0 + 128)
+        rows = q1 - q0
+        o = torch.zeros(B, H, rows, D, device=q.device)
+        m = torch.full((B, H, rows), float("-inf"), device=q.device)
+        l = torch.zeros(B, H, rows, device=q.device)
+        qi = torch.arange(q0, q1, device=q.device)
+        n_blocks = (L + block - 1) // block
+        if causal:
+            n_blocks = min(n_blocks, (q0 + 128 + block - 1) // block)
+        for j in range(n_blocks):
+            k0, k1 = j * block, min(L, (j + 1) * block)
+            s = (qf[:, :, q0:q1] @ kf[:, :, k0:k1].transpose(-1, -2)) * sc
+            if key_mask is not None:
+                s = s + key_mask[:, None, None, k0:k1].float() * log2e
+            if causal:
+                key = torch.arange(k0, k1, device=q.device)
+                s = s.masked_fill(key[None, :] > qi[:, None], float("-inf"))
+            m_new = torch.maximum(m, s.max(-1).values)
+            alpha = torch.where(torch.isinf(m) & (m < 0), torch.zeros_like(m), torch.exp2(m - m_new))
+            m_use = torch.where(torch.isinf(m_new), torch.zeros_like(m_new), m_new)
+            p = torch.exp2(s - m_use[..., None])
+            l = l * alpha + p.sum(-1)
+            o = o * alpha[..., None] + p.to(torch.bfloat16).float() @ vf[:, :, k0:k1]
+            m = m_new
+        out[:, :, q0:q1] = o * torch.where(l > 0, 1.0 / l, torch.zeros_like(l))[..., None]
+    return out
+
+
 def attention_kernel(q, k, v, key_mask=None, causal=False, scale=True):
     """K8 forward.  q, k, v: [B, H, L, 64] (any float dtype; computed in bf16); key_mask: additive [B, L] or None."""
     from ..native import lib as _nl
