@@ -144,3 +144,95 @@ def test_onnx_run_node(op, ins, attrs, ref):
 
     out = OnnxLoader.run_node(_node(op, [f"i{k}" for k in range(len(ins))], ["o"], **attrs), ins)[0]
     np.testing.assert_allclose(out, ref(*ins), atol=1e-6)
+
+
+def test_tfrecord_examples_roundtrip_and_dataset(tmp_path):
+    import struct
+
+    from zoo.tfpark import TFDataset
+    from zoo.tfpark.tfrecord import decode_example, encode_example, read_examples, read_tfrecord, write_tfrecord
+
+    rng = np.random.RandomState(0)
+    recs = [{"x": rng.randn(6).astype(np.float32), "label": np.int64(i % 3), "ids": np.array([-1, 2 ** 40, i], np.int64), "name": f"r{i}",
+             "blob": [b"\\x00\\x01", b""]} for i in range(25)]
+    ex = decode_example(encode_example(recs[3]))
+    np.testing.assert_allclose(ex["x"], recs[3]["x"])
+    assert ex["label"].tolist() == [0] and ex["ids"].tolist() == [-1, 2 ** 40, 3] and ex["name"] == [b"r3"] and ex["blob"] == [b"\\x00\\x01", b""]
+    path = str(tmp_path / "data.tfrecord")
+    assert write_tfrecord(path, recs) == 25
+    assert write_tfrecord(path, [b"raw-payload"], append=True) == 1
+    payloads = list(read_tfrecord(path))
+    assert len(payloads) == 26 and payloads[-1] == b"raw-payload"
+    # the framing is TensorFlow's: u64 length, masked crc of the length, payload, masked crc of the payload
+    raw = open(path, "rb").read()
+    assert struct.unpack("<Q", raw[:8])[0] == len(payloads[0])
+    # corruption is detected
+    bad = bytearray(raw); bad[20] ^= 0xFF
+    (tmp_path / "bad.tfrecord").write_bytes(bytes(bad))
+    with pytest.raises(IOError):
+        list(read_tfrecord(str(tmp_path / "bad.tfrecord")))
+    (tmp_path / "short.tfrecord").write_bytes(raw[:-3])
+    with pytest.raises(IOError):
+        list(read_tfrecord(str(tmp_path / "short.tfrecord")))
+    write_tfrecord(str(tmp_path / "train.tfrecord"), recs)
+    ds = TFDataset.from_tfrecord_file(None, str(tmp_path / "train.tfrecord"), batch_size=5, features="x", labels="label")
+    assert len(ds) == 25
+    xs = np.stack([e["x"] for e in read_examples(str(tmp_path / "train*.tfrecord"))])
+    np.testing.assert_allclose(xs, np.stack([r["x"] for r in recs]))
+    m = nn.Sequential(nn.Linear(6, 3))
+    from zoo.tfpark import KerasModel
+
+    km = KerasModel(m, optimizer="adam", loss="sparse_categorical_crossentropy")
+    km.fit(ds, epochs=1)
+
+
+def test_example_wire_format_matches_protobuf():
+    """The hand-written Example codec against google.protobuf with the tf.train.Example schema built at run time."""
+    pb = pytest.importorskip("google.protobuf")
+    from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+
+    from zoo.tfpark.tfrecord import decode_example, encode_example
+
+    f = descriptor_pb2.FileDescriptorProto(name="zoo_example_test.proto", package="zoo_t", syntax="proto3")
+    T = descriptor_pb2.FieldDescriptorProto
+
+    def msg(name, fields):
+        m = f.message_type.add(name=name)
+        for fname, num, typ, label, tname, oneof in fields:
+            fd = m.field.add(name=fname, number=num, type=typ, label=label)
+            if tname:
+                fd.type_name = tname
+            if oneof is not None:
+                fd.oneof_index = oneof
+        return m
+
+    msg("BytesList", [("value", 1, T.TYPE_BYTES, T.LABEL_REPEATED, None, None)])
+    msg("FloatList", [("value", 1, T.TYPE_FLOAT, T.LABEL_REPEATED, None, None)])
+    msg("Int64List", [("value", 1, T.TYPE_INT64, T.LABEL_REPEATED, None, None)])
+    feat = msg("Feature", [("bytes_list", 1, T.TYPE_MESSAGE, T.LABEL_OPTIONAL, ".zoo_t.BytesList", 0),
+                           ("float_list", 2, T.TYPE_MESSAGE, T.LABEL_OPTIONAL, ".zoo_t.FloatList", 0),
+                           ("int64_list", 3, T.TYPE_MESSAGE, T.LABEL_OPTIONAL, ".zoo_t.Int64List", 0)])
+    feat.oneof_decl.add(name="kind")
+    feats = msg("Features", [("feature", 1, T.TYPE_MESSAGE, T.LABEL_REPEATED, ".zoo_t.Features.FeatureEntry", None)])
+    entry = feats.nested_type.add(name="FeatureEntry")
+    entry.field.add(name="key", number=1, type=T.TYPE_STRING, label=T.LABEL_OPTIONAL)
+    entry.field.add(name="value", number=2, type=T.TYPE_MESSAGE, label=T.LABEL_OPTIONAL, type_name=".zoo_t.Feature")
+    entry.options.map_entry = True
+    msg("Example", [("features", 1, T.TYPE_MESSAGE, T.LABEL_OPTIONAL, ".zoo_t.Features", None)])
+    pool = descriptor_pool.DescriptorPool()
+    pool.Add(f)
+    Example = message_factory.GetMessageClass(pool.FindMessageTypeByName("zoo_t.Example"))
+
+    ours = encode_example({"x": np.array([1.5, -2.0], np.float32), "n": np.array([3, -7, 2 ** 35], np.int64), "s": [b"ab", b"c"]})
+    theirs = Example()
+    theirs.ParseFromString(ours)
+    assert list(theirs.features.feature["x"].float_list.value) == [1.5, -2.0]
+    assert list(theirs.features.feature["n"].int64_list.value) == [3, -7, 2 ** 35]
+    assert list(theirs.features.feature["s"].bytes_list.value) == [b"ab", b"c"]
+    e = Example()
+    e.features.feature["img"].bytes_list.value.append(b"\\xff\\xd8jpeg")
+    e.features.feature["y"].int64_list.value.extend([5, -1])
+    e.features.feature["w"].float_list.value.extend([0.25, 4.0, 1e-3])
+    got = decode_example(e.SerializeToString())
+    assert got["img"] == [b"\\xff\\xd8jpeg"] and got["y"].tolist() == [5, -1]
+    np.testing.assert_allclose(got["w"], [0.25, 4.0, 1e-3], rtol=1e-6)

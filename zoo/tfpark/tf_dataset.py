@@ -1,6 +1,7 @@
 """TFDataset (reference: pyzoo/zoo/tfpark/tf_dataset.py:115-1179): the 11 constructors of the reference, producing a
 batched, rank-shardable data set.  Here it wraps a `FeatureSet`; `batch_size` is the global training batch,
-`batch_per_thread` the inference batch, exactly one of them (tf_dataset.py:160-178)."""
+`batch_per_thread` the inference batch, exactly one of them (tf_dataset.py:160-178).  TFRecord files of tf.train.Example
+records are read natively (`zoo.tfpark.tfrecord`); only `from_tf_data_dataset` needs TensorFlow itself."""
 from __future__ import annotations
 
 import numpy as np
@@ -81,8 +82,30 @@ class TFDataset:
                                   "zoo-b200; load the data into ndarrays and use from_ndarrays / from_feature_set")
 
     @staticmethod
-    def from_tfrecord_file(*a, **kw):
-        TFDataset._needs_tf("from_tfrecord_file")
+    def from_tfrecord_file(sc=None, file_path=None, batch_size=-1, batch_per_thread=-1, hard_code_batch_size=False, validation_file_path=None,
+                           features=None, labels=None, image_decoder=None, **kw):
+        """TFRecord files of tf.train.Example records (read natively, `zoo.tfpark.tfrecord`).  The reference returns the serialized
+        strings for a TF parsing graph; here `features` / `labels` name the Example features that become the dataset's tensors
+        (all features except `labels` when `features` is None)."""
+        from .tfrecord import examples_to_arrays, read_examples
+
+        if file_path is None and isinstance(sc, str):      # from_tfrecord_file(path, ...) without a SparkContext
+            sc, file_path = None, sc
+
+        def load(path):
+            exs = list(read_examples(path))
+            if not exs:
+                raise ValueError(f"no records in {path}")
+            lab = [] if labels is None else ([labels] if isinstance(labels, str) else list(labels))
+            feats = features if features is not None else sorted(k for k in exs[0] if k not in lab)
+            return examples_to_arrays(exs, feats, labels, image_decoder)
+
+        x, y = load(file_path)
+        val = None
+        if validation_file_path is not None:
+            vx, vy = load(validation_file_path)
+            val = FeatureSet.numpy(vx, vy)
+        return TFDataset(FeatureSet.numpy(x, y), batch_size, batch_per_thread, hard_code_batch_size, val)
 
     @staticmethod
     def from_tf_data_dataset(*a, **kw):
