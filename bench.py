@@ -201,7 +201,7 @@ def main():
 
         def on_step(it, loss_t):
             k = marks.setdefault("n", 0)
-            if k == Wm:
+            if k == Wm - 1:      # called after step k+1 was issued: exactly Wm warm-up steps lie before t0, K steps after it
                 torch.cuda.synchronize(); barrier(); marks["t0"] = time.time()
             marks["n"] = k + 1
             if os.environ.get("ZOO_BENCH_TRACE"):

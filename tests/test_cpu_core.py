@@ -349,3 +349,13 @@ def test_gloo_world2_ncf():
            "--master-port", "29533", os.path.join(ROOT, "tests", "workers", "gloo_ncf_worker.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
     assert r.returncode == 0 and "GLOO_NCF_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def test_gloo_world2_clip_and_retry():
+    """ADVICE r1 (clipping on the averaged gradient) and VERDICT r1 #9 (distributed retry from the newest checkpoint)."""
+    env = dict(os.environ, ZOO_FORCE_CPU="1", OMP_NUM_THREADS="2")
+    env.pop("ZOO_FAULT_INJECT", None)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29534", os.path.join(ROOT, "tests", "workers", "gloo_retry_clip_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert r.returncode == 0 and "GLOO_RETRY_CLIP_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

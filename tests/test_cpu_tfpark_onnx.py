@@ -40,8 +40,8 @@ def test_tfdataset_and_keras_model(tmp_path):
     assert rdd.get_training_data().size() == 50
     df = pd.DataFrame({"f": list(x[:40]), "l": y[:40]})
     assert len(TFDataset.from_dataframe(df, ["f"], ["l"], batch_size=8)) == 40
-    with pytest.raises(NotImplementedError):
-        TFDataset.from_tfrecord_file("x")
+    with pytest.raises(FileNotFoundError):      # the reader is real (zoo/tfpark/tfrecord.py); a missing file is an IO error
+        TFDataset.from_tfrecord_file(str(tmp_path / "missing.tfrecord"))
     net = Sequential([Dense(16, activation="relu", input_shape=(6,)), Dense(2, activation="softmax")])
     net.compile(optimizer="adam", loss="sparse_categorical_crossentropy", metrics=["accuracy"])
     km = KerasModel(net)

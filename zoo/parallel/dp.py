@@ -90,10 +90,14 @@ def make_grad_sync(ctx, mode="auto"):
     if mode in ("nccl", "gloo", "allreduce"):
         return AllReduceSync(ctx)
     if mode == "p2p":
-        try:
-            from .p2p import P2PFusedSync
+        # No silent fallback: a job that asked for (or defaulted to) the fused peer-memory path and cannot have it must not
+        # quietly run on the library all-reduce and still report itself as the product path.  Select the baseline explicitly
+        # with ZOO_COMM_BACKEND=nccl / conf zoo.comm.backend=nccl.
+        from .p2p import P2PFusedSync
 
+        try:
             return P2PFusedSync(ctx)
-        except Exception as e:  # peer access unavailable (e.g. GPUs without NVLink/P2P)
-            log.warning("P2P fused gradient path unavailable (%r); using the NCCL baseline path", e)
-    return AllReduceSync(ctx)
+        except Exception as e:
+            raise RuntimeError(f"the fused P2P gradient path could not be set up ({e!r}); set ZOO_COMM_BACKEND=nccl to run "
+                               "on the NCCL all-reduce baseline instead") from e
+    raise ValueError(f"unknown gradient-exchange backend {mode!r} (auto | p2p | nccl | gloo)")

@@ -312,13 +312,17 @@ class FusedOptimizer:
 
     # -- the step ---------------------------------------------------------------
     def clip_gradients(self):
+        """Clipping acts on the AVERAGED gradient (the reference divides the aggregated gradient by the replica count before
+        its clipping processors run).  `flat_g` holds the SUM over ranks and 1/world is applied later inside the optimizer
+        kernel (`grad_scale`), so the thresholds are expressed on the sum: bounds and norm limit divided by `grad_scale`."""
         a = self.arena
+        gs = self.grad_scale if self.grad_scale > 0 else 1.0
         if self.clip_const is not None:
+            lo, hi = self.clip_const[0] / gs, self.clip_const[1] / gs
             if a.device.type == "cuda":
-                _nl.check(_nl.cuda_lib().zoo_clip_const(a.flat_g.data_ptr(), a.numel, self.clip_const[0], self.clip_const[1],
-                                                        _nl.stream_ptr()), "zoo_clip_const")
+                _nl.check(_nl.cuda_lib().zoo_clip_const(a.flat_g.data_ptr(), a.numel, lo, hi, _nl.stream_ptr()), "zoo_clip_const")
             else:
-                a.flat_g.clamp_(self.clip_const[0], self.clip_const[1])
+                a.flat_g.clamp_(lo, hi)
         elif self.clip_l2 is not None:
             if a.device.type == "cuda":
                 lib = _nl.cuda_lib()
@@ -326,12 +330,12 @@ class FusedOptimizer:
                     self._norm_scratch = torch.zeros(int(lib.zoo_sumsq_scratch_bytes()), dtype=torch.uint8, device=a.device)
                 _nl.check(lib.zoo_sumsq(a.flat_g.data_ptr(), a.numel, self._norm_scratch.data_ptr(), self.sumsq.data_ptr(), 0,
                                         _nl.stream_ptr()), "zoo_sumsq")
-                _nl.check(lib.zoo_clip_l2(a.flat_g.data_ptr(), a.numel, self.sumsq.data_ptr(), self.clip_l2, _nl.stream_ptr()),
+                _nl.check(lib.zoo_clip_l2(a.flat_g.data_ptr(), a.numel, self.sumsq.data_ptr(), self.clip_l2 / gs, _nl.stream_ptr()),
                           "zoo_clip_l2")
             else:
                 norm = a.flat_g.norm()
-                if norm > self.clip_l2:
-                    a.flat_g.mul_(self.clip_l2 / (norm + 1e-6))
+                if norm > self.clip_l2 / gs:
+                    a.flat_g.mul_((self.clip_l2 / gs) / (norm + 1e-6))
 
     def step(self, zero_grad=True):
         a = self.arena

@@ -126,5 +126,24 @@ class P2PFusedSync:
                                         g.start, g.end, W, r, 0, OPT_IDS[g.cfg.name], 1 | (2 if rep else 0),
                                         self._grid_for(g.end - g.start, rep), st), "zoo_rs_opt_ag")
 
+    def gather_optimizer_state(self):
+        """Owner-computes ranges keep m / v only on the rank that owns a shard; before a checkpoint every rank's copy is made
+        complete (collective, NCCL -- checkpoint time, not the step)."""
+        import torch.distributed as dist
+
+        f, W, r = self.fopt, self.ctx.world_size, self.ctx.rank
+        for g in f.groups:
+            n = g.end - g.start
+            if self._replicated(n):
+                continue
+            shard = n // W
+            for t in (f.m, f.v):
+                if t is None:
+                    continue
+                full = t[g.start:g.end]
+                own = full[r * shard:(r + 1) * shard].clone()
+                dist.all_gather_into_tensor(full, own)
+        torch.cuda.synchronize()
+
     def close(self):
         pass

@@ -28,6 +28,7 @@ from __future__ import annotations
 import glob
 import logging
 import os
+import re
 import time
 from datetime import datetime
 
@@ -280,6 +281,12 @@ class TrainingEngine:
         if self.model_dir is None or self.run_dir is not None:
             return
         ts = datetime.now().strftime("%Y-%m-%d_%H-%M-%S")
+        if self.ctx.world_size > 1:      # one run directory per job: rank 0's timestamp
+            import torch.distributed as dist
+
+            box = [ts]
+            dist.broadcast_object_list(box, src=0)
+            ts = box[0]
         self.run_dir = os.path.join(self.model_dir, ts)
         if self.ckpt_dir is None:
             self.set_checkpoint(os.path.join(self.run_dir, "models"))
@@ -291,19 +298,46 @@ class TrainingEngine:
         gname = lambda g: "optimMethod-" + (type(self.model).__name__ if g.name == "None" else g.name)
         return os.path.join(self.ckpt_dir, f"model.{neval}"), [os.path.join(self.ckpt_dir, f"{gname(g)}.{neval}") for g in self.fopt.groups]
 
+    def _sharded_tables(self):
+        from ..ops.embedding import EmbeddingTable
+
+        return [(n, m) for n, m in self.model.named_modules() if isinstance(m, EmbeddingTable) and m.world > 1]
+
     def save_checkpoint(self):
-        if self.ckpt_dir is None or self.ctx.rank != 0:
+        """Write `model.<neval>` + `optimMethod-<name>.<neval>` (rank 0) and, when tables are row-sharded, one
+        `model.<neval>.shard-<r>-of-<W>` per rank with that rank's rows and their optimizer state.  Collective when
+        world_size > 1: every rank must call it (the owner-computes optimizer state is gathered first)."""
+        if self.ckpt_dir is None:
             return None
+        ctx, W = self.ctx, self.ctx.world_size
         neval = self.state["neval"] - 1
         mpath, opaths = self._ckpt_paths(neval)
-        if self.overwrite_checkpoint:
+        sharded = self._sharded_tables()
+        if W > 1 and hasattr(self._dp, "gather_optimizer_state"):
+            self._dp.gather_optimizer_state()       # K1 keeps m / v of a range only on its owner: make rank 0's copy complete
+        if ctx.rank == 0 and self.overwrite_checkpoint:
             for f in glob.glob(os.path.join(self.ckpt_dir, "model.*")) + glob.glob(os.path.join(self.ckpt_dir, "optimMethod-*")):
                 os.remove(f)
-        torch.save({"model": {k: v.detach().cpu() for k, v in self.model.state_dict().items()},
-                    "sparse": self._sparse_state(), "state": dict(self.state)}, mpath)
-        osd = self.fopt.state_dict()
-        for g, p in zip(self.fopt.groups, opaths):
-            torch.save({"group": g.name, "range": (g.start, g.end), "optim": osd}, p)
+        if W > 1:
+            ctx.barrier()                           # old files are gone before any rank writes its shard
+        skip = {f"{n}.weight" if n else "weight" for n, _ in sharded}
+        if sharded:
+            blob = {}
+            for n, m in sharded:
+                m._ensure_state()
+                blob[n] = {"weight": m.weight.detach().cpu(), "rows_local": m.rows_local, "num_embeddings": m.num_embeddings,
+                           "exp_avg": None if m.exp_avg is None else m.exp_avg.cpu(),
+                           "exp_avg_sq": None if m.exp_avg_sq is None else m.exp_avg_sq.cpu(), "hyper": m.hyper.cpu()}
+            torch.save({"world": W, "rank": ctx.rank, "tables": blob}, f"{mpath}.shard-{ctx.rank}-of-{W}")
+        if ctx.rank == 0:
+            torch.save({"model": {k: v.detach().cpu() for k, v in self.model.state_dict().items() if k not in skip},
+                        "sparse": self._sparse_state(), "state": dict(self.state), "world": W,
+                        "sharded_tables": [n for n, _ in sharded]}, mpath)
+            osd = self.fopt.state_dict()
+            for g, p in zip(self.fopt.groups, opaths):
+                torch.save({"group": g.name, "range": (g.start, g.end), "optim": osd}, p)
+        if W > 1:
+            ctx.barrier()                           # the checkpoint is complete on disk before anyone trains on
         return mpath
 
     def _sparse_state(self):
@@ -311,27 +345,51 @@ class TrainingEngine:
 
         out = {}
         for n, m in self.model.named_modules():
-            if isinstance(m, EmbeddingTable) and m.fused_sparse and m._state_ready:
+            if isinstance(m, EmbeddingTable) and m.world == 1 and m.fused_sparse and m._state_ready:
                 out[n] = {"exp_avg": None if m.exp_avg is None else m.exp_avg.cpu(),
                           "exp_avg_sq": None if m.exp_avg_sq is None else m.exp_avg_sq.cpu(), "hyper": m.hyper.cpu()}
         return out
 
+    @staticmethod
+    def _model_files(d):
+        return [f for f in glob.glob(os.path.join(d, "model.*")) if re.fullmatch(r"model\.\d+", os.path.basename(f))]
+
     def latest_checkpoint(self):
         if self.ckpt_dir is None:
             return None
-        files = [f for f in glob.glob(os.path.join(self.ckpt_dir, "model.*"))]
-        return max(files, key=os.path.getmtime) if files else None
+        files = self._model_files(self.ckpt_dir)
+        return max(files, key=lambda f: (os.path.getmtime(f), int(f.rsplit(".", 1)[-1]))) if files else None
+
+    def find_resume_checkpoint(self):
+        """Newest `model.<n>` under any earlier run directory of `model_dir` (used when a restarted job resumes)."""
+        if self.model_dir is None or not os.path.isdir(self.model_dir):
+            return None
+        files = []
+        for d in glob.glob(os.path.join(self.model_dir, "*", "models")):
+            files += self._model_files(d)
+        return max(files, key=lambda f: (os.path.getmtime(f), int(f.rsplit(".", 1)[-1]))) if files else None
 
     def load_checkpoint(self, path=None):
+        """Restore model, optimizer state and trigger state.  Collective when world_size > 1: every rank loads the replicated
+        part from `model.<n>` and its OWN row shard from `model.<n>.shard-<rank>-of-<world>`."""
         path = path or self.latest_checkpoint()
         if path is None:
             raise FileNotFoundError("no checkpoint to load")
         self.prepare()
+        ctx, W = self.ctx, self.ctx.world_size
         blob = torch.load(path, map_location="cpu", weights_only=False)
+        sharded = self._sharded_tables()
+        saved_sharded = blob.get("sharded_tables", [])
+        if sharded or saved_sharded:
+            if blob.get("world", 1) != W or sorted(saved_sharded) != sorted(n for n, _ in sharded):
+                raise ValueError(f"checkpoint {path} was written with world_size={blob.get('world', 1)} and sharded tables "
+                                 f"{saved_sharded}; this job has world_size={W} and {[n for n, _ in sharded]} (re-sharding a "
+                                 "checkpoint across a different number of GPUs is not supported)")
+        skip = {f"{n}.weight" if n else "weight" for n, _ in sharded}
         with torch.no_grad():
             own = self.model.state_dict()
             for k, v in blob["model"].items():
-                if k in own:
+                if k in own and k not in skip:
                     own[k].copy_(v)
         neval = path.rsplit(".", 1)[-1]
         ofiles = sorted(glob.glob(os.path.join(os.path.dirname(path), f"optimMethod-*.{neval}")))
@@ -339,8 +397,27 @@ class TrainingEngine:
             self.fopt.load_state_dict(torch.load(ofiles[0], map_location="cpu", weights_only=False)["optim"])
         from ..ops.embedding import EmbeddingTable
 
+        if sharded:
+            sp = f"{path}.shard-{ctx.rank}-of-{W}"
+            if not os.path.exists(sp):
+                raise FileNotFoundError(f"row-shard file {sp} of the checkpoint is missing")
+            sb = torch.load(sp, map_location="cpu", weights_only=False)["tables"]
+            with torch.no_grad():
+                for n, m in sharded:
+                    st = sb[n]
+                    if st["rows_local"] != m.rows_local or st["num_embeddings"] != m.num_embeddings:
+                        raise ValueError(f"shard of table {n} has {st['rows_local']} rows, expected {m.rows_local}")
+                    m._ensure_state()
+                    m.weight.data.copy_(st["weight"])
+                    if st["exp_avg"] is not None and m.exp_avg is not None:
+                        m.exp_avg.copy_(st["exp_avg"])
+                    if st["exp_avg_sq"] is not None and m.exp_avg_sq is not None:
+                        m.exp_avg_sq.copy_(st["exp_avg_sq"])
+                    m.hyper.copy_(st["hyper"])
+            for n, m in sharded:
+                m.refresh_shadow()                  # collective: peers never gather a half-restored shard
         for n, m in self.model.named_modules():
-            if isinstance(m, EmbeddingTable) and n in blob.get("sparse", {}):
+            if isinstance(m, EmbeddingTable) and m.world == 1 and n in blob.get("sparse", {}):
                 m._ensure_state()
                 st = blob["sparse"][n]
                 if st["exp_avg"] is not None:
@@ -348,10 +425,17 @@ class TrainingEngine:
                 if st["exp_avg_sq"] is not None:
                     m.exp_avg_sq.copy_(st["exp_avg_sq"])
                 m.hyper.copy_(st["hyper"])
+                m.refresh_shadow()
         self.state.update(blob.get("state", {}))
         if self.fopt.arena.flat_p16 is not None:
             self.fopt.arena.flat_p16.copy_(self.fopt.arena.flat_p)
         self._after_step_shadows()
+        if W > 1:
+            if self.device.type == "cuda":
+                torch.cuda.synchronize()
+            if hasattr(self._dp, "after_restore"):
+                self._dp.after_restore()
+            ctx.barrier()
         return self
 
     # --------------------------------------------------------------- the step --
@@ -480,24 +564,56 @@ class TrainingEngine:
             from ..utils.watchdog import RankWatchdog
 
             self.watchdog = RankWatchdog(ctx.world_size, ctx.rank, timeout=wd_timeout).start()
-        while True:
-            try:
-                self._train_loop(fs, criterion, end_trigger, checkpoint_trigger, validation_set, metrics, local_bs,
-                                 batch_size, log_every)
-                break
-            except (ValueError, TypeError, KeyboardInterrupt):
-                raise
-            except Exception as e:  # retry from the newest checkpoint (Topology.scala:1209-1258)
-                if self.latest_checkpoint() is None or ctx.world_size > 1:
+        # A restarted job (torchrun --max-restarts after a watchdog abort, or conf zoo.failure.autoResume) continues from the
+        # newest checkpoint of an earlier run directory instead of starting over.
+        resume = str(conf.get("zoo.failure.autoResume", os.environ.get("ZOO_AUTO_RESUME", "auto")))
+        if resume != "0" and not getattr(self, "_resumed", False):
+            self._resumed = True
+            if resume == "1" or int(os.environ.get("TORCHELASTIC_RESTART_COUNT", "0") or 0) > 0:
+                prev = self.find_resume_checkpoint()
+                if prev is not None:
+                    log.warning("resuming from %s", prev)
+                    self.load_checkpoint(prev)
+        # Ranks agree at every step boundary on "go" or "somebody failed" (zoo.utils.agreement); only needed when a retry is
+        # possible at all, i.e. when checkpoints are being written.
+        from ..utils.agreement import PeerFailure, StepAgreement
+
+        self._agree = None
+        if ctx.world_size > 1 and self.ckpt_dir is not None and checkpoint_trigger is not None and str(conf.get("zoo.failure.agree", "1")) != "0":
+            self._agree_gen = getattr(self, "_agree_gen", 0) + 1
+            apath = StepAgreement.default_path(f"agree-{self._agree_gen}")
+            if ctx.rank == 0:
+                StepAgreement.reset(apath, ctx.world_size)
+            ctx.barrier()
+            self._agree = StepAgreement(ctx.world_size, ctx.rank, path=apath, timeout=float(conf.get("zoo.failure.agreeTimeout", 120)))
+        try:
+            while True:
+                try:
+                    self._train_loop(fs, criterion, end_trigger, checkpoint_trigger, validation_set, metrics, local_bs,
+                                     batch_size, log_every)
+                    break
+                except (ValueError, TypeError, KeyboardInterrupt):
                     raise
-                now = time.time()
-                if now - window_start > retry_budget * retry_window:
-                    failures, window_start = 0, now
-                failures += 1
-                if failures > retry_budget:
-                    raise
-                log.warning("training failed with %r; retry %d/%d from %s", e, failures, retry_budget, self.latest_checkpoint())
-                self.load_checkpoint()
+                except Exception as e:  # retry from the newest checkpoint (Topology.scala:1209-1258)
+                    if ctx.world_size > 1:
+                        if self._agree is None:
+                            raise
+                        if not isinstance(e, PeerFailure):
+                            self._agree.report_failure()     # peers waiting at this step boundary learn about it and recover too
+                    if self.latest_checkpoint() is None:
+                        raise
+                    now = time.time()
+                    if now - window_start > retry_budget * retry_window:
+                        failures, window_start = 0, now
+                    failures += 1
+                    if failures > retry_budget:
+                        raise
+                    log.warning("training failed with %r; retry %d/%d from %s", e, failures, retry_budget, self.latest_checkpoint())
+                    self.load_checkpoint()
+        finally:
+            if self._agree is not None:
+                self._agree.close()
+                self._agree = None
         if self.async_loss and getattr(self, "_final_loss_dev", None) is not None:
             self.state["Loss"] = float(self._final_loss_dev)
             self._final_loss_dev = None
@@ -524,6 +640,8 @@ class TrainingEngine:
             seen, t_last, loss_dev = 0, time.time(), None
             for batch in it:
                 self._maybe_inject_fault()
+                if getattr(self, "_agree", None) is not None:
+                    self._agree.check_in()          # every rank starts this step, or all of them recover together
                 self.fopt.epoch = st["epoch"]
                 loss_dev = self.train_step(criterion, batch)
                 if self.watchdog is not None:

@@ -42,11 +42,25 @@ class MXNetRunner:
                 loss = self.loss(self.model(torch.as_tensor(x)), torch.as_tensor(y))
                 self.optimizer.zero_grad()
                 loss.backward()
+                self._exchange_gradients()
                 self.optimizer.step()
                 tot, n = tot + float(loss.detach()), n + 1
             self.epoch += 1
             stats = {"epoch": self.epoch, "train_loss": tot / max(n, 1)}
         return stats
+
+    def _exchange_gradients(self):
+        """`kvstore=dist_sync` semantics: every worker applies the mean gradient.  Runners started inside a process group (the
+        pool sets RANK / WORLD_SIZE) average through it; a lone runner has nothing to exchange."""
+        import torch.distributed as dist
+
+        if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+            return
+        W = dist.get_world_size()
+        for p in self.model.parameters():
+            if p.grad is not None:
+                dist.all_reduce(p.grad)
+                p.grad.div_(W)
 
     def shutdown(self):
         for k in ("model", "data", "optimizer"):
