@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = config default)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink table sizes (debug only; marks the run invalid)")
+    ap.add_argument("--zipf", type=float, default=0.0, help="ncf: draw ids from Zipf(alpha) instead of uniformly (duplicate-heavy batches)")
+    ap.add_argument("--no-baseline", action="store_true", help="skip the same-box torch + NCCL baseline arm (baseline/ddp_bench.py)")
+    ap.add_argument("--baseline-steps", type=int, default=0, help="timed steps of the baseline arm (0 = min(K, 20))")
     return ap.parse_args()
 
 
@@ -107,19 +110,20 @@ def build_ncf(args, ctx, torch):
     model = NeuralCF(users, items, 5, sparse=True, world=W, rank=ctx.rank, device=ctx.device, **dims)
     loss = SparseCategoricalCrossEntropy(zero_based_label=False, padding_value=None)
 
+    from baseline.ddp_bench import make_ncf_batch      # the product and the baseline arm draw their batches the same way
+
     def make_batches(n, device, pin=False):
         g = torch.Generator(device="cpu").manual_seed(1234 + ctx.rank)
         out = []
         for _ in range(n):
-            x = torch.stack([torch.randint(1, users + 1, (batch,), generator=g),
-                             torch.randint(1, items + 1, (batch,), generator=g)], 1)
-            y = torch.randint(1, 6, (batch,), generator=g)
+            x, y = make_ncf_batch(batch, users, items, g, args.zipf)
             out.append((x.to(device), y.to(device)) if device.type == "cuda" else (x, y))
         return out
 
     return dict(model=model, loss=loss, batch=batch, make_batches=make_batches, model_name=model_name,
                 parallelism=("single" if W == 1 else f"dp{W} dense + row-sharded tables x{W}"),
-                extra={"users": users, "items": items, "lr": 1e-3, "optimizer": "adam(dense)+lazy-adam(tables)"})
+                extra={"users": users, "items": items, "lr": 1e-3, "optimizer": "adam(dense)+lazy-adam(tables)",
+                       "ids": f"zipf({args.zipf})" if args.zipf > 0 else "uniform"})
 
 
 def main():
@@ -139,6 +143,21 @@ def main():
         print(json.dumps({"error": "bench.py needs a CUDA device"}))
         return 1
     dev = ctx.device
+    # ---------------- same-box anchor: plain torch + NCCL (DDP / all_to_all_single) on the same config, same process group ----
+    nccl_base = None
+    if not args.no_baseline and args.config in ("ncf", "wnd", "resnet50"):
+        try:
+            from baseline.ddp_bench import run_baseline
+
+            bsteps = args.baseline_steps or min(args.steps, 20)
+            nccl_base = run_baseline(args.config, ctx.world_size, ctx.rank, dev, bsteps, args.warmup, args.batch, args.scale,
+                                     args.zipf, e2e=not args.no_e2e)
+        except Exception as e:  # the anchor must never take the product line down with it
+            nccl_base = {"impl": "torch-nccl-baseline", "error": repr(e)[:300]}
+        import gc
+
+        gc.collect()
+        torch.cuda.empty_cache()
     if args.config in ("ncf", "ncf-ml1m"):
         cfg = build_ncf(args, ctx, torch)
     else:
@@ -240,6 +259,13 @@ def main():
                           **cfg["extra"]},
                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": loss_val,
                "invalid_debug_scale": args.scale if args.scale != 1.0 else None}
+        out["config"]["comm_backend"] = getattr(eng._dp, "name", "?")
+        out["config"]["shard_bwd"] = os.environ.get("ZOO_SHARD_BWD", "default") if ctx.world_size > 1 else None
+        if nccl_base is not None:
+            out["nccl_baseline"] = nccl_base
+            if nccl_base.get("value"):
+                out["vs_nccl_baseline"] = {"value_ratio": value / nccl_base["value"],
+                                           "e2e_ratio": (e2e["value"] / nccl_base["e2e"]["value"]) if (e2e and nccl_base.get("e2e")) else None}
         print(json.dumps(out))
     return 0
 

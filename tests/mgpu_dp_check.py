@@ -18,12 +18,20 @@ ctx = init_nncontext()
 torch.manual_seed(0)
 base = nn.Sequential(FusedMLP(64, [128, 64]), FusedDense(64, 8))
 results = {}
-for mode in ("nccl", "p2p"):
+for mode in ("nccl", "p2p", "p2p-owner", "nccl-clip", "p2p-clip"):
     m = copy.deepcopy(base)
-    eng = TrainingEngine(m, torch.optim.Adam(m.parameters(), lr=1e-2), ctx=ctx, grad_sync=mode)
+    # "p2p": small arenas take the one-handshake push all-reduce with a bf16 wire (csrc/comm/ar_push.cu);
+    # "p2p-owner": force the owner-computes reduce-scatter + optimizer + all-gather kernel (csrc/comm/rs_opt_ag.cu, fp32 wire)
+    os.environ["ZOO_K1_SMALL"] = "0" if mode == "p2p-owner" else "auto"
+    eng = TrainingEngine(m, torch.optim.Adam(m.parameters(), lr=1e-2), ctx=ctx, grad_sync="nccl" if mode.startswith("nccl") else "p2p")
     eng.use_cuda_graph = False
+    if mode.endswith("clip"):
+        eng.set_gradient_clipping_by_l2_norm(0.05)
     eng.prepare()
-    assert eng._dp.name == ("p2p" if mode == "p2p" else "allreduce"), eng._dp.name
+    assert eng._dp.name == ("allreduce" if mode.startswith("nccl") else "p2p"), eng._dp.name
+    if mode.startswith("p2p"):
+        assert eng._dp.small == (mode != "p2p-owner")
+        assert eng._dp.graph_safe() or mode == "p2p-owner"
     g = torch.Generator().manual_seed(100 + ctx.rank)
     crit = MeanSquaredError()
     for step in range(6):
@@ -36,8 +44,12 @@ for mode in ("nccl", "p2p"):
     w = results[mode].clone()
     torch.distributed.broadcast(w, src=0)
     assert torch.equal(w, results[mode]), f"{mode}: ranks diverged"
-diff = (results["nccl"] - results["p2p"]).abs().max().item()
-assert diff < 1e-4, diff
+    eng.close()
+d_owner = (results["nccl"] - results["p2p-owner"]).abs().max().item()
+d_push = (results["nccl"] - results["p2p"]).abs().max().item()        # gradients travel as bf16: Adam steps differ at rounding size
+d_clip = (results["nccl-clip"] - results["p2p-clip"]).abs().max().item()
+moved = (results["nccl-clip"] - results["nccl"]).abs().max().item()     # the clip must actually bite
+assert d_owner < 1e-4 and d_push < 3e-3 and d_clip < 3e-3 and moved > 1e-3, (d_owner, d_push, d_clip, moved)
 torch.distributed.barrier()
 if ctx.rank == 0:
-    print(f"MGPU_DP_OK world={ctx.world_size} max|nccl-p2p|={diff:.2e}")
+    print(f"MGPU_DP_OK world={ctx.world_size} max|nccl-owner|={d_owner:.2e} max|nccl-push|={d_push:.2e} max|clip nccl-push|={d_clip:.2e}")

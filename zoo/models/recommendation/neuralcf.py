@@ -59,15 +59,25 @@ class NeuralCF(Recommender):
     def forward_logits(self, x):
         """x: [B, 2] (user_id, item_id), 1-based like the reference."""
         ids = x.long() if x.dtype != torch.int64 else x
-        h = multi_lookup(ids, [LookupSpec(self.mlp_user_embed, 0), LookupSpec(self.mlp_item_embed, 1)])
-        h = self.mlp(h)
-        if self.include_mf:
-            mf = multi_lookup(ids, [LookupSpec(self.mf_user_embed, 0, mul_table=self.mf_item_embed, mul_col=1)])
-            bits = getattr(h, "_zoo_relu_bits", None)
-            h = torch.cat([h, mf.to(h.dtype)], dim=1)
-            if bits is not None:            # sign bits of the MLP half travel with the concatenated activation
-                h._zoo_relu_bits = bits
-        return self.linear_last(h)
+        specs = [LookupSpec(self.mlp_user_embed, 0), LookupSpec(self.mlp_item_embed, 1)]
+        if not self.include_mf:
+            return self.linear_last(self.mlp(multi_lookup(ids, specs)))
+        # ONE lookup for all four tables: [MLP-user | MLP-item | MF-user * MF-item]; the tower reads the first window, the
+        # GMF product is the second.  Tables of one id column share their sparse update (zoo.ops.embedding_group).
+        specs.append(LookupSpec(self.mf_user_embed, 0, mul_table=self.mf_item_embed, mul_col=1))
+        h_in, mf = multi_lookup(ids, specs, splits=[self.user_embed + self.item_embed, self.mf_embed])
+        h = self.mlp(h_in)
+        bits = getattr(h, "_zoo_relu_bits", None)
+        hc = torch.cat([h, mf.to(h.dtype)], dim=1)
+        if bits is not None:                # sign bits of the MLP half travel with the concatenated activation
+            hc._zoo_relu_bits = bits
+        if self.mf_user_embed.world > 1 and hc.is_cuda and torch.is_grad_enabled():
+            # sharded tables: the last layer writes its input gradient into peer-readable memory, so the owners of the MF rows
+            # read their gradient rows in place (no staging copy of the MF half)
+            from ...ops.embedding import ShardRuntime
+
+            hc._zoo_dx_out = ShardRuntime.get().stage(("ncf-last-dx", id(self), hc.shape[0]), tuple(hc.shape), torch.bfloat16)[1]
+        return self.linear_last(hc)
 
     def forward(self, x):
         return torch.softmax(self.forward_logits(x).float(), dim=-1)

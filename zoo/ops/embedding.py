@@ -107,6 +107,17 @@ class ShardRuntime:
             self.stages[("recv",) + tuple(key)] = rb
         return rb
 
+    def peer_ptrs_of(self, t, byte_offset=0):
+        """If tensor `t` lives inside a symmetric buffer: the addresses of the same element (+ byte_offset) in every rank's copy of
+        that buffer (index = rank); else None."""
+        p = t.data_ptr()
+        for v in self.stages.values():
+            buf = v[0] if isinstance(v, tuple) else None
+            if buf is not None and buf.local_ptr <= p < buf.local_ptr + buf.nbytes:
+                rel = p - buf.local_ptr + byte_offset
+                return [q + rel for q in buf.ptrs]
+        return None
+
     def scratch(self, E, D):
         if self.accum is None or self.accum.shape[0] < E or self.accum.shape[1] < D:
             E2 = max(E, 0 if self.accum is None else self.accum.shape[0])
@@ -523,13 +534,35 @@ def _flat_tables(specs):
     return ts
 
 
-def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None):
-    """ids: int64 [B, ncols].  specs: list of _LookupSpec.  Returns bf16 [B, sum(D)] on GPU, fp32 on CPU."""
+def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None, splits=None):
+    """ids: int64 [B, ncols].  specs: list of _LookupSpec.  Returns bf16 [B, sum(D)] on GPU, fp32 on CPU; with `splits`
+    (a list of column widths summing to sum(D)) a tuple of those column windows instead."""
+    if splits is not None:
+        if ids.dim() == 1:
+            ids = ids.unsqueeze(1)
+        if ids.is_cuda:
+            if ids.dtype != torch.int64:
+                ids = ids.long()
+            from . import embedding_group as _eg
+
+            if len(specs) <= _eg.MAX_SPECS and _eg.eligible(specs):
+                return _eg.grouped_lookup(ids, specs, splits)
+        full = multi_lookup(ids, specs, anchor)
+        outs, off = [], 0
+        for w in splits:
+            outs.append(full[:, off:off + w])
+            off += w
+        return tuple(outs)
     if ids.dim() == 1:
         ids = ids.unsqueeze(1)
     if ids.is_cuda:
         if ids.dtype != torch.int64:
             ids = ids.long()
+        from . import embedding_group as _eg
+
+        if len(specs) <= _eg.MAX_SPECS and _eg.eligible(specs):
+            # every lookup in one gather launch; sparse updates of all tables at the end of backward (column groups)
+            return _eg.grouped_lookup(ids, specs)
         weights = [t.anchor if t.sparse else t.weight for t in _flat_tables(specs)]
         _MultiLookupFn.offered_dx_out = None
         res = _MultiLookupFn.apply(ids, specs, *weights)

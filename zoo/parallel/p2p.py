@@ -12,9 +12,17 @@ import os
 
 import torch
 
+import ctypes as C
+
 from ..native import lib as _nl
 from .flat import OPT_IDS
 from .symm import get_heap, ptr_array
+
+_nl.register_cuda_sigs({
+    "zoo_ar_push": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p],
+    "zoo_ar_reduce": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p],
+})
+AR_MAX_CTAS = 1024      # kArMaxCtas of csrc/comm/ar_push.cu
 
 
 class P2PFusedSync:
@@ -41,11 +49,15 @@ class P2PFusedSync:
         return alloc
 
     def pad_to(self):
-        return max(8, 4 * self.ctx.world_size)
+        import math
+
+        return math.lcm(8, 4 * self.ctx.world_size)      # ar_push moves 8-float units, rs_opt_ag float4 units per rank
 
     def graph_safe(self):
         f = getattr(self, "fopt", None)
-        return f is None or (f.clip_l2 is None and f.clip_const is None)      # the clipping fallback calls NCCL: no capture
+        if f is None or getattr(self, "small", False):
+            return True                 # push all-reduce + local fused optimizer (clipping included): kernels only
+        return f.clip_l2 is None and f.clip_const is None      # large arenas with clipping take the library all-reduce: no capture
 
     def attach(self, fopt):
         self.fopt = fopt
@@ -74,6 +86,41 @@ class P2PFusedSync:
         self._epoch = loc(self.epoch)
         self._bflags = ptr_array(self.bar_flags.ptrs)
         self._bepoch = loc(self.bar_epoch)
+        # Small arenas (a recommender's dense part): one-handshake push all-reduce with a bf16 wire (csrc/comm/ar_push.cu),
+        # then the ordinary local fused optimizer -- clipping included -- on the summed gradient.
+        n = a.numel
+        mode = os.environ.get("ZOO_K1_SMALL", "auto")
+        self.small = (mode == "1") or (mode == "auto" and n * 2 * W <= (64 << 20))
+        self._pushed = False
+        if self.small:
+            if n % 8:
+                raise RuntimeError("flat arena length must be a multiple of 8 (pad_to)")
+            self.mail = self.heap.alloc(2 * W * n * 2)
+            self.ar_flags = self.heap.alloc(4 * 2 * W * AR_MAX_CTAS)
+            self.ar_flags.tensor(torch.int32, 2 * W * AR_MAX_CTAS).zero_()
+            self.ar_epoch = torch.zeros(2 * AR_MAX_CTAS, dtype=torch.int32, device=self.ctx.device)
+            self._mail, self._arflags = ptr_array(self.mail.ptrs), ptr_array(self.ar_flags.ptrs)
+            self.ar_grid = int(min(592, max(1, (n // 8 + 255) // 256)))
+            torch.cuda.synchronize()
+            self.ctx.barrier()
+            from ..ops import embedding_group as _eg
+
+            # dense gradients are final when backward ends: push them before the sparse embedding updates start, so the
+            # flags have long arrived when the reduce runs after those updates
+            import weakref
+
+            ref = weakref.ref(self)
+
+            def _hook():
+                me = ref()
+                if me is None:              # the engine that owned this exchange is gone
+                    _eg.PRE_FLUSH_HOOKS.remove(_hook)
+                elif me.fopt is not None and me._armed:
+                    me.push_gradients()
+
+            self._hook = _hook
+            self._armed = True
+            _eg.PRE_FLUSH_HOOKS.append(_hook)
 
     def broadcast_parameters(self):
         import torch.distributed as dist
@@ -103,8 +150,25 @@ class P2PFusedSync:
             return mode == "1"
         return n * 4 * self.ctx.world_size <= (32 << 20)
 
+    def push_gradients(self):
+        """First half of the small-arena exchange (no waiting): bf16 copies of this rank's gradients into every mailbox."""
+        if not self.small or self._pushed:
+            return
+        a = self.fopt.arena
+        _nl.check(_nl.cuda_lib().zoo_ar_push(a.flat_g.data_ptr(), self._mail, self._arflags, self.ar_epoch.data_ptr(), a.numel,
+                                            self.ctx.world_size, self.ctx.rank, self.ar_grid, _nl.stream_ptr()), "zoo_ar_push")
+        self._pushed = True
+
     def step(self):
         f = self.fopt
+        if self.small:
+            self.push_gradients()
+            self._pushed = False
+            a = f.arena
+            _nl.check(_nl.cuda_lib().zoo_ar_reduce(a.flat_g.data_ptr(), self._mail, self._arflags, self.ar_epoch.data_ptr(), a.numel,
+                                                  self.ctx.world_size, self.ctx.rank, self.ar_grid, _nl.stream_ptr()), "zoo_ar_reduce")
+            f.step()        # clip (on the averaged gradient) + optimizer + bf16 shadows + zero the gradients, all local kernels
+            return
         if f.clip_l2 is not None or f.clip_const is not None:
             # clipping needs the global gradient norm / clamp BEFORE the update, which the owner-computes kernel does not
             # have: take the library all-reduce + local fused optimizer for this step (same arenas, same optimizer state)
@@ -132,6 +196,8 @@ class P2PFusedSync:
         import torch.distributed as dist
 
         f, W, r = self.fopt, self.ctx.world_size, self.ctx.rank
+        if self.small:
+            return          # every rank runs the full optimizer on the summed gradient: state is complete everywhere
         for g in f.groups:
             n = g.end - g.start
             if self._replicated(n):
@@ -146,4 +212,10 @@ class P2PFusedSync:
         torch.cuda.synchronize()
 
     def close(self):
-        pass
+        h = getattr(self, "_hook", None)
+        if h is not None:
+            from ..ops import embedding_group as _eg
+
+            if h in _eg.PRE_FLUSH_HOOKS:
+                _eg.PRE_FLUSH_HOOKS.remove(h)
+            self._hook = None
