@@ -149,49 +149,48 @@ eg_accum_kernel(const __grid_constant__ ZooEgParams p) {
           red_add_f32x4(arow + c, gr[0], gr[1], gr[2], gr[3]);
         }
       }
-      if (lane == 0) g.dup_flag[rep] = 1;
+      if (lane < g.ntabs) g.dup_flag[(long long)lane * g.max_entries + rep] = 1;
     }
     __syncthreads();               // s_wcount / s_base are reused by the next round
   }
 }
 
-// ---- pass 3: representatives apply the optimizer to their row of EVERY table of the group --------------------------------
-// A row of the group is `units` float4 columns (all tables side by side); G lanes serve one row, a warp covers 32 / G rows per
-// pass, and every lane issues the loads of all of its units (gradient row -- possibly over NVLink --, w, m, v, duplicate sum)
-// before it computes anything.
-struct EgHyp { float lr, b1, b2, eps, wd, bc1, bc2; };
-
-template <int ITERS>
-__global__ void __launch_bounds__(256, ITERS == 1 ? 4 : (ITERS == 2 ? 3 : 2))
-eg_apply_kernel(const __grid_constant__ ZooEgParams p, int G) {
+// ---- pass 3: representatives apply the optimizer to their rows -----------------------------------------------------------------
+// blockIdx.y = (group, table): every table of a group walks the group's ONE winner list.  The update is latency-bound -- a row
+// is a handful of 16-byte loads (gradient row, possibly from a peer over NVLink, plus w / m / v) and a little math -- so the
+// kernel is organised for loads in flight: a row uses only as many lanes as it has float4 columns (G = 8 / 16 / 32, two passes
+// of 32 lanes for 256-wide rows), a warp covers 32 / G rows, and all loads of a row are issued before anything is computed.
+// LOOP == false: one pass per warp over a grid sized for the entries (world == 1: the entry count is known on the host; no
+// register cost of the loop, CTAs at different phases overlap their load and store phases).  LOOP == true: a grid sized for
+// one GPU's share of the entries strides over what the owner really received.
+// Duplicate flags are per table (dup_flag + table * max_entries) so tables never race on resetting them; table 0 restores the
+// row map.
+template <int ITERS, bool LOOP>
+__global__ void __launch_bounds__(256, ITERS == 1 ? (LOOP ? 5 : 6) : 3)
+eg_apply_kernel(const __grid_constant__ ZooEgParams p) {
   pdl_wait();
   pdl_launch_dependents();
-  const EgGroup& g = p.g[blockIdx.y];
+  const EgGroup& g = p.g[blockIdx.y / ZOO_EG_MAX_TABS];
+  const int k = blockIdx.y % ZOO_EG_MAX_TABS;
+  if (k >= g.ntabs) return;
+  const EgTab& t = g.t[k];
   const int count = *g.win_count;
+  const int units = t.D >> 2;
+  int G = 32;
+  while (G > 8 && (G >> 1) >= units) G >>= 1;
   const int lane = threadIdx.x & 31;
   const int P = 32 / G, slot = lane / G, l = lane - slot * G;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
-  if (warp * P >= count) return;
+  int base = warp * P;
+  if (base >= count) return;
   const EgIndex ix = eg_index(g);
-  EgHyp hy[ZOO_EG_MAX_TABS];
-  int ubeg[ZOO_EG_MAX_TABS + 1];
-  ubeg[0] = 0;
-#pragma unroll
-  for (int k = 0; k < ZOO_EG_MAX_TABS; ++k) {
-    if (k < g.ntabs) {
-      const float* h = g.t[k].hyper;
-      hy[k].lr = h[0]; hy[k].b1 = h[1]; hy[k].b2 = h[2]; hy[k].eps = h[3]; hy[k].wd = h[4];
-      hy[k].bc1 = 1.f; hy[k].bc2 = 1.f;
-      if (g.t[k].opt == 1) { hy[k].bc1 = 1.f - powf(h[1], h[5]); hy[k].bc2 = 1.f - powf(h[2], h[5]); }
-      ubeg[k + 1] = ubeg[k] + (g.t[k].D >> 2);
-    } else {
-      hy[k] = hy[0];
-      ubeg[k + 1] = ubeg[k];
-    }
-  }
-  const int units = ubeg[ZOO_EG_MAX_TABS];
-  for (int base = warp * P; base < count; base += nwarps * P) {
+  const float* h = t.hyper;
+  const float lr = h[0], b1 = h[1], b2 = h[2], eps = h[3], wd = h[4];
+  float bc1 = 1.f, bc2 = 1.f;
+  if (t.opt == 1) { bc1 = 1.f - powf(b1, h[5]); bc2 = 1.f - powf(b2, h[5]); }
+  int* dupf = g.dup_flag + (long long)k * g.max_entries;
+  do {
     const int idx = base + slot;
     const bool row_ok = idx < count;
     int i = 0, local = 0, src = 0, ent = 0;
@@ -201,61 +200,51 @@ eg_apply_kernel(const __grid_constant__ ZooEgParams p, int G) {
       i = wlv.x; local = wlv.y;
       int lc;
       eg_decode(g, ix, i, src, ent, lc);
-      dup = g.dup_flag[i] != 0;
+      dup = dupf[i] != 0;
     }
     float gr[ITERS][4];
     float4 w4[ITERS], m4[ITERS], v4[ITERS], a4[ITERS];
-    int tk[ITERS], cc[ITERS];
     bool ok[ITERS];
 #pragma unroll
     for (int it = 0; it < ITERS; ++it) {                      // ---- issue every load first
-      const int u = l + it * G;
-      ok[it] = row_ok && u < units;
-      int k = 0;
-#pragma unroll
-      for (int q = 1; q < ZOO_EG_MAX_TABS; ++q)
-        if (u >= ubeg[q] && q < g.ntabs) k = q;
-      tk[it] = k;
-      cc[it] = (u - ubeg[k]) << 2;
+      const int c = (l + it * G) << 2;
+      ok[it] = row_ok && c < t.D;
       if (ok[it]) {
-        const EgTab& t = g.t[k];
-        eg_grad(t, g.bag, src, ent, cc[it], gr[it]);
-        const long long o = (long long)local * t.D + cc[it];
+        eg_grad(t, g.bag, src, ent, c, gr[it]);
+        const long long o = (long long)local * t.D + c;
         w4[it] = *reinterpret_cast<const float4*>(t.w + o);
         if (t.m) m4[it] = *reinterpret_cast<const float4*>(t.m + o);
         if (t.v) v4[it] = *reinterpret_cast<const float4*>(t.v + o);
-        if (dup) a4[it] = *reinterpret_cast<const float4*>(t.accum + (long long)i * t.D + cc[it]);
+        if (dup) a4[it] = *reinterpret_cast<const float4*>(t.accum + (long long)i * t.D + c);
       }
     }
 #pragma unroll
     for (int it = 0; it < ITERS; ++it) {                      // ---- then compute and store
       if (!ok[it]) continue;
-      const int k = tk[it];
-      const EgTab& t = g.t[k];
-      const EgHyp h = k == 0 ? hy[0] : hy[1];
+      const int c = (l + it * G) << 2;
       float w[4] = {w4[it].x, w4[it].y, w4[it].z, w4[it].w};
       float m[4] = {0.f, 0.f, 0.f, 0.f}, v[4] = {0.f, 0.f, 0.f, 0.f};
       if (t.m) { m[0] = m4[it].x; m[1] = m4[it].y; m[2] = m4[it].z; m[3] = m4[it].w; }
       if (t.v) { v[0] = v4[it].x; v[1] = v4[it].y; v[2] = v4[it].z; v[3] = v4[it].w; }
       if (dup) {
         gr[it][0] += a4[it].x; gr[it][1] += a4[it].y; gr[it][2] += a4[it].z; gr[it][3] += a4[it].w;
-        *reinterpret_cast<float4*>(t.accum + (long long)i * t.D + cc[it]) = make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(t.accum + (long long)i * t.D + c) = make_float4(0.f, 0.f, 0.f, 0.f);
       }
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const float gg = gr[it][q] + h.wd * w[q];
+        const float gg = gr[it][q] + wd * w[q];
         if (t.opt == 1) {
-          m[q] = h.b1 * m[q] + (1.f - h.b1) * gg;
-          v[q] = h.b2 * v[q] + (1.f - h.b2) * gg * gg;
-          w[q] -= h.lr * (m[q] / h.bc1) / (sqrtf(v[q] / h.bc2) + h.eps);
+          m[q] = b1 * m[q] + (1.f - b1) * gg;
+          v[q] = b2 * v[q] + (1.f - b2) * gg * gg;
+          w[q] -= lr * (m[q] / bc1) / (sqrtf(v[q] / bc2) + eps);
         } else if (t.opt == 2) {
           m[q] += gg * gg;
-          w[q] -= h.lr * gg / (sqrtf(m[q]) + h.eps);
+          w[q] -= lr * gg / (sqrtf(m[q]) + eps);
         } else {
-          w[q] -= h.lr * gg;
+          w[q] -= lr * gg;
         }
       }
-      const long long o = (long long)local * t.D + cc[it];
+      const long long o = (long long)local * t.D + c;
       *reinterpret_cast<float4*>(t.w + o) = make_float4(w[0], w[1], w[2], w[3]);
       if (t.m) *reinterpret_cast<float4*>(t.m + o) = make_float4(m[0], m[1], m[2], m[3]);
       if (t.v) *reinterpret_cast<float4*>(t.v + o) = make_float4(v[0], v[1], v[2], v[3]);
@@ -265,10 +254,11 @@ eg_apply_kernel(const __grid_constant__ ZooEgParams p, int G) {
       }
     }
     if (row_ok && l == 0) {                                   // one lane per row restores the scratch
-      g.rep_of_row[local] = INT_MAX;
-      if (dup) g.dup_flag[i] = 0;
+      if (k == 0) g.rep_of_row[local] = INT_MAX;
+      if (dup) dupf[i] = 0;
     }
-  }
+    base += nwarps * P;
+  } while (LOOP && base < count);
 }
 
 // ---- forward: every lookup of the step in one launch ----------------------------------------------------------------------
@@ -296,8 +286,63 @@ __device__ __forceinline__ const T* eg_row(const void* const (&tabs)[ZOO_EG_MAX_
   return reinterpret_cast<const T*>(tabs[(int)(id % world)]) + (id / world) * (long long)D;
 }
 
+__device__ __forceinline__ uint32_t eg_mul_bf16x2(uint32_t a, uint32_t b) {
+  __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&a), y = *reinterpret_cast<__nv_bfloat162*>(&b);
+  __nv_bfloat162 z = __hmul2(x, y);          // fp32 product rounded once to bf16: the same value as multiply-then-pack
+  return *reinterpret_cast<uint32_t*>(&z);
+}
+
+// bag == 1 (one row, or the product of two rows, per sample): no accumulator, no conversion for bf16 rows -- the kernel is a
+// latency-bound copy, so the fewer registers it needs the more rows are in flight.
 template <typename T>
-__device__ __forceinline__ void eg_gather_body(const ZooEgGatherParams& p, const ZooEgSpec& s, int sample, int lane, int G) {
+__device__ __forceinline__ void eg_gather_one(const ZooEgGatherParams& p, const ZooEgSpec& s, int sample, int lane, int G) {
+  constexpr int VN = EgVec<T>::N;
+  const long long* idr = p.ids + (long long)sample * p.id_stride;
+  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(s.out) + (long long)sample * s.ldo;
+  const bool mul = s.tb[0] != nullptr;
+  const long long ia = idr[s.id_col];
+  const bool oka = ia >= 0 && ia < s.rows_a;
+  long long ib = 0;
+  bool okb = false;
+  if (mul) { ib = idr[s.id_col2]; okb = ib >= 0 && ib < s.rows_b; }
+  const T* ra = oka ? eg_row<T>(s.ta, ia, p.world, s.D) : nullptr;
+  const T* rb = okb ? eg_row<T>(s.tb, ib, p.world, s.D) : nullptr;
+  for (int c = lane * VN; c < s.D; c += G * VN) {
+    if (VN == 8) {
+      uint4 a = make_uint4(0, 0, 0, 0), b = make_uint4(0, 0, 0, 0);
+      if (ra) a = *reinterpret_cast<const uint4*>(ra + c);
+      if (mul) {
+        if (rb) b = *reinterpret_cast<const uint4*>(rb + c);
+        if (s.save_a) {
+          *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(s.save_a) + (long long)sample * s.D + c) = a;
+          *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(s.save_b) + (long long)sample * s.D + c) = b;
+        }
+        a.x = eg_mul_bf16x2(a.x, b.x); a.y = eg_mul_bf16x2(a.y, b.y); a.z = eg_mul_bf16x2(a.z, b.z); a.w = eg_mul_bf16x2(a.w, b.w);
+      }
+      *reinterpret_cast<uint4*>(o + c) = a;
+    } else {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ra) a = *reinterpret_cast<const float4*>(ra + c);
+      if (mul) {
+        if (rb) b = *reinterpret_cast<const float4*>(rb + c);
+        if (s.save_a) {
+          uint2 ua, ub;
+          ua.x = pack_bf16(a.x, a.y); ua.y = pack_bf16(a.z, a.w);
+          ub.x = pack_bf16(b.x, b.y); ub.y = pack_bf16(b.z, b.w);
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(s.save_a) + (long long)sample * s.D + c) = ua;
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(s.save_b) + (long long)sample * s.D + c) = ub;
+        }
+        a.x *= b.x; a.y *= b.y; a.z *= b.z; a.w *= b.w;
+      }
+      uint2 pk;
+      pk.x = pack_bf16(a.x, a.y); pk.y = pack_bf16(a.z, a.w);
+      *reinterpret_cast<uint2*>(o + c) = pk;
+    }
+  }
+}
+
+template <typename T>
+__device__ __noinline__ void eg_gather_body(const ZooEgGatherParams& p, const ZooEgSpec& s, int sample, int lane, int G) {
   constexpr int VN = EgVec<T>::N;
   const long long* idr = p.ids + (long long)sample * p.id_stride;
   __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(s.out) + (long long)sample * s.ldo;
@@ -360,7 +405,7 @@ __device__ __forceinline__ void eg_gather_body(const ZooEgGatherParams& p, const
 
 struct EgLanes { int G[ZOO_EG_MAX_SPECS]; };
 
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__(256, 6)
 eg_gather_kernel(const __grid_constant__ ZooEgGatherParams p, const EgLanes lanes) {
   pdl_wait();
   pdl_launch_dependents();
@@ -370,8 +415,13 @@ eg_gather_kernel(const __grid_constant__ ZooEgGatherParams p, const EgLanes lane
   const int sample = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / G) + gl / G;
   const int lane = gl - (gl / G) * G;
   if (sample >= p.B) return;
-  if (s.dtype == 0) eg_gather_body<float>(p, s, sample, lane, G);
-  else eg_gather_body<__nv_bfloat16>(p, s, sample, lane, G);
+  if (s.bag == 1) {
+    if (s.dtype == 0) eg_gather_one<float>(p, s, sample, lane, G);
+    else eg_gather_one<__nv_bfloat16>(p, s, sample, lane, G);
+  } else {
+    if (s.dtype == 0) eg_gather_body<float>(p, s, sample, lane, G);
+    else eg_gather_body<__nv_bfloat16>(p, s, sample, lane, G);
+  }
 }
 
 // ---- forward, world > 1: route every entry of an id column to the owner of its row ---------------------------------------
@@ -507,7 +557,7 @@ ZOO_API int zoo_eg_update(const ZooEgParams* p, void* stream) {
     const ZooEgGroup& g = p->g[k];
     bool ok = g.rep_of_row && g.dup_flag && g.win_list && g.win_count && g.ntabs >= 1 && g.ntabs <= ZOO_EG_MAX_TABS && g.bag >= 1 &&
               g.world >= 1 && g.world <= ZOO_EG_MAX_PEERS && g.rank >= 0 && g.rank < g.world && g.E_local >= 0 &&
-              (g.world == 1 ? g.ids != nullptr : (g.pairs && g.counts && g.cap >= 1)) && (g.rows + g.world - 1) / g.world <= INT_MAX;
+              (g.world == 1 ? g.ids != nullptr : (g.pairs && g.counts && g.cap >= 1)) && g.max_entries >= (g.world == 1 ? g.E_local : 1) && (g.rows + g.world - 1) / g.world <= INT_MAX;
     int units = 0;
     for (int q = 0; q < g.ntabs && ok; ++q) {
       const ZooEgTab& t = g.t[q];
@@ -535,18 +585,25 @@ ZOO_API int zoo_eg_update(const ZooEgParams* p, void* stream) {
   if (eb > (unsigned)sms * 16) eb = (unsigned)sms * 16;
   ZOO_CUDA_CHECK(zoo_launch_pdl(eg_mark_kernel, dim3(eb, (unsigned)p->ngroups), dim3(256), 0, s, *p));
   ZOO_CUDA_CHECK(zoo_launch_pdl(eg_accum_kernel, dim3(eb, (unsigned)p->ngroups), dim3(256), 0, s, *p));
-  int G = 32;
-  while (G > 1 && G / 2 >= max_units) G /= 2;
-  const int iters = (max_units + G - 1) / G;
-  const int P = 32 / G;
-  long long ab = ((long long)max_e + 8 * P - 1) / (8 * P);     // one pass per warp when the entry count is small
-  const long long cap_blocks = (long long)sms * 8 / p->ngroups;
-  if (ab > cap_blocks) ab = cap_blocks;
+  // apply: blockIdx.y = (group, table); G lanes per row from the table's own width
+  int max_d = 4;
+  bool any_sharded = false;
+  for (int k = 0; k < p->ngroups; ++k) {
+    for (int q = 0; q < p->g[k].ntabs; ++q) if (p->g[k].t[q].D > max_d) max_d = p->g[k].t[q].D;
+    if (p->g[k].world > 1) any_sharded = true;
+  }
+  const long long rows_per_cta = 8;                             // 8 warps x >= 1 row
+  long long ab = ((long long)max_e + rows_per_cta - 1) / rows_per_cta;
+  const bool loop = any_sharded || ab > (long long)sms * 64;
+  if (loop) { const long long capb = (long long)sms * 16 / (p->ngroups > 2 ? 2 : 1); if (ab > capb) ab = capb; }
   if (ab < 1) ab = 1;
-  const dim3 grid((unsigned)ab, (unsigned)p->ngroups);
-  if (iters <= 1) ZOO_CUDA_CHECK(zoo_launch_pdl(eg_apply_kernel<1>, grid, dim3(256), 0, s, *p, G));
-  else if (iters == 2) ZOO_CUDA_CHECK(zoo_launch_pdl(eg_apply_kernel<2>, grid, dim3(256), 0, s, *p, G));
-  else ZOO_CUDA_CHECK(zoo_launch_pdl(eg_apply_kernel<4>, grid, dim3(256), 0, s, *p, G));
+  const dim3 grid((unsigned)ab, (unsigned)(p->ngroups * ZOO_EG_MAX_TABS));
+  if (max_d <= 128) {
+    if (loop) ZOO_CUDA_CHECK(zoo_launch_pdl(eg_apply_kernel<1, true>, grid, dim3(256), 0, s, *p));
+    else      ZOO_CUDA_CHECK(zoo_launch_pdl(eg_apply_kernel<1, false>, grid, dim3(256), 0, s, *p));
+  } else {
+    ZOO_CUDA_CHECK(zoo_launch_pdl(eg_apply_kernel<2, true>, grid, dim3(256), 0, s, *p));
+  }
   ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;
 }

@@ -43,12 +43,13 @@ typedef struct ZooEgGroup {
   const void* pairs;        /* world > 1: int2 [world * cap] = (local row, entry index at the source), filled by zoo_eg_route */
   const int* counts;        /* world > 1: int32 [world] valid pairs per source */
   int* rep_of_row;          /* int32 [rows_local], INT_MAX everywhere on entry, restored on exit */
-  int* dup_flag;            /* int32 [max_entries], zero on entry, restored on exit */
+  int* dup_flag;            /* int32 [ntabs * max_entries] (one flag array per table), zero on entry, restored on exit */
   void* win_list;           /* int2 [max_entries] scratch (any contents) */
   int* win_count;           /* int32 [1] scratch */
   long long rows;           /* global (unsharded) row count */
   int id_stride, id_col, bag, E_local;   /* E_local = B * bag */
   int cap, world, rank, ntabs;
+  int max_entries, pad_;    /* capacity of the scratch arrays: >= B * bag (world == 1), >= the entries this rank can own (world > 1) */
   ZooEgTab t[ZOO_EG_MAX_TABS];
 } ZooEgGroup;
 

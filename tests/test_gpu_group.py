@@ -97,13 +97,13 @@ def test_route_and_grouped_update_emulated(world, dist_kind):
             e = p.g[c]
             rep = torch.full((rl,), INT_MAX, dtype=torch.int32, device="cuda")
             maxE = B if W == 1 else W * cap
-            dup = torch.zeros(maxE, dtype=torch.int32, device="cuda")
+            dup = torch.zeros(2 * maxE, dtype=torch.int32, device="cuda")
             win = torch.full((2 * maxE + 2,), -9, dtype=torch.int32, device="cuda")
             wc = torch.full((2,), 77, dtype=torch.int32, device="cuda")
             e.ids, e.id_stride, e.id_col, e.bag, e.E_local = ids[r].data_ptr(), 2, c, 1, B
             e.pairs, e.counts = pairs[c][r].data_ptr(), counts[c][r].data_ptr()
             e.rep_of_row, e.dup_flag, e.win_list, e.win_count = rep.data_ptr(), dup.data_ptr(), win.data_ptr(), wc.data_ptr()
-            e.rows, e.cap, e.world, e.rank, e.ntabs = rows[c], cap, W, r, 2
+            e.rows, e.cap, e.world, e.rank, e.ntabs, e.max_entries = rows[c], cap, W, r, 2, maxE
             keep += [win, wc]
             reps.append(rep)
             dups.append(dup)

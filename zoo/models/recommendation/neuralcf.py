@@ -65,10 +65,24 @@ class NeuralCF(Recommender):
         # ONE lookup for all four tables: [MLP-user | MLP-item | MF-user * MF-item]; the tower reads the first window, the
         # GMF product is the second.  Tables of one id column share their sparse update (zoo.ops.embedding_group).
         specs.append(LookupSpec(self.mf_user_embed, 0, mul_table=self.mf_item_embed, mul_col=1))
-        h_in, mf = multi_lookup(ids, specs, splits=[self.user_embed + self.item_embed, self.mf_embed])
-        h = self.mlp(h_in)
-        bits = getattr(h, "_zoo_relu_bits", None)
-        hc = torch.cat([h, mf.to(h.dtype)], dim=1)
+        hl = self.hidden_layers[-1]
+        h_in, mf, wide = multi_lookup(ids, specs, splits=[self.user_embed + self.item_embed, self.mf_embed],
+                                      embed=(1, hl + self.mf_embed, hl))
+        if wide is not None and hl % 8 == 0:
+            # fused concat: the gather wrote the GMF product into columns [hl, hl + mf) of `wide`, the last tower layer writes
+            # its output into columns [0, hl)
+            h = h_in
+            for layer in list(self.mlp)[:-1]:
+                h = layer(h)
+            h = self.mlp[-1](h, out=wide[:, :hl])
+            bits = getattr(h, "_zoo_relu_bits", None)
+            from ...ops.embedding_group import join_columns
+
+            hc = join_columns(wide, h, mf)
+        else:
+            h = self.mlp(h_in)
+            bits = getattr(h, "_zoo_relu_bits", None)
+            hc = torch.cat([h, mf.to(h.dtype)], dim=1)
         if bits is not None:                # sign bits of the MLP half travel with the concatenated activation
             hc._zoo_relu_bits = bits
         if self.mf_user_embed.world > 1 and hc.is_cuda and torch.is_grad_enabled():

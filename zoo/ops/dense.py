@@ -128,14 +128,18 @@ class _FusedDenseFn(torch.autograd.Function):
     when the parameters carry ``_zoo_grad`` views (set by the flat-parameter arena)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False, relu_input_cols=0, x_bits=None, emit_bits=False, dx_out=None):
+    def forward(ctx, x, weight, bias, w16, act, relu_input, skip_relu_bwd=False, relu_input_cols=0, x_bits=None, emit_bits=False, dx_out=None,
+                y_out=None):
         x16 = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
         if not _aligned(x16):
             x16 = _pad_cols(x16)
         bits = None
         if emit_bits:
             bits = torch.empty((x16.shape[0], (w16.shape[0] + 31) // 32), dtype=torch.int32, device=x16.device)
-        y = dense_forward(x16, w16, bias, act, relu_bits=bits)
+        if y_out is not None:      # the caller's column window of a wider buffer (fused concat); returned as a fresh view
+            y = dense_forward(x16, w16, bias, act, out=y_out, relu_bits=bits)[:, :]
+        else:
+            y = dense_forward(x16, w16, bias, act, relu_bits=bits)
         ctx.x_bits = x_bits
         ctx.dx_out = dx_out
         ctx.act = act
@@ -154,7 +158,7 @@ class _FusedDenseFn(torch.autograd.Function):
     def backward(ctx, dy, *_unused):
         x16, w16, y, weight, bias = ctx.saved_tensors
         if dy is None:
-            return (None,) * 11
+            return (None,) * 12
         dy16 = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
         if ctx.act == "relu":
             if not ctx.skip_relu_bwd:  # otherwise the consumer's dgrad epilogue already applied the mask
@@ -188,7 +192,7 @@ class _FusedDenseFn(torch.autograd.Function):
             dense_wgrad(dy16, x16[:, :K], dw_ret, gb)
         elif gb is not None:
             colsum(dy16, gb)
-        return dx, dw_ret, db_ret, None, None, None, None, None, None, None, None
+        return dx, dw_ret, db_ret, None, None, None, None, None, None, None, None, None
 
 
 def _pad_cols(t: torch.Tensor) -> torch.Tensor:
@@ -242,7 +246,8 @@ class FusedDense(nn.Module):
         """Called by the fused optimizer after it wrote the bf16 shadow itself."""
         self._shadow_version = self.weight._version
 
-    def forward(self, x):
+    def forward(self, x, out=None):
+        """`out` (CUDA path only): a bf16 [M, out_features] column window of a wider buffer that receives the result."""
         if _use_kernel(x):
             lead = x.shape[:-1]
             x2 = x.reshape(-1, x.shape[-1])
@@ -255,7 +260,7 @@ class FusedDense(nn.Module):
                 x_bits = None
             emit = self.activation == "relu" and self.skip_relu_bwd and torch.is_grad_enabled() and self.out_features % 32 == 0
             y = _FusedDenseFn.apply(x2, self.weight, self.bias, self.weight_bf16, self.activation, self.relu_input,
-                                    self.skip_relu_bwd, self.relu_input_cols, x_bits, emit, getattr(x, "_zoo_dx_out", None))
+                                    self.skip_relu_bwd, self.relu_input_cols, x_bits, emit, getattr(x, "_zoo_dx_out", None), out)
             bits = None
             if emit:
                 y, bits = y

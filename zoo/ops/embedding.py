@@ -534,7 +534,7 @@ def _flat_tables(specs):
     return ts
 
 
-def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None, splits=None):
+def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None, splits=None, embed=None):
     """ids: int64 [B, ncols].  specs: list of _LookupSpec.  Returns bf16 [B, sum(D)] on GPU, fp32 on CPU; with `splits`
     (a list of column widths summing to sum(D)) a tuple of those column windows instead."""
     if splits is not None:
@@ -546,12 +546,16 @@ def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None, s
             from . import embedding_group as _eg
 
             if len(specs) <= _eg.MAX_SPECS and _eg.eligible(specs):
-                return _eg.grouped_lookup(ids, specs, splits)
+                # embed = (split index, width, column): that split is produced inside a fresh [B, width] buffer, which is
+                # returned as one more element of the tuple (see zoo.ops.embedding_group.join_columns)
+                return _eg.grouped_lookup(ids, specs, splits, embed)
         full = multi_lookup(ids, specs, anchor)
         outs, off = [], 0
         for w in splits:
             outs.append(full[:, off:off + w])
             off += w
+        if embed is not None:
+            outs.append(None)      # no fused buffer on this path: the caller concatenates
         return tuple(outs)
     if ids.dim() == 1:
         ids = ids.unsqueeze(1)

@@ -37,7 +37,7 @@ class EgTab(C.Structure):
 class EgGroup(C.Structure):
     _fields_ = [("ids", _V), ("pairs", _V), ("counts", _V), ("rep_of_row", _V), ("dup_flag", _V), ("win_list", _V),
                 ("win_count", _V), ("rows", _L), ("id_stride", _I), ("id_col", _I), ("bag", _I), ("E_local", _I), ("cap", _I),
-                ("world", _I), ("rank", _I), ("ntabs", _I), ("t", EgTab * MAX_TABS)]
+                ("world", _I), ("rank", _I), ("ntabs", _I), ("max_entries", _I), ("pad_", _I), ("t", EgTab * MAX_TABS)]
 
 
 class EgParams(C.Structure):
@@ -165,7 +165,7 @@ class _Plan:
             tabs = [m[0] for m in g["members"]]
             for t in tabs:
                 t._ensure_state()
-            g["dup_flag"] = torch.zeros(g["maxE"], dtype=torch.int32, device=device)
+            g["dup_flag"] = torch.zeros(MAX_TABS * g["maxE"], dtype=torch.int32, device=device)
             g["win_list"] = torch.zeros(2 * g["maxE"] + 2, dtype=torch.int32, device=device)
             g["win_count"] = torch.zeros(2, dtype=torch.int32, device=device)
             g["accum"] = [torch.zeros((g["maxE"], t.embedding_dim), dtype=torch.float32, device=device) for t in tabs]
@@ -218,8 +218,9 @@ class _Plan:
         p.id_stride = ids.stride(0)
         for k, s in enumerate(self.specs):
             e = p.s[k]
-            e.out = out.data_ptr() + 2 * self.offsets[k]
-            e.ldo = out.stride(0)
+            dst, rel = out[k]          # (buffer, column offset inside it) for this lookup
+            e.out = dst.data_ptr() + 2 * rel
+            e.ldo = dst.stride(0)
             sv = saves.get(k)
             e.save_a, e.save_b = (sv[0].data_ptr(), sv[1].data_ptr()) if sv is not None else (None, None)
         return p
@@ -260,6 +261,15 @@ def _plan_for(specs, ids):
     return p
 
 
+def scratch_is_clean():
+    """True when every plan's backward scratch is back at its start values (duplicate flags and accumulation rows zero)."""
+    for p in _PLANS.values():
+        for g in p.groups:
+            if int(g["dup_flag"].sum()) != 0 or any(float(a.abs().sum()) != 0.0 for a in g["accum"]):
+                return False
+    return True
+
+
 def reset_plans():
     _PLANS.clear()
     _PENDING.clear()
@@ -267,7 +277,7 @@ def reset_plans():
 
 class _GroupedLookupFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, ids, plan, splits, *anchors):
+    def forward(ctx, ids, plan, splits, training, embed, *anchors):
         lib = _lib()
         B = ids.shape[0]
         if plan.sharded:
@@ -276,16 +286,27 @@ class _GroupedLookupFn(torch.autograd.Function):
         out = torch.empty((B, plan.ld), dtype=torch.bfloat16, device=ids.device)
         if plan.ld != plan.total:
             out[:, plan.total:].zero_()
+        dests = [(out, plan.offsets[k]) for k in range(len(plan.specs))]
+        wide = None
+        if embed is not None:
+            # one split lands directly in a column window of a wider, fresh buffer (the consumer's concat is fused away): the
+            # other columns of that buffer are filled by whoever produces them (FusedDense(out=...)), see `join_columns`
+            j, width, col = embed
+            wide = torch.empty((B, width), dtype=torch.bfloat16, device=ids.device)
+            lo = sum(splits[:j])
+            for k in range(len(plan.specs)):
+                if lo <= plan.offsets[k] < lo + splits[j]:
+                    dests[k] = (wide, col + plan.offsets[k] - lo)
         saves = {}
         for k, s in enumerate(plan.specs):
             if s.mul_table is None:
                 continue
             if plan.sharded:
                 saves[k] = plan.saves[k][:2]
-            elif torch.is_grad_enabled():
+            elif training:       # (grad mode is off inside Function.forward: the caller passes it in)
                 saves[k] = (torch.empty((B, s.dim), dtype=torch.bfloat16, device=ids.device),
                             torch.empty((B, s.dim), dtype=torch.bfloat16, device=ids.device))
-        _nl.check(lib.zoo_eg_gather(C.byref(plan.gather_params(ids, out, saves)), _nl.stream_ptr()), "zoo_eg_gather")
+        _nl.check(lib.zoo_eg_gather(C.byref(plan.gather_params(ids, dests, saves)), _nl.stream_ptr()), "zoo_eg_gather")
         ctx.plan, ctx.splits = plan, splits
         ctx.saves = saves
         flat = [ids] + [t for k in sorted(saves) for t in saves[k]]
@@ -293,9 +314,16 @@ class _GroupedLookupFn(torch.autograd.Function):
         if splits is None:
             return out[:, :plan.total]
         outs, off = [], 0
-        for w in splits:
-            outs.append(out[:, off:off + w])
+        for j, w in enumerate(splits):
+            if embed is not None and j == embed[0]:
+                outs.append(wide[:, embed[2]:embed[2] + w])
+            else:
+                outs.append(out[:, off:off + w])
             off += w
+        if wide is not None:
+            ctx.mark_non_differentiable(wide)
+            ctx.set_materialize_grads(False)
+            outs.append(wide)
         return tuple(outs)
 
     @staticmethod
@@ -320,7 +348,7 @@ class _GroupedLookupFn(torch.autograd.Function):
         _PENDING.append({"plan": plan, "ids": ids, "wins": wins, "saves": saves})
         if len(_PENDING) == 1:
             torch.autograd.Variable._execution_engine.queue_callback(flush_pending)
-        return (None, None, None) + (None,) * (len(ctx.needs_input_grad) - 3)
+        return (None,) * len(ctx.needs_input_grad)
 
 
 def _window_for(wins, col_off, width):
@@ -350,7 +378,7 @@ def flush_pending():
             e = EgGroup()
             tabs = g["members"]
             e.ids, e.id_stride, e.id_col, e.bag, e.E_local = ids.data_ptr(), ids.stride(0), g["col"], g["bag"], g["E"]
-            e.world, e.rank, e.ntabs, e.cap = plan.world, plan.rank, len(tabs), g["cap"]
+            e.world, e.rank, e.ntabs, e.cap, e.max_entries = plan.world, plan.rank, len(tabs), g["cap"], g["maxE"]
             e.rows = tabs[0][0].num_embeddings
             for table, _, _ in tabs:
                 table._ensure_state()
@@ -426,7 +454,30 @@ def flush_pending():
     del keep
 
 
-def grouped_lookup(ids, specs, splits=None):
+class _JoinFn(torch.autograd.Function):
+    """`wide` already holds its column windows (each written in place by its producer); this node only ties the producers'
+    autograd histories to the joined tensor.  Backward hands every producer its column window of the gradient (views)."""
+
+    @staticmethod
+    def forward(ctx, wide, *parts):
+        ctx.widths = [p.shape[1] for p in parts]
+        return wide.view_as(wide)
+
+    @staticmethod
+    def backward(ctx, d):
+        outs, off = [], 0
+        for w in ctx.widths:
+            outs.append(d[:, off:off + w])
+            off += w
+        return (None, *outs)
+
+
+def join_columns(wide, *parts):
+    """torch.cat(parts, 1) for parts that were produced directly inside `wide` (in column order)."""
+    return _JoinFn.apply(wide, *parts)
+
+
+def grouped_lookup(ids, specs, splits=None, embed=None):
     """ids int64 [B, ncols] on a CUDA device; returns bf16 [B, sum(D)] or, with `splits` (column widths), a tuple of windows of
     that buffer.  In a sharded run the attribute `_zoo_dx_out` of each result is peer-readable memory its gradient may be written
     into directly (FusedDense does)."""
@@ -436,7 +487,7 @@ def grouped_lookup(ids, specs, splits=None):
         anchors.append(s.table.anchor)
         if s.mul_table is not None:
             anchors.append(s.mul_table.anchor)
-    res = _GroupedLookupFn.apply(ids, plan, tuple(splits) if splits else None, *anchors)
+    res = _GroupedLookupFn.apply(ids, plan, tuple(splits) if splits else None, torch.is_grad_enabled(), embed, *anchors)
     if plan.sharded and torch.is_grad_enabled():
         if splits is None:
             res._zoo_dx_out = plan.dout[:, :plan.total]
