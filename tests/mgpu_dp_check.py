@@ -18,15 +18,18 @@ ctx = init_nncontext()
 torch.manual_seed(0)
 base = nn.Sequential(FusedMLP(64, [128, 64]), FusedDense(64, 8))
 results = {}
-for mode in ("nccl", "p2p", "p2p-owner", "nccl-clip", "p2p-clip"):
+for mode in ("nccl", "p2p", "nccl-adam", "p2p-owner", "nccl-clip", "p2p-clip"):
     m = copy.deepcopy(base)
     # "p2p": small arenas take the one-handshake push all-reduce with a bf16 wire (csrc/comm/ar_push.cu);
     # "p2p-owner": force the owner-computes reduce-scatter + optimizer + all-gather kernel (csrc/comm/rs_opt_ag.cu, fp32 wire)
     os.environ["ZOO_K1_SMALL"] = "0" if mode == "p2p-owner" else "auto"
-    eng = TrainingEngine(m, torch.optim.Adam(m.parameters(), lr=1e-2), ctx=ctx, grad_sync="nccl" if mode.startswith("nccl") else "p2p")
+    # the owner-computes path moves fp32 and must track NCCL + Adam to rounding; the push path rounds gradients to bf16, which
+    # Adam's normalisation would turn into +-lr steps on near-zero gradients, so wire-format parity is checked with SGD (linear)
+    opt = torch.optim.Adam(m.parameters(), lr=1e-2) if mode in ("nccl-adam", "p2p-owner") else torch.optim.SGD(m.parameters(), lr=0.05)
+    eng = TrainingEngine(m, opt, ctx=ctx, grad_sync="nccl" if mode.startswith("nccl") else "p2p")
     eng.use_cuda_graph = False
     if mode.endswith("clip"):
-        eng.set_gradient_clipping_by_l2_norm(0.05)
+        eng.set_gradient_clipping_by_l2_norm(0.2)
     eng.prepare()
     assert eng._dp.name == ("allreduce" if mode.startswith("nccl") else "p2p"), eng._dp.name
     if mode.startswith("p2p"):
@@ -45,11 +48,11 @@ for mode in ("nccl", "p2p", "p2p-owner", "nccl-clip", "p2p-clip"):
     torch.distributed.broadcast(w, src=0)
     assert torch.equal(w, results[mode]), f"{mode}: ranks diverged"
     eng.close()
-d_owner = (results["nccl"] - results["p2p-owner"]).abs().max().item()
+d_owner = (results["nccl-adam"] - results["p2p-owner"]).abs().max().item()
 d_push = (results["nccl"] - results["p2p"]).abs().max().item()        # gradients travel as bf16: Adam steps differ at rounding size
 d_clip = (results["nccl-clip"] - results["p2p-clip"]).abs().max().item()
 moved = (results["nccl-clip"] - results["nccl"]).abs().max().item()     # the clip must actually bite
-assert d_owner < 1e-4 and d_push < 3e-3 and d_clip < 3e-3 and moved > 1e-3, (d_owner, d_push, d_clip, moved)
+assert d_owner < 1e-4 and d_push < 2e-3 and d_clip < 2e-3 and moved > 2e-3, (d_owner, d_push, d_clip, moved)
 torch.distributed.barrier()
 if ctx.rank == 0:
     print(f"MGPU_DP_OK world={ctx.world_size} max|nccl-owner|={d_owner:.2e} max|nccl-push|={d_push:.2e} max|clip nccl-push|={d_clip:.2e}")

@@ -90,7 +90,9 @@ class NeuralCF(Recommender):
             # read their gradient rows in place (no staging copy of the MF half)
             from ...ops.embedding import ShardRuntime
 
-            hc._zoo_dx_out = ShardRuntime.get().stage(("ncf-last-dx", id(self), hc.shape[0]), tuple(hc.shape), torch.bfloat16)[1]
+            # (keyed by the table's serial number: an id() could be reused by a later object on one rank only, and symmetric
+            # allocations are collective)
+            hc._zoo_dx_out = ShardRuntime.get().stage(("ncf-last-dx", self.mf_user_embed.uid, hc.shape[0]), tuple(hc.shape), torch.bfloat16)[1]
         return self.linear_last(hc)
 
     def forward(self, x):

@@ -24,6 +24,7 @@ import torch.nn.functional as F
 from ..native import lib as _nl
 
 SPARSE_OPTS = {"sgd": 0, "adam": 1, "adagrad": 2}
+_TABLE_SERIAL = [0]      # construction order is the same on every rank (sharded tables are allocated collectively)
 INT_MAX = 2**31 - 1
 
 _V, _I, _L, _F = C.c_void_p, C.c_int, C.c_longlong, C.c_float
@@ -134,6 +135,8 @@ class EmbeddingTable(nn.Module):
                  world=1, rank=0, shadow_bf16=None, padding_idx=None, device=None):
         super().__init__()
         self.num_embeddings, self.embedding_dim = int(num_embeddings), int(embedding_dim)
+        _TABLE_SERIAL[0] += 1
+        self.uid = _TABLE_SERIAL[0]      # stable key for plans / staging buffers (id() values can be reused after a free)
         self.world, self.rank = int(world), int(rank)
         self.sparse = bool(sparse)
         self.optimizer = optimizer
@@ -408,7 +411,7 @@ class _MultiLookupFn(torch.autograd.Function):
             # backward DISPATCHES gradient rows to their owners (zoo_embedding_dispatch): forward stages nothing
             rt = ShardRuntime.get()
             rt.settle()
-            key = ("lookup", tuple((id(s.table), s.col, s.bag, id(s.mul_table), s.mul_col) for s in specs), B, ids.shape[1])
+            key = ("lookup", tuple((s.table.uid, s.col, s.bag, s.mul_table.uid if s.mul_table is not None else 0, s.mul_col) for s in specs), B, ids.shape[1])
             if torch.is_grad_enabled():
                 for k, s in enumerate(specs):      # receive buffers exist (collectively allocated) before the first backward
                     for which, t in enumerate([s.table] + ([s.mul_table] if s.mul_table is not None else [])):
@@ -418,7 +421,7 @@ class _MultiLookupFn(torch.autograd.Function):
             # ids (and GMF factors below) are staged in symmetric buffers: peers read them in backward
             rt = ShardRuntime.get()
             rt.settle()        # peers are done with what the previous backward staged before anything is staged again
-            key = ("lookup", tuple((id(s.table), s.col, s.bag, id(s.mul_table), s.mul_col) for s in specs), B, ids.shape[1])
+            key = ("lookup", tuple((s.table.uid, s.col, s.bag, s.mul_table.uid if s.mul_table is not None else 0, s.mul_col) for s in specs), B, ids.shape[1])
             # every rank PUSHES its id matrix into slot [rank] of every peer's copy, so the owner-side passes of backward
             # (election, duplicate accumulation) scan all world * B entries from local memory
             W, r = rt.ctx.world_size, rt.ctx.rank
