@@ -36,6 +36,7 @@ struct AttArgs {
   int causal;
   const float* mask;           // additive, [B, L] per key, or null
   __nv_bfloat16* out;          // [B, H, L, 64]
+  float* lse;                  // optional [B, H, L]: log2-domain log-sum-exp of every row's scaled, masked scores (for backward)
 };
 
 __global__ void __launch_bounds__(kAttThreads, 1)
@@ -205,6 +206,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       tc_fence_before();
     }
     if (q < a.L) {
+      if (a.lse) a.lse[row_base + q] = l > 0.f ? m + log2f(l) : INFINITY;      // a row with no live key: p = exp2(s - inf) = 0 in backward
       const float inv = l > 0.f ? 1.f / l : 0.f;
       __nv_bfloat16* orow = a.out + (row_base + q) * kAttD;
 #pragma unroll
@@ -260,8 +262,8 @@ static int att_tmap(CUtensorMap* m, const void* base, long long rows, int box_ro
 
 // out[B,H,L,64] = softmax(scale * q k^T + mask[b, key] (+ causal)) v ;  q, k, v, out: contiguous bf16 [B,H,L,64];
 // mask: additive fp32 [B, L] or null.
-ZOO_API int zoo_attention_fwd_bf16(const void* q, const void* k, const void* v, void* out, const float* mask, int B, int H, int L, int D,
-                                   float scale, int causal, void* stream) {
+static int attention_fwd_launch(const void* q, const void* k, const void* v, void* out, float* lse, const float* mask, int B, int H, int L,
+                                int D, float scale, int causal, void* stream) {
   if (!q || !k || !v || !out || B <= 0 || H <= 0 || L <= 0) { zoo_set_last_error("attention: bad arguments", __FILE__, __LINE__); return ZOO_ERR_ARG; }
   if (D != kAttD) { zoo_set_last_error("attention: the kernel is specialised for head dimension 64", __FILE__, __LINE__); return ZOO_ERR_ARG; }
   const long long rows = (long long)B * H * L;
@@ -272,7 +274,7 @@ ZOO_API int zoo_attention_fwd_bf16(const void* q, const void* k, const void* v, 
   if ((rc = att_tmap(&tk, k, rows, kAttBN))) return rc;
   if ((rc = att_tmap(&tv, v, rows, 64))) return rc;
   AttArgs a{};
-  a.B = B; a.H = H; a.L = L; a.scale = scale; a.causal = causal; a.mask = mask; a.out = (__nv_bfloat16*)out;
+  a.B = B; a.H = H; a.L = L; a.scale = scale; a.causal = causal; a.mask = mask; a.out = (__nv_bfloat16*)out; a.lse = lse;
   static bool attr_set = false;
   if (!attr_set) {
     ZOO_CUDA_CHECK(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem));
@@ -282,4 +284,16 @@ ZOO_API int zoo_attention_fwd_bf16(const void* q, const void* k, const void* v, 
   attention_fwd_kernel<<<(unsigned)((long long)B * H * q_tiles), kAttThreads, kAttSmem, (cudaStream_t)stream>>>(tq, tk, tv, a);
   ZOO_CUDA_CHECK(cudaGetLastError());
   return ZOO_OK;
+}
+
+ZOO_API int zoo_attention_fwd_bf16(const void* q, const void* k, const void* v, void* out, const float* mask, int B, int H, int L, int D,
+                                   float scale, int causal, void* stream) {
+  return attention_fwd_launch(q, k, v, out, nullptr, mask, B, H, L, D, scale, causal, stream);
+}
+
+// Forward that also writes lse[B,H,L] (fp32, log2 domain), which zoo_attention_bwd_bf16 needs to recompute the probabilities.
+ZOO_API int zoo_attention_fwd_lse_bf16(const void* q, const void* k, const void* v, void* out, float* lse, const float* mask, int B, int H,
+                                       int L, int D, float scale, int causal, void* stream) {
+  if (!lse) { zoo_set_last_error("attention: lse buffer missing", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+  return attention_fwd_launch(q, k, v, out, lse, mask, B, H, L, D, scale, causal, stream);
 }

@@ -972,6 +972,9 @@ static __device__ __align__(256) unsigned char g_zoo_noalloc_scratch[zoo::kNaTot
 
 namespace zoo {
 constexpr int kNaMaxDevices = 64;
+// Cache of the array's device address per device ordinal.  Several host threads may fill an entry at the same time without a
+// lock: every writer stores the SAME value (cudaGetSymbolAddress is a pure lookup for a given device), a pointer-sized store
+// is not torn on the supported hosts, and a reader that still sees null simply repeats the lookup.
 static void* g_na_base[kNaMaxDevices] = {nullptr};
 
 // Per-device set-up: resolve the device address of the static array for the CURRENT device.

@@ -171,13 +171,11 @@ class Broker {
     listen_fd_ = -1;
     cv_.notify_all();
     if (acceptor_.joinable()) acceptor_.join();
-    std::vector<std::thread> ws;
     {
       std::lock_guard<std::mutex> lk(conn_mu_);
       for (int c : conns_) ::shutdown(c, SHUT_RDWR);
-      ws.swap(workers_);
     }
-    for (auto& t : ws) if (t.joinable()) t.join();
+    for (int spin = 0; active_conns_.load() > 0 && spin < 5000; ++spin) std::this_thread::sleep_for(std::chrono::milliseconds(1));
     stopping_ = false;
   }
 
@@ -343,7 +341,11 @@ class Broker {
     else if (!parse_id(a[i], &e.id) || !(s.last_id < e.id)) { r_err(out, "The ID specified in XADD is equal or smaller than the target stream top item"); return; }
     ++i;
     size_t bytes = 32;
-    for (; i + 1 < a.size(); i += 2) { e.fields.emplace_back(a[i], a[i + 1]); bytes += a[i].size() + a[i + 1].size() + 16; }
+    for (; i + 1 < a.size(); i += 2) {
+      // packed batch reads join the uris of a batch with '\n' (read_pack / hset_topn): a uri may not contain one
+      if (a[i] == "uri" && a[i + 1].find('\n') != std::string::npos) { r_err(out, "the uri field must not contain a newline"); return; }
+      e.fields.emplace_back(a[i], a[i + 1]); bytes += a[i].size() + a[i + 1].size() + 16;
+    }
     if (maxmemory_ > 0 && used_ + (long long)bytes > maxmemory_) { out += "-OOM command not allowed when used memory > 'maxmemory'.\r\n"; return; }
     e.bytes = bytes;
     used_ += bytes;
@@ -561,38 +563,63 @@ class Broker {
       setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
       std::lock_guard<std::mutex> lk(conn_mu_);
       conns_.insert(c);
-      workers_.emplace_back([this, c] { conn_loop(c); });
+      ++active_conns_;
+      std::thread([this, c] { conn_loop(c); --active_conns_; }).detach();      // finished connections leave nothing behind
     }
   }
 
-  static bool parse_one(const std::string& buf, size_t& pos, std::vector<std::string>& args) {
-    // returns false when more bytes are needed; supports RESP arrays of bulk strings and inline commands
+  // Limits of the socket protocol: a client that exceeds them (or sends something that is not RESP) gets -ERR and is disconnected,
+  // instead of growing the connection buffer without bound.
+  static constexpr long long kMaxBulk = 512LL << 20;      // one argument (a base64 image batch is a few MB)
+  static constexpr long long kMaxArgs = 1 << 20;          // arguments per command
+  static constexpr size_t kMaxInline = 64 << 10;          // an inline (non-array) command line
+  static constexpr size_t kMaxBuffered = 1ULL << 30;      // unparsed bytes per connection
+
+  // 1 = one command parsed (pos advanced), 0 = need more bytes, -1 = protocol error
+  static int parse_one(const std::string& buf, size_t& pos, std::vector<std::string>& args) {
     args.clear();
-    if (pos >= buf.size()) return false;
+    if (pos >= buf.size()) return 0;
     size_t p = pos;
-    auto line = [&](std::string& l) -> bool { size_t e = buf.find("\r\n", p); if (e == std::string::npos) return false; l = buf.substr(p, e - p); p = e + 2; return true; };
+    bool too_long = false;
+    auto line = [&](std::string& l, size_t limit) -> bool {
+      size_t e = buf.find("\r\n", p);
+      if (e == std::string::npos) { if (buf.size() - p > limit) too_long = true; return false; }
+      if (e - p > limit) { too_long = true; return false; }
+      l = buf.substr(p, e - p); p = e + 2; return true;
+    };
+    auto number = [](const std::string& l, long long& out) -> bool {
+      if (l.size() < 2 || l.size() > 20) return false;
+      size_t i = 1;
+      if (l[i] == '-') ++i;
+      if (i >= l.size()) return false;
+      for (size_t k = i; k < l.size(); ++k) if (l[k] < '0' || l[k] > '9') return false;
+      out = atoll(l.c_str() + 1);
+      return true;
+    };
     if (buf[p] != '*') {
       std::string l;
-      if (!line(l)) return false;
+      if (!line(l, kMaxInline)) return too_long ? -1 : 0;
       size_t s = 0;
       while (s < l.size()) { size_t e = l.find(' ', s); if (e == std::string::npos) e = l.size(); if (e > s) args.push_back(l.substr(s, e - s)); s = e + 1; }
       pos = p;
-      return true;
+      return 1;
     }
     std::string l;
-    if (!line(l)) return false;
-    long long n = atoll(l.c_str() + 1);
+    if (!line(l, 32)) return too_long ? -1 : 0;
+    long long n = 0;
+    if (!number(l, n) || n < 0 || n > kMaxArgs) return -1;
     for (long long k = 0; k < n; ++k) {
-      if (!line(l)) return false;
-      if (l.empty() || l[0] != '$') return false;
-      long long len = atoll(l.c_str() + 1);
+      if (!line(l, 32)) return too_long ? -1 : 0;
+      long long len = 0;
+      if (l.empty() || l[0] != '$' || !number(l, len) || len > kMaxBulk) return -1;
       if (len < 0) { args.emplace_back(); continue; }
-      if (p + (size_t)len + 2 > buf.size()) return false;
+      if (p + (size_t)len + 2 > buf.size()) return 0;
+      if (buf[p + (size_t)len] != '\r' || buf[p + (size_t)len + 1] != '\n') return -1;
       args.emplace_back(buf, p, (size_t)len);
       p += (size_t)len + 2;
     }
     pos = p;
-    return true;
+    return 1;
   }
 
   void conn_loop(int fd) {
@@ -605,12 +632,18 @@ class Broker {
       buf.append(tmp, (size_t)n);
       size_t pos = 0;
       std::string reply;
-      while (parse_one(buf, pos, args)) {
+      int st;
+      while ((st = parse_one(buf, pos, args)) == 1) {
         if (args.empty()) continue;
         if (upper(args[0]) == "QUIT") { reply += "+OK\r\n"; running_conn_quit(fd, reply); goto done; }
         reply += execute(args);
       }
       buf.erase(0, pos);
+      if (st < 0 || buf.size() > kMaxBuffered) {
+        reply += "-ERR Protocol error: malformed or oversized request\r\n";
+        send_all(fd, reply);
+        break;
+      }
       if (!reply.empty() && !send_all(fd, reply)) break;
     }
   done:
@@ -637,7 +670,7 @@ class Broker {
   std::thread acceptor_;
   std::mutex conn_mu_;
   std::set<int> conns_;
-  std::vector<std::thread> workers_;
+  std::atomic<int> active_conns_{0};
 };
 
 }  // namespace

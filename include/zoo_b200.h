@@ -47,11 +47,18 @@ int zoo_dense_wgrad_bias_bf16(const void* dy, long long lddy, const void* x, lon
                               long long lddw, float* db, int M, int N, int K, void* stream);
 int zoo_colsum_bf16(const void* x, long long ldx, int rows, int cols, float* out, void* stream);
 
-/* ---- K8: blockwise attention forward (csrc/ops/attention.cu) ---------------------------------
- * out[B,H,L,64] = softmax(scale * q k^T + mask[b,key] (+causal)) v; q, k, v, out contiguous bf16 [B,H,L,64]; mask additive
- * fp32 [B,L] or null.  Head dimension 64 only.  Not yet validated on hardware (see the file header); opt in with
- * ZOO_ATTN_KERNEL=1 on the Python side. */
+/* ---- K8: blockwise attention, forward and backward (csrc/ops/attention.cu, csrc/ops/attention_bwd.cu) ------------
+ * Replaces the dense [batch, heads, L, L] attention of TransformerLayer.scala:163-181 (mm -> mask -> softmax -> mm) and its
+ * autograd.  out[B,H,L,64] = softmax(scale * q k^T + mask[b,key] (+causal)) v; q, k, v, out contiguous bf16 [B,H,L,64]; mask
+ * additive fp32 [B,L] or null.  Head dimension 64 only.  The _lse form also writes one fp32 log-sum-exp per row (log2 domain),
+ * which the backward needs to recompute the probabilities block by block. */
 int zoo_attention_fwd_bf16(const void* q, const void* k, const void* v, void* out, const float* mask, int B, int H, int L, int D,
+                           float scale, int causal, void* stream);
+int zoo_attention_fwd_lse_bf16(const void* q, const void* k, const void* v, void* out, float* lse, const float* mask, int B, int H,
+                               int L, int D, float scale, int causal, void* stream);
+/* delta: fp32 [B,H,L] scratch (written); dq: fp32 [B,H,L,64], ZERO on entry (key blocks accumulate); dk, dv: bf16 [B,H,L,64]. */
+int zoo_attention_bwd_bf16(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
+                           float* delta, const float* mask, float* dq, void* dk, void* dv, int B, int H, int L, int D,
                            float scale, int causal, void* stream);
 
 /* ---- K2/K4: embedding gather and sparse optimizer (csrc/ops/embedding.cu) --------------------
@@ -197,7 +204,21 @@ int zoo_pair_score(const void* probs, long long ldp, long long P, int C, int dty
                    long long* rank_key, void* stream);
 int zoo_segment_head(const long long* keys, long long P, int n, unsigned char* keep, void* stream);
 
+/* ---- K2/K4 grouped form (csrc/ops/embedding_group.cu): parameter blocks and entry points in zoo_emb_group.h ---- */
+
+/* ---- K1, small-range form (csrc/comm/ar_push.cu): one-handshake all-reduce with a bf16 wire --------------------
+ * Replaces AllReduceParameter's put / aggregate of gradient slices (Topology.scala:1128-1206; FP16-compressed blocks,
+ * Topology.scala:1043-1047) for dense parts of a few MB.  zoo_ar_push: bf16 copies of g[0..n) into every rank's mailbox
+ * (mail: HOST array of `world` device pointers, each [2][world][n] bf16; flags: [2][world][1024] uint32, zero at start;
+ * epoch: local uint32 [2][1024], zero at start) -- never waits.  zoo_ar_reduce: waits for every rank's push of this step and
+ * leaves the fp32 sum (rank order) in g.  Same `grid` on every rank for both; n % 8 == 0. */
+int zoo_ar_push(float* g, void* const* mail, void* const* flags, unsigned int* epoch, long long n, int world, int rank,
+                int grid, void* stream);
+int zoo_ar_reduce(float* g, void* const* mail, void* const* flags, unsigned int* epoch, long long n, int world, int rank,
+                  int grid, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
+#include "zoo_emb_group.h"
 #endif /* ZOO_B200_H_ */

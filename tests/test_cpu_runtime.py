@@ -162,3 +162,29 @@ def test_broker_native_topn_results_match_python_format():
     with pytest.raises(RespError):
         b.hset_topn("result:", "value", b"zzz\n", idx[:1], val[:1])
     b.close()
+
+
+def test_broker_socket_rejects_malformed_requests():
+    """A request that is not RESP (or is oversized) is answered with -ERR and the connection is closed; the broker keeps serving."""
+    import socket
+
+    from zoo.native import rt
+
+    b = rt.Broker()
+    port = b.serve("127.0.0.1", 0)
+    try:
+        for bad in (b"*2\r\n$3\r\nGET\r\nnot-a-bulk-header\r\n", b"*99999999999\r\n", b"*1\r\n$-5x\r\n", b"*1\r\n$4\r\nPINGxx"):
+            c = socket.create_connection(("127.0.0.1", port), timeout=5)
+            c.sendall(bad)
+            data = c.recv(4096)
+            assert data.startswith(b"-ERR"), (bad, data)
+            assert c.recv(16) == b""            # closed by the server
+            c.close()
+        c = socket.create_connection(("127.0.0.1", port), timeout=5)
+        c.sendall(b"*1\r\n$4\r\nPING\r\n")
+        assert c.recv(64).startswith(b"+PONG")
+        c.sendall(b"*5\r\n$4\r\nXADD\r\n$1\r\ns\r\n$1\r\n*\r\n$3\r\nuri\r\n$3\r\na\nb\r\n")
+        assert c.recv(128).startswith(b"-ERR")
+        c.close()
+    finally:
+        b.stop_server()

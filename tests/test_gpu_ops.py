@@ -181,3 +181,27 @@ def test_sigmoid_bce():
     r.backward()
     torch.testing.assert_close(l, r, atol=1e-5, rtol=1e-4)
     torch.testing.assert_close(x.grad, xr.grad, atol=1e-7, rtol=1e-3)
+
+
+def test_mean_pooled_padded_bags_match_cpu():
+    """Mean pooling divides by the number of PRESENT ids (padding = -1) in forward AND backward, on the GPU kernels and on the
+    plain-torch CPU path alike."""
+    import copy
+
+    from zoo.ops.embedding import EmbeddingTable, lookup
+
+    torch.manual_seed(0)
+    rows, D, B, bag = 50, 16, 64, 4
+    t_cpu = EmbeddingTable(rows, D, sparse=False)
+    t_gpu = copy.deepcopy(t_cpu).cuda()
+    ids = torch.randint(0, rows, (B, bag))
+    ids[torch.rand(B, bag) < 0.4] = -1
+    ids[:, 0] = torch.randint(0, rows, (B,))               # at least one present id per bag
+    w = torch.randn(B, D)
+    out_c = lookup(ids, t_cpu, 0, bag, mean=True)
+    (out_c * w).sum().backward()
+    out_g = lookup(ids.cuda(), t_gpu, 0, bag, mean=True)
+    (out_g.float() * w.cuda()).sum().backward()
+    torch.testing.assert_close(out_g.float().cpu(), out_c, atol=2e-2, rtol=2e-2)
+    g_gpu = t_gpu.weight.grad if t_gpu.weight.grad is not None else t_gpu.weight._zoo_grad
+    torch.testing.assert_close(g_gpu.float().cpu(), t_cpu.weight.grad, atol=3e-2, rtol=3e-2)

@@ -84,3 +84,32 @@ def test_noalloc_rejects_oversized_problems():
     assert lib.zoo_embedding_sparse_update_noalloc(*base, (1 << 20) + 1, 1, 0, 64, *tail) == 3  # too many rows
     big = [ids.data_ptr(), 1, 0, 8193, 1, dout.data_ptr(), 256, None, 0, 1.0]
     assert lib.zoo_embedding_sparse_update_noalloc(*big, 4, 1, 0, 64, *tail) == 3               # too many entries
+
+
+def test_noalloc_on_a_shard_of_a_two_rank_table():
+    """world = 2: the caller owns the odd rows of a table with an odd row count (local rows = rows / world rounded up); only
+    entries of its own rows are applied, exactly like the regular entry point."""
+    lib = _lib()
+    torch.manual_seed(1)
+    rows, D, B, world, rank = 5001, 32, 2048, 2, 1
+    rows_local = (rows + world - 1) // world
+    stream = torch.cuda.current_stream().cuda_stream
+    w0 = torch.randn(rows_local, D, device="cuda") * 0.1
+    st = {n: dict(w=w0.clone(), m=torch.zeros(rows_local, D, device="cuda"), v=torch.zeros(rows_local, D, device="cuda")) for n in ("ref", "new")}
+    rep = torch.full((rows_local,), INT_MAX, dtype=torch.int32, device="cuda")
+    accum = torch.zeros(B, D, device="cuda")
+    dup = torch.zeros(B, dtype=torch.int32, device="cuda")
+    for call in (1, 2):
+        ids = torch.randint(0, rows, (B, 1), device="cuda")
+        dout = torch.randn(B, D, device="cuda").to(torch.bfloat16)
+        hyper = _hyper(call)
+        common = lambda s: [ids.data_ptr(), 1, 0, B, 1, dout.data_ptr(), D, None, 0, 1.0, rows, world, rank, D, s["w"].data_ptr(),
+                            None, s["m"].data_ptr(), s["v"].data_ptr(), 1, hyper.data_ptr()]
+        assert lib.zoo_embedding_sparse_update(*common(st["ref"]), rep.data_ptr(), accum.data_ptr(), dup.data_ptr(), stream) == 0
+        assert lib.zoo_embedding_sparse_update_noalloc(*common(st["new"]), stream) == 0, lib.zoo_last_error()
+        torch.cuda.synchronize()
+        torch.testing.assert_close(st["new"]["w"], st["ref"]["w"], atol=2e-3, rtol=2e-2)
+        torch.testing.assert_close(st["new"]["v"], st["ref"]["v"], atol=2e-3, rtol=2e-2)
+    owned = torch.zeros(rows_local, dtype=torch.bool, device="cuda")
+    owned[(ids[:, 0][ids[:, 0] % world == rank]) // world] = True
+    assert not torch.equal(st["new"]["w"][owned], w0[owned])

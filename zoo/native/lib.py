@@ -25,6 +25,8 @@ _CUDA_SIGS = {
     "zoo_dense_fwd_bf16_bits": [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p],
     "zoo_dense_dgrad_bf16_bits": [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_int, c_int, c_void_p, c_ll, c_int, c_int, c_int, c_void_p],
     "zoo_attention_fwd_bf16": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p],
+    "zoo_attention_fwd_lse_bf16": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p],
+    "zoo_attention_bwd_bf16": [c_void_p] * 11 + [c_int, c_int, c_int, c_int, c_float, c_int, c_void_p],
     "zoo_dense_wgrad_bias_bf16": [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_int, c_int, c_int, c_void_p],
     "zoo_dense_wgrad_bf16": [c_void_p, c_ll, c_void_p, c_ll, c_void_p, c_ll, c_int, c_int, c_int, c_void_p],
     "zoo_embedding_gather": [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_ll, c_void_p, c_ll, c_int,

@@ -3,10 +3,9 @@
 Reference: TransformerLayer.scala:163-181 materialises `[batch, heads, L, L]` scores (`mm(q,k)` -> mask ->
 softmax -> dropout -> `mm(w,v)`).  Here one fused call is used: blockwise (flash-style) attention through
 torch's SDPA on the GPU, which never writes the L x L matrix; the explicit reference math is kept as
-`attention_reference` (CPU path and oracle).  The hand-written tcgen05 kernel for this op (K8, csrc/ops/attention.cu: forward,
-head dimension 64, key-padding mask and causal) was written after round 1's GPU budget was spent and has not run on hardware
-yet: it is taken only with ZOO_ATTN_KERNEL=1 and only for inference calls; until it is validated this op counts as a library
-call.
+`attention_reference` (CPU path and oracle).  The hand-written tcgen05 kernels for this op (K8: csrc/ops/attention.cu forward, csrc/ops/attention_bwd.cu
+backward with recomputed probabilities; head dimension 64, key-padding mask and causal) are the default on the GPU; the cases they do
+not cover (other head dimensions, arbitrary [L, L] masks, attention dropout in training) take torch SDPA.
 """
 from __future__ import annotations
 
@@ -73,24 +72,59 @@ def attention_blockwise_reference(q, k, v, key_mask=None, causal=False, scale=Tr
     return out
 
 
-def attention_kernel(q, k, v, key_mask=None, causal=False, scale=True):
-    """K8 forward.  q, k, v: [B, H, L, 64] (any float dtype; computed in bf16); key_mask: additive [B, L] or None."""
-    from ..native import lib as _nl
+class _AttentionFn(torch.autograd.Function):
+    """K8: forward keeps one log-sum-exp per row; backward recomputes the probabilities block by block (csrc/ops/attention_bwd.cu)."""
 
-    B, H, L, D = q.shape
-    q16, k16, v16 = (t.to(torch.bfloat16).contiguous() for t in (q, k, v))
-    out = torch.empty_like(q16)
-    km = None if key_mask is None else key_mask.to(torch.float32).contiguous()
-    _nl.check(_nl.cuda_lib().zoo_attention_fwd_bf16(q16.data_ptr(), k16.data_ptr(), v16.data_ptr(), out.data_ptr(), _nl.ptr(km), B, H, L, D,
-                                                    (1.0 / math.sqrt(D)) if scale else 1.0, int(causal), _nl.stream_ptr()), "zoo_attention_fwd_bf16")
-    return out.to(q.dtype)
+    @staticmethod
+    def forward(ctx, q, k, v, key_mask, causal, scale):
+        from ..native import lib as _nl
+
+        B, H, L, D = q.shape
+        q16, k16, v16 = (t.to(torch.bfloat16).contiguous() for t in (q, k, v))
+        out = torch.empty_like(q16)
+        km = None if key_mask is None else key_mask.to(torch.float32).contiguous()
+        sc = (1.0 / math.sqrt(D)) if scale else 1.0
+        need_bwd = any(ctx.needs_input_grad[:3])
+        lib = _nl.cuda_lib()
+        if need_bwd:
+            lse = torch.empty((B, H, L), dtype=torch.float32, device=q.device)
+            _nl.check(lib.zoo_attention_fwd_lse_bf16(q16.data_ptr(), k16.data_ptr(), v16.data_ptr(), out.data_ptr(), lse.data_ptr(), _nl.ptr(km),
+                                                     B, H, L, D, sc, int(causal), _nl.stream_ptr()), "zoo_attention_fwd_lse_bf16")
+            ctx.save_for_backward(q16, k16, v16, out, lse, km)
+            ctx.sc, ctx.causal, ctx.dtypes = sc, bool(causal), (q.dtype, k.dtype, v.dtype)
+        else:
+            _nl.check(lib.zoo_attention_fwd_bf16(q16.data_ptr(), k16.data_ptr(), v16.data_ptr(), out.data_ptr(), _nl.ptr(km), B, H, L, D, sc,
+                                                 int(causal), _nl.stream_ptr()), "zoo_attention_fwd_bf16")
+        return out.to(q.dtype)
+
+    @staticmethod
+    def backward(ctx, d_out):
+        from ..native import lib as _nl
+
+        q16, k16, v16, out, lse, km = ctx.saved_tensors
+        B, H, L, D = q16.shape
+        do16 = d_out.to(torch.bfloat16).contiguous()
+        dq = torch.zeros((B, H, L, D), dtype=torch.float32, device=q16.device)       # key blocks accumulate into it
+        dk, dv = torch.empty_like(k16), torch.empty_like(v16)
+        delta = torch.empty((B, H, L), dtype=torch.float32, device=q16.device)
+        _nl.check(_nl.cuda_lib().zoo_attention_bwd_bf16(q16.data_ptr(), k16.data_ptr(), v16.data_ptr(), out.data_ptr(), do16.data_ptr(),
+                                                        lse.data_ptr(), delta.data_ptr(), _nl.ptr(km), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(),
+                                                        B, H, L, D, ctx.sc, int(ctx.causal), _nl.stream_ptr()), "zoo_attention_bwd_bf16")
+        _nl.LAUNCH_COUNT["n"] += 1      # delta pre-pass + the main kernel
+        tq, tk, tv = ctx.dtypes
+        return dq.to(tq), dk.to(tk), dv.to(tv), None, None, None
+
+
+def attention_kernel(q, k, v, key_mask=None, causal=False, scale=True):
+    """K8.  q, k, v: [B, H, L, 64] (any float dtype; computed in bf16); key_mask: additive [B, L] or None.  Differentiable."""
+    return _AttentionFn.apply(q, k, v, key_mask, causal, scale)
 
 
 def _kernel_eligible(q, additive_mask, dropout_p, training):
-    if os.environ.get("ZOO_ATTN_KERNEL", "0") != "1" or q.shape[-1] != 64 or (dropout_p > 0 and training):
+    """The kernel covers head dimension 64, key-padding masks and the causal mask, without attention dropout in training (the
+    remaining cases take torch SDPA).  ZOO_ATTN_KERNEL=0 switches it off."""
+    if os.environ.get("ZOO_ATTN_KERNEL", "1") == "0" or q.shape[-1] != 64 or (dropout_p > 0 and training):
         return False
-    if torch.is_grad_enabled() and q.requires_grad:
-        return False                      # forward only: training goes through SDPA
     if additive_mask is None:
         return True
     m = additive_mask                     # only key-padding masks [B, 1, 1, L] (or [B, L]) map onto the kernel

@@ -492,7 +492,13 @@ class _MultiLookupFn(torch.autograd.Function):
             if ctx.has_save[2 * k]:
                 sa, sb = saved[si], saved[si + 1]
                 si += 2
-            scale = 1.0 / s.bag if (s.mean and s.bag > 1) else 1.0
+            scale = 1.0
+            if s.mean and s.bag > 1:
+                # mean pooling divides by the number of PRESENT ids of the bag (the reference's sparse `mean` combiner; the forward
+                # kernel does the same), so every sample's gradient row is scaled by 1 / count before it is scattered
+                idc = ids[:, s.col:s.col + s.bag]
+                cnt = ((idc >= 0) & (idc < s.table.num_embeddings)).sum(1).clamp(min=1).to(torch.float32)
+                win = (win.float() / cnt[:, None]).to(torch.bfloat16)
             pairs = [(s.table, s.col, sb, 1)]
             if s.mul_table is not None:
                 pairs.append((s.mul_table, s.mul_col, sa, 0))
@@ -506,6 +512,8 @@ class _MultiLookupFn(torch.autograd.Function):
                     jobs.append((table, rb))
                     grads.append(None)
                 elif table.world > 1:
+                    if s.mean and s.bag > 1:
+                        raise NotImplementedError("mean-pooled bags over row-sharded tables are not supported (use sum pooling)")
                     if not table.sparse:
                         raise _nl.NativeError("row-sharded tables are trained with the sparse optimizer (sparse=True)")
                     mb = ctx.mul_bufs[k][which] if (mul is not None and ctx.mul_bufs[k] is not None) else None
@@ -586,7 +594,7 @@ def multi_lookup(ids: torch.Tensor, specs, anchor: torch.Tensor | None = None, s
             idb = ids[:, s.mul_col:s.mul_col + s.bag].long()
             okb = (idb >= 0) & (idb < s.mul_table.num_embeddings)
             e = e * (s.mul_table.lookup_torch(idb.clamp(0, s.mul_table.num_embeddings - 1)) * okb.unsqueeze(-1))
-        e = e.mean(1) if (s.mean and s.bag > 1) else e.sum(1)
+        e = e.sum(1) / ok.sum(1, keepdim=True).clamp(min=1).to(e.dtype) if (s.mean and s.bag > 1) else e.sum(1)
         outs.append(e)
     return torch.cat(outs, dim=1) if len(outs) > 1 else outs[0]
 
