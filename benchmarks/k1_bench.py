@@ -18,10 +18,16 @@ mp = float(sys.argv[1]) if len(sys.argv) > 1 else 25.6
 n = int(mp * 1e6) // 4096 * 4096
 rows = n // 4096
 out = {}
-for mode in ("nccl", "p2p"):
+nvls = {}
+for mode in ("nccl", "p2p", "p2p-nonvls"):
+    os.environ["ZOO_NVLS"] = "0" if mode == "p2p-nonvls" else "1"
+    if mode == "p2p-nonvls":
+        from zoo.parallel import symm as _symm
+
+        _symm._HEAP._mc_gran = None         # re-decide multicast for the buffers of this mode
     torch.manual_seed(0)
     m = nn.Linear(4096, rows, bias=False).to(ctx.device)
-    eng = TrainingEngine(m, torch.optim.Adam(m.parameters(), lr=1e-3), ctx=ctx, grad_sync=mode)
+    eng = TrainingEngine(m, torch.optim.Adam(m.parameters(), lr=1e-3), ctx=ctx, grad_sync="nccl" if mode == "nccl" else "p2p")
     eng.use_cuda_graph = False
     eng.prepare()
     g = eng.fopt.arena.flat_g
@@ -40,6 +46,7 @@ for mode in ("nccl", "p2p"):
     t = torch.tensor([sorted(ts)[len(ts) // 2]], device=ctx.device)
     torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     out[mode] = float(t)
+    nvls[mode] = bool(getattr(eng._dp, "nvls", False))
     chk = eng.fopt.arena.flat_p.double().sum().reshape(1)
     lo, hi = chk.clone(), chk.clone()
     torch.distributed.all_reduce(lo, op=torch.distributed.ReduceOp.MIN)
@@ -52,6 +59,9 @@ if ctx.rank == 0:
     out_bytes = (W - 1) / W * n * (4 + 2)
     in_bytes = (W - 1) / W * n * 4
     roof_ms = max(out_bytes, in_bytes) / 900e9 * 1e3
-    print(f"K1_BENCH world={W} params={n / 1e6:.1f}M  p2p fused {out['p2p']:.3f} ms  nccl all-reduce + optimizer {out['nccl']:.3f} ms  "
-          f"NVLink roofline {roof_ms:.3f} ms -> {100 * roof_ms / out['p2p']:.0f} % of roofline; speed-up {out['nccl'] / out['p2p']:.2f}x")
+    # roofline per the profiling recipe: bytes that must cross NVLink per GPU and direction / 770 GB/s (measured peer copy)
+    roof770 = max(out_bytes, in_bytes) / 770e9 * 1e3
+    print(f"K1_BENCH world={W} params={n / 1e6:.1f}M  fused (NVLS={nvls['p2p']}) {out['p2p']:.3f} ms  fused peer-pointer path {out['p2p-nonvls']:.3f} ms  "
+          f"nccl all-reduce + optimizer {out['nccl']:.3f} ms  NVLink roofline {roof_ms:.3f} ms @900 / {roof770:.3f} ms @770 GB/s -> "
+          f"{100 * roof770 / min(out['p2p'], out['p2p-nonvls']):.0f} % of the 770 GB/s roofline; speed-up over nccl {out['nccl'] / min(out['p2p'], out['p2p-nonvls']):.2f}x")
 torch.distributed.barrier()

@@ -47,7 +47,27 @@ struct RsArgs {
   long long start, end;              // arena range of this launch; (end - start) % (4 * world) == 0
   int world, rank, emulate, opt, zero_grad;
   int replicated;                    // 1: every rank reduces and updates the WHOLE range locally (no publish stores)
+  // NVLS: multicast addresses of the local gradient / parameter / shadow arenas (null = peer loads and stores).  One
+  // multimem.ld_reduce returns the sum of every GPU's gradients (reduced inside the NVSwitch), one multimem.st writes all copies.
+  const float* g_mc;
+  float* p_mc;
+  __nv_bfloat16* p16_mc;
+  int clip;                          // 1: clamp the summed gradient to [clip_lo, clip_hi] (bounds already divided by the gradient scale)
+  float clip_lo, clip_hi;
 };
+
+__device__ __forceinline__ float4 mm_ld_reduce_f32x4(const float* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+  return r;
+}
+__device__ __forceinline__ void mm_st_f32x4(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void mm_st_bf16x4(__nv_bfloat16* mc, const uint2& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" :: "l"(mc), "r"(v.x), "r"(v.y) : "memory");
+}
 
 __device__ __forceinline__ float4 ld_f4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 
@@ -86,12 +106,20 @@ rs_opt_ag_kernel(const RsArgs a) {
   for (long long u = u0 + b * (long long)kRsThreads + threadIdx.x; u < u0 + shard_units; u += (long long)G * kRsThreads) {
     const long long off = a.start + (u << 2);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.g_mc) {
+      acc = mm_ld_reduce_f32x4(a.g_mc + off);                 // the switch adds all `world` copies
+    } else {
 #pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r) {
-      if (r < W) {
-        const float4 t = ld_f4(a.g[r] + off);
-        acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < W) {
+          const float4 t = ld_f4(a.g[r] + off);
+          acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+        }
       }
+    }
+    if (a.clip) {
+      acc.x = fminf(fmaxf(acc.x, a.clip_lo), a.clip_hi); acc.y = fminf(fmaxf(acc.y, a.clip_lo), a.clip_hi);
+      acc.z = fminf(fmaxf(acc.z, a.clip_lo), a.clip_hi); acc.w = fminf(fmaxf(acc.w, a.clip_lo), a.clip_hi);
     }
     float4 pp = ld_f4(a.p[rank] + off);
     float4 mm = m_loc ? ld_f4(m_loc + off) : make_float4(0, 0, 0, 0);
@@ -107,6 +135,13 @@ rs_opt_ag_kernel(const RsArgs a) {
     if (a.replicated) {
       *reinterpret_cast<float4*>(a.p[rank] + off) = pp;
       if (a.p16[rank]) *reinterpret_cast<uint2*>(a.p16[rank] + off) = pk;
+    } else if (a.p_mc) {
+      mm_st_f32x4(a.p_mc + off, pp);                          // one store, replicated by the switch into every copy
+      if (a.p16_mc) mm_st_bf16x4(a.p16_mc + off, pk);
+      else if (a.p16[rank]) {
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r) if (r < W) *reinterpret_cast<uint2*>(a.p16[r] + off) = pk;
+      }
     } else {
 #pragma unroll
       for (int r = 0; r < kMaxRanks; ++r) {
@@ -209,9 +244,24 @@ ZOO_API int zoo_symm_free(void* ptr) {
 ZOO_API int zoo_ipc_handle_bytes() { return (int)sizeof(cudaIpcMemHandle_t); }
 
 // ptrs: HOST arrays of `world` device pointers each (m/v/p16 entries may be null).
+// zoo_rs_opt_ag plus: NVLS multicast addresses of the LOCAL arenas (g_mc / p_mc / p16_mc, each may be null: peer loads / stores are
+// used for that arena) and constant clipping of the summed gradient inside the kernel (clip != 0: clamp to [clip_lo, clip_hi]).
+ZOO_API int zoo_rs_opt_ag_ex(void* const* g, void* const* p, void* const* p16, void* const* m, void* const* v,
+                             void* const* flags, void* const* epoch, void* const* hyper, long long start, long long end,
+                             int world, int rank, int emulate, int opt, int zero_grad, int grid, const void* g_mc, void* p_mc,
+                             void* p16_mc, int clip, float clip_lo, float clip_hi, void* stream);
+
 ZOO_API int zoo_rs_opt_ag(void* const* g, void* const* p, void* const* p16, void* const* m, void* const* v,
                           void* const* flags, void* const* epoch, void* const* hyper, long long start, long long end,
                           int world, int rank, int emulate, int opt, int zero_grad, int grid, void* stream) {
+  return zoo_rs_opt_ag_ex(g, p, p16, m, v, flags, epoch, hyper, start, end, world, rank, emulate, opt, zero_grad, grid, nullptr, nullptr,
+                          nullptr, 0, 0.f, 0.f, stream);
+}
+
+ZOO_API int zoo_rs_opt_ag_ex(void* const* g, void* const* p, void* const* p16, void* const* m, void* const* v,
+                             void* const* flags, void* const* epoch, void* const* hyper, long long start, long long end,
+                             int world, int rank, int emulate, int opt, int zero_grad, int grid, const void* g_mc, void* p_mc,
+                             void* p16_mc, int clip, float clip_lo, float clip_hi, void* stream) {
   if (!g || !p || !flags || !epoch || !hyper || world < 1 || world > kMaxRanks || rank < 0 || rank >= world || grid < 1 || grid > kFlagStride ||
       end <= start || ((end - start) % (4LL * world)) || (start % 4)) {
     zoo_set_last_error("rs_opt_ag: bad arguments (range must be a multiple of 4*world floats)", __FILE__, __LINE__);
@@ -228,6 +278,10 @@ ZOO_API int zoo_rs_opt_ag(void* const* g, void* const* p, void* const* p16, void
   if (!opt_needs_v(opt)) for (int r = 0; r < world; ++r) a.v[r] = nullptr;
   a.start = start; a.end = end; a.world = world; a.rank = rank; a.emulate = emulate; a.opt = opt;
   a.zero_grad = zero_grad & 1; a.replicated = (zero_grad >> 1) & 1;     // bit 0: zero the gradient range afterwards, bit 1: replicated update
+  a.g_mc = emulate ? nullptr : (const float*)g_mc;
+  a.p_mc = (emulate || a.replicated) ? nullptr : (float*)p_mc;
+  a.p16_mc = (emulate || a.replicated) ? nullptr : (__nv_bfloat16*)p16_mc;
+  a.clip = clip ? 1 : 0; a.clip_lo = clip_lo; a.clip_hi = clip_hi;
   cudaStream_t s = (cudaStream_t)stream;
   if (emulate) {
     void* args[] = {(void*)&a};

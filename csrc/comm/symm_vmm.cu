@@ -140,3 +140,135 @@ ZOO_API int zoo_vmm_free(void* ptr, long long mapped_bytes) {
 }
 
 ZOO_API int zoo_close_fd(int fd) { return fd >= 0 ? ::close(fd) : 0; }
+
+// ------------------------------------------------------------------ NVLS multicast objects (C1) --
+// A multicast object gives every GPU of the team ONE extra virtual address range over the same offsets of everybody's
+// buffer: a store to it is replicated by the NVSwitch into every GPU's copy (`multimem.st`), a `multimem.ld_reduce` returns the
+// element-wise sum of all copies, reduced inside the switch.  The gradient exchange (csrc/comm/rs_opt_ag.cu) uses it so that the
+// owner of a shard issues one load instead of `world` peer loads and one store instead of `world` peer stores.
+//   rank 0     : zoo_mc_create  -> handle + POSIX fd (sent to the peers like the buffer fds)
+//   other ranks: zoo_mc_import(fd) -> handle
+//   every rank : zoo_mc_add_device(handle); barrier; zoo_mc_bind(handle, local buffer) -> multicast pointer
+// The bound buffer must come from zoo_vmm_alloc_aligned with the multicast granularity (zoo_mc_granularity).
+namespace {
+typedef CUresult (*PFN_mcCreate)(CUmemGenericAllocationHandle*, const CUmulticastObjectProp*);
+typedef CUresult (*PFN_mcAddDevice)(CUmemGenericAllocationHandle, CUdevice);
+typedef CUresult (*PFN_mcBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long);
+typedef CUresult (*PFN_mcGran)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags);
+typedef CUresult (*PFN_retain)(CUmemGenericAllocationHandle*, void*);
+typedef CUresult (*PFN_devAttr)(int*, CUdevice_attribute, CUdevice);
+typedef CUresult (*PFN_devGet)(CUdevice*, int);
+
+CUmulticastObjectProp mc_prop(int world, size_t size) {
+  CUmulticastObjectProp p{};
+  p.numDevices = (unsigned)world;
+  p.size = size;
+  p.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  p.flags = 0;
+  return p;
+}
+}  // namespace
+
+// 1 when the current device can take part in switch multicast / in-switch reductions.
+ZOO_API int zoo_mc_supported(int* out) {
+  if (!out) return ZOO_ERR_ARG;
+  *out = 0;
+  int dev = 0;
+  ZOO_CUDA_CHECK(cudaGetDevice(&dev));
+  ZOO_CUDA_CHECK(cudaFree(0));
+  auto attr = drv<PFN_devAttr>("cuDeviceGetAttribute");
+  auto dget = drv<PFN_devGet>("cuDeviceGet");
+  if (!attr || !dget || !drv<PFN_mcCreate>("cuMulticastCreate")) return ZOO_OK;
+  CUdevice d;
+  if (dget(&d, dev) != CUDA_SUCCESS) return ZOO_OK;
+  int v = 0;
+  if (attr(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d) == CUDA_SUCCESS) *out = v;
+  return ZOO_OK;
+}
+
+// Size granularity of multicast objects for a team of `world` GPUs (bind sizes and buffer sizes must be multiples of it).
+ZOO_API int zoo_mc_granularity(int world, long long* gran) {
+  if (!gran || world < 2) return ZOO_ERR_ARG;
+  auto g = drv<PFN_mcGran>("cuMulticastGetGranularity");
+  if (!g) return fail("resolving cuMulticastGetGranularity", CUDA_ERROR_NOT_SUPPORTED, __LINE__);
+  CUmulticastObjectProp p = mc_prop(world, 0);
+  size_t v = 0;
+  CUresult r = g(&v, &p, CU_MULTICAST_GRANULARITY_RECOMMENDED);
+  if (r != CUDA_SUCCESS || v == 0) return fail("cuMulticastGetGranularity", r, __LINE__);
+  *gran = (long long)v;
+  return ZOO_OK;
+}
+
+// zoo_vmm_alloc whose size is rounded up to a multiple of `align` bytes as well (multicast binding needs that).
+ZOO_API int zoo_vmm_alloc_aligned(long long bytes, long long align, void** ptr, int* fd, long long* mapped_bytes) {
+  if (align <= 0) return ZOO_ERR_ARG;
+  const long long rounded = (bytes + align - 1) / align * align;
+  return zoo_vmm_alloc(rounded, ptr, fd, mapped_bytes);
+}
+
+ZOO_API int zoo_mc_create(long long bytes, int world, unsigned long long* handle, int* fd) {
+  if (!handle || !fd || bytes <= 0 || world < 2) return ZOO_ERR_ARG;
+  ZOO_CUDA_CHECK(cudaFree(0));
+  auto create = drv<PFN_mcCreate>("cuMulticastCreate");
+  auto exp = drv<PFN_export>("cuMemExportToShareableHandle");
+  if (!create || !exp) return fail("resolving cuMulticast* entry points", CUDA_ERROR_NOT_SUPPORTED, __LINE__);
+  CUmulticastObjectProp p = mc_prop(world, (size_t)bytes);
+  CUmemGenericAllocationHandle h;
+  CUresult r = create(&h, &p);
+  if (r != CUDA_SUCCESS) return fail("cuMulticastCreate", r, __LINE__);
+  int out_fd = -1;
+  r = exp(&out_fd, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+  if (r != CUDA_SUCCESS) return fail("cuMemExportToShareableHandle(multicast)", r, __LINE__);
+  *handle = (unsigned long long)h;
+  *fd = out_fd;
+  return ZOO_OK;
+}
+
+ZOO_API int zoo_mc_import(int fd, unsigned long long* handle) {
+  if (!handle || fd < 0) return ZOO_ERR_ARG;
+  ZOO_CUDA_CHECK(cudaFree(0));
+  auto imp = drv<PFN_import>("cuMemImportFromShareableHandle");
+  if (!imp) return fail("resolving cuMemImportFromShareableHandle", CUDA_ERROR_NOT_SUPPORTED, __LINE__);
+  CUmemGenericAllocationHandle h;
+  CUresult r = imp(&h, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+  if (r != CUDA_SUCCESS) return fail("cuMemImportFromShareableHandle(multicast)", r, __LINE__);
+  *handle = (unsigned long long)h;
+  return ZOO_OK;
+}
+
+ZOO_API int zoo_mc_add_device(unsigned long long handle) {
+  int dev = 0;
+  ZOO_CUDA_CHECK(cudaGetDevice(&dev));
+  auto add = drv<PFN_mcAddDevice>("cuMulticastAddDevice");
+  auto dget = drv<PFN_devGet>("cuDeviceGet");
+  if (!add || !dget) return fail("resolving cuMulticastAddDevice", CUDA_ERROR_NOT_SUPPORTED, __LINE__);
+  CUdevice d;
+  CUresult r = dget(&d, dev);
+  if (r != CUDA_SUCCESS) return fail("cuDeviceGet", r, __LINE__);
+  r = add((CUmemGenericAllocationHandle)handle, d);
+  if (r != CUDA_SUCCESS) return fail("cuMulticastAddDevice", r, __LINE__);
+  return ZOO_OK;
+}
+
+// Bind the local buffer (from zoo_vmm_alloc_aligned; `bytes` = its mapped size) at offset 0 of the multicast object and map the
+// object into this process: *mc_ptr addresses all GPUs' copies at once.  Call after EVERY rank has added its device.
+ZOO_API int zoo_mc_bind(unsigned long long handle, void* local_ptr, long long bytes, void** mc_ptr) {
+  if (!local_ptr || !mc_ptr || bytes <= 0) return ZOO_ERR_ARG;
+  int dev = 0;
+  ZOO_CUDA_CHECK(cudaGetDevice(&dev));
+  auto bind = drv<PFN_mcBindMem>("cuMulticastBindMem");
+  auto retain = drv<PFN_retain>("cuMemRetainAllocationHandle");
+  auto release = drv<PFN_release>("cuMemRelease");
+  if (!bind || !retain || !release) return fail("resolving cuMulticastBindMem", CUDA_ERROR_NOT_SUPPORTED, __LINE__);
+  CUmemGenericAllocationHandle mem;
+  CUresult r = retain(&mem, local_ptr);
+  if (r != CUDA_SUCCESS) return fail("cuMemRetainAllocationHandle", r, __LINE__);
+  r = bind((CUmemGenericAllocationHandle)handle, 0, mem, 0, (size_t)bytes, 0);
+  release(mem);
+  if (r != CUDA_SUCCESS) return fail("cuMulticastBindMem", r, __LINE__);
+  CUmemAllocationProp prop = prop_for(dev);
+  auto gran_fn = drv<PFN_gran>("cuMemGetAllocationGranularity");
+  size_t gran = 0;
+  if (!gran_fn || gran_fn(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED) != CUDA_SUCCESS || gran == 0) gran = 2u << 20;
+  return map_handle((CUmemGenericAllocationHandle)handle, (size_t)bytes, gran, dev, mc_ptr);
+}

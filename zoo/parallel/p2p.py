@@ -20,6 +20,8 @@ from .symm import get_heap, ptr_array
 
 _nl.register_cuda_sigs({
     "zoo_ar_push": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p],
+    "zoo_rs_opt_ag_ex": [C.c_void_p] * 8 + [C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                         C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p],
     "zoo_ar_reduce": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p],
 })
 AR_MAX_CTAS = 1024      # kArMaxCtas of csrc/comm/ar_push.cu
@@ -42,11 +44,17 @@ class P2PFusedSync:
     def allocator(self):
         def alloc(n, dtype):
             esize = torch.empty(0, dtype=dtype).element_size()
-            buf = self.heap.alloc(n * esize)
+            # arenas of the owner-computes kernel are also bound to an NVLS multicast object (in-switch gradient reduction and
+            # one-store weight broadcast); small arenas take the push all-reduce and need none
+            buf = self.heap.alloc(n * esize, multicast=not self._is_small(n))
             self._bufs.append(buf)
             return buf.tensor(dtype, n)
 
         return alloc
+
+    def _is_small(self, n):
+        mode = os.environ.get("ZOO_K1_SMALL", "auto")
+        return (mode == "1") or (mode == "auto" and n * 2 * self.ctx.world_size <= (64 << 20))
 
     def pad_to(self):
         import math
@@ -57,7 +65,7 @@ class P2PFusedSync:
         f = getattr(self, "fopt", None)
         if f is None or getattr(self, "small", False):
             return True                 # push all-reduce + local fused optimizer (clipping included): kernels only
-        return f.clip_l2 is None and f.clip_const is None      # large arenas with clipping take the library all-reduce: no capture
+        return f.clip_l2 is None      # large arenas with L2 clipping take the library all-reduce: no capture
 
     def attach(self, fopt):
         self.fopt = fopt
@@ -89,8 +97,8 @@ class P2PFusedSync:
         # Small arenas (a recommender's dense part): one-handshake push all-reduce with a bf16 wire (csrc/comm/ar_push.cu),
         # then the ordinary local fused optimizer -- clipping included -- on the summed gradient.
         n = a.numel
-        mode = os.environ.get("ZOO_K1_SMALL", "auto")
-        self.small = (mode == "1") or (mode == "auto" and n * 2 * W <= (64 << 20))
+        self.small = self._is_small(n)
+        self.nvls = (not self.small) and self.buf_g.mc_ptr is not None and self.buf_p.mc_ptr is not None
         self._pushed = False
         if self.small:
             if n % 8:
@@ -169,9 +177,9 @@ class P2PFusedSync:
                                                   self.ctx.world_size, self.ctx.rank, self.ar_grid, _nl.stream_ptr()), "zoo_ar_reduce")
             f.step()        # clip (on the averaged gradient) + optimizer + bf16 shadows + zero the gradients, all local kernels
             return
-        if f.clip_l2 is not None or f.clip_const is not None:
-            # clipping needs the global gradient norm / clamp BEFORE the update, which the owner-computes kernel does not
-            # have: take the library all-reduce + local fused optimizer for this step (same arenas, same optimizer state)
+        if f.clip_l2 is not None:
+            # the global gradient norm is only known after the whole reduction, which the owner-computes kernel does not have:
+            # large arenas with L2 clipping take the library all-reduce + local fused optimizer (same arenas, same state)
             import torch.distributed as dist
 
             dist.all_reduce(f.arena.flat_g)
@@ -186,9 +194,13 @@ class P2PFusedSync:
             _nl.check(lib.zoo_hyper_step(hp, f.hyper_stage[i].data_ptr() if refresh else None, st), "zoo_hyper_step")
             hy = ptr_array([hp if k == r else None for k in range(W)])
             rep = self._replicated(g.end - g.start)
-            _nl.check(lib.zoo_rs_opt_ag(self._g, self._p, self._p16, self._m, self._v, self._flags, self._epoch, hy,
-                                        g.start, g.end, W, r, 0, OPT_IDS[g.cfg.name], 1 | (2 if rep else 0),
-                                        self._grid_for(g.end - g.start, rep), st), "zoo_rs_opt_ag")
+            mc = lambda b: b.mc_ptr if (self.nvls and b is not None and b.mc_ptr) else None      # (the kernel adds the range offset)
+            clip = f.clip_const is not None
+            lo, hi = ((f.clip_const[0] / f.grad_scale, f.clip_const[1] / f.grad_scale) if clip else (0.0, 0.0))
+            _nl.check(lib.zoo_rs_opt_ag_ex(self._g, self._p, self._p16, self._m, self._v, self._flags, self._epoch, hy,
+                                           g.start, g.end, W, r, 0, OPT_IDS[g.cfg.name], 1 | (2 if rep else 0),
+                                           self._grid_for(g.end - g.start, rep), mc(self.buf_g), mc(self.buf_p),
+                                           mc(self.buf_p16), int(clip), lo, hi, st), "zoo_rs_opt_ag")
 
     def gather_optimizer_state(self):
         """Owner-computes ranges keep m / v only on the rank that owns a shard; before a checkpoint every rank's copy is made

@@ -26,6 +26,13 @@ _nl.register_cuda_sigs({
     "zoo_vmm_import": [C.c_int, C.c_longlong, C.c_void_p],
     "zoo_vmm_free": [C.c_void_p, C.c_longlong],
     "zoo_close_fd": [C.c_int],
+    "zoo_mc_supported": [C.c_void_p],
+    "zoo_mc_granularity": [C.c_int, C.c_void_p],
+    "zoo_vmm_alloc_aligned": [C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p],
+    "zoo_mc_create": [C.c_longlong, C.c_int, C.c_void_p, C.c_void_p],
+    "zoo_mc_import": [C.c_int, C.c_void_p],
+    "zoo_mc_add_device": [C.c_ulonglong],
+    "zoo_mc_bind": [C.c_ulonglong, C.c_void_p, C.c_longlong, C.c_void_p],
 })
 
 _TYPESTR = {torch.float32: "<f4", torch.int32: "<i4", torch.int64: "<i8", torch.uint8: "|u1", torch.int16: "<i2"}
@@ -53,6 +60,7 @@ class SymmBuffer:
     def __init__(self, ptrs, nbytes, rank, device, owner, kind="ipc", mapped=None):
         self.ptrs, self.nbytes, self.rank, self.device, self._owner = list(ptrs), nbytes, rank, device, owner
         self.kind, self.mapped = kind, mapped or [nbytes] * len(self.ptrs)
+        self.mc_ptr = None      # NVLS multicast address of the same offsets on every rank (SymmetricHeap.alloc(multicast=True))
 
     @property
     def local_ptr(self):
@@ -126,10 +134,81 @@ class SymmetricHeap:
         self.mode = os.environ.get("ZOO_SYMM", "vmm")
         self._fdx = None
 
-    def _alloc_vmm(self, nbytes):
+    def multicast_granularity(self):
+        """Size granularity of NVLS multicast objects for this team, or 0 when some rank cannot use them (decided collectively,
+        once).  ZOO_NVLS=0 switches multicast off."""
+        import os
+
+        if getattr(self, "_mc_gran", None) is None:
+            g = 0
+            if self.ctx.world_size > 1 and self.mode == "vmm" and os.environ.get("ZOO_NVLS", "1") != "0":
+                import torch.distributed as dist
+
+                ok, gran = C.c_int(0), C.c_longlong(0)
+                try:
+                    self.lib.zoo_mc_supported(C.byref(ok))
+                    if ok.value and self.lib.zoo_mc_granularity(self.ctx.world_size, C.byref(gran)) != 0:
+                        ok.value = 0
+                except Exception:
+                    ok.value = 0
+                t = torch.tensor([gran.value if ok.value else 0], dtype=torch.int64, device=self.ctx.device)
+                dist.all_reduce(t, op=dist.ReduceOp.MIN)
+                g = int(t)
+            self._mc_gran = g
+        return self._mc_gran
+
+    def _agree(self, ok):
+        import torch.distributed as dist
+
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=self.ctx.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(int(t))
+
+    def _bind_multicast(self, buf):
+        """Create one multicast object over `buf` on every rank (collective); on any failure the buffer stays an ordinary symmetric
+        buffer (mc_ptr None) on ALL ranks."""
+        import logging
+        import os
+
+        ctx, W = self.ctx, self.ctx.world_size
+        mapped = buf.mapped[ctx.rank]
+        handle, mfd, err = C.c_ulonglong(0), C.c_int(-1), None
+        if ctx.rank == 0:
+            if self.lib.zoo_mc_create(mapped, W, C.byref(handle), C.byref(mfd)) != 0:
+                err = self.lib.zoo_last_error().decode(errors="replace")
+        if not self._agree(err is None):
+            logging.getLogger("zoo").warning("NVLS multicast object could not be created (%s); using peer loads / stores", err)
+            return
+        send_fd = mfd.value if ctx.rank == 0 else os.open(os.devnull, os.O_RDONLY)
+        got = self._fdx.exchange(send_fd, b"mc")
+        if ctx.rank != 0:
+            os.close(send_fd)
+            if self.lib.zoo_mc_import(got[0][0], C.byref(handle)) != 0:
+                err = self.lib.zoo_last_error().decode(errors="replace")
+        for r, (pfd, _) in got.items():
+            self.lib.zoo_close_fd(pfd)
+        if ctx.rank == 0:
+            self.lib.zoo_close_fd(mfd.value)
+        if err is None and self.lib.zoo_mc_add_device(handle) != 0:
+            err = self.lib.zoo_last_error().decode(errors="replace")
+        if not self._agree(err is None):        # (also the barrier: every device is added before anyone binds)
+            logging.getLogger("zoo").warning("NVLS multicast set-up failed (%s); using peer loads / stores", err)
+            return
+        mc = C.c_void_p()
+        if self.lib.zoo_mc_bind(handle, C.c_void_p(buf.local_ptr), mapped, C.byref(mc)) != 0:
+            err = self.lib.zoo_last_error().decode(errors="replace")
+        if not self._agree(err is None):
+            logging.getLogger("zoo").warning("NVLS multicast bind failed (%s); using peer loads / stores", err)
+            return
+        buf.mc_ptr = mc.value
+
+    def _alloc_vmm(self, nbytes, align=0):
         ctx = self.ctx
         ptr, fd, mapped = C.c_void_p(), C.c_int(-1), C.c_longlong(0)
-        _nl.check(self.lib.zoo_vmm_alloc(nbytes, C.byref(ptr), C.byref(fd), C.byref(mapped)), "zoo_vmm_alloc")
+        if align:
+            _nl.check(self.lib.zoo_vmm_alloc_aligned(nbytes, align, C.byref(ptr), C.byref(fd), C.byref(mapped)), "zoo_vmm_alloc_aligned")
+        else:
+            _nl.check(self.lib.zoo_vmm_alloc(nbytes, C.byref(ptr), C.byref(fd), C.byref(mapped)), "zoo_vmm_alloc")
         if ctx.world_size == 1:
             self.lib.zoo_close_fd(fd.value)
             return SymmBuffer([ptr.value], nbytes, 0, ctx.device, self, "vmm", [mapped.value])
@@ -146,14 +225,19 @@ class SymmetricHeap:
             ptrs[r], sizes[r] = p.value, sz
         return SymmBuffer(ptrs, nbytes, ctx.rank, ctx.device, self, "vmm", sizes)
 
-    def alloc(self, nbytes) -> SymmBuffer:
+    def alloc(self, nbytes, multicast=False) -> SymmBuffer:
+        """`multicast=True` additionally binds the buffer to an NVLS multicast object when every rank supports it
+        (`buf.mc_ptr`; None otherwise)."""
         import torch.distributed as dist
 
         nbytes = (int(nbytes) + 255) // 256 * 256
         if self.mode == "vmm":
             try:
-                buf = self._alloc_vmm(nbytes)
+                gran = self.multicast_granularity() if multicast else 0
+                buf = self._alloc_vmm(nbytes, gran)
                 self.buffers.append(buf)
+                if gran:
+                    self._bind_multicast(buf)
                 return buf
             except _nl.NativeError as e:
                 if self.buffers or self.ctx.world_size > 1:

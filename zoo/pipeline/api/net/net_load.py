@@ -48,7 +48,10 @@ class Net:
 
     @staticmethod
     def load_caffe(def_path, model_path, bigdl_type="float"):
-        _unsupported("Net.load_caffe")
+        """prototxt + caffemodel -> GraphNet over the converted torch graph (zoo.models.caffe; Net.scala loadCaffe)."""
+        from ....models.caffe import load_caffe as _load
+
+        return GraphNet(_load(def_path, model_path))
 
     @staticmethod
     def load_keras(json_path=None, hdf5_path=None, by_name=False):
