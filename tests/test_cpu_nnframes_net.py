@@ -120,9 +120,23 @@ def test_torchnet_torchcriterion_gradient_match(tmp_path):
     w = net.get_weights()
     net.set_weights(np.zeros_like(w))
     assert float(net(x).exp().sum()) == pytest.approx(6.0)
-    for fn, args in [(Net.load_caffe, ("a", "b")), (Net.load_keras, ("a",)), (Net.load_tf, ("a",))]:
-        with pytest.raises(NotImplementedError):
-            fn(*args)
+    # Keras-1 JSON definition + weights (npz) -> zoo Sequential
+    import json
+
+    spec = {"class_name": "Sequential", "config": [
+        {"class_name": "Dense", "config": {"output_dim": 5, "activation": "relu", "batch_input_shape": [None, 4], "W_regularizer": None}},
+        {"class_name": "Dropout", "config": {"p": 0.2}},
+        {"class_name": "Dense", "config": {"output_dim": 3, "activation": "softmax"}}]}
+    (tmp_path / "k.json").write_text(json.dumps(spec))
+    rng = np.random.RandomState(0)
+    ws = [rng.randn(4, 5).astype(np.float32), rng.randn(5).astype(np.float32), rng.randn(5, 3).astype(np.float32), rng.randn(3).astype(np.float32)]
+    np.savez(str(tmp_path / "k.npz"), *ws)
+    km = Net.load_keras(str(tmp_path / "k.json"), str(tmp_path / "k.npz")).eval()
+    xk = torch.randn(7, 4)
+    want = torch.softmax(torch.relu(xk @ torch.from_numpy(ws[0]) + torch.from_numpy(ws[1])) @ torch.from_numpy(ws[2]) + torch.from_numpy(ws[3]), -1)
+    torch.testing.assert_close(km(xk), want, atol=1e-5, rtol=1e-5)
+    with pytest.raises(NotImplementedError):
+        Net.load_keras(None, "weights.h5")
 
 
 def test_graphnet_and_multi_io():

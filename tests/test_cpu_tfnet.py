@@ -1,0 +1,95 @@
+"""TensorFlow frozen-graph import / export without TensorFlow (zoo/tfpark/graphdef.py, TFNet, zoo.util.tf.export_tf / strip_unused).
+The GraphDef wire format written here is checked against google.protobuf's own decoder, so files are readable by TensorFlow."""
+import json
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+
+def _cnn():
+    torch.manual_seed(0)
+    m = nn.Sequential(nn.Conv2d(3, 8, 3, padding=1), nn.BatchNorm2d(8), nn.ReLU(), nn.MaxPool2d(2), nn.Conv2d(8, 8, 3, groups=8), nn.Tanh(),
+                      nn.AvgPool2d(2), nn.Flatten(), nn.Dropout(0.5), nn.Linear(8 * 3 * 3, 16), nn.LeakyReLU(0.1), nn.Linear(16, 5), nn.Softmax(-1))
+    with torch.no_grad():
+        m[1].running_mean.uniform_(-0.5, 0.5)
+        m[1].running_var.uniform_(0.5, 1.5)
+    return m.eval()
+
+
+def test_export_tf_roundtrip_through_tfnet(tmp_path):
+    from zoo.pipeline.api.net import Net
+    from zoo.tfpark import TFNet
+    from zoo.util.tf import export_tf
+
+    m = _cnn()
+    x = torch.randn(4, 3, 16, 16)
+    ins, outs = export_tf(m, str(tmp_path / "exp"), x[:1])
+    assert ins == ["input:0"] and outs == ["output:0"]
+    assert json.load(open(tmp_path / "exp" / "graph_meta.json"))["output_names"] == ["output:0"]
+    net = TFNet.from_export_folder(str(tmp_path / "exp"))
+    y = net(x.permute(0, 2, 3, 1).contiguous())             # TensorFlow graphs take NHWC
+    torch.testing.assert_close(y, m(x), atol=1e-5, rtol=1e-5)
+    p = net.predict(x.permute(0, 2, 3, 1).numpy(), batch_per_thread=3)
+    np.testing.assert_allclose(p, m(x).detach().numpy(), atol=1e-5)
+    g = Net.load_tf(str(tmp_path / "exp"))
+    torch.testing.assert_close(g.forward(x.permute(0, 2, 3, 1).contiguous()), m(x), atol=1e-5, rtol=1e-5)
+    with pytest.raises(NotImplementedError):
+        TFNet.from_session(None, [], [])
+
+
+def test_graphdef_bytes_are_real_protobuf(tmp_path):
+    """Decode the written file with google.protobuf through a dynamically built descriptor of GraphDef's outer layers."""
+    from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+
+    from zoo.tfpark.graphdef import read_graphdef, write_graphdef
+
+    fd = descriptor_pb2.FileDescriptorProto(name="mini_graph.proto", package="mini", syntax="proto3")
+    node = fd.message_type.add(name="NodeDef")
+    for i, (n, t, lab) in enumerate([("name", 9, 1), ("op", 9, 1), ("input", 9, 3), ("device", 9, 1)], 1):
+        node.field.add(name=n, number=i, type=t, label=lab)
+    graph = fd.message_type.add(name="GraphDef")
+    graph.field.add(name="node", number=1, type=11, label=3, type_name=".mini.NodeDef")
+    pool = descriptor_pool.DescriptorPool()
+    pool.Add(fd)
+    GraphDef = message_factory.GetMessageClass(pool.FindMessageTypeByName("mini.GraphDef"))
+    data = write_graphdef(str(tmp_path / "g.pb"), [("x", "Placeholder", [], {"dtype": np.float32}),
+                                                  ("w", "Const", [], {"dtype": np.float32, "value": np.eye(3, dtype=np.float32)}),
+                                                  ("y", "MatMul", ["x", "w"], {"T": np.float32, "transpose_b": True})])
+    g = GraphDef()
+    g.ParseFromString(data)
+    assert [(n.name, n.op, list(n.input)) for n in g.node] == [("x", "Placeholder", []), ("w", "Const", []), ("y", "MatMul", ["x", "w"])]
+    nodes = read_graphdef(str(tmp_path / "g.pb"))
+    assert nodes[2].a("transpose_b") is True and nodes[1].a("value").shape == (3, 3)
+
+
+def test_tfnet_ops_and_strip_unused(tmp_path):
+    from zoo.tfpark import TFNet
+    from zoo.tfpark.graphdef import write_graphdef
+    from zoo.util.tf import strip_unused
+
+    f32, i32 = np.float32, np.int32
+    rng = np.random.RandomState(0)
+    W = rng.randn(6, 4).astype(f32)
+    nodes = [("x", "Placeholder", [], {"dtype": f32}), ("unused", "Placeholder", [], {"dtype": f32}),
+             ("w", "Const", [], {"dtype": f32, "value": W}), ("axis", "Const", [], {"dtype": i32, "value": np.array([1], i32)}),
+             ("mm", "MatMul", ["x", "w"], {"T": f32}), ("sq", "Square", ["mm"], {"T": f32}),
+             ("mean", "Mean", ["sq", "axis"], {"T": f32, "keep_dims": True}), ("rs", "Rsqrt", ["mean"], {"T": f32}),
+             ("norm", "Mul", ["mm", "rs"], {"T": f32}), ("one", "Const", [], {"dtype": i32, "value": np.array(1, i32)}),
+             ("cat", "ConcatV2", ["norm", "mm", "one"], {"T": f32, "N": 2}), ("dead", "Relu", ["unused"], {"T": f32}),
+             ("out", "Sigmoid", ["cat"], {"T": f32})]
+    write_graphdef(str(tmp_path / "g.pb"), nodes)
+    net = TFNet(str(tmp_path / "g.pb"), ["x"], ["out"])
+    x = torch.randn(5, 6)
+    mm = x @ torch.from_numpy(W)
+    want = torch.sigmoid(torch.cat([mm * torch.rsqrt((mm * mm).mean(1, keepdim=True)), mm], 1))
+    torch.testing.assert_close(net(x), want, atol=1e-5, rtol=1e-5)
+    pruned = strip_unused(str(tmp_path / "g.pb"), ["mm"], ["out"])
+    (tmp_path / "p.pb").write_bytes(pruned)
+    net2 = TFNet(str(tmp_path / "p.pb"), ["mm"], ["out"])
+    assert set(net2.graph.nodes) == {"mm", "axis", "sq", "mean", "rs", "norm", "one", "cat", "out"}
+    torch.testing.assert_close(net2(mm), want, atol=1e-5, rtol=1e-5)
+    with pytest.raises(NotImplementedError):
+        write_graphdef(str(tmp_path / "bad.pb"), [("x", "Placeholder", [], {"dtype": f32}), ("y", "SomeExoticOp", ["x"], {})])
+        TFNet(str(tmp_path / "bad.pb"), ["x"], ["y"])(x)

@@ -3,7 +3,9 @@
 `Net.load` / `load_bigdl` read a model written by this framework (`ZooModel.save_model`, `KerasNet.saveModel`);
 `load_torch` reads a TorchScript archive or a pickled module.  The foreign formats of the reference (BigDL
 protobuf, Torch7 `.t7`, Caffe prototxt/caffemodel, Keras-1 json/hdf5, TensorFlow frozen graphs) need engines
-that are not on this box; those loaders raise a `NotImplementedError` that names the supported route."""
+are imported where a file format can be read without its engine: Caffe (zoo.models.caffe), TensorFlow frozen graphs
+(zoo.tfpark.graphdef), Keras-1 JSON definitions; a BigDL protobuf or a Torch7 `.t7` file raises a `NotImplementedError` that names
+the supported route."""
 from __future__ import annotations
 
 import torch
@@ -55,11 +57,70 @@ class Net:
 
     @staticmethod
     def load_keras(json_path=None, hdf5_path=None, by_name=False):
-        _unsupported("Net.load_keras")
+        """A Keras-1.2.2 model definition (`model.to_json()`) -> zoo Keras-style Sequential (the zoo layers keep Keras-1 argument
+        names, so the layer configs map one to one); weights from `hdf5_path` when h5py is importable, or from an `.npz` file holding
+        the arrays of `model.get_weights()` in order (reference: Net.load_keras, net_load.py:117-140)."""
+        import inspect
+        import json
+
+        import numpy as np
+
+        from ..keras import layers as L
+        from ..keras.engine.topology import Sequential
+
+        if json_path is None:
+            raise NotImplementedError("Net.load_keras needs the model definition (json_path); an hdf5 file alone carries a pickled "
+                                      "Keras object graph that only Keras can rebuild")
+        spec = json.load(open(json_path))
+        if spec.get("class_name") != "Sequential":
+            raise NotImplementedError(f"Net.load_keras: only Sequential definitions are imported (got {spec.get('class_name')!r}); build "
+                                      "functional graphs with zoo.pipeline.api.keras.models.Model")
+        model = Sequential()
+        for entry in spec["config"]:
+            cname, cfg = entry["class_name"], dict(entry.get("config", {}))
+            cls = getattr(L, cname, None)
+            if cls is None:
+                raise NotImplementedError(f"Net.load_keras: no zoo layer named {cname}")
+            if cfg.get("batch_input_shape"):
+                cfg["input_shape"] = tuple(cfg.pop("batch_input_shape")[1:])
+            for k in ("W_regularizer", "b_regularizer", "activity_regularizer", "W_constraint", "b_constraint"):
+                cfg.pop(k, None)          # Keras serialises these as dicts / None; the zoo layers take objects
+            accepted = inspect.signature(cls.__init__).parameters
+            kwargs = {k: (tuple(v) if isinstance(v, list) else v) for k, v in cfg.items() if k in accepted and v is not None}
+            model.add(cls(**kwargs))
+        if hdf5_path is not None:
+            if str(hdf5_path).endswith(".npz"):
+                arrays = [v for _, v in sorted(np.load(hdf5_path).items(), key=lambda kv: int("".join(ch for ch in kv[0] if ch.isdigit()) or 0))]
+            else:
+                try:
+                    import h5py
+                except ImportError as e:
+                    raise NotImplementedError("Net.load_keras(hdf5_path=...): h5py is not installed; save the weights with "
+                                              "np.savez(path, *model.get_weights()) and pass the .npz file") from e
+                arrays = []
+                with h5py.File(hdf5_path, "r") as f:
+                    g = f["model_weights"] if "model_weights" in f else f
+                    for lname in [n.decode() if isinstance(n, bytes) else n for n in g.attrs["layer_names"]]:
+                        for wname in [n.decode() if isinstance(n, bytes) else n for n in g[lname].attrs["weight_names"]]:
+                            arrays.append(np.asarray(g[lname][wname]))
+            params = [p for p in model.parameters()]
+            if len(params) != len(arrays):
+                raise ValueError(f"Net.load_keras: the definition has {len(params)} weight tensors, the file {len(arrays)}")
+            with torch.no_grad():
+                for p, a in zip(params, arrays):
+                    t = torch.from_numpy(np.asarray(a, dtype=np.float32))
+                    if t.shape != p.shape and t.t().shape == p.shape:
+                        t = t.t()             # Keras Dense kernels are [in, out]
+                    p.copy_(t.reshape(p.shape))
+        return model
 
     @staticmethod
     def load_tf(path, inputs=None, outputs=None, byte_order="little_endian", bin_file=None, bigdl_type="float"):
-        _unsupported("Net.load_tf")
+        """A frozen GraphDef (`.pb` + input / output names) or an export folder (frozen_inference_graph.pb + graph_meta.json) ->
+        GraphNet over the imported torch graph (zoo.tfpark.graphdef; Net.scala loadTF)."""
+        from .tfnet import TFNet
+
+        return GraphNet(TFNet(path, inputs, outputs))
 
 
 class JavaToPython:

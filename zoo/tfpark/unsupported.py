@@ -18,7 +18,7 @@ def _stub(name, methods=()):
 
 TFOptimizer = _stub("TFOptimizer", ("from_loss", "from_keras", "from_train_op"))
 TFEstimator = _stub("TFEstimator", ("from_model_fn",))
-TFNet = _stub("TFNet", ("from_export_folder", "from_session", "from_saved_model"))
+from ..pipeline.api.net.tfnet import TFNet  # noqa: E402,F401  (real: frozen graphs are imported into torch, see zoo.tfpark.graphdef)
 TFPredictor = _stub("TFPredictor", ("from_outputs", "from_keras"))
 
 
