@@ -135,3 +135,37 @@ def test_nest():
     assert nest.pack_sequence_as(s, [10, 11, 12, 13]) == {"a": 10, "b": [11, (12, 13)]}
     with pytest.raises(ValueError):
         nest.pack_sequence_as(s, [1, 2])
+
+
+def test_remote_filesystem_scheme(tmp_path):
+    """hdfs:// / s3:// handling goes through pyarrow file systems; a directory mounted as `mock://` stands in for a remote store."""
+    import pandas as pd
+    import pyarrow.fs as pafs
+
+    from zoo.common.utils import get_file_list, get_remote_file_to_local, load_from_file, put_local_file_to_remote, save_file
+    from zoo.util import filesystem as zfs
+    from zoo.xshard.pandas import read_csv
+
+    store = tmp_path / "store"
+    store.mkdir()
+    zfs.register_filesystem("mock", pafs.SubTreeFileSystem(str(store), pafs.LocalFileSystem()))
+    try:
+        for i in range(3):
+            pd.DataFrame({"a": range(i * 10, i * 10 + 10), "b": 1.5}).to_csv(tmp_path / f"part{i}.csv", index=False)
+            put_local_file_to_remote(str(tmp_path / f"part{i}.csv"), f"mock://data/part{i}.csv")
+        assert get_file_list("mock://data") == [f"mock://data/part{i}.csv" for i in range(3)]
+        assert zfs.exists("mock://data/part1.csv") and not zfs.exists("mock://data/nope.csv") and zfs.isdir("mock://data")
+        shards = read_csv("mock://data")
+        df = pd.concat(shards.collect(), ignore_index=True)
+        assert len(df) == 30 and sorted(df["a"]) == list(range(30))
+        get_remote_file_to_local("mock://data/part2.csv", str(tmp_path / "back.csv"))
+        assert pd.read_csv(tmp_path / "back.csv")["a"].tolist() == list(range(20, 30))
+        import pytest as _pt
+        with _pt.raises(FileExistsError):
+            put_local_file_to_remote(str(tmp_path / "part0.csv"), "mock://data/part0.csv")
+        save_file(lambda p, obj: open(p, "w").write(obj), "mock://models/m.txt", obj="hello")
+        assert load_from_file(lambda p: open(p).read(), "mock://models/m.txt") == "hello"
+        with _pt.raises(OSError):
+            get_file_list("hdfs://no-such-namenode:1/x")       # no Hadoop client on this box: a clear error, not a hang
+    finally:
+        zfs.unregister_filesystem("mock")

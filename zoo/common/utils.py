@@ -76,31 +76,23 @@ def _is_remote(path):
 
 
 def get_file_list(path, recursive=False):
-    path = path[len("file://"):] if path.startswith("file://") else path
-    if _is_remote(path):
-        raise NotImplementedError("remote file systems (hdfs://, s3://) need clients that are not on this box")
-    if os.path.isfile(path):
-        return [path]
-    out = []
-    for root, _, files in os.walk(path):
-        out += [os.path.join(root, f) for f in sorted(files)]
-        if not recursive:
-            break
-    return out
+    """Files under a local, hdfs:// or s3:// path (reference: Utils.listPaths, common/Utils.scala:52-73)."""
+    from ..util import filesystem as zfs
+
+    return zfs.ls(path, recursive)
 
 
 def get_remote_file_to_local(remote_path, local_path, over_write=False):
-    src = remote_path[len("file://"):] if remote_path.startswith("file://") else remote_path
-    if _is_remote(src):
-        raise NotImplementedError("remote file systems (hdfs://, s3://) need clients that are not on this box")
-    if os.path.exists(local_path) and not over_write:
-        raise FileExistsError(local_path)
-    shutil.copy(src, local_path)
-    return local_path
+    """Utils.getRemoteFileToLocal (common/Utils.scala:249-264): any scheme zoo.util.filesystem resolves."""
+    from ..util import filesystem as zfs
+
+    return zfs.get(remote_path, local_path, over_write)
 
 
 def put_local_file_to_remote(local_path, remote_path, over_write=False):
-    return get_remote_file_to_local(local_path, remote_path, over_write)
+    from ..util import filesystem as zfs
+
+    return zfs.put(local_path, remote_path, over_write)
 
 
 def set_core_number(num):
@@ -137,12 +129,28 @@ def to_list_of_numpy(elements):
 
 
 def save_file(save_func, path, **kwargs):
-    if not is_local_path(path):
-        raise NotImplementedError("remote file systems need clients that are not on this box")
-    save_func(path[len("file://"):] if path.startswith("file://") else path, **kwargs)
+    """Run `save_func(local_path)`; for a remote `path` the file is written to a temporary local file and uploaded (the reference
+    does the same dance through Hadoop's FileSystem, utils/File.scala)."""
+    from ..util import filesystem as zfs
+
+    if is_local_path(path):
+        return save_func(zfs.local_path(path), **kwargs)
+    import tempfile
+
+    with tempfile.TemporaryDirectory() as d:
+        tmp = os.path.join(d, os.path.basename(path) or "file")
+        save_func(tmp, **kwargs)
+        zfs.put(tmp, path, over_write=True)
 
 
 def load_from_file(load_func, path):
-    if not is_local_path(path):
-        raise NotImplementedError("remote file systems need clients that are not on this box")
-    return load_func(path[len("file://"):] if path.startswith("file://") else path)
+    from ..util import filesystem as zfs
+
+    if is_local_path(path):
+        return load_func(zfs.local_path(path))
+    import tempfile
+
+    with tempfile.TemporaryDirectory() as d:
+        tmp = os.path.join(d, os.path.basename(path) or "file")
+        zfs.get(path, tmp, over_write=True)
+        return load_func(tmp)

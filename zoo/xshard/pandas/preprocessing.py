@@ -2,8 +2,8 @@
 
 Reference: pyzoo/zoo/xshard/pandas/preprocessing.py:26-189 -- `file_path` is one file, several comma
 separated files, or a directory; files are spread over the workers and every worker loads its files
-into one DataFrame.  Local paths (and `file://`) are supported; hdfs:// and s3:// need clients that are
-not on this box and raise a clear error.
+into one DataFrame.  Local paths, `file://`, and every scheme `zoo.util.filesystem` resolves (hdfs://, s3://, registered
+schemes) are supported.
 """
 from __future__ import annotations
 
@@ -13,19 +13,15 @@ from ..shard import XShards, _chunks
 
 
 def list_files(file_path, file_type):
+    """One file, several comma separated files, or directories -- local, hdfs:// or s3:// (zoo.util.filesystem)."""
+    from ...util import filesystem as zfs
+
     paths = []
     for p in str(file_path).split(","):
         p = p.strip()
-        if p.startswith("file://"):
-            p = p[len("file://"):]
-        if "://" in p:
-            raise NotImplementedError(f"{p.split('://')[0]}:// paths need a remote file-system client that is not available here")
-        if os.path.isdir(p):
-            paths += sorted(os.path.join(p, f) for f in os.listdir(p) if f.endswith("." + file_type))
-        elif os.path.exists(p):
-            paths.append(p)
-        else:
+        if not zfs.exists(p):
             raise FileNotFoundError(p)
+        paths += zfs.ls(p, suffix="." + file_type) if zfs.isdir(p) else [zfs.local_path(p) if zfs.is_local(p) else p]
     if not paths:
         raise Exception(f"no {file_type} files found under {file_path}")
     return paths
@@ -34,9 +30,20 @@ def list_files(file_path, file_type):
 def _load(files, file_type, kwargs):
     import pandas as pd
 
+    from ...util import filesystem as zfs
+
     reader = {"csv": pd.read_csv, "json": lambda f, **k: pd.read_json(f, **({"orient": "columns", "lines": False} | k)),
               "parquet": pd.read_parquet}[file_type]
-    dfs = [reader(f, **kwargs) for f in files]
+
+    def read_one(f):
+        if zfs.is_local(f):
+            return reader(zfs.local_path(f), **kwargs)
+        with zfs.open_file(f, "rb") as fh:          # remote: stream through pyarrow
+            import io
+
+            return reader(io.BytesIO(fh.read()), **kwargs)
+
+    dfs = [read_one(f) for f in files]
     return dfs[0] if len(dfs) == 1 else pd.concat(dfs, ignore_index=True)
 
 
