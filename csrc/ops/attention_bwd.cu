@@ -215,20 +215,18 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       }
       tc_fence_before();
     }
-    // dK_j, dV_j: thread t = key row t.  The last dq_bar wait covered every MMA of this CTA.
+    // dK_j, dV_j: thread t = key row t.  The last dq_bar wait covered every MMA of this CTA.  (tcgen05.ld is warp-collective:
+    // every lane of the warp executes it, only the rows inside the sequence are stored.)
     const int key = k0 + t;
-    if (key < a.L) {
 #pragma unroll
-      for (int which = 0; which < 2; ++which) {
-        __nv_bfloat16* dst = (which ? a.dk : a.dv) + (row_base + key) * kAbD;
+    for (int which = 0; which < 2; ++which) {
+      __nv_bfloat16* dst = (which ? a.dk : a.dv) + (row_base + key) * kAbD;
 #pragma unroll
-        for (int c = 0; c < kAbD / 32; ++c) {
-          uint32_t r[32];
-          if (n_iter > 0) { tmem_ld_32x32((which ? t_dk : t_dv) + lane_addr + c * 32, r); tmem_ld_wait(); }
-          else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) r[i] = 0u;
-          }
+      for (int c = 0; c < kAbD / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32((which ? t_dk : t_dv) + lane_addr + c * 32, r);
+        tmem_ld_wait();
+        if (key < a.L) {
 #pragma unroll
           for (int i = 0; i < 32; i += 8) {
             uint4 v;
