@@ -67,7 +67,35 @@ struct GemmArgs {
   const uint32_t* mask_bits;          // dgrad, optional: same layout, replaces `mask`
   int bits_wpr;                       // words per row of relu_bits / mask_bits
   float* colsum;                      // split-K mode, optional: colsum[m] += sum_r A(m, r)  (the bias gradient of a wgrad)
+  // Low-precision inference (forward only): A and B are FP8 E4M3 (one byte per element, K-major), products accumulate in fp32
+  // on the tensor core (tcgen05.mma kind::f8f6f4), alpha = scale_a * scale_b brings the accumulator back to real units before
+  // bias / activation, and the output is bf16 or -- quantised for the next FP8 layer -- E4M3 of (value * out_qscale).
+  int fp8;
+  float alpha;
+  int out_fp8;
+  float out_qscale;
 };
+
+__device__ __forceinline__ uint32_t pack_e4m3x4(float a, float b, float c, float d) {
+  uint16_t lo, hi;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %2, %1;" : "=h"(lo) : "f"(a), "f"(b));      // (upper, lower) operand order
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %2, %1;" : "=h"(hi) : "f"(c), "f"(d));
+  return (uint32_t)lo | ((uint32_t)hi << 16);
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]; FP8 (E4M3 / E5M2 per the instruction descriptor) -> fp32, K = 32 per instruction.
+__device__ __forceinline__ void umma_f8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n"
+      "}\n"
+      :: "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// kind::f8f6f4 instruction descriptor: fp32 accumulator, A and B E4M3 (format 0), both K-major.
+__host__ __device__ constexpr uint32_t make_idesc_e4m3(uint32_t m, uint32_t n) {
+  return (1u << 4) | ((n >> 3) << 17) | ((m >> 4) << 24);
+}
 
 template <int ACT>
 __device__ __forceinline__ float act_fn(float v) {
@@ -110,8 +138,27 @@ __device__ __forceinline__ void epilogue_chunk(const GemmArgs& g, const uint32_t
 #pragma unroll
     for (int t = 0; t < 8; ++t) v[t] = __uint_as_float(r[j + t]);
     if (EPI == EPI_BIAS_ACT) {
+      if (g.fp8) {
+#pragma unroll
+        for (int t = 0; t < 8; ++t) v[t] *= g.alpha;
+      }
 #pragma unroll
       for (int t = 0; t < 8; ++t) v[t] = act_fn<ACT>(v[t] + s_bias[j + t]);
+      if (g.out_fp8) {       // quantised output for the next FP8 layer: one byte per element
+        uint8_t* o8 = reinterpret_cast<uint8_t*>(g.out) + row * g.ldd + col + j;
+        const float q = g.out_qscale;
+        if (FULL || col + j + 8 <= g.No) {
+          uint2 pk8;
+          pk8.x = pack_e4m3x4(v[0] * q, v[1] * q, v[2] * q, v[3] * q);
+          pk8.y = pack_e4m3x4(v[4] * q, v[5] * q, v[6] * q, v[7] * q);
+          *reinterpret_cast<uint2*>(o8) = pk8;
+        } else {
+#pragma unroll
+          for (int t = 0; t < 8; ++t)
+            if (col + j + t < g.No) o8[t] = (uint8_t)(pack_e4m3x4(v[t] * q, 0.f, 0.f, 0.f) & 0xffu);
+        }
+        continue;
+      }
     } else {  // EPI_MASK
       if (g.mask && col + j < g.mask_cols) {
         const uint4 m4 = mk[j >> 3];
@@ -187,7 +234,8 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const uint32_t tmem_base = tmem_base_slot;
 
   const int total_work = g.m_blocks * g.n_blocks * g.k_splits;
-  const int total_kb = (g.R + kBlockK - 1) / kBlockK;
+  const int kbe = g.fp8 ? 2 * kBlockK : kBlockK;      // elements per k-block: always one 128-byte swizzle row
+  const int total_kb = (g.R + kbe - 1) / kbe;
   const uint32_t a_stage_bytes = kABytes;
   const uint32_t b_boxes = g.b_mn ? (uint32_t)((g.block_n + 63) / 64) : 1u;
   const uint32_t b_stage_bytes = g.b_mn ? b_boxes * kMnBoxBytes : (uint32_t)g.block_n * 128u;
@@ -208,7 +256,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         for (int kb = 0; kb < total_kb; ++kb) {
           uint8_t* sb = smem_al + b_res_base + kb * b_stage_bytes;
           if (!g.b_mn) {
-            tma_load_2d(sb, &tmap_b, &b_full_bar, kb * kBlockK, 0);
+            tma_load_2d(sb, &tmap_b, &b_full_bar, kb * kbe, 0);
           } else {
             for (uint32_t bx = 0; bx < b_boxes; ++bx) tma_load_2d(sb + bx * kMnBoxBytes, &tmap_b, &b_full_bar, (int)bx * 64, kb * kBlockK);
           }
@@ -225,7 +273,7 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           uint8_t* sa = smem_al + stage * a_ring_stride;
           uint8_t* sb = sa + kABytes;
           mbar_arrive_expect_tx(&full_bar[stage], resident ? a_stage_bytes : a_stage_bytes + b_stage_bytes);
-          const int r0 = kb * kBlockK;
+          const int r0 = kb * kbe;
           if (!g.a_mn) {
             tma_load_2d(sa, &tmap_a, &full_bar[stage], r0, m_blk * kBlockM);
           } else {
@@ -248,7 +296,8 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   } else if (warp == 1) {
     // ===================== MMA issuer (one elected lane) =======================
     if (elect_one()) {
-      const uint32_t idesc = make_idesc_bf16(kBlockM, (uint32_t)g.block_n, (uint32_t)g.a_mn, (uint32_t)g.b_mn);
+      const uint32_t idesc = g.fp8 ? make_idesc_e4m3(kBlockM, (uint32_t)g.block_n)
+                                   : make_idesc_bf16(kBlockM, (uint32_t)g.block_n, (uint32_t)g.a_mn, (uint32_t)g.b_mn);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
       if (resident && (int)blockIdx.x < total_work) {
         mbar_wait(&b_full_bar, 0);
@@ -277,7 +326,8 @@ dense_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                                        : make_smem_desc_sw128(sa + k * 32, 16, 1024);
             const uint64_t db = g.b_mn ? make_smem_desc_sw128(sb + k * 2048, kMnBoxBytes, 1024)
                                        : make_smem_desc_sw128(sb + k * 32, 16, 1024);
-            umma_bf16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (g.fp8) umma_f8(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);      // 32 one-byte elements = the same 32-byte step
+            else umma_bf16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             // row sums of A ride along as a 16-column MMA against ones (accumulator: the unused second TMEM stage)
             if (do_colsum) umma_bf16(tmem_base + kMaxN, da, d_ones, idesc_ones, (kb > kb0 || k > 0) ? 1u : 0u);
           }
@@ -510,12 +560,12 @@ static PFN_encodeTiled get_encode() {
 
 // rows x cols bf16 matrix, row-major with leading dimension ld (elements).
 static int make_tmap(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld,
-                     int box_cols, int box_rows, bool f32 = false) {
+                     int box_cols, int box_rows, bool f32 = false, bool u8 = false) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) { zoo_set_last_error("cuTensorMapEncodeTiled unavailable", __FILE__, __LINE__); return ZOO_ERR_CUDA; }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * (f32 ? 4 : 2)};
-  const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  cuuint64_t strides[1] = {(cuuint64_t)ld * (f32 ? 4 : (u8 ? 1 : 2))};
+  const CUtensorMapDataType dt = f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (u8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
   cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
@@ -557,8 +607,13 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
     zoo_set_last_error("dense_tcgen05: null pointer or empty shape", __FILE__, __LINE__);
     return ZOO_ERR_ARG;
   }
-  if ((lda % 8) || (ldb % 8) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) {
-    zoo_set_last_error("dense_tcgen05: operands need 16-byte aligned rows (ld % 8 == 0)", __FILE__, __LINE__);
+  const int ld_mult = g.fp8 ? 16 : 8;
+  if ((lda % ld_mult) || (ldb % ld_mult) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) {
+    zoo_set_last_error("dense_tcgen05: operands need 16-byte aligned rows (ld % 8 == 0 for bf16, % 16 for fp8)", __FILE__, __LINE__);
+    return ZOO_ERR_ARG;
+  }
+  if (g.fp8 && (a_mn || b_mn || g.epilogue != EPI_BIAS_ACT)) {
+    zoo_set_last_error("dense_tcgen05: the FP8 mode is forward only (K-major operands, bias/activation epilogue)", __FILE__, __LINE__);
     return ZOO_ERR_ARG;
   }
   g.a_mn = a_mn; g.b_mn = b_mn;
@@ -567,7 +622,8 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
   g.block_n = bn;
   g.m_blocks = (g.Mo + kBlockM - 1) / kBlockM;
   g.n_blocks = (g.No + bn - 1) / bn;
-  const int total_kb = (g.R + kBlockK - 1) / kBlockK;
+  const int kbe = g.fp8 ? 2 * kBlockK : kBlockK;
+  const int total_kb = (g.R + kbe - 1) / kbe;
   if (g.epilogue == EPI_RED_F32) {
     int want = max_ctas / (g.m_blocks * g.n_blocks);
     if (want < 1) want = 1;
@@ -593,15 +649,16 @@ static int launch(const void* A, long long lda, int a_mn, const void* B, long lo
   }
   CUtensorMap ta, tb;
   int rc;
-  if (!a_mn) rc = make_tmap(&ta, A, g.Mo, g.R, lda, kBlockK, kBlockM);
+  if (!a_mn) rc = make_tmap(&ta, A, g.Mo, g.R, lda, kbe, kBlockM, false, g.fp8 != 0);
   else       rc = make_tmap(&ta, A, g.R, g.Mo, lda, 64, kBlockK);
   if (rc) return rc;
-  if (!b_mn) rc = make_tmap(&tb, B, g.No, g.R, ldb, kBlockK, bn);
+  if (!b_mn) rc = make_tmap(&tb, B, g.No, g.R, ldb, kbe, bn, false, g.fp8 != 0);
   else       rc = make_tmap(&tb, B, g.R, g.No, ldb, 64, kBlockK);
   if (rc) return rc;
   static int allow_tma_epi = -1;
   if (allow_tma_epi < 0) { const char* ev = getenv("ZOO_DENSE_TMA_EPI"); allow_tma_epi = ev ? atoi(ev) : 1; }
   g.tma_epi = (allow_tma_epi || g.relu_bits || g.mask_bits || g.colsum) ? 1 : 0;   // the bit-mask forms exist only in the staged epilogue
+  if (g.fp8) g.tma_epi = 0;            // scaled / one-byte outputs leave through the direct epilogue
   CUtensorMap to = ta;
   if (g.tma_epi) {
     if (g.epilogue == EPI_RED_F32) rc = make_tmap(&to, g.out, g.Mo, g.No, g.ldd, 32, 32, true);
@@ -724,4 +781,18 @@ ZOO_API int zoo_dense_wgrad_bf16(const void* dy, long long lddy, const void* x, 
   g.out = dw; g.ldd = lddw; g.bias = nullptr; g.mask = nullptr; g.ldmask = 0;
   if (lddw % 4 || ((uintptr_t)dw & 15)) { zoo_set_last_error("dense_wgrad: lddw % 4 != 0", __FILE__, __LINE__); return ZOO_ERR_ARG; }
   return launch(dy, lddy, 1, x, ldx, 1, g, num_sms(), (cudaStream_t)stream);
+}
+
+// FP8 inference GEMM: Y[M,N] = act(alpha * (Xq[M,K] (E4M3, ldx) * Wq[N,K]^T (E4M3, ldw)) + bias[N]); alpha = scale_x * scale_w.
+// out_fp8 == 0: Y is bf16 (ldy elements).  out_fp8 != 0: Y is E4M3 of (value * out_qscale) -- the quantised input of the next
+// FP8 layer, ldy in bytes.  Stands where the reference runs OpenVINO / BigDL int8 inference
+// (zoo/.../pipeline/inference/OpenVinoInferenceSupportive.scala:35-57; examples/vnni): 8-bit operands, 32-bit accumulation.
+ZOO_API int zoo_dense_fwd_fp8(const void* xq, long long ldx, const void* wq, long long ldw, const float* bias, void* y, long long ldy,
+                              int M, int N, int K, int act, float alpha, int out_fp8, float out_qscale, void* stream) {
+  GemmArgs g{};
+  g.Mo = M; g.No = N; g.R = K; g.epilogue = EPI_BIAS_ACT; g.act = act;
+  g.out = y; g.ldd = ldy; g.bias = bias; g.mask = nullptr; g.ldmask = 0;
+  g.fp8 = 1; g.alpha = alpha; g.out_fp8 = out_fp8 ? 1 : 0; g.out_qscale = out_qscale;
+  if ((out_fp8 ? (ldy % 16) : (ldy % 8)) || ((uintptr_t)y & 15)) { zoo_set_last_error("dense_fwd_fp8: output rows must be 16-byte aligned", __FILE__, __LINE__); return ZOO_ERR_ARG; }
+  return launch(xq, ldx, 0, wq, ldw, 0, g, num_sms(), (cudaStream_t)stream);
 }

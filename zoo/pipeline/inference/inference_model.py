@@ -8,9 +8,9 @@ a clone, runs forward, offers it back; with auto-scaling, clones are made on dem
 Here a "clone" is an execution slot: its own CUDA stream plus (for static shapes) a CUDA graph of
 the forward pass captured into slot-private input/output buffers.  Weights are shared by
 construction (one module).  Several threads calling `predict` therefore overlap on the GPU the way
-the reference's clones overlap on CPU cores.  Loaders for engines that do not exist on this box
-(Caffe, OpenVINO, TensorFlow) raise `NotImplementedError` naming the supported route
-(TorchScript / a pickled zoo model / a module object).
+the reference's clones overlap on CPU cores.  Foreign formats are imported into torch graphs (Caffe prototxt /
+caffemodel, TensorFlow frozen graphs); the reference's 8-bit engines (OpenVINO int8 IR, BigDL int8) are replaced by
+`quantize()`: FP8 Linear layers on the tcgen05 kernel.
 """
 from __future__ import annotations
 
@@ -86,21 +86,57 @@ class InferenceModel:
 
     load_bigdl = load
 
-    def _unavailable(self, what):
-        raise NotImplementedError(f"{what} needs an engine that is not part of zoo-b200 (no TensorFlow/Caffe/OpenVINO runtime); "
-                                  "export the model to TorchScript and use load_torch(path)")
-
     def load_caffe(self, model_path, weight_path):
-        self._unavailable("load_caffe")
+        """prototxt + caffemodel, converted to a torch graph (zoo.models.caffe; reference: doLoadCaffe)."""
+        from ...models.caffe import load_caffe
+
+        return self._install(load_caffe(model_path, weight_path))
+
+    def load_tensorflow(self, model_path, model_type="frozenModel", intra_op_parallelism_threads=1, inter_op_parallelism_threads=1,
+                        use_per_session_threads=True, inputs=None, outputs=None):
+        """A frozen GraphDef (`.pb` + input / output names) or an export folder with graph_meta.json, imported into torch
+        (zoo.tfpark.graphdef; reference: doLoadTF / doLoadTensorflow, frozen models)."""
+        from ..api.net.tfnet import TFNet
+
+        if model_type not in ("frozenModel", "frozen_model", None):
+            raise NotImplementedError(f"load_tensorflow(model_type={model_type!r}): only frozen graphs can be imported without a TensorFlow "
+                                      "runtime; freeze the SavedModel first")
+        return self._install(TFNet(model_path, inputs, outputs))
+
+    def load_tf(self, model_path, backend="tensorflow", intra_op_parallelism_threads=1, inter_op_parallelism_threads=1,
+                use_per_session_threads=True, inputs=None, outputs=None):
+        return self.load_tensorflow(model_path, "frozenModel", inputs=inputs, outputs=outputs)
 
     def load_openvino(self, model_path, weight_path, batch_size=0):
-        self._unavailable("load_openvino")
+        """OpenVINO IR (`.xml` + `.bin`) is the reference's low-precision CPU engine.  Its job -- 8-bit inference -- is done here by
+        the FP8 tensor-core path: load the original model with load_torch / load_caffe / load_tf and call `quantize(calib_batch)`.
+        The IR container itself (an Intel-specific op set) is not imported."""
+        raise NotImplementedError("load_openvino: OpenVINO IR files are not imported; load the source model (load_torch / load_caffe / "
+                                  "load_tf) and call InferenceModel.quantize(calibration_batch) for 8-bit (FP8) inference")
 
-    def load_tensorflow(self, *a, **kw):
-        self._unavailable("load_tensorflow")
+    def load_tf_as_openvino(self, *a, **kw):
+        raise NotImplementedError("the *_as_openvino loaders convert a TensorFlow model to OpenVINO IR; here: load_tf(...) followed by "
+                                  "quantize(calibration_batch)")
 
-    load_tf = load_tf_object_detection_as_openvino = load_tf_image_classification_as_openvino = load_tensorflow
-    load_tf_as_calibrated_openvino = load_tensorflow
+    load_tf_object_detection_as_openvino = load_tf_image_classification_as_openvino = load_tf_as_calibrated_openvino = load_tf_as_openvino
+
+    def quantize(self, calib_inputs, skip=()):
+        """8-bit inference (reference: doLoadOpenVINOInt8 / BigDL int8 quantisation, OpenVinoInferenceSupportive.scala:35-57): every
+        Linear / Dense layer of the loaded model becomes an FP8 (E4M3) layer on the tcgen05 kernel, with activation scales taken
+        from `calib_inputs` (a tensor, a tuple of tensors, or a list of those).  See zoo.ops.quant."""
+        from ...ops.quant import quantize_linear_layers
+
+        if self.model is None:
+            raise RuntimeError("load a model first")
+        move = lambda t: t.to(self.device) if torch.is_tensor(t) else torch.as_tensor(np.asarray(t)).to(self.device)
+        batches = calib_inputs if isinstance(calib_inputs, list) else [calib_inputs]
+        batches = [tuple(move(t) for t in b) if isinstance(b, tuple) else move(b) for b in batches]
+        quantize_linear_layers(self.model, batches, skip)
+        for _ in range(self._slots.qsize()):          # captured graphs of the old layers are stale
+            sl = self._slots.get()
+            sl.graphs.clear(); sl.seen.clear()
+            self._slots.put(sl)
+        return self
 
     # ---------------------------------------------------------------- predict --
     def _take(self):
