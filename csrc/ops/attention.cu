@@ -26,7 +26,11 @@ constexpr int kAttQBytes = kAttBM * kAttD * 2;          // 16 KiB
 constexpr int kAttKBytes = kAttBN * kAttD * 2;          // 16 KiB
 constexpr int kAttVBytes = kAttBN * kAttD * 2;          // 16 KiB (two MN-major boxes of 64 keys)
 constexpr int kAttPBytes = kAttBM * kAttBN * 2;         // 32 KiB (two k-blocks of 64 keys)
-constexpr int kAttSmem = kAttQBytes + 2 * (kAttKBytes + kAttVBytes) + kAttPBytes + 1024;
+constexpr int kAttTiles = kAttQBytes + 2 * (kAttKBytes + kAttVBytes) + kAttPBytes;      // 112 KiB of operand tiles
+// Barriers live behind the tiles in the SAME dynamic allocation and the kernel has no static shared memory, so the 1024-byte
+// aligned tiles start at the CTA's shared-memory base and two CTAs (2 x 112.1 KiB + the per-CTA reserve) fit one SM: while one
+// CTA's softmax warps work, the other CTA's MMAs run.  (With a padded allocation only one CTA fit: ncu showed 9 % active warps.)
+constexpr int kAttSmem = kAttTiles + 128;
 constexpr int kAttThreads = 192;
 constexpr float kLog2e = 1.4426950408889634f;
 
@@ -39,15 +43,22 @@ struct AttArgs {
   float* lse;                  // optional [B, H, L]: log2-domain log-sum-exp of every row's scaled, masked scores (for backward)
 };
 
-__global__ void __launch_bounds__(kAttThreads, 1)
+__global__ void __launch_bounds__(kAttThreads, 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                      const __grid_constant__ CUtensorMap tmap_v, const AttArgs a) {
-  extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t q_bar, kv_full[2], kv_empty[2], s_bar, p_bar, o_bar;
-  __shared__ uint32_t tmem_slot;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + kAttTiles);
+  uint64_t& q_bar = bars[0];
+  uint64_t* kv_full = bars + 1;
+  uint64_t* kv_empty = bars + 3;
+  uint64_t& s_bar = bars[5];
+  uint64_t& p_bar = bars[6];
+  uint64_t& o_bar = bars[7];
+  uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(bars + 8);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t smem_base = smem_u32(smem_raw);
+  uint8_t* smem_al = smem_raw;
+  if (smem_base & 1023u) { if (threadIdx.x == 0) printf("zoo attention: shared memory base is not 1024-byte aligned\n"); __trap(); }
   const uint32_t off_q = 0, off_kv = kAttQBytes, off_p = kAttQBytes + 2 * (kAttKBytes + kAttVBytes);
 
   const int q_tiles = (a.L + kAttBM - 1) / kAttBM;

@@ -53,6 +53,7 @@ class ServingConfig:
         c = load_config(config)
         m, d, p, r = c["model"], c["data"], c["params"], c["redis"]
         self.model_path = overrides.get("model_path", m.get("path"))
+        self.model_inputs, self.model_outputs = m.get("inputs"), m.get("outputs")
         src = str(d.get("src") or "localhost:6379")
         self.host, _, port = src.partition(":")
         self.port = int(port or 6379)
@@ -98,7 +99,10 @@ class ClusterServing:
             self.db.xgroup_create(INPUT_STREAM, GROUP, id="0", mkstream=True)
         except RespError:
             pass
-        dt = {"bf16": torch.bfloat16, "fp16": torch.float16}.get(self.conf.dtype) if self.device.type == "cuda" else None
+        # params.dtype: bf16 | fp16 (autocast) | fp32 | fp8 (Linear / Dense layers on the FP8 tensor-core path, calibrated on the first
+        # batch that is served -- the 8-bit route of the reference's OpenVINO int8 serving; the rest of the model runs in bf16)
+        dt = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp8": torch.bfloat16}.get(self.conf.dtype) if self.device.type == "cuda" else None
+        self._quantize_pending = self.conf.dtype == "fp8"
         self.model = InferenceModel(1, self.device, dtype=dt, channels_last=False)
         if model is not None:
             self.model.load_torch(model)
@@ -128,9 +132,18 @@ class ClusterServing:
         if path.endswith((".pt", ".pth")):
             self.model.load_torch(path)
         elif path.endswith((".caffemodel", ".prototxt")):
-            self.model.load_caffe(path, None)
-        elif path.endswith((".pb", ".xml", ".bin")):
-            self.model.load_tensorflow(path)
+            stem = path.rsplit(".", 1)[0]
+            proto, weights = stem + ".prototxt", stem + ".caffemodel"
+            self.model.load_caffe(proto, weights if os.path.exists(weights) else None)
+        elif path.endswith(".pb"):
+            folder = os.path.dirname(path)
+            if os.path.exists(os.path.join(folder, "graph_meta.json")):
+                self.model.load_tensorflow(folder)
+            else:       # config.yaml: model.inputs / model.outputs name the tensors of a bare frozen graph
+                split = lambda v: [t.strip() for t in str(v).split(",") if t.strip()] if v else None
+                self.model.load_tensorflow(path, inputs=split(getattr(self.conf, "model_inputs", None)), outputs=split(getattr(self.conf, "model_outputs", None)))
+        elif path.endswith((".xml", ".bin")):
+            self.model.load_openvino(path, None)
         else:
             self.model.load(path)
 
@@ -159,6 +172,13 @@ class ClusterServing:
             self.db.xtrim(INPUT_STREAM, n // 2)
             log.warning("broker memory above 48%%: trimmed %s to %d entries", INPUT_STREAM, n // 2)
 
+    def _predict(self, x):
+        """Model forward for one batch; the first batch also calibrates the FP8 layers when params.dtype is fp8."""
+        if self._quantize_pending:
+            self._quantize_pending = False
+            self.model.quantize(x)
+        return self.model.predict_tensor(x)
+
     def _infer(self, items):
         """items: list of decoded arrays -> (kind, payload) for the writer."""
         c = self.conf
@@ -170,10 +190,10 @@ class ClusterServing:
             dtype = self.model.dtype or torch.float32
             x = preprocess_images(items, (c.H, c.W), None, c.mean[:c.C], c.std[:c.C], swap_rb=(c.C == 3), chw=c.chw,
                                   dtype=dtype if self.device.type == "cuda" else torch.float32, device=self.device)
-            out = self.model.predict_tensor(x)
+            out = self._predict(x)
         else:
             xs = torch.from_numpy(np.stack(items))
-            out = self.model.predict_tensor(xs)
+            out = self._predict(xs)
         if isinstance(out, (tuple, list)):
             out = out[0]
         out = out.reshape(out.shape[0], -1)
@@ -207,7 +227,7 @@ class ClusterServing:
                 uris, batch = got
                 t0 = time.perf_counter()
                 try:
-                    out = self.model.predict_tensor(torch.from_numpy(batch))
+                    out = self._predict(torch.from_numpy(batch))
                     out = (out[0] if isinstance(out, (tuple, list)) else out)
                     out = out.reshape(out.shape[0], -1)
                     if self.conf.top_n is not None:
