@@ -10,6 +10,7 @@ serving-* Cluster Serving records/s and p50/p99 latency: enqueue -> broker -> en
 from __future__ import annotations
 
 import json
+import os
 import time
 
 import numpy as np
@@ -108,16 +109,29 @@ def _serving(args, ctx, torch):
     kind = "resnet50" if "resnet" in args.config else "ncf"
     bs = args.batch or (64 if kind == "resnet50" else 4096)
     dev = ctx.device
+    base = None
+    if not getattr(args, "no_baseline", False):        # same-box anchor: a plain torch batched server (baseline/serving_bench.py)
+        try:
+            from baseline.serving_bench import run_serving_baseline
+
+            base = run_serving_baseline(kind, dev, min(args.steps, 20), args.warmup, args.batch, ctx.rank)
+            if ctx.world_size > 1:
+                t = torch.tensor([base["value"]], dtype=torch.float64, device=dev)
+                torch.distributed.all_reduce(t)
+                base["value_all_ranks"] = float(t)
+        except Exception as e:
+            base = {"impl": "torch-baseline-server", "error": repr(e)[:300]}
+        torch.cuda.empty_cache()
     if kind == "resnet50":
         import torchvision
 
         model = torch.nn.Sequential(torchvision.models.resnet50(num_classes=1000), torch.nn.Softmax(-1))
-        conf = {"data": {"image_shape": "3,224,224", "filter": "topN(5)"}, "params": {"batch_size": bs, "dtype": "bf16"}}
+        conf = {"data": {"image_shape": "3,224,224", "filter": "topN(5)"}, "params": {"batch_size": bs, "dtype": os.environ.get("ZOO_SERVING_DTYPE", "bf16")}}
     else:
         from zoo.models.recommendation import NeuralCF
 
         model = NeuralCF(1_000_000, 100_000, 5, user_embed=64, item_embed=64, hidden_layers=[128, 64, 32], mf_embed=32, sparse=False)
-        conf = {"data": {"filter": "topN(1)"}, "params": {"batch_size": bs, "dtype": "fp32"}}
+        conf = {"data": {"filter": "topN(1)"}, "params": {"batch_size": bs, "dtype": os.environ.get("ZOO_SERVING_DTYPE", "fp32")}}
     srv = ClusterServing(conf, model=model, device=dev).start()
     q = InputQueue(conf, broker=srv.db)
     K, Wm = args.steps, max(args.warmup, 3)
@@ -165,6 +179,8 @@ def _serving(args, ctx, torch):
                           "n_gpus": ctx.world_size, "steps": K, "warmup": Wm, "ms_per_step": float(res[1]) * 1e3 / K,
                           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": conf["params"]["dtype"], "data": "synthetic",
                           "impl": "zoo-b200", "p50_batch_ms": float(np.percentile(lat, 50)), "p99_batch_ms": float(np.percentile(lat, 99)),
+                          "torch_baseline": base,
+                          "vs_torch_baseline": (float(res[0] / res[1]) / (base.get("value_all_ranks") or base["value"])) if base and base.get("value") else None,
                           "config": {"model": kind, "global_batch": bs * ctx.world_size, "seq_len": None,
                                      "parallelism": f"{ctx.world_size} serving replicas (one engine + in-process broker per GPU)",
                                      "timing": "wall clock over the whole pipeline: enqueue -> broker -> decode -> K13 -> model -> K14 -> result hash"}}))

@@ -20,7 +20,7 @@ rows = n // 4096
 out = {}
 nvls = {}
 for mode in ("nccl", "p2p", "p2p-nonvls"):
-    os.environ["ZOO_NVLS"] = "0" if mode == "p2p-nonvls" else "1"
+    os.environ["ZOO_NVLS"] = "0" if mode == "p2p-nonvls" else "1"      # force both variants: the default (`auto`) picks by world size
     if mode == "p2p-nonvls":
         from zoo.parallel import symm as _symm
 

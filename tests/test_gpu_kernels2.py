@@ -116,3 +116,30 @@ def test_recommend_topn():
         by.setdefault(int(users[i]), []).append((-int(rc[i]), -float(rp[i]), i))
     want = [i for u in sorted(by) for _, _, i in sorted(by[u])[:N]]
     assert sel.tolist() == want
+
+
+def test_nvjpeg_batch_decode_and_preprocess_match_cv2():
+    """JPEG bytes -> nvJPEG batched decode on the GPU -> K13 must match cv2.imdecode + the CPU preprocessing oracle (decoders may
+    differ by a couple of grey levels in their IDCT / chroma upsampling)."""
+    import cv2
+    import numpy as np
+
+    from zoo.ops.serving_ops import JpegBatchDecoder, preprocess_jpegs, preprocess_reference
+
+    if not JpegBatchDecoder.available():
+        pytest.skip("libnvjpeg not available")
+    rng = np.random.RandomState(0)
+    imgs = []
+    for (h, w) in [(224, 224), (180, 260), (300, 200), (64, 64)]:
+        base = cv2.resize(rng.randint(0, 256, (h // 8, w // 8, 3), dtype=np.uint8), (w, h), interpolation=cv2.INTER_CUBIC)   # smooth content
+        imgs.append(base)
+    jpgs = [cv2.imencode(".jpg", im, [cv2.IMWRITE_JPEG_QUALITY, 92])[1].tobytes() for im in imgs]
+    dec = JpegBatchDecoder("cuda:0")
+    mean, std = [123.68, 116.779, 103.939], [58.393, 57.12, 57.375]
+    for _ in range(2):                              # twice: the decoder state is reused
+        got = preprocess_jpegs(jpgs, (112, 112), dec, None, mean, std, swap_rb=True, chw=True, dtype=torch.float32)
+        torch.cuda.synchronize()
+    want = preprocess_reference([cv2.imdecode(np.frombuffer(j, np.uint8), cv2.IMREAD_COLOR) for j in jpgs], (112, 112), None, mean, std, True, True)
+    diff = (got.cpu() - want).abs() * 58.0        # back to grey levels
+    assert float(diff.mean()) < 1.5 and float(diff.max()) < 24, (float(diff.mean()), float(diff.max()))
+    dec.close()

@@ -20,6 +20,10 @@ _V, _I, _L = C.c_void_p, C.c_int, C.c_longlong
 _nl.register_cuda_sigs({
     "zoo_serving_preproc": [_V, _V, _V, _V, _I, _I, _I, _I, _I, _I, _V, _V, _I, _I, _I, _V],
     "zoo_serving_topk": [_V, _L, _I, _I, _I, _I, _I, _V, _V, _V],
+    "zoo_jpeg_batch_create": [_I, _I, _V, _V],
+    "zoo_jpeg_batch_destroy": [_V],
+    "zoo_jpeg_batch_info": [_V, _V, _V, _I, _V, _V, _V],
+    "zoo_jpeg_batch_decode": [_V, _V, _V, _I, _V, _V, _V, _I, _V],
 })
 
 
@@ -122,6 +126,87 @@ def preprocess_images(images, out_hw, resize_hw=None, mean=None, std=None, swap_
                                                  C.cast(m, _V) if m is not None else None, C.cast(s, _V) if s is not None else None,
                                                  int(swap_rb), int(chw), int(dtype == torch.bfloat16), _nl.stream_ptr()),
               "zoo_serving_preproc")
+    return out
+
+
+class JpegBatchDecoder:
+    """nvJPEG batched decode into device memory (csrc/ops/jpeg_batch.cu): a list of JPEG byte strings -> one packed uint8 device
+    buffer of interleaved BGR images + their offsets / sizes, the layout K13 consumes.  `JpegBatchDecoder.available()` tells whether
+    libnvjpeg could be loaded; the serving engine falls back to cv2 on host threads when it cannot."""
+
+    def __init__(self, device, max_bytes=96 << 20, max_batch=512, cpu_threads=8, backend=-1):
+        self.device = torch.device(device)
+        lib = _nl.cuda_lib()
+        h, used = C.c_void_p(), C.c_int(-1)
+        with torch.cuda.device(self.device):
+            _nl.check(lib.zoo_jpeg_batch_create(backend, cpu_threads, C.byref(h), C.byref(used)), "zoo_jpeg_batch_create")
+        _nl.LAUNCH_COUNT["n"] -= 1          # (not a kernel launch)
+        self.handle, self.backend = h, used.value
+        self.dev = torch.empty(max_bytes, dtype=torch.uint8, device=self.device)
+        self.meta_host = torch.empty(max_batch * 4, dtype=torch.int64).pin_memory()
+        self.meta_dev = torch.empty(max_batch * 4, dtype=torch.int64, device=self.device)
+        self.max_batch = max_batch
+
+    @staticmethod
+    def available():
+        try:
+            return bool(_nl.cuda_lib().zoo_jpeg_available()) and torch.cuda.is_available()
+        except Exception:
+            return False
+
+    def decode(self, jpegs):
+        """jpegs: list of bytes.  Returns (B, offsets/hw already on the device in self.meta_dev, total bytes); the pixels are in
+        self.dev.  Asynchronous on the current stream."""
+        B = len(jpegs)
+        if B > self.max_batch:
+            raise ValueError(f"batch {B} > max_batch {self.max_batch}")
+        lib = _nl.cuda_lib()
+        bufs = [np.frombuffer(j, dtype=np.uint8) for j in jpegs]
+        ptrs = (C.c_void_p * B)(*[b.ctypes.data for b in bufs])
+        lens = (C.c_size_t * B)(*[b.size for b in bufs])
+        ws, hs = (C.c_int * B)(), (C.c_int * B)()
+        rc = lib.zoo_jpeg_batch_info(self.handle, ptrs, lens, B, ws, hs, None)
+        if rc != 0:
+            raise _nl.NativeError("zoo_jpeg_batch_info: " + lib.zoo_last_error().decode(errors="replace"))
+        offs = self.meta_host[:B].numpy()
+        hw = self.meta_host[B:2 * B].numpy().view(np.int32)
+        off = 0
+        for i in range(B):
+            offs[i] = off
+            hw[2 * i], hw[2 * i + 1] = hs[i], ws[i]
+            off += (hs[i] * ws[i] * 3 + 15) // 16 * 16
+        if off > self.dev.numel():
+            raise ValueError("decoded batch exceeds the device staging buffer")
+        coffs = (C.c_longlong * B)(*[int(o) for o in offs])
+        with torch.cuda.device(self.device):
+            rc = lib.zoo_jpeg_batch_decode(self.handle, ptrs, lens, B, self.dev.data_ptr(), coffs, ws, 1, _nl.stream_ptr())
+        if rc != 0:
+            raise _nl.NativeError("zoo_jpeg_batch_decode: " + lib.zoo_last_error().decode(errors="replace"))
+        self.meta_dev[:2 * B].copy_(self.meta_host[:2 * B], non_blocking=True)
+        self._keep = bufs                       # the bitstreams must outlive the asynchronous decode
+        return B, off
+
+    def close(self):
+        if self.handle:
+            _nl.cuda_lib().zoo_jpeg_batch_destroy(self.handle)
+            self.handle = None
+
+
+def preprocess_jpegs(jpegs, out_hw, decoder: JpegBatchDecoder, resize_hw=None, mean=None, std=None, swap_rb=False, chw=True,
+                     dtype=torch.float32, out=None):
+    """JPEG byte strings -> [B,3,OH,OW] on the decoder's device: nvJPEG batched decode + K13, no pixels on the host."""
+    OH, OW = out_hw
+    RH, RW = resize_hw or out_hw
+    B, _ = decoder.decode(jpegs)
+    shape = (B, 3, OH, OW) if chw else (B, OH, OW, 3)
+    if out is None:
+        out = torch.empty(shape, dtype=dtype, device=decoder.device)
+    fa = lambda v: None if v is None else (C.c_float * 4)(*(list(np.asarray(v, np.float32).reshape(-1)) + [1.0] * 4)[:4])
+    m, s = fa(mean), fa(std)
+    _nl.check(_nl.cuda_lib().zoo_serving_preproc(decoder.dev.data_ptr(), decoder.meta_dev.data_ptr(), decoder.meta_dev[B:].data_ptr(),
+                                                 out.data_ptr(), B, 3, OH, OW, RH, RW, C.cast(m, _V) if m is not None else None,
+                                                 C.cast(s, _V) if s is not None else None, int(swap_rb), int(chw),
+                                                 int(dtype == torch.bfloat16), _nl.stream_ptr()), "zoo_serving_preproc")
     return out
 
 

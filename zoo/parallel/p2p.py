@@ -98,7 +98,12 @@ class P2PFusedSync:
         # then the ordinary local fused optimizer -- clipping included -- on the summed gradient.
         n = a.numel
         self.small = self._is_small(n)
-        self.nvls = (not self.small) and self.buf_g.mc_ptr is not None and self.buf_p.mc_ptr is not None
+        # NVLS (in-switch reduction / broadcast): measured on 2 GPUs the multicast path is SLOWER than peer loads and stores
+        # (0.420 vs 0.302 ms for 25.6 M parameters: with two ranks the switch saves nothing and every access, the local copy
+        # included, crosses NVLink); it pays when one load replaces many, so `auto` takes it from 4 ranks on.  ZOO_NVLS=1 / 0 force it.
+        want = os.environ.get("ZOO_NVLS", "auto")
+        self.nvls = ((not self.small) and self.buf_g.mc_ptr is not None and self.buf_p.mc_ptr is not None
+                     and (want == "1" or (want == "auto" and W >= 4)))
         self._pushed = False
         if self.small:
             if n % 8:

@@ -141,7 +141,7 @@ class SymmetricHeap:
 
         if getattr(self, "_mc_gran", None) is None:
             g = 0
-            if self.ctx.world_size > 1 and self.mode == "vmm" and os.environ.get("ZOO_NVLS", "1") != "0":
+            if self.ctx.world_size > 1 and self.mode == "vmm" and os.environ.get("ZOO_NVLS", "auto") != "0":
                 import torch.distributed as dist
 
                 ok, gran = C.c_int(0), C.c_longlong(0)

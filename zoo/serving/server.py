@@ -179,6 +179,35 @@ class ClusterServing:
             self.model.quantize(x)
         return self.model.predict_tensor(x)
 
+    def _jpeg_decoder(self):
+        """nvJPEG batched decoder on the engine's GPU (None on CPU, without libnvjpeg, or with ZOO_SERVING_NVJPEG=0)."""
+        if not hasattr(self, "_jpeg"):
+            self._jpeg = None
+            if self.device.type == "cuda" and os.environ.get("ZOO_SERVING_NVJPEG", "1") != "0":
+                from ..ops.serving_ops import JpegBatchDecoder
+
+                if JpegBatchDecoder.available():
+                    try:
+                        self._jpeg = JpegBatchDecoder(self.device, max_batch=max(512, self.conf.batch_size))
+                    except Exception as e:
+                        log.warning("nvJPEG decoder unavailable (%r); decoding on host threads", e)
+        return self._jpeg
+
+    def _infer_jpegs(self, fields):
+        """JPEG records of one batch: base64 -> nvJPEG batched decode on the GPU -> K13 -> model -> K14; pixels never touch the host.
+        A batch nvJPEG cannot decode (progressive / CMYK / corrupt records) is retried on the host path."""
+        from ..ops.serving_ops import preprocess_jpegs
+
+        c = self.conf
+        raws = list(self.pool.map(lambda f: base64.b64decode(f["image"]), fields))
+        try:
+            dtype = self.model.dtype or torch.float32
+            x = preprocess_jpegs(raws, (c.H, c.W), self._jpeg, None, c.mean[:3], c.std[:3], swap_rb=True, chw=c.chw, dtype=dtype)
+        except Exception as e:
+            log.warning("nvJPEG batch decode failed (%r); decoding this batch on the host", e)
+            return self._infer(list(self.pool.map(self._decode_one, fields)))
+        return self._finish(self._predict(x))
+
     def _infer(self, items):
         """items: list of decoded arrays -> (kind, payload) for the writer."""
         c = self.conf
@@ -194,6 +223,11 @@ class ClusterServing:
         else:
             xs = torch.from_numpy(np.stack(items))
             out = self._predict(xs)
+        return self._finish(out)
+
+    def _finish(self, out):
+        """Model output -> (kind, payload) for the writer: per-row top-N on the GPU (K14) or the raw tensor."""
+        c = self.conf
         if isinstance(out, (tuple, list)):
             out = out[0]
         out = out.reshape(out.shape[0], -1)
@@ -254,8 +288,11 @@ class ClusterServing:
                 # tensor records: from the next batch on use the packed batch path (homogeneous shape / dtype)
                 self._tensor_meta = ([int(v) for v in f0["shape"].decode().split(",") if v], np.dtype(f0["dtype"].decode()))
             try:
-                items = list(self.pool.map(self._decode_one, [f for _, f in entries]))
-                kind, payload = self._infer(items)
+                if "image" in f0 and self._jpeg_decoder() is not None and self.conf.C == 3:
+                    kind, payload = self._infer_jpegs([f for _, f in entries])
+                else:
+                    items = list(self.pool.map(self._decode_one, [f for _, f in entries]))
+                    kind, payload = self._infer(items)
             except Exception as e:  # a bad record must not stop the service
                 log.exception("batch failed: %r", e)
                 self._out_q.put((uris, "error", repr(e), t0))
