@@ -27,7 +27,10 @@ def run_serving_baseline(kind, dev, steps, warmup, batch=0, rank=0):
         import torchvision
 
         model = torch.nn.Sequential(torchvision.models.resnet50(num_classes=1000), torch.nn.Softmax(-1)).to(dev).eval()
-        jpgs = [cv2.imencode(".jpg", rng.randint(0, 256, (224, 224, 3), dtype=np.uint8))[1].tobytes() for _ in range(64)]
+        import base64
+
+        # records arrive base64-encoded, as in the reference's client protocol (pyzoo/zoo/serving/client.py:87-126)
+        jpgs = [base64.b64encode(cv2.imencode(".jpg", rng.randint(0, 256, (224, 224, 3), dtype=np.uint8))[1].tobytes()) for _ in range(64)]
         mean = torch.tensor([123.68, 116.779, 103.939], device=dev).view(1, 3, 1, 1)
         std = torch.tensor([58.393, 57.12, 57.375], device=dev).view(1, 3, 1, 1)
         pool = ThreadPoolExecutor(16)
@@ -37,7 +40,7 @@ def run_serving_baseline(kind, dev, steps, warmup, batch=0, rank=0):
                 q.put((f"r{i}", jpgs[i % 64], time.perf_counter()))
 
         def infer(items):
-            imgs = list(pool.map(lambda b: cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_COLOR), [it[1] for it in items]))
+            imgs = list(pool.map(lambda b: cv2.imdecode(np.frombuffer(base64.b64decode(b), np.uint8), cv2.IMREAD_COLOR), [it[1] for it in items]))
             x = torch.from_numpy(np.stack(imgs)).to(dev, non_blocking=True).permute(0, 3, 1, 2).float()
             x = (F.interpolate(x, size=(224, 224), mode="bilinear", align_corners=False).flip(1) - mean) / std
             with torch.autocast("cuda", dtype=torch.bfloat16):

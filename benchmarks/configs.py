@@ -179,7 +179,8 @@ def _serving(args, ctx, torch):
                           "n_gpus": ctx.world_size, "steps": K, "warmup": Wm, "ms_per_step": float(res[1]) * 1e3 / K,
                           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": conf["params"]["dtype"], "data": "synthetic",
                           "impl": "zoo-b200", "p50_batch_ms": float(np.percentile(lat, 50)), "p99_batch_ms": float(np.percentile(lat, 99)),
-                          "torch_baseline": base,
+                          "torch_baseline": base, "engine_stage_seconds": getattr(srv, "stage_s", None),
+                          "jpeg_backend": getattr(getattr(srv, "_jpeg", None), "backend", None),
                           "vs_torch_baseline": (float(res[0] / res[1]) / (base.get("value_all_ranks") or base["value"])) if base and base.get("value") else None,
                           "config": {"model": kind, "global_batch": bs * ctx.world_size, "seq_len": None,
                                      "parallelism": f"{ctx.world_size} serving replicas (one engine + in-process broker per GPU)",

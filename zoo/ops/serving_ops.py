@@ -142,6 +142,8 @@ class JpegBatchDecoder:
             _nl.check(lib.zoo_jpeg_batch_create(backend, cpu_threads, C.byref(h), C.byref(used)), "zoo_jpeg_batch_create")
         _nl.LAUNCH_COUNT["n"] -= 1          # (not a kernel launch)
         self.handle, self.backend = h, used.value
+        self._by_size = {}          # padded batch size -> decoder state (nvJPEG's batched state is sized for ONE batch size)
+        self._create_args = (backend, cpu_threads)
         self.dev = torch.empty(max_bytes, dtype=torch.uint8, device=self.device)
         self.meta_host = torch.empty(max_batch * 4, dtype=torch.int64).pin_memory()
         self.meta_dev = torch.empty(max_batch * 4, dtype=torch.int64, device=self.device)
@@ -157,15 +159,33 @@ class JpegBatchDecoder:
     def decode(self, jpegs):
         """jpegs: list of bytes.  Returns (B, offsets/hw already on the device in self.meta_dev, total bytes); the pixels are in
         self.dev.  Asynchronous on the current stream."""
-        B = len(jpegs)
-        if B > self.max_batch:
-            raise ValueError(f"batch {B} > max_batch {self.max_batch}")
+        n_real = len(jpegs)
+        if n_real > self.max_batch:
+            raise ValueError(f"batch {n_real} > max_batch {self.max_batch}")
         lib = _nl.cuda_lib()
+        # The engine batches continuously (whatever has arrived), so batch sizes vary; the batch is padded to the next power of two
+        # with repeats of its first image (decoded into spare space) and every padded size keeps its own decoder state.
+        B = 1
+        while B < n_real:
+            B *= 2
+        B = min(B, self.max_batch)
+        handle = self._by_size.get(B)
+        if handle is None:
+            if not self._by_size:
+                handle = self.handle
+            else:
+                handle, used = C.c_void_p(), C.c_int(-1)
+                with torch.cuda.device(self.device):
+                    rc = lib.zoo_jpeg_batch_create(self.backend, self._create_args[1], C.byref(handle), C.byref(used))
+                if rc != 0:
+                    raise _nl.NativeError("zoo_jpeg_batch_create: " + lib.zoo_last_error().decode(errors="replace"))
+            self._by_size[B] = handle
         bufs = [np.frombuffer(j, dtype=np.uint8) for j in jpegs]
+        bufs += [bufs[0]] * (B - n_real)
         ptrs = (C.c_void_p * B)(*[b.ctypes.data for b in bufs])
         lens = (C.c_size_t * B)(*[b.size for b in bufs])
         ws, hs = (C.c_int * B)(), (C.c_int * B)()
-        rc = lib.zoo_jpeg_batch_info(self.handle, ptrs, lens, B, ws, hs, None)
+        rc = lib.zoo_jpeg_batch_info(handle, ptrs, lens, B, ws, hs, None)
         if rc != 0:
             raise _nl.NativeError("zoo_jpeg_batch_info: " + lib.zoo_last_error().decode(errors="replace"))
         offs = self.meta_host[:B].numpy()
@@ -179,17 +199,21 @@ class JpegBatchDecoder:
             raise ValueError("decoded batch exceeds the device staging buffer")
         coffs = (C.c_longlong * B)(*[int(o) for o in offs])
         with torch.cuda.device(self.device):
-            rc = lib.zoo_jpeg_batch_decode(self.handle, ptrs, lens, B, self.dev.data_ptr(), coffs, ws, 1, _nl.stream_ptr())
+            rc = lib.zoo_jpeg_batch_decode(handle, ptrs, lens, B, self.dev.data_ptr(), coffs, ws, 1, _nl.stream_ptr())
         if rc != 0:
             raise _nl.NativeError("zoo_jpeg_batch_decode: " + lib.zoo_last_error().decode(errors="replace"))
-        self.meta_dev[:2 * B].copy_(self.meta_host[:2 * B], non_blocking=True)
+        # offsets of the real images, then their (h, w) pairs, contiguous for K13
+        if B != n_real:
+            self.meta_host[n_real:n_real + n_real] = self.meta_host[B:B + n_real].clone()
+        self.meta_dev[:2 * n_real].copy_(self.meta_host[:2 * n_real], non_blocking=True)
         self._keep = bufs                       # the bitstreams must outlive the asynchronous decode
-        return B, off
+        return n_real, off
 
     def close(self):
-        if self.handle:
-            _nl.cuda_lib().zoo_jpeg_batch_destroy(self.handle)
-            self.handle = None
+        handles = set(h.value for h in self._by_size.values() if h) | ({self.handle.value} if self.handle else set())
+        for h in handles:
+            _nl.cuda_lib().zoo_jpeg_batch_destroy(C.c_void_p(h))
+        self.handle, self._by_size = None, {}
 
 
 def preprocess_jpegs(jpegs, out_hw, decoder: JpegBatchDecoder, resize_hw=None, mean=None, std=None, swap_rb=False, chw=True,

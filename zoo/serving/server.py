@@ -116,6 +116,7 @@ class ClusterServing:
         self._threads = []
         self._out_q = queue.Queue(maxsize=8)
         self.total_records = 0
+        self.stage_s = {"read": 0.0, "b64": 0.0, "decode+preproc": 0.0, "model+post": 0.0, "batches": 0}   # host time per stage
         self.latencies = []           # per-batch (n, seconds in engine)
         self.summary = None
         self.stop_file = os.path.join(self.conf.log_dir, "running")
@@ -199,14 +200,21 @@ class ClusterServing:
         from ..ops.serving_ops import preprocess_jpegs
 
         c = self.conf
+        t0 = time.perf_counter()
         raws = list(self.pool.map(lambda f: base64.b64decode(f["image"]), fields))
+        t1 = time.perf_counter()
         try:
             dtype = self.model.dtype or torch.float32
             x = preprocess_jpegs(raws, (c.H, c.W), self._jpeg, None, c.mean[:3], c.std[:3], swap_rb=True, chw=c.chw, dtype=dtype)
         except Exception as e:
             log.warning("nvJPEG batch decode failed (%r); decoding this batch on the host", e)
             return self._infer(list(self.pool.map(self._decode_one, fields)))
-        return self._finish(self._predict(x))
+        t2 = time.perf_counter()
+        res = self._finish(self._predict(x))
+        t3 = time.perf_counter()
+        st = self.stage_s
+        st["b64"] += t1 - t0; st["decode+preproc"] += t2 - t1; st["model+post"] += t3 - t2; st["batches"] += 1
+        return res
 
     def _infer(self, items):
         """items: list of decoded arrays -> (kind, payload) for the writer."""
@@ -275,7 +283,10 @@ class ClusterServing:
                     log.exception("batch failed: %r", e)
                     self._out_q.put((uris.decode().split("\n")[:-1], "error", repr(e), t0))
                 continue
+            tr = time.perf_counter()
             entries = self._read_batch(5)
+            if entries:
+                self.stage_s["read"] += time.perf_counter() - tr
             if not entries:
                 idle += 1
                 if idle % 200 == 0 and not os.path.exists(self.stop_file) and getattr(self, "_watch_file", False):
