@@ -32,6 +32,7 @@ def rt():
             "zoo_records_create": ([_V], _V), "zoo_records_destroy": ([_V], None), "zoo_records_count": ([_V], _L),
             "zoo_records_append": ([_V, _V, _L], _L), "zoo_records_get": ([_V, _L, C.POINTER(_V)], _L),
             "zoo_records_gather": ([_V, _V, _L, _V, _L, _V, _I], _L),
+            "zoo_b64_decode_batch": ([_V, _V, _I, _V, _V, _V, _I], _I),
             "zoo_crc32c": ([_V, _L], C.c_uint), "zoo_masked_crc32c": ([_V, _L], C.c_uint), "zoo_tfrecord_frame": ([_V, _L, _V], _L),
         }
         for name, (args, res) in sig.items():
@@ -443,3 +444,21 @@ def tfrecord_frame(data: bytes) -> bytes:
     out = C.create_string_buffer(len(data) + 16)
     n = rt().zoo_tfrecord_frame(data, len(data), out)
     return out.raw[:n]
+
+
+def b64_decode_batch(strings, out: "np.ndarray | None" = None, threads=8):
+    """Decode a list of base64 byte strings on native threads (no interpreter lock).  Returns (buffer uint8, offsets, lengths):
+    record i is buffer[offsets[i] : offsets[i] + lengths[i]]; a malformed record has length -1."""
+    n = len(strings)
+    lens = np.fromiter((len(s) for s in strings), dtype=np.int64, count=n)
+    caps = (lens + 3) // 4 * 3
+    offs = np.zeros(n, dtype=np.int64)
+    if n:
+        np.cumsum((caps[:-1] + 15) // 16 * 16, out=offs[1:])
+    total = int(offs[-1] + caps[-1]) if n else 0
+    if out is None or out.size < total:
+        out = np.empty(max(total, 1), dtype=np.uint8)
+    out_len = np.zeros(n, dtype=np.int64)
+    ptrs = (C.c_char_p * n)(*strings)
+    rt().zoo_b64_decode_batch(C.cast(ptrs, _V), lens.ctypes.data, n, out.ctypes.data, offs.ctypes.data, out_len.ctypes.data, int(threads))
+    return out, offs, out_len

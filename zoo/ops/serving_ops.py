@@ -159,7 +159,7 @@ class JpegBatchDecoder:
     def decode(self, jpegs):
         """jpegs: list of bytes.  Returns (B, offsets/hw already on the device in self.meta_dev, total bytes); the pixels are in
         self.dev.  Asynchronous on the current stream."""
-        n_real = len(jpegs)
+        n_real = len(jpegs[1]) if isinstance(jpegs, tuple) else len(jpegs)
         if n_real > self.max_batch:
             raise ValueError(f"batch {n_real} > max_batch {self.max_batch}")
         lib = _nl.cuda_lib()
@@ -180,10 +180,20 @@ class JpegBatchDecoder:
                 if rc != 0:
                     raise _nl.NativeError("zoo_jpeg_batch_create: " + lib.zoo_last_error().decode(errors="replace"))
             self._by_size[B] = handle
-        bufs = [np.frombuffer(j, dtype=np.uint8) for j in jpegs]
-        bufs += [bufs[0]] * (B - n_real)
-        ptrs = (C.c_void_p * B)(*[b.ctypes.data for b in bufs])
-        lens = (C.c_size_t * B)(*[b.size for b in bufs])
+        if isinstance(jpegs, tuple):        # (buffer, offsets, lengths) from zoo.native.rt.b64_decode_batch: no per-record objects
+            buf, boffs, blens = jpegs
+            base = buf.ctypes.data
+            addr = [base + int(o) for o in boffs] + [base + int(boffs[0])] * (B - n_real)
+            size = [int(v) for v in blens] + [int(blens[0])] * (B - n_real)
+            if min(size) <= 0:
+                raise ValueError("a record of the batch is not valid base64")
+            bufs = [buf]
+        else:
+            bufs = [np.frombuffer(j, dtype=np.uint8) for j in jpegs]
+            addr = [b.ctypes.data for b in bufs] + [bufs[0].ctypes.data] * (B - n_real)
+            size = [b.size for b in bufs] + [bufs[0].size] * (B - n_real)
+        ptrs = (C.c_void_p * B)(*addr)
+        lens = (C.c_size_t * B)(*size)
         ws, hs = (C.c_int * B)(), (C.c_int * B)()
         rc = lib.zoo_jpeg_batch_info(handle, ptrs, lens, B, ws, hs, None)
         if rc != 0:
@@ -206,7 +216,7 @@ class JpegBatchDecoder:
         if B != n_real:
             self.meta_host[n_real:n_real + n_real] = self.meta_host[B:B + n_real].clone()
         self.meta_dev[:2 * n_real].copy_(self.meta_host[:2 * n_real], non_blocking=True)
-        self._keep = bufs                       # the bitstreams must outlive the asynchronous decode
+        self._keep = (getattr(self, "_keep", (None, None))[1], bufs)      # the bitstreams outlive the asynchronous decode (two generations)
         return n_real, off
 
     def close(self):

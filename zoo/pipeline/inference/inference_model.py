@@ -32,12 +32,15 @@ class _Slot:
 
 
 class InferenceModel:
-    def __init__(self, supported_concurrent_num=1, device=None, dtype=None, use_cuda_graph=True, channels_last=False):
+    def __init__(self, supported_concurrent_num=1, device=None, dtype=None, use_cuda_graph=True, channels_last=False, cast_weights=False):
         self.concurrent_num = int(supported_concurrent_num)
         self.device = torch.device(device) if device is not None else torch.device("cuda" if torch.cuda.is_available() else "cpu")
         self.dtype = dtype                     # None = model's own precision; torch.bfloat16 = autocast
         self.use_cuda_graph = use_cuda_graph
         self.channels_last = channels_last
+        # cast_weights: convert floating-point parameters and buffers to `dtype` ONCE at load time and feed inputs in that dtype,
+        # instead of autocasting every call (autocast re-casts fp32 weights per forward; for inference the copy is pure overhead)
+        self.cast_weights = bool(cast_weights) and dtype is not None
         self.model: nn.Module | None = None
         self._slots: queue.Queue | None = None
         self._made = 0
@@ -50,8 +53,12 @@ class InferenceModel:
         model = model.to(self.device).eval()
         for p in model.parameters():
             p.requires_grad_(False)
+        if self.channels_last == "auto":
+            self.channels_last = any(isinstance(m, nn.Conv2d) for m in model.modules())
         if self.channels_last:
             model = model.to(memory_format=torch.channels_last)
+        if self.cast_weights and self.device.type == "cuda":
+            model = model.to(self.dtype)
         self.model = model
         n = self.concurrent_num if self.concurrent_num > 0 else 1
         self._slots = queue.Queue()
@@ -150,6 +157,8 @@ class InferenceModel:
             return _Slot(self.device, self.use_cuda_graph)
 
     def _forward(self, xs):
+        if self.cast_weights and self.device.type == "cuda":
+            return self.model(*[x.to(self.dtype) if x.is_floating_point() else x for x in xs])
         if self.dtype is not None and self.device.type == "cuda":
             with torch.autocast("cuda", dtype=self.dtype):
                 return self.model(*xs)

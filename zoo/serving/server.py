@@ -103,7 +103,8 @@ class ClusterServing:
         # batch that is served -- the 8-bit route of the reference's OpenVINO int8 serving; the rest of the model runs in bf16)
         dt = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp8": torch.bfloat16}.get(self.conf.dtype) if self.device.type == "cuda" else None
         self._quantize_pending = self.conf.dtype == "fp8"
-        self.model = InferenceModel(1, self.device, dtype=dt, channels_last=False)
+        # image models: NHWC (channels_last) activations and weights cast once to the compute dtype (no per-call autocast)
+        self.model = InferenceModel(1, self.device, dtype=dt, channels_last="auto", cast_weights=dt is not None and self.conf.dtype != "fp8")
         if model is not None:
             self.model.load_torch(model)
         elif self.conf.model_path:
@@ -194,27 +195,98 @@ class ClusterServing:
                         log.warning("nvJPEG decoder unavailable (%r); decoding on host threads", e)
         return self._jpeg
 
-    def _infer_jpegs(self, fields):
-        """JPEG records of one batch: base64 -> nvJPEG batched decode on the GPU -> K13 -> model -> K14; pixels never touch the host.
-        A batch nvJPEG cannot decode (progressive / CMYK / corrupt records) is retried on the host path."""
+    def _prep_jpegs(self, fields):
+        """base64 (native threads) -> nvJPEG batched decode -> K13, all enqueued on the CURRENT stream; returns the model input."""
+        from ..native.rt import b64_decode_batch
         from ..ops.serving_ops import preprocess_jpegs
 
         c = self.conf
         t0 = time.perf_counter()
-        raws = list(self.pool.map(lambda f: base64.b64decode(f["image"]), fields))
+        self._b64_buf, offs, lens = b64_decode_batch([f["image"] for f in fields], getattr(self, "_b64_buf", None),
+                                                     threads=min(8, os.cpu_count() or 4))
         t1 = time.perf_counter()
+        dtype = self.model.dtype or torch.float32
+        # NHWC output when the model runs channels_last: K13 writes the layout the convolutions want, no transpose pass
+        nhwc = bool(self.model.channels_last) and c.chw
+        x = preprocess_jpegs((self._b64_buf, offs, lens), (c.H, c.W), self._jpeg, None, c.mean[:3], c.std[:3], swap_rb=True,
+                             chw=not nhwc and c.chw, dtype=dtype)
+        if nhwc:
+            x = x.permute(0, 3, 1, 2)           # logical NCHW over channels_last memory
+        st = self.stage_s
+        st["b64"] += t1 - t0; st["decode+preproc"] += time.perf_counter() - t1
+        return x
+
+    def _infer_jpegs(self, fields):
+        """JPEG records of one batch: base64 -> nvJPEG batched decode on the GPU -> K13 -> model -> K14; pixels never touch the host.
+        A batch nvJPEG cannot decode (progressive / CMYK / corrupt records) is retried on the host path."""
         try:
-            dtype = self.model.dtype or torch.float32
-            x = preprocess_jpegs(raws, (c.H, c.W), self._jpeg, None, c.mean[:3], c.std[:3], swap_rb=True, chw=c.chw, dtype=dtype)
+            x = self._prep_jpegs(fields)
         except Exception as e:
             log.warning("nvJPEG batch decode failed (%r); decoding this batch on the host", e)
             return self._infer(list(self.pool.map(self._decode_one, fields)))
         t2 = time.perf_counter()
         res = self._finish(self._predict(x))
-        t3 = time.perf_counter()
-        st = self.stage_s
-        st["b64"] += t1 - t0; st["decode+preproc"] += t2 - t1; st["model+post"] += t3 - t2; st["batches"] += 1
+        self.stage_s["model+post"] += time.perf_counter() - t2
+        self.stage_s["batches"] += 1
         return res
+
+    def _prep_loop(self):
+        """Pipelined image mode: this thread reads, base64-decodes and enqueues decode + K13 on its own CUDA stream while the engine
+        thread runs the model of the previous batch; batches are handed over with a CUDA event (no host synchronisation)."""
+        stream = torch.cuda.Stream(self.device)
+        while not self._stop.is_set():
+            tr = time.perf_counter()
+            entries = self._read_batch(5)
+            if not entries:
+                continue
+            self.stage_s["read"] += time.perf_counter() - tr
+            t0 = time.perf_counter()
+            uris = [f["uri"].decode() for _, f in entries]
+            fields = [f for _, f in entries]
+            item = None
+            if all("image" in f for f in fields):
+                try:
+                    with torch.cuda.stream(stream):
+                        x = self._prep_jpegs(fields)
+                        ev = torch.cuda.Event()
+                        ev.record(stream)
+                    item = (uris, x, ev, None, t0)
+                except Exception as e:
+                    log.warning("nvJPEG batch decode failed (%r); decoding this batch on the host", e)
+            if item is None:
+                item = (uris, None, None, fields, t0)
+            while not self._stop.is_set():
+                try:
+                    self._prep_q.put(item, timeout=0.2)
+                    break
+                except queue.Full:
+                    continue
+
+    def _engine_from_prep(self):
+        """Engine side of the pipelined image mode."""
+        cur = torch.cuda.current_stream(self.device)
+        while not self._stop.is_set():
+            try:
+                uris, x, ev, fields, t0 = self._prep_q.get(timeout=0.2)
+            except queue.Empty:
+                continue
+            try:
+                if x is not None:
+                    cur.wait_event(ev)
+                    x.record_stream(cur)
+                    t2 = time.perf_counter()
+                    kind, payload = self._finish(self._predict(x))
+                    self.stage_s["model+post"] += time.perf_counter() - t2
+                    self.stage_s["batches"] += 1
+                else:
+                    kind, payload = self._infer(list(self.pool.map(self._decode_one, fields)))
+            except Exception as e:
+                log.exception("batch failed: %r", e)
+                self._out_q.put((uris, "error", repr(e), t0))
+                continue
+            self._out_q.put((uris, kind, payload, t0))
+            if self.total_records % 2048 < len(uris):
+                self._memory_guard()
 
     def _infer(self, items):
         """items: list of decoded arrays -> (kind, payload) for the writer."""
@@ -301,6 +373,14 @@ class ClusterServing:
             try:
                 if "image" in f0 and self._jpeg_decoder() is not None and self.conf.C == 3:
                     kind, payload = self._infer_jpegs([f for _, f in entries])
+                    if os.environ.get("ZOO_SERVING_PIPELINE", "1") != "0":
+                        # image stream on a GPU with nvJPEG: from here on a second thread prepares batch i+1 while this one runs batch i
+                        self._out_q.put((uris, kind, payload, t0))
+                        self._prep_q = queue.Queue(maxsize=2)
+                        t = threading.Thread(target=self._prep_loop, daemon=True, name="zoo-serving-prep")
+                        t.start()
+                        self._threads.append(t)
+                        return self._engine_from_prep()
                 else:
                     items = list(self.pool.map(self._decode_one, [f for _, f in entries]))
                     kind, payload = self._infer(items)
