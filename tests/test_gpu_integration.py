@@ -78,7 +78,9 @@ def test_serving_on_gpu_matches_direct_inference():
         top = p.topk(3)
         got = eval(res[uri])
         assert [g[0] for g in got] == top.indices.tolist()
-        np.testing.assert_allclose([g[1] for g in got], top.values.detach().numpy(), atol=1e-4)
+        # the engine decodes with nvJPEG on the GPU, this check with OpenCV on the host: the two decoders differ by a grey level or
+        # two (IDCT rounding, chroma upsampling), which moves the probabilities in the third decimal
+        np.testing.assert_allclose([g[1] for g in got], top.values.detach().numpy(), atol=5e-3)
 
 
 def test_inference_model_graph_replay_matches_eager():
