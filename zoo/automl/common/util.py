@@ -106,8 +106,41 @@ def process(command, fail_fast=False, timeout=120):
     return session_execute(command, fail_fast=fail_fast, timeout=timeout)
 
 
+def _join(base, *parts):
+    return "/".join([str(base).rstrip("/")] + [str(q).strip("/") for q in parts])
+
+
 def get_remote_list(dir_in):
-    raise NotImplementedError("remote file systems (hdfs://) need clients that are not on this box")
+    """Names of the files under a remote directory (hdfs:// s3:// gs:// file://), through `zoo.util.filesystem`
+    (reference: util.py:193-207 shells out to `hadoop fs -ls`)."""
+    from ...util import filesystem as zfs
+
+    return [os.path.basename(q.rstrip("/")) for q in zfs.ls(dir_in)]
 
 
-upload_ppl_hdfs = restore_hdfs = get_remote_list
+def upload_ppl_hdfs(upload_dir, ckpt_name):
+    """Copy the local checkpoint `ckpt_name` (a file, or every file of a directory) into `upload_dir` (reference: util.py:210-220)."""
+    from ...util import filesystem as zfs
+
+    zfs.makedirs(upload_dir)
+    if os.path.isdir(ckpt_name):
+        base = os.path.basename(ckpt_name.rstrip("/"))
+        for root, _, files in os.walk(ckpt_name):
+            rel = os.path.relpath(root, ckpt_name)
+            for f in files:
+                zfs.put(os.path.join(root, f), _join(upload_dir, base, *([] if rel == "." else [rel]), f), over_write=True)
+    else:
+        zfs.put(ckpt_name, _join(upload_dir, os.path.basename(ckpt_name)), over_write=True)
+
+
+def restore_hdfs(model_path, remote_dir, feature_transformers=None, model=None, config=None):
+    """Fetch the zipped pipeline `basename(model_path)` from `remote_dir` and restore it (reference: util.py:223-239)."""
+    from ...util import filesystem as zfs
+
+    name = os.path.basename(model_path)
+    d = tempfile.mkdtemp(prefix="automl_save_")
+    try:
+        local = zfs.get(_join(remote_dir, name), os.path.join(d, name))
+        return restore_zip(local, feature_transformers, model, config)
+    finally:
+        shutil.rmtree(d, ignore_errors=True)

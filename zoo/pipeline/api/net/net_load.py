@@ -53,7 +53,7 @@ class Net:
         """prototxt + caffemodel -> GraphNet over the converted torch graph (zoo.models.caffe; Net.scala loadCaffe)."""
         from ....models.caffe import load_caffe as _load
 
-        return GraphNet(_load(def_path, model_path))
+        return GraphNet(_load(def_path, model_path)).eval()     # inference mode, as a freshly loaded Caffe net; training code calls .train()
 
     @staticmethod
     def load_keras(json_path=None, hdf5_path=None, by_name=False):

@@ -233,6 +233,7 @@ class ClusterServing:
     def _prep_loop(self):
         """Pipelined image mode: this thread reads, base64-decodes and enqueues decode + K13 on its own CUDA stream while the engine
         thread runs the model of the previous batch; batches are handed over with a CUDA event (no host synchronisation)."""
+        self._bind_device()
         stream = torch.cuda.Stream(self.device)
         while not self._stop.is_set():
             tr = time.perf_counter()
@@ -330,7 +331,14 @@ class ClusterServing:
         shape, dtype = self._tensor_meta
         return uris, data.view(dtype).reshape(n, *shape)
 
+    def _bind_device(self):
+        """The current CUDA device is per THREAD: a worker thread starts on device 0, and a kernel launched from it through the
+        native library would run there while its pointers live on this rank's device."""
+        if self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
+
     def _engine_loop(self):
+        self._bind_device()
         idle = 0
         self._pack_buf, self._tensor_meta = None, None
         while not self._stop.is_set():
@@ -395,6 +403,7 @@ class ClusterServing:
     def _writer_loop(self):
         from ..ops.serving_ops import format_topn
 
+        self._bind_device()
         while True:
             item = self._out_q.get()
             if item is None:

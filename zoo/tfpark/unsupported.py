@@ -10,16 +10,26 @@ def _stub(name, methods=()):
     def __init__(self, *a, **kw):
         raise NotImplementedError(_MSG.format(name=name))
 
-    ns = {"__init__": __init__, "__doc__": _MSG.format(name=name)}
+    ns = {"__init__": __init__, "__doc__": _MSG.format(name=name), "__zoo_stub__": True}
     for m in methods:
         ns[m] = staticmethod(lambda *a, _n=f"{name}.{m}", **kw: (_ for _ in ()).throw(NotImplementedError(_MSG.format(name=_n))))
     return type(name, (), ns)
 
 
-TFOptimizer = _stub("TFOptimizer", ("from_loss", "from_keras", "from_train_op"))
-TFEstimator = _stub("TFEstimator", ("from_model_fn",))
 from ..pipeline.api.net.tfnet import TFNet  # noqa: E402,F401  (real: frozen graphs are imported into torch, see zoo.tfpark.graphdef)
-TFPredictor = _stub("TFPredictor", ("from_outputs", "from_keras"))
+
+
+def __getattr__(name):      # TFOptimizer / TFEstimator / TFPredictor are real now and live in their own modules
+    if name == "TFOptimizer":
+        from .tf_optimizer import TFOptimizer
+        return TFOptimizer
+    if name == "TFEstimator":
+        from .estimator import TFEstimator
+        return TFEstimator
+    if name == "TFPredictor":
+        from .tf_predictor import TFPredictor
+        return TFPredictor
+    raise AttributeError(name)
 
 
 class ZooOptimizer:

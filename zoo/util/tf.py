@@ -191,15 +191,22 @@ def strip_unused(input_graph_def, input_tensor_names, output_tensor_names, place
     for n in read_graphdef(input_graph_def):          # original order
         if n.name not in seen:
             continue
-        if n.name in cut:
-            out.append((n.name, "Placeholder", [], {"dtype": dtype}))
-        else:
-            attrs = {}
-            for key in n.attr:
-                v = n.a(key)
-                if isinstance(v, int) and key in ("T", "dtype", "DstT", "SrcT", "Tshape", "Tperm", "U", "Tidx", "Tpaddings", "Tparams", "Tindices", "Taxis"):
-                    v = DT.get(v, np.float32)
-                if v is not None and not (isinstance(v, list) and len(v) == 0):
-                    attrs[key] = v
-            out.append((n.name, n.op, list(n.inputs), attrs))
+        out.append((n.name, "Placeholder", [], {"dtype": dtype}) if n.name in cut else node_tuple(n))
     return write_graphdef(None, out)
+
+
+_TYPE_ATTRS = ("T", "dtype", "DstT", "SrcT", "Tshape", "Tperm", "U", "Tidx", "Tpaddings", "Tparams", "Tindices", "Taxis")
+
+
+def node_tuple(n):
+    """A parsed `graphdef.Node` -> the (name, op, inputs, attrs) tuple `write_graphdef` takes."""
+    from ..tfpark.graphdef import DT
+
+    attrs = {}
+    for key in n.attr:
+        v = n.a(key)
+        if isinstance(v, int) and key in _TYPE_ATTRS:
+            v = DT.get(v, np.float32)
+        if v is not None and not (isinstance(v, list) and len(v) == 0):
+            attrs[key] = v
+    return (n.name, n.op, list(n.inputs), attrs)
