@@ -1,0 +1,48 @@
+"""Low-precision image inference through InferenceModel (reference examples: pyzoo/zoo/examples/openvino/predict.py and
+pyzoo/zoo/examples/vnni/openvino/predict.py: `InferenceModel.load_tf_object_detection_as_openvino` / `load_openvino(xml, bin)`,
+read an image folder with ImageSet, resize + channel order + to-tensor, `model.predict(batch)`, print the top classes).
+
+OpenVINO IRs are not loadable on this stack (`load_openvino` raises and names this route); the engine with the same role is
+InferenceModel on a torch model: convolutions in bf16 channels_last through cuDNN and, after `quantize(calibration_batch)`, every
+Linear / Dense layer in FP8 (E4M3) on the tcgen05 GEMM kernel."""
+import os
+import sys
+import tempfile
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import _common  # noqa: F401
+import cv2
+import numpy as np
+import torch
+import torch.nn as nn
+
+from zoo.feature.common import ChainedPreprocessing
+from zoo.feature.image import ImageCenterCrop, ImageChannelNormalize, ImageMatToTensor, ImageResize, ImageSet
+from zoo.pipeline.inference import InferenceModel
+
+folder = tempfile.mkdtemp()
+rng = np.random.RandomState(0)
+for i in range(8):
+    cv2.imwrite(os.path.join(folder, "img%d.jpg" % i), rng.randint(0, 255, (240, 320, 3)).astype(np.uint8))
+
+torch.manual_seed(0)
+net = nn.Sequential(nn.Conv2d(3, 16, 7, stride=4), nn.ReLU(), nn.Conv2d(16, 32, 3, stride=2), nn.ReLU(), nn.AdaptiveAvgPool2d(2), nn.Flatten(),
+                    nn.Linear(128, 256), nn.ReLU(), nn.Linear(256, 1000), nn.Softmax(-1)).eval()
+images = ImageSet.read(folder).transform(ChainedPreprocessing([ImageResize(256, 256), ImageCenterCrop(224, 224),
+                                                                ImageChannelNormalize(123.0, 117.0, 104.0), ImageMatToTensor()]))
+batch = torch.from_numpy(np.stack(images.get_image()))
+
+cuda = torch.cuda.is_available() and not os.environ.get("ZOO_FORCE_CPU")
+try:
+    InferenceModel().load_openvino("model.xml", "model.bin")
+except NotImplementedError as e:
+    print("load_openvino:", str(e)[:90], "...")
+model = InferenceModel(1, "cuda" if cuda else "cpu", dtype=torch.bfloat16 if cuda else None)
+model.load_torch(net)
+ref = model.predict(batch.numpy())
+model.quantize(batch)                                   # calibration on the batch itself; Linear layers -> FP8
+out = model.predict(batch.numpy())
+for uri, p in zip([f["uri"] for f in images.get_image_features()], out):
+    top = np.argsort(-p)[:3]
+    print(os.path.basename(uri), "->", [(int(c), round(float(p[c]), 4)) for c in top])
+print("predicted %d images; top-1 agreement FP8 vs unquantised: %.2f" % (len(out), float((out.argmax(1) == ref.argmax(1)).mean())))

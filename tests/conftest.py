@@ -26,7 +26,7 @@ def pytest_collection_modifyitems(config, items):
 
             for item in items:
                 if "gpu" in item.keywords and item.get_closest_marker("timeout") is None:
-                    item.add_marker(pytest.mark.timeout(240))
+                    item.add_marker(pytest.mark.timeout(int(os.environ.get("ZOO_GPU_TEST_TIMEOUT", "240"))))
         except ImportError:
             pass
         return
