@@ -139,6 +139,13 @@ int zoo_softmax_nll(const void* logits, long long ldl, const long long* labels, 
                     void* dlogits, long long ldd, float* probs, long long ldp, void* stream);
 int zoo_sigmoid_bce(const void* logits, const float* targets, long long n, int dtype, int from_probs, float eps,
                     float loss_scale, float grad_scale, float* loss_out, void* dlogits, void* stream);
+/* K5b (csrc/ops/head_loss.cu): last Dense layer + softmax + NLL + the head's dgrad / wgrad / bias gradient in one pass over the
+ * head's input (NeuralCF.scala:89-96).  x [B, K] bf16, w [C, K] bf16 (C <= 8, K % 8 == 0, K <= 256); dw / db are accumulated. */
+int zoo_head_softmax_nll(const void* x, long long ldx, const void* w, long long ldw, const float* bias,
+                         const long long* labels, int B, int K, int C, int zero_based, long long padding_value,
+                         int has_padding, int size_average, float eps, int relu_cols, float* loss_out, void* dx,
+                         long long ldd, float* dw, long long lddw, float* db, float* logits_out, long long ldl,
+                         float* valid_scratch, int impl, void* stream);
 
 /* ---- K1: fused reduce-scatter + optimizer + all-gather over NVLink peer memory (csrc/comm/rs_opt_ag.cu)
  * Replaces BigDL AllReduceParameter + OptimMethod.optimize (Topology.scala:1128,1187-1206).  Pointer

@@ -58,10 +58,25 @@ class NeuralCF(Recommender):
 
     def forward_logits(self, x):
         """x: [B, 2] (user_id, item_id), 1-based like the reference."""
+        return self.linear_last(self._head_input(x))
+
+    def training_loss(self, x, y, criterion):
+        """Loss of one training batch (the engine's fused route, `TrainingEngine.forward_loss`): the head -- Dense(class_num) +
+        softmax + NLL and its whole backward -- runs as ONE kernel over the head's input when it applies (zoo.ops.head_loss),
+        layer by layer otherwise."""
+        from ...ops import head_loss as _hl
+
+        hc = self._head_input(x)
+        if _hl.applicable(hc, self.linear_last, criterion, y):
+            return _hl.head_loss(hc, self.linear_last, criterion, y)
+        return criterion.from_logits(self.linear_last(hc), y)
+
+    def _head_input(self, x):
+        """Everything below the last Dense layer: [tower output | GMF product]."""
         ids = x.long() if x.dtype != torch.int64 else x
         specs = [LookupSpec(self.mlp_user_embed, 0), LookupSpec(self.mlp_item_embed, 1)]
         if not self.include_mf:
-            return self.linear_last(self.mlp(multi_lookup(ids, specs)))
+            return self.mlp(multi_lookup(ids, specs))
         # ONE lookup for all four tables: [MLP-user | MLP-item | MF-user * MF-item]; the tower reads the first window, the
         # GMF product is the second.  Tables of one id column share their sparse update (zoo.ops.embedding_group).
         specs.append(LookupSpec(self.mf_user_embed, 0, mul_table=self.mf_item_embed, mul_col=1))
@@ -93,7 +108,7 @@ class NeuralCF(Recommender):
             # (keyed by the table's serial number: an id() could be reused by a later object on one rank only, and symmetric
             # allocations are collective)
             hc._zoo_dx_out = ShardRuntime.get().stage(("ncf-last-dx", self.mf_user_embed.uid, hc.shape[0]), tuple(hc.shape), torch.bfloat16)[1]
-        return self.linear_last(hc)
+        return hc
 
     def forward(self, x):
         return torch.softmax(self.forward_logits(x).float(), dim=-1)

@@ -444,6 +444,8 @@ class TrainingEngine:
         m = self.model
         kind = m.logits_kind() if hasattr(m, "logits_kind") else None
         if kind is not None and kind == getattr(criterion, "logits_kind", None):
+            if hasattr(m, "training_loss") and torch.is_grad_enabled() and not isinstance(x, tuple):
+                return m.training_loss(x, y, criterion), None      # the model may fuse its head with the loss (zoo.ops.head_loss)
             logits = m.forward_logits(*x) if isinstance(x, tuple) else m.forward_logits(x)
             return criterion.from_logits(logits, y), logits
         if self.autocast_dtype is not None and self.device.type == "cuda":
@@ -457,17 +459,22 @@ class TrainingEngine:
         return criterion(out, y), out
 
     def _eager_step(self, criterion, inputs, targets):
+        from ..ops import head_loss as _head_loss
         from ..ops import loss as _fused_loss
 
-        loss, _ = self.forward_loss(criterion, inputs, targets)
-        reg = self.model.regularization_loss() if hasattr(self.model, "regularization_loss") else None
-        if reg is not None:
-            loss = loss + reg
-        _fused_loss.UNIT_UPSTREAM["on"] = True   # we seed backward with exactly 1.0
+        # forward + backward of THIS step: gradients were zeroed by the previous optimizer step and backward is seeded with 1, so
+        # a fused head may accumulate its weight gradients while it computes the loss
+        _head_loss.ENGINE_STEP["on"] = os.environ.get("ZOO_FUSED_HEAD", "1") != "0"
         try:
+            loss, _ = self.forward_loss(criterion, inputs, targets)
+            reg = self.model.regularization_loss() if hasattr(self.model, "regularization_loss") else None
+            if reg is not None:
+                loss = loss + reg
+            _fused_loss.UNIT_UPSTREAM["on"] = True   # we seed backward with exactly 1.0
             loss.backward()
         finally:
             _fused_loss.UNIT_UPSTREAM["on"] = False
+            _head_loss.ENGINE_STEP["on"] = False
         self._dp.step()          # gradient exchange fused with the optimizer
         self._after_step_shadows()
         return loss.detach()
