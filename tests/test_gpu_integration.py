@@ -77,10 +77,13 @@ def test_serving_on_gpu_matches_direct_inference():
         p = model(x)[0]
         top = p.topk(3)
         got = eval(res[uri])
-        assert [g[0] for g in got] == top.indices.tolist()
         # the engine decodes with nvJPEG on the GPU, this check with OpenCV on the host: the two decoders differ by a grey level or
-        # two (IDCT rounding, chroma upsampling), which moves the probabilities in the third decimal
-        np.testing.assert_allclose([g[1] for g in got], top.values.detach().numpy(), atol=5e-3)
+        # two (IDCT rounding, chroma upsampling), which moves the probabilities in the third decimal -- classes whose probabilities
+        # are closer than that may swap places, so every returned (class, probability) is checked against the direct model output
+        assert got[0][0] == int(top.indices[0]) or abs(float(p[got[0][0]]) - float(top.values[0])) < 5e-3
+        for cls, prob in got:
+            assert abs(prob - float(p[cls])) < 5e-3, (uri, got, top)
+        assert min(g[1] for g in got) >= float(top.values[2]) - 5e-3
 
 
 def test_inference_model_graph_replay_matches_eager():

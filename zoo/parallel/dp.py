@@ -39,6 +39,10 @@ class LocalSync:
     def broadcast_parameters(self):
         pass
 
+    def begin_step(self):
+        """Start of a training step (before forward); see FusedOptimizer.begin_step."""
+        self.fopt.begin_step()
+
     def step(self):
         self.fopt.step()
 

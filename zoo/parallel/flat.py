@@ -226,6 +226,8 @@ class FusedOptimizer:
         self.clip_l2 = None
         self.clip_const = None
         self.graph_mode = False   # inside a captured step: hyper-parameters are re-read from pinned memory
+        self._side = None         # side stream of `begin_step`
+        self._begun = None        # event recorded there once this step's hyper-parameters are live on the device
 
     def pre_graph_replay(self):
         """Host-side part of a step whose device part is replayed from a CUDA graph."""
@@ -337,11 +339,40 @@ class FusedOptimizer:
                 if norm > self.clip_l2 / gs:
                     a.flat_g.mul_((self.clip_l2 / gs) / (norm + 1e-6))
 
-    def step(self, zero_grad=True):
+    def begin_step(self):
+        """Optional, at the START of a training step (before forward): the pinned->device copy of the hyper-parameters and the
+        `zoo_hyper_step` launches do not depend on the step's gradients, so they run on a side stream next to forward / backward
+        -- in a captured step a parallel branch of the graph -- instead of as ~10 us of serial tail (copy node, kernel, two
+        launch gaps) before the optimizer kernel.  `step()` joins the branch."""
         a = self.arena
+        if a.device.type != "cuda" or self._begun is not None:
+            return
         self.step_count += 1
         self._apply_schedules()
-        refresh = self._sync_hyper()
+        if self._side is None:
+            self._side = torch.cuda.Stream(a.device)
+        cur = torch.cuda.current_stream(a.device)
+        self._side.wait_stream(cur)
+        with torch.cuda.stream(self._side):
+            refresh = self._sync_hyper()
+            lib, st = _nl.cuda_lib(), _nl.stream_ptr()
+            for i in range(len(self.groups)):
+                src = self.hyper_stage[i].data_ptr() if refresh else None
+                _nl.check(lib.zoo_hyper_step(self.hyper_dev[i].data_ptr(), src, st), "zoo_hyper_step")
+            ev = torch.cuda.Event()
+            ev.record(self._side)
+        self._begun = ev
+
+    def step(self, zero_grad=True):
+        a = self.arena
+        begun, self._begun = self._begun, None
+        if begun is not None:
+            torch.cuda.current_stream(a.device).wait_event(begun)
+            refresh = False
+        else:
+            self.step_count += 1
+            self._apply_schedules()
+            refresh = self._sync_hyper()
         self.clip_gradients()
         if a.device.type == "cuda":
             lib, st = _nl.cuda_lib(), _nl.stream_ptr()
@@ -349,7 +380,8 @@ class FusedOptimizer:
                 n = g.end - g.start
                 hp = self.hyper_dev[i].data_ptr()
                 src = self.hyper_stage[i].data_ptr() if refresh else None
-                _nl.check(lib.zoo_hyper_step(hp, src, st), "zoo_hyper_step")
+                if begun is None:
+                    _nl.check(lib.zoo_hyper_step(hp, src, st), "zoo_hyper_step")
                 _nl.check(lib.zoo_dense_opt_step(
                     a.flat_p[g.start:].data_ptr(), a.flat_g[g.start:].data_ptr(),
                     self.m[g.start:].data_ptr() if (self.m is not None and g.cfg.needs_m) else None,

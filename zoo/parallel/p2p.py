@@ -172,6 +172,12 @@ class P2PFusedSync:
                                             self.ctx.world_size, self.ctx.rank, self.ar_grid, _nl.stream_ptr()), "zoo_ar_push")
         self._pushed = True
 
+    def begin_step(self):
+        """Small arenas finish with the local fused optimizer (`f.step()`): its hyper-parameter refresh can start now, on a side
+        stream.  The owner-computes path of large arenas refreshes inside its own step."""
+        if self.small and self.fopt.clip_l2 is None:
+            self.fopt.begin_step()
+
     def step(self):
         f = self.fopt
         if self.small:

@@ -71,9 +71,16 @@ class Prefetcher:
     """Overlap the H2D copy of batch i+1 with the compute of batch i (pinned source -> async DMA
     on a side stream).  Device-resident FeatureSets pass straight through."""
 
+    _streams = {}       # one copy stream per device, shared by the passes of a run (creating a stream per pass costs ~1 ms)
+
     def __init__(self, it, device):
         self.it, self.device = iter(it), device
-        self.stream = torch.cuda.Stream(device) if device.type == "cuda" else None
+        self.stream = None
+        if device.type == "cuda":
+            key = device.index if device.index is not None else torch.cuda.current_device()
+            self.stream = Prefetcher._streams.get(key)
+            if self.stream is None:
+                self.stream = Prefetcher._streams[key] = torch.cuda.Stream(device)
         self.h2d_bytes = 0
         self._next = None
         self._preload()
@@ -465,6 +472,8 @@ class TrainingEngine:
         # forward + backward of THIS step: gradients were zeroed by the previous optimizer step and backward is seeded with 1, so
         # a fused head may accumulate its weight gradients while it computes the loss
         _head_loss.ENGINE_STEP["on"] = os.environ.get("ZOO_FUSED_HEAD", "1") != "0"
+        if hasattr(self._dp, "begin_step") and os.environ.get("ZOO_HYPER_PREFETCH", "1") != "0":
+            self._dp.begin_step()      # hyper-parameter refresh on a side stream, next to forward / backward
         try:
             loss, _ = self.forward_loss(criterion, inputs, targets)
             reg = self.model.regularization_loss() if hasattr(self.model, "regularization_loss") else None

@@ -334,7 +334,7 @@ class ClusterServing:
     def _bind_device(self):
         """The current CUDA device is per THREAD: a worker thread starts on device 0, and a kernel launched from it through the
         native library would run there while its pointers live on this rank's device."""
-        if self.device.type == "cuda":
+        if self.device.type == "cuda" and self.device.index is not None:
             torch.cuda.set_device(self.device)
 
     def _engine_loop(self):
