@@ -1,6 +1,7 @@
 """TensorFlow frozen-graph import / export without TensorFlow (zoo/tfpark/graphdef.py, TFNet, zoo.util.tf.export_tf / strip_unused).
 The GraphDef wire format written here is checked against google.protobuf's own decoder, so files are readable by TensorFlow."""
 import json
+import os
 
 import numpy as np
 import pytest
@@ -93,3 +94,24 @@ def test_tfnet_ops_and_strip_unused(tmp_path):
     with pytest.raises(NotImplementedError):
         write_graphdef(str(tmp_path / "bad.pb"), [("x", "Placeholder", [], {"dtype": f32}), ("y", "SomeExoticOp", ["x"], {})])
         TFNet(str(tmp_path / "bad.pb"), ["x"], ["y"])(x)
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/zoo/src/test/resources/tfnet/frozen_inference_graph.pb"),
+                    reason="reference test resources are not on this machine")
+def test_reference_frozen_graph_written_by_tensorflow():
+    """The reference's own TFNet fixture -- a graph frozen by real TensorFlow (TFNetSpec.scala loads the same folder) -- through
+    the GraphDef reader and `TFNet.from_export_folder`, checked against the same arithmetic done with the graph's constants."""
+    import torch
+
+    from zoo.pipeline.api.net import TFNet
+    from zoo.tfpark.graphdef import read_graphdef
+
+    folder = "/root/reference/zoo/src/test/resources/tfnet"
+    nodes = {n.name: n for n in read_graphdef(folder + "/frozen_inference_graph.pb")}
+    assert nodes["dense/MatMul"].op == "MatMul" and nodes["dense_1/Sigmoid"].inputs == ["dense_1/BiasAdd"]
+    w1, b1 = nodes["dense/kernel"].a("value"), nodes["dense/bias"].a("value")
+    w2, b2 = nodes["dense_1/kernel"].a("value"), nodes["dense_1/bias"].a("value")
+    net = TFNet.from_export_folder(folder)
+    x = torch.rand(5, w1.shape[0])
+    want = torch.sigmoid(torch.relu(x @ torch.from_numpy(w1) + torch.from_numpy(b1)) @ torch.from_numpy(w2) + torch.from_numpy(b2))
+    torch.testing.assert_close(net(x), want)

@@ -23,6 +23,10 @@ class Net:
     def load(model_path, weight_path=None, bigdl_type="float"):
         from ....models.common.zoo_model import ZooModel
 
+        with open(model_path, "rb") as f:
+            head = f.read(2)
+        if head not in (b"PK", b"\x80\x02", b"\x80\x03", b"\x80\x04", b"\x80\x05"):      # not a torch archive: BigDL's own format
+            return Net.load_bigdl(model_path, weight_path)
         try:
             m = ZooModel.load_model(model_path, weight_path)
         except Exception:
@@ -33,11 +37,23 @@ class Net:
 
     @staticmethod
     def load_bigdl(model_path, weight_path=None, bigdl_type="float"):
+        """A model saved by BigDL / Analytics Zoo (`saveModule` / `saveModel`: BigDL's protobuf format, decoded by
+        `zoo.models.bigdl`) or by this framework (`ZooModel.save_model`: a torch archive)."""
         with open(model_path, "rb") as f:
             head = f.read(2)
         if head not in (b"PK", b"\x80\x02", b"\x80\x03", b"\x80\x04", b"\x80\x05"):
-            _unsupported("Net.load_bigdl on a BigDL protobuf file")
+            from ....models.bigdl import load_bigdl as _load
+
+            return GraphNet(_load(model_path))
         return Net.load(model_path, weight_path)
+
+    @staticmethod
+    def save_bigdl(model, path):
+        """Write a feed-forward torch model in BigDL's module format (loadable by BigDL / Analytics Zoo and by `load_bigdl`)."""
+        from ....models.bigdl import save_bigdl as _save
+
+        _save(getattr(model, "model", model) if not isinstance(model, torch.nn.Module) else model, path)
+        return path
 
     @staticmethod
     def load_torch(path, bigdl_type="float"):

@@ -83,6 +83,12 @@ class InferenceModel:
         """A model written by `ZooModel.save_model` / `KerasNet.saveModel` (reference: load_bigdl)."""
         from ...models.common.zoo_model import ZooModel
 
+        with open(model_path, "rb") as fh:
+            head = fh.read(2)
+        if head not in (b"PK", b"\x80\x02", b"\x80\x03", b"\x80\x04", b"\x80\x05"):      # BigDL's protobuf format
+            from ...models.bigdl import load_bigdl
+
+            return self._install(load_bigdl(model_path))
         try:
             m = ZooModel.load_model(model_path, weight_path)
         except Exception:
