@@ -2,7 +2,7 @@ import sys; sys.path.insert(0,'/root/repo')
 import torch, torch.nn.functional as F
 from torch.profiler import profile, ProfilerActivity
 from zoo.ops.tcn import causal_conv1d
-B,C,T,K,d = 1024,30,64,3,4
+B,C,T,K,d = (int(v) for v in (sys.argv[1:6] + ["1024","30","64","3","4"][len(sys.argv)-1:]))
 x = torch.randn(B, C, T, device="cuda", requires_grad=True)
 w = (torch.randn(C, C, K, device="cuda")*0.1).requires_grad_(True)
 b = torch.zeros(C, device="cuda", requires_grad=True)

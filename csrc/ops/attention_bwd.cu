@@ -28,6 +28,12 @@ constexpr int kAbSmem = 2 * kAbTile /*K,V*/ + 4 * kAbTile /*Q,dO x2*/ + 2 * kAbP
 constexpr int kAbThreads = 192;
 constexpr float kAbLog2e = 1.4426950408889634f;
 
+__device__ __forceinline__ float ab_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct AttBwdArgs {
   int B, H, L;
   float scale;
@@ -162,6 +168,8 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       const bool q_ok = q < a.L;
       const float lse = q_ok ? a.lse[row_base + q] : INFINITY;
       const float dl = q_ok ? a.delta[row_base + q] : 0.f;
+      const int qb0 = (i_begin + it) * kAbB;                 // a block pair is FULL when nothing in it needs masking
+      const bool full = !mrow && k0 + kAbB <= a.L && qb0 + kAbB <= a.L && (!a.causal || k0 + kAbB - 1 <= qb0) && sc > 0.f;
       mbar_wait(&s_bar, it & 1);
       tc_fence_after();
       // (P / dS of the previous block were MMA operands until its dQ commit, which was waited for before the previous read-back)
@@ -172,6 +180,16 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
         tmem_ld_32x32(t_dp + lane_addr + c * 32, rd);
         tmem_ld_wait();
         uint32_t pk[16], dk[16];
+        if (full) {                                          // no per-element predicate (see the forward kernel)
+          const float neg_lse = -lse, ndl = -dl * a.scale;
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const float p0 = ab_ex2(fmaf(__uint_as_float(rs[i]), sc, neg_lse)), p1 = ab_ex2(fmaf(__uint_as_float(rs[i + 1]), sc, neg_lse));
+            const float d0 = p0 * fmaf(__uint_as_float(rd[i]), a.scale, ndl), d1 = p1 * fmaf(__uint_as_float(rd[i + 1]), a.scale, ndl);
+            pk[i >> 1] = pack_bf16(p0, p1);
+            dk[i >> 1] = pack_bf16(d0, d1);
+          }
+        } else {
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
           float p2[2], d2[2];
@@ -186,6 +204,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
           }
           pk[i >> 1] = pack_bf16(p2[0], p2[1]);
           dk[i >> 1] = pack_bf16(d2[0], d2[1]);
+        }
         }
         const uint32_t kb_off = (uint32_t)(c >> 1) * 16384u;
 #pragma unroll
