@@ -57,10 +57,11 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   uint64_t& q_bar = bars[0];
   uint64_t* kv_full = bars + 1;
   uint64_t* kv_empty = bars + 3;
-  uint64_t& s_bar = bars[5];
+  uint64_t* s_bar = bars + 10;                              // one per score buffer (the issuer runs one block ahead)
   uint64_t& p_bar = bars[6];
   uint64_t& o_bar = bars[7];
-  uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t& oread_bar = bars[8];
+  uint32_t& tmem_slot = *reinterpret_cast<uint32_t*>(bars + 12);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   const uint32_t smem_base = smem_u32(smem_raw);
   uint8_t* smem_al = smem_raw;
@@ -79,8 +80,9 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   if (warp == 4 && lane == 0) {
     mbar_init(&q_bar, 1);
     for (int i = 0; i < 2; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
-    mbar_init(&s_bar, 1); mbar_init(&o_bar, 1);
+    mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1); mbar_init(&o_bar, 1);
     mbar_init(&p_bar, 128);                                  // every softmax thread arrives once per key block
+    mbar_init(&oread_bar, 128);                              // ... and once per output read-back
     fence_mbar_init();
   }
   if (warp == 4) tmem_alloc(&tmem_slot, 256);
@@ -88,7 +90,10 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  const uint32_t tmem_s = tmem, tmem_o = tmem + kAttBN;
+  // Two score buffers of 128 columns: S_{j+1} = Q K_{j+1}^T is issued while the softmax warps still work on S_j.  O_j = P_j V_j is
+  // written over the first 64 columns of S_j's own buffer once S_j has been consumed (no third region: 256 columns per CTA, two
+  // CTAs per SM).
+  const uint32_t tmem_sbuf[2] = {tmem, tmem + kAttBN};
 
   if (warp == 5) {
     // ------------------------------------------------------------------ TMA producer
@@ -115,25 +120,35 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
       mbar_wait(&q_bar, 0);
       tc_fence_after();
       const uint32_t sq = smem_base + off_q, sp = smem_base + off_p;
-      for (int j = 0; j < n_blocks; ++j) {
+      auto issue_scores = [&](int j) {
         const int s = j & 1;
-        const uint32_t sk = smem_base + off_kv + s * (kAttKBytes + kAttVBytes), sv = sk + kAttKBytes;
+        const uint32_t sk = smem_base + off_kv + s * (kAttKBytes + kAttVBytes);
         mbar_wait(&kv_full[s], (j >> 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < kAttD / 16; ++k)
-          umma_bf16(tmem_s, make_smem_desc_sw128(sq + k * 32, 16, 1024), make_smem_desc_sw128(sk + k * 32, 16, 1024), idesc_s, k ? 1u : 0u);
-        umma_commit(&s_bar);                                   // scores of block j are in TMEM
+          umma_bf16(tmem_sbuf[s], make_smem_desc_sw128(sq + k * 32, 16, 1024), make_smem_desc_sw128(sk + k * 32, 16, 1024), idesc_s, k ? 1u : 0u);
+        umma_commit(&s_bar[s]);                                // scores of block j are in TMEM
+      };
+      issue_scores(0);
+      for (int j = 0; j < n_blocks; ++j) {
+        const int s = j & 1;
+        const uint32_t sv = smem_base + off_kv + s * (kAttKBytes + kAttVBytes) + kAttKBytes;
+        if (j + 1 < n_blocks) {
+          // buffer (j+1)&1 held S_{j-1}, then O_{j-1}: free once every softmax thread has read O_{j-1} back
+          if (j > 0) { mbar_wait(&oread_bar, (j - 1) & 1); tc_fence_after(); }
+          issue_scores(j + 1);
+        }
         mbar_wait(&p_bar, j & 1);                              // P_j is in shared memory (and S_j has been read)
         tc_fence_after();
 #pragma unroll
         for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
           for (int k = 0; k < 4; ++k)
-            umma_bf16(tmem_o, make_smem_desc_sw128(sp + kb * 16384 + k * 32, 16, 1024),
+            umma_bf16(tmem_sbuf[s], make_smem_desc_sw128(sp + kb * 16384 + k * 32, 16, 1024),
                       make_smem_desc_sw128(sv + kb * 8192 + k * 2048, 8192, 1024), idesc_o, (kb | k) ? 1u : 0u);
         umma_commit(&kv_empty[s]);                             // K_j / V_j may be overwritten
-        umma_commit(&o_bar);                                   // O_j is in TMEM
+        umma_commit(&o_bar);                                   // O_j is in TMEM (first 64 columns of buffer s)
       }
     }
   } else {
@@ -149,19 +164,34 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
 #pragma unroll
     for (int i = 0; i < kAttD; ++i) o[i] = 0.f;
     float m = -INFINITY, l = 0.f;
+    // O_j = P_j V_j sits in the first 64 columns of score buffer j & 1 once o_bar completes for block j
+    auto add_output = [&](int j) {
+      mbar_wait(&o_bar, j & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < kAttD / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_sbuf[j & 1] + lane_addr + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[c * 32 + i] += __uint_as_float(r[i]);
+      }
+      tc_fence_before();
+      mbar_arrive(&oread_bar);                                 // the issuer may overwrite this buffer with S_{j+2}
+    };
     for (int j = 0; j < n_blocks; ++j) {
       const int key0 = j * kAttBN;
-      mbar_wait(&s_bar, j & 1);
+      const uint32_t tmem_s = tmem_sbuf[j & 1];
+      mbar_wait(&s_bar[j & 1], (j >> 1) & 1);
       tc_fence_after();
       // A key block is FULL when every key is in range, no key is above the diagonal for any row of this CTA and there is no
       // additive mask: then no per-element predicate is needed.  (ncu on the general form: 2,760 warp instructions per tile,
       // most of them ISETP / FSEL / VIADD of the masking logic; the full form needs ~700.)
       const bool full = !mrow && key0 + kAttBN <= a.L && (!a.causal || key0 + kAttBN - 1 <= q0) && sc > 0.f;
-      float mx = m;
       float lsum = 0.f;
       float m_new, alpha, m_use;
-      if (full) {
-        // sweep 1: maximum of the raw scores (scale > 0 keeps the order), two 32-column loads in flight
+      // ---- sweep 1: row maximum (log2 domain)
+      if (full) {                                              // raw scores (scale > 0 keeps the order), two loads in flight
         float raw = -INFINITY;
 #pragma unroll 1
         for (int c = 0; c < kAttBN / 64; ++c) {
@@ -174,9 +204,32 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
         }
         m_new = fmaxf(m, raw * sc);
         alpha = (m == -INFINITY) ? 0.f : ex2_approx(m - m_new);
-        m_use = m_new;                                        // finite: a full block has live keys
+        m_use = m_new;                                         // finite: a full block has live keys
+      } else {
+        float mx = m;
+#pragma unroll 1
+        for (int c = 0; c < kAttBN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_s + lane_addr + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int key = key0 + c * 32 + i;
+            float sv = __uint_as_float(r[i]) * sc;
+            if (mrow && key < a.L) sv += mrow[key] * kLog2e;
+            if (key >= a.L || (a.causal && key > q)) sv = -INFINITY;
+            mx = fmaxf(mx, sv);
+          }
+        }
+        m_new = mx;
+        alpha = (m == -INFINITY) ? 0.f : exp2f(m - m_new);
+        m_use = (m_new == -INFINITY) ? 0.f : m_new;            // a fully masked row keeps p = 0 without NaNs
+      }
+      // ---- the previous block's output: its MMA ran under sweep 1; P may be rewritten once it has completed
+      if (j > 0) add_output(j - 1);
+      // ---- sweep 2: probabilities -> bf16 -> swizzled K-major tile (A operand of the second MMA)
+      if (full) {
         const float neg_m = -m_use;
-        // sweep 2: p = 2^(s * sc - m), packed to bf16 into the swizzled K-major tile
 #pragma unroll 1
         for (int c = 0; c < kAttBN / 32; ++c) {
           uint32_t r[32];
@@ -197,76 +250,46 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
           }
         }
       } else {
-      // sweep 1: row maximum of the masked, scaled scores (log2 domain)
 #pragma unroll 1
-      for (int c = 0; c < kAttBN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_s + lane_addr + c * 32, r);
-        tmem_ld_wait();
+        for (int c = 0; c < kAttBN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_s + lane_addr + c * 32, r);
+          tmem_ld_wait();
+          uint32_t pk[16];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int key = key0 + c * 32 + i;
-          float s = __uint_as_float(r[i]) * sc;
-          if (mrow && key < a.L) s += mrow[key] * kLog2e;
-          if (key >= a.L || (a.causal && key > q)) s = -INFINITY;
-          mx = fmaxf(mx, s);
-        }
-      }
-      m_new = mx;
-      alpha = (m == -INFINITY) ? 0.f : exp2f(m - m_new);
-      m_use = (m_new == -INFINITY) ? 0.f : m_new;  // a fully masked row keeps p = 0 without NaNs
-      // sweep 2: probabilities -> bf16 -> swizzled K-major tile (A operand of the second MMA)
-#pragma unroll 1
-      for (int c = 0; c < kAttBN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_s + lane_addr + c * 32, r);
-        tmem_ld_wait();
-        uint32_t pk[16];
+          for (int i = 0; i < 32; i += 2) {
+            float p2[2];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p2[2];
-#pragma unroll
-          for (int u = 0; u < 2; ++u) {
-            const int key = key0 + c * 32 + i + u;
-            float s = __uint_as_float(r[i + u]) * sc;
-            if (mrow && key < a.L) s += mrow[key] * kLog2e;
-            const bool dead = key >= a.L || (a.causal && key > q);
-            p2[u] = dead ? 0.f : exp2f(s - m_use);
+            for (int u = 0; u < 2; ++u) {
+              const int key = key0 + c * 32 + i + u;
+              float sv = __uint_as_float(r[i + u]) * sc;
+              if (mrow && key < a.L) sv += mrow[key] * kLog2e;
+              const bool dead = key >= a.L || (a.causal && key > q);
+              p2[u] = dead ? 0.f : exp2f(sv - m_use);
+            }
+            lsum += p2[0] + p2[1];
+            pk[i >> 1] = pack_bf16(p2[0], p2[1]);
           }
-          lsum += p2[0] + p2[1];
-          pk[i >> 1] = pack_bf16(p2[0], p2[1]);
-        }
-        // chunk c covers keys [32c, 32c+32) = 64 bytes of row t inside k-block (c >> 1): 16-byte pieces 4*(c&1) .. +3
-        const uint32_t kb_off = (uint32_t)(c >> 1) * 16384u;
+          // chunk c covers keys [32c, 32c+32) = 64 bytes of row t inside k-block (c >> 1): 16-byte pieces 4*(c&1) .. +3
+          const uint32_t kb_off = (uint32_t)(c >> 1) * 16384u;
 #pragma unroll
-        for (int piece = 0; piece < 4; ++piece) {
-          const uint32_t pi = (uint32_t)((c & 1) * 4 + piece);
-          st_shared_u4(p_row + kb_off + ((pi ^ swz) << 4), pk[4 * piece], pk[4 * piece + 1], pk[4 * piece + 2], pk[4 * piece + 3]);
+          for (int piece = 0; piece < 4; ++piece) {
+            const uint32_t pi = (uint32_t)((c & 1) * 4 + piece);
+            st_shared_u4(p_row + kb_off + ((pi ^ swz) << 4), pk[4 * piece], pk[4 * piece + 1], pk[4 * piece + 2], pk[4 * piece + 3]);
+          }
         }
-      }
       }
       l = l * alpha + lsum;
       m = m_new;
-      if (alpha != 1.f) {                                      // the maximum moved (rare after the first blocks)
+      if (alpha != 1.f) {                                      // the maximum moved (rare after the first blocks); o includes O_{j-1}
 #pragma unroll
         for (int i = 0; i < kAttD; ++i) o[i] *= alpha;
       }
       tc_fence_before();                                       // our tcgen05.ld of S_j are done before the issuer overwrites S
       fence_proxy_async_smem();                                // P_j visible to the tensor core (async proxy)
       mbar_arrive(&p_bar);
-      // O_j = P_j V_j from TMEM, added to the running row
-      mbar_wait(&o_bar, j & 1);
-      tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < kAttD / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_o + lane_addr + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[c * 32 + i] += __uint_as_float(r[i]);
-      }
-      tc_fence_before();
     }
+    add_output(n_blocks - 1);
     if (q < a.L) {
       if (a.lse) a.lse[row_base + q] = l > 0.f ? m + log2f(l) : INFINITY;      // a row with no live key: p = exp2(s - inf) = 0 in backward
       const float inv = l > 0.f ? 1.f / l : 0.f;
