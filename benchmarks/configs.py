@@ -132,8 +132,25 @@ def _serving(args, ctx, torch):
 
         model = NeuralCF(1_000_000, 100_000, 5, user_embed=64, item_embed=64, hidden_layers=[128, 64, 32], mf_embed=32, sparse=False)
         conf = {"data": {"filter": "topN(1)"}, "params": {"batch_size": bs, "dtype": os.environ.get("ZOO_SERVING_DTYPE", "fp32")}}
-    srv = ClusterServing(conf, model=model, device=dev).start()
-    q = InputQueue(conf, broker=srv.db)
+    # ZOO_SERVING_SHARED_BROKER=1: the reference's deployment shape -- ONE broker (hosted by rank 0, RESP socket), every rank's engine
+    # a consumer of the same group, every rank's feeder a producer.  Default: one in-process broker per engine (replicas).
+    shared = os.environ.get("ZOO_SERVING_SHARED_BROKER", "0") == "1" and ctx.world_size > 1
+    if shared:
+        from zoo.native.rt import Broker, RespClient
+
+        port = [None]
+        if ctx.rank == 0:
+            host_broker = Broker(0)
+            port[0] = host_broker.serve("127.0.0.1", 0)
+        torch.distributed.broadcast_object_list(port, src=0)
+        broker = host_broker if ctx.rank == 0 else RespClient("127.0.0.1", port[0])
+        srv = ClusterServing(conf, model=model, device=dev, broker=broker, consumer=f"engine-{ctx.rank}").start()
+        feed_db = host_broker if ctx.rank == 0 else RespClient("127.0.0.1", port[0])       # producers use their own connection
+        feed_prog = host_broker if ctx.rank == 0 else RespClient("127.0.0.1", port[0])     # and so does the progress poll
+    else:
+        srv = ClusterServing(conf, model=model, device=dev).start()
+        feed_db = srv.db
+    q = InputQueue(conf, broker=feed_db)
     K, Wm = args.steps, max(args.warmup, 3)
     total = (K + Wm) * bs
     rng = np.random.RandomState(ctx.rank)
@@ -145,7 +162,7 @@ def _serving(args, ctx, torch):
     def feed():
         if kind == "resnet50":
             for i in range(total):
-                srv.db.xadd("image_stream", {"uri": f"r{i}", "image": jpgs[i % 64]})
+                feed_db.xadd("image_stream", {"uri": f"r{ctx.rank}_{i}", "image": jpgs[i % 64]})
             return
         q.enqueue_tensor("r0", np.array([1, 1], dtype=np.int64))          # one record through the per-record path
         chunk = 1024                                                        # then bulk producers (one native call per 1024 records)
@@ -157,15 +174,34 @@ def _serving(args, ctx, torch):
 
     t = threading.Thread(target=feed, daemon=True)
     t.start()
-    srv.wait_until(Wm * bs, 600)
+
+    def wait_global(target, limit_s):
+        """Engines of a shared broker take whatever they get: progress is the SUM over ranks.  The ranks publish their counts in
+        a hash of the broker itself (no CUDA or NCCL call from this thread: the engine thread may be capturing a CUDA graph)."""
+        end = time.time() + limit_s
+        while time.time() < end:
+            feed_prog.hset("bench_progress", str(ctx.rank), str(srv.total_records))
+            got = feed_prog.hgetall("bench_progress")
+            if sum(int(v) for v in got.values()) >= target:
+                return True
+            time.sleep(0.02)
+        return False
+
+    if shared:
+        wait_global(Wm * bs * ctx.world_size, 600)
+    else:
+        srv.wait_until(Wm * bs, 600)
     torch.cuda.synchronize()
     if ctx.world_size > 1:
         torch.distributed.barrier()
     n0, t0, l0 = srv.total_records, time.perf_counter(), len(srv.latencies)
-    srv.wait_until(total, 1200)
+    if shared:
+        wait_global(total * ctx.world_size, 1200)
+    else:
+        srv.wait_until(total, 1200)
     torch.cuda.synchronize()
     t1, n1 = time.perf_counter(), srv.total_records
-    lat = np.array([d for _, d in srv.latencies[l0:]]) * 1e3
+    lat = np.array([d for _, d in srv.latencies[l0:]] or [0.0]) * 1e3
     res = torch.tensor([n1 - n0, t1 - t0], dtype=torch.float64, device=dev)
     if ctx.world_size > 1:
         cnt = res[:1].clone()
@@ -183,6 +219,7 @@ def _serving(args, ctx, torch):
                           "jpeg_backend": getattr(getattr(srv, "_jpeg", None), "backend", None),
                           "vs_torch_baseline": (float(res[0] / res[1]) / (base.get("value_all_ranks") or base["value"])) if base and base.get("value") else None,
                           "config": {"model": kind, "global_batch": bs * ctx.world_size, "seq_len": None,
-                                     "parallelism": f"{ctx.world_size} serving replicas (one engine + in-process broker per GPU)",
+                                     "parallelism": (f"{ctx.world_size} engines in one consumer group of ONE broker (rank 0 hosts it; RESP socket)" if shared
+                                                     else f"{ctx.world_size} serving replicas (one engine + in-process broker per GPU)"),
                                      "timing": "wall clock over the whole pipeline: enqueue -> broker -> decode -> K13 -> model -> K14 -> result hash"}}))
     return 0

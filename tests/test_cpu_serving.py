@@ -145,3 +145,35 @@ def test_serving_bulk_tensor_path():
         assert abs(p - float(probs[i].max())) < 1e-5 and float(probs[i][idx]) == pytest.approx(float(probs[i].max()))
     assert srv._tensor_meta is not None
     srv.close()
+
+
+def test_two_engines_share_one_broker_over_the_socket():
+    """The reference's deployment shape: several serving engines in one consumer group of ONE broker (ClusterServing.scala:105-140
+    creates the group, each Flink / Spark task reads as a consumer).  Engine A owns the broker and listens; engine B and the
+    clients talk to it through the RESP socket.  Every record is served exactly once, by either engine."""
+    from zoo.native.rt import RespClient
+    from zoo.serving import ClusterServing, InputQueue, OutputQueue
+
+    class Scale(nn.Module):
+        def forward(self, x):
+            return x.float() * 3
+
+    conf = {"data": {"filter": "", "src": "localhost:0"}, "params": {"batch_size": 4}}
+    a = ClusterServing(conf, model=Scale(), device="cpu", serve_socket=True, consumer="engine-a").start()
+    b = ClusterServing(conf, model=Scale(), device="cpu", broker=RespClient("127.0.0.1", a.port), consumer="engine-b").start()
+    q, o = InputQueue({}, host="127.0.0.1", port=a.port), OutputQueue({}, host="127.0.0.1", port=a.port)
+    n = 60
+    for i in range(n):
+        q.enqueue_tensor(f"r{i}", np.full((2,), i, np.float32))
+        if i % 10 == 9:
+            time.sleep(0.02)                 # let both consumers get a turn
+    deadline = time.time() + 30
+    while a.total_records + b.total_records < n and time.time() < deadline:
+        time.sleep(0.02)
+    assert a.total_records + b.total_records == n        # exactly once across the group
+    assert a.total_records > 0 and b.total_records > 0   # and both engines took part
+    time.sleep(0.1)
+    res = o.dequeue()
+    assert len(res) == n and res["r7"].replace(" ", "") == "[21.,21.]"
+    b.close()
+    a.close()

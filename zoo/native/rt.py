@@ -4,6 +4,7 @@ from __future__ import annotations
 
 import ctypes as C
 import socket
+import threading
 
 import numpy as np
 
@@ -298,21 +299,23 @@ class RespClient(_Commands):
         self.sock = socket.create_connection((host, int(port)), timeout=timeout)
         self.sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
         self._buf = b""
+        self._lock = threading.Lock()      # one request / reply at a time: a serving engine calls from several threads
 
     def execute(self, *args):
-        self.sock.sendall(encode_command(args))
-        while True:
-            try:
-                v, nxt = parse_reply(self._buf)
-                self._buf = self._buf[nxt:]
-                if isinstance(v, RespError):
-                    raise v
-                return v
-            except (ValueError, IndexError):
-                chunk = self.sock.recv(1 << 20)
-                if not chunk:
-                    raise ConnectionError("broker closed the connection")
-                self._buf += chunk
+        with self._lock:
+            self.sock.sendall(encode_command(args))
+            while True:
+                try:
+                    v, nxt = parse_reply(self._buf)
+                    self._buf = self._buf[nxt:]
+                    if isinstance(v, RespError):
+                        raise v
+                    return v
+                except (ValueError, IndexError):
+                    chunk = self.sock.recv(1 << 20)
+                    if not chunk:
+                        raise ConnectionError("broker closed the connection")
+                    self._buf += chunk
 
     def close(self):
         try:
