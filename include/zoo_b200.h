@@ -131,6 +131,14 @@ int zoo_clip_const(float* g, long long n, float lo, float hi, void* stream);
 int zoo_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
 int zoo_cast_bf16_to_f32(const void* in, float* out, long long n, void* stream);
 
+/* K3, whole-tower form (csrc/gemm/mlp3_tcgen05.cu): three Dense + ReLU layers K0 -> N1 -> N2 -> 64 in one persistent kernel; the
+ * intermediate activations stay in shared memory as the next layer's A operand and are written once for backward. */
+int zoo_mlp3_supported(int K0, int N1, int N2, int N3);
+int zoo_mlp3_fwd_bf16(const void* x, long long ldx, const void* w1, long long ldw1, const float* b1, const void* w2, long long ldw2,
+                      const float* b2, const void* w3, long long ldw3, const float* b3, void* h1, long long ldh1, void* h2,
+                      long long ldh2, void* h3, long long ldh3, int M, int K0, int N1, int N2, int N3, unsigned int* bits1,
+                      unsigned int* bits2, unsigned int* bits3, void* stream);
+
 /* ---- K5: fused losses (csrc/ops/loss.cu) ------------------------------------------------------
  * ZooClassNLLCriterion.scala:48-121 + SoftMax, BinaryCrossEntropy.scala:36-42. dtype 0 fp32, 1 bf16. */
 int zoo_softmax_nll(const void* logits, long long ldl, const long long* labels, int B, int C, int dtype,

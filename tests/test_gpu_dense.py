@@ -185,3 +185,49 @@ def test_fused_mlp_autograd_matches_torch():
     torch.testing.assert_close(y.float(), h, atol=3e-2, rtol=3e-2)
     torch.testing.assert_close(xk.grad.float(), xr.grad, atol=2e-3, rtol=5e-2)
     assert mlp[0].weight.grad is not None and torch.isfinite(mlp[0].weight.grad).all()
+
+
+@pytest.mark.parametrize("M,dims,window", [(1000, (256, 256, 128, 64), False), (130, (64, 64, 64, 64), False), (4099, (128, 192, 128, 64), True),
+                                           (65536, (256, 256, 128, 64), True)])
+def test_fused_tower_matches_layer_by_layer_and_fp32(M, dims, window):
+    """K3 whole-tower kernel (csrc/gemm/mlp3_tcgen05.cu): forward values, the activations saved for backward and every gradient
+    against the layer-by-layer kernels (same arithmetic: bit-equal forward expected up to accumulation order) and an fp32 torch tower."""
+    import os
+
+    from zoo.ops.dense import FusedMLP
+
+    torch.manual_seed(M + sum(dims))
+    dev = "cuda"
+    mlp = FusedMLP(dims[0], list(dims[1:]), activation="relu").to(dev)
+    with torch.no_grad():
+        for l in mlp:
+            l.bias.uniform_(-0.1, 0.1)
+    x = (torch.randn(M, dims[0], device=dev) * 0.5).to(torch.bfloat16)
+    wide = torch.zeros(M, dims[3] + 64, dtype=torch.bfloat16, device=dev) if window else None
+
+    def run(fused):
+        os.environ["ZOO_FUSED_TOWER"] = "1" if fused else "0"
+        try:
+            for p in mlp.parameters():
+                p.grad = None
+            xi = x.clone().requires_grad_(True)
+            out = None if wide is None else wide[:, :dims[3]]
+            y = mlp(xi, out=out) if out is not None else mlp(xi)
+            (y.float() * torch.linspace(-1, 1, dims[3], device=dev)).sum().backward()
+            return y.detach().float().clone(), xi.grad.float().clone(), [p.grad.float().clone() for p in mlp.parameters()]
+        finally:
+            os.environ.pop("ZOO_FUSED_TOWER", None)
+
+    yf, dxf, gf = run(True)
+    yu, dxu, gu = run(False)
+    torch.testing.assert_close(yf, yu, atol=2e-2, rtol=2e-2)
+    torch.testing.assert_close(dxf, dxu, atol=3e-2, rtol=5e-2)
+    for a, b in zip(gf, gu):
+        torch.testing.assert_close(a, b, atol=2e-2 * max(1.0, float(b.abs().max())), rtol=5e-2)
+    # fp32 reference of the same tower (bf16 inputs / weights, fp32 math)
+    h = x.float()
+    for l in mlp:
+        h = torch.relu(h @ l.weight.detach().to(torch.bfloat16).float().t() + l.bias.detach().float())
+    assert float((yf - h).abs().max()) <= 0.03 * max(1.0, float(h.abs().max()))
+    if window:
+        assert float(wide[:, dims[3]:].abs().max()) == 0.0          # the kernel wrote only its column window

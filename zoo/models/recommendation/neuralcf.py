@@ -86,10 +86,7 @@ class NeuralCF(Recommender):
         if wide is not None and hl % 8 == 0:
             # fused concat: the gather wrote the GMF product into columns [hl, hl + mf) of `wide`, the last tower layer writes
             # its output into columns [0, hl)
-            h = h_in
-            for layer in list(self.mlp)[:-1]:
-                h = layer(h)
-            h = self.mlp[-1](h, out=wide[:, :hl])
+            h = self.mlp(h_in, out=wide[:, :hl])          # three-layer ReLU towers run as one kernel (zoo.ops.dense.FusedMLP.forward)
             bits = getattr(h, "_zoo_relu_bits", None)
             from ...ops.embedding_group import join_columns
 

@@ -18,6 +18,15 @@ import torch.nn.functional as F
 
 from ..native import lib as _nl
 
+import ctypes as _C
+
+_nl.register_cuda_sigs({
+    "zoo_mlp3_supported": [_C.c_int, _C.c_int, _C.c_int, _C.c_int],
+    "zoo_mlp3_fwd_bf16": [_C.c_void_p, _C.c_longlong, _C.c_void_p, _C.c_longlong, _C.c_void_p, _C.c_void_p, _C.c_longlong, _C.c_void_p,
+                          _C.c_void_p, _C.c_longlong, _C.c_void_p, _C.c_void_p, _C.c_longlong, _C.c_void_p, _C.c_longlong, _C.c_void_p,
+                          _C.c_longlong, _C.c_int, _C.c_int, _C.c_int, _C.c_int, _C.c_int, _C.c_void_p, _C.c_void_p, _C.c_void_p, _C.c_void_p],
+})
+
 ACT_IDS = {None: 0, "linear": 0, "none": 0, "relu": 1, "gelu": 2, "sigmoid": 3, "tanh": 4}
 
 
@@ -275,6 +284,88 @@ class FusedDense(nn.Module):
         return f"{self.in_features}, {self.out_features}, activation={self.activation}"
 
 
+def _tower_shapes_ok(layers, x):
+    """The whole-tower kernel (csrc/gemm/mlp3_tcgen05.cu) covers three ReLU layers K0 -> N1 -> N2 -> 64 with widths in steps of 64."""
+    if len(layers) != 3 or not all(isinstance(l, FusedDense) and l.activation == "relu" and l.bias is not None for l in layers):
+        return False
+    if not (torch.is_tensor(x) and x.is_cuda and x.dim() == 2 and x.dtype == torch.bfloat16 and _aligned(x)):
+        return False
+    if layers[0].in_features != x.shape[1] or layers[1].in_features != layers[0].out_features or layers[2].in_features != layers[1].out_features:
+        return False
+    try:
+        return bool(_nl.cuda_lib().zoo_mlp3_supported(layers[0].in_features, layers[0].out_features, layers[1].out_features, layers[2].out_features))
+    except AttributeError:
+        return False
+
+
+class _Tower3Fn(torch.autograd.Function):
+    """Forward: one launch for the three layers (activations h1, h2, h3 and their ReLU sign bits are written for backward).
+    Backward: the per-layer dgrad / wgrad kernels, exactly what three chained `_FusedDenseFn` would run."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w16_1, w2, b2, w16_2, w3, b3, w16_3, y_out, mask_last, relu_input, relu_input_cols, x_bits, dx_out):
+        M, K0 = x.shape
+        N1, N2, N3 = w16_1.shape[0], w16_2.shape[0], w16_3.shape[0]
+        dev = x.device
+        h1 = torch.empty((M, N1), dtype=torch.bfloat16, device=dev)
+        h2 = torch.empty((M, N2), dtype=torch.bfloat16, device=dev)
+        h3 = y_out if y_out is not None else torch.empty((M, N3), dtype=torch.bfloat16, device=dev)
+        need = any(ctx.needs_input_grad)
+        bits1 = torch.empty((M, N1 // 32), dtype=torch.int32, device=dev) if need else None
+        bits2 = torch.empty((M, N2 // 32), dtype=torch.int32, device=dev) if need else None
+        bits3 = torch.empty((M, N3 // 32), dtype=torch.int32, device=dev) if need else None
+        _nl.check(_nl.cuda_lib().zoo_mlp3_fwd_bf16(
+            x.data_ptr(), x.stride(0), w16_1.data_ptr(), w16_1.stride(0), _nl.ptr(b1), w16_2.data_ptr(), w16_2.stride(0), _nl.ptr(b2),
+            w16_3.data_ptr(), w16_3.stride(0), _nl.ptr(b3), h1.data_ptr(), h1.stride(0), h2.data_ptr(), h2.stride(0), h3.data_ptr(), h3.stride(0),
+            M, K0, N1, N2, N3, _nl.ptr(bits1), _nl.ptr(bits2), _nl.ptr(bits3), _nl.stream_ptr()), "zoo_mlp3_fwd_bf16")
+        y = h3[:, :] if y_out is not None else h3
+        if need:
+            ctx.save_for_backward(x, h1, h2, y if mask_last else None, bits1, bits2, w16_1, w16_2, w16_3, w1, b1, w2, b2, w3, b3)
+            ctx.mask_last, ctx.relu_input, ctx.relu_input_cols, ctx.x_bits, ctx.dx_out = mask_last, relu_input, relu_input_cols, x_bits, dx_out
+            ctx.mark_non_differentiable(bits3)
+            ctx.set_materialize_grads(False)
+            return y, bits3
+        return y, None
+
+    @staticmethod
+    def backward(ctx, dy, *_unused):
+        x, h1, h2, y, bits1, bits2, w16_1, w16_2, w16_3, w1, b1, w2, b2, w3, b3 = ctx.saved_tensors
+        none = (None,) * 16
+        if dy is None:
+            return none
+        dy16 = dy if dy.dtype == torch.bfloat16 else dy.to(torch.bfloat16)
+        if ctx.mask_last:                       # otherwise the consumer's dgrad epilogue (or the head kernel) already applied the mask
+            dy16 = torch.where(y > 0, dy16, torch.zeros_like(dy16))
+        if not _aligned(dy16):
+            dy16 = _pad_cols(dy16)
+
+        def wgrad(d, inp, w, b):
+            gw, gb = getattr(w, "_zoo_grad", None), getattr(b, "_zoo_grad", None)
+            rw = rb = None
+            if gb is None:
+                gb = rb = torch.zeros_like(b, dtype=torch.float32)
+            if gw is None:
+                gw = rw = torch.zeros_like(w, dtype=torch.float32)
+            dense_wgrad(d, inp, gw, gb)
+            return rw, rb
+
+        dh2 = dense_dgrad(dy16, w16_3, mask_bits=bits2)                 # masks carry the ReLU of the layer below
+        gw3, gb3 = wgrad(dy16, h2, w3, b3)
+        dh1 = dense_dgrad(dh2, w16_2, mask_bits=bits1)
+        gw2, gb2 = wgrad(dh2, h1, w2, b2)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dxo = ctx.dx_out
+            if dxo is not None and (tuple(dxo.shape) != tuple(x.shape) or dxo.dtype != torch.bfloat16):
+                dxo = None
+            if ctx.relu_input and ctx.x_bits is not None:
+                dx = dense_dgrad(dh1, w16_1, out=dxo, mask_bits=ctx.x_bits, mask_cols=ctx.relu_input_cols)
+            else:
+                dx = dense_dgrad(dh1, w16_1, x if ctx.relu_input else None, out=dxo, mask_cols=ctx.relu_input_cols)
+        gw1, gb1 = wgrad(dh1, x, w1, b1)
+        return (dx, gw1, gb1, None, gw2, gb2, None, gw3, gb3, None) + (None,) * 6
+
+
 class FusedMLP(nn.Sequential):
     """Dense(+ReLU) tower; every hidden layer feeds the next layer's dgrad its ReLU mask."""
 
@@ -287,3 +378,24 @@ class FusedMLP(nn.Sequential):
         for a, b in zip(layers[:-1], layers[1:]):
             a.skip_relu_bwd = b.relu_input
         super().__init__(*layers)
+
+    def forward(self, x, out=None):
+        """`out` (CUDA path only): a bf16 [M, last width] column window of a wider buffer that receives the result.  Three-layer
+        ReLU towers with supported widths run as ONE kernel (`ZOO_FUSED_TOWER=0` keeps the layer-by-layer path)."""
+        import os
+
+        layers = list(self)
+        if os.environ.get("ZOO_FUSED_TOWER", "1") != "0" and _tower_shapes_ok(layers, x) and (out is None or _aligned(out)):
+            l1, l2, l3 = layers
+            for l in layers:
+                l.refresh_shadow()
+            x_bits = getattr(x, "_zoo_relu_bits", None) if l1.relu_input else None
+            y, bits = _Tower3Fn.apply(x, l1.weight, l1.bias, l1.weight_bf16, l2.weight, l2.bias, l2.weight_bf16, l3.weight, l3.bias, l3.weight_bf16,
+                                      out, not l3.skip_relu_bwd, l1.relu_input, l1.relu_input_cols, x_bits, getattr(x, "_zoo_dx_out", None))
+            if bits is not None:
+                y._zoo_relu_bits = bits
+            return y
+        h = x
+        for l in layers[:-1]:
+            h = l(h)
+        return layers[-1](h, out=out) if (out is not None and isinstance(layers[-1], FusedDense)) else layers[-1](h)

@@ -72,11 +72,14 @@ class ImageBatcher:
         self.dev = torch.empty(max_bytes, dtype=torch.uint8, device=self.device)
         self.meta_dev = torch.empty(max_batch * 4, dtype=torch.int64, device=self.device)
         self.max_batch = max_batch
+        self._meta_ev = None        # the pinned buffers may be rewritten only after their last asynchronous copies have run
 
     def stage(self, images):
         B = len(images)
         if B > self.max_batch:
             raise ValueError(f"batch {B} > max_batch {self.max_batch}")
+        if self._meta_ev is not None:        # small batches in quick succession: the previous H2D copies may still be queued
+            self._meta_ev.synchronize()
         off, hb = 0, self.host.numpy()
         offs = self.meta_host[:B].numpy()
         hw = self.meta_host[B:2 * B].numpy().view(np.int32)    # B int64 slots viewed as 2B int32 = [B,2]
@@ -97,6 +100,9 @@ class ImageBatcher:
             off += (n + 15) // 16 * 16
         self.dev[:off].copy_(self.host[:off], non_blocking=True)
         self.meta_dev[:2 * B].copy_(self.meta_host[:2 * B], non_blocking=True)
+        if self.device.type == "cuda":
+            self._meta_ev = torch.cuda.Event()
+            self._meta_ev.record(torch.cuda.current_stream(self.device))
         return B, C_, off
 
 
@@ -148,6 +154,7 @@ class JpegBatchDecoder:
         self.meta_host = torch.empty(max_batch * 4, dtype=torch.int64).pin_memory()
         self.meta_dev = torch.empty(max_batch * 4, dtype=torch.int64, device=self.device)
         self.max_batch = max_batch
+        self._meta_ev = None        # the pinned meta buffer may be rewritten only after its last asynchronous copy has run
 
     @staticmethod
     def available():
@@ -198,6 +205,8 @@ class JpegBatchDecoder:
         rc = lib.zoo_jpeg_batch_info(handle, ptrs, lens, B, ws, hs, None)
         if rc != 0:
             raise _nl.NativeError("zoo_jpeg_batch_info: " + lib.zoo_last_error().decode(errors="replace"))
+        if self._meta_ev is not None:        # small batches in quick succession: the previous H2D copy of this buffer may still be queued
+            self._meta_ev.synchronize()
         offs = self.meta_host[:B].numpy()
         hw = self.meta_host[B:2 * B].numpy().view(np.int32)
         off = 0
@@ -216,6 +225,8 @@ class JpegBatchDecoder:
         if B != n_real:
             self.meta_host[n_real:n_real + n_real] = self.meta_host[B:B + n_real].clone()
         self.meta_dev[:2 * n_real].copy_(self.meta_host[:2 * n_real], non_blocking=True)
+        self._meta_ev = torch.cuda.Event()
+        self._meta_ev.record(torch.cuda.current_stream(self.device))
         self._keep = (getattr(self, "_keep", (None, None))[1], bufs)      # the bitstreams outlive the asynchronous decode (two generations)
         return n_real, off
 
