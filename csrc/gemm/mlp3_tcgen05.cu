@@ -150,11 +150,10 @@ mlp3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
       uint32_t stage = 0, phase = 0;
       mbar_wait(&w3_bar, 0);
       tc_fence_after();
-      int it = 0;
-      for (int tile = blockIdx.x; tile < a.m_blocks; tile += gridDim.x, ++it) {
-        const uint32_t par = (uint32_t)(it & 1);
-        // ---- layer 1
-        mbar_wait(&acc_empty[0], par ^ 1u);
+      // Layer 1 of the NEXT tile is issued between layers 2 and 3 of the current one (its accumulator is free once h1 is out), so its
+      // loads and MMAs run under the epilogues of layers 2 and 3; the ring is consumed in the producer's order L1(0) L2(0) L1(1) L2(1) ...
+      auto layer1 = [&](int it_) {
+        mbar_wait(&acc_empty[0], (uint32_t)(it_ & 1) ^ 1u);
         tc_fence_after();
         for (int kb = 0; kb < kb0n; ++kb) {
           mbar_wait(&full_bar[stage], phase);
@@ -167,6 +166,11 @@ mlp3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
           if (++stage == kT3Stages) { stage = 0; phase ^= 1u; }
         }
         umma_commit(&acc_full[0]);
+      };
+      int it = 0;
+      layer1(0);
+      for (int tile = blockIdx.x; tile < a.m_blocks; tile += gridDim.x, ++it) {
+        const uint32_t par = (uint32_t)(it & 1);
         // ---- layer 2: A = h1 tile in shared memory
         mbar_wait(&h_ready[0], par);
         mbar_wait(&acc_empty[1], par ^ 1u);
@@ -182,6 +186,7 @@ mlp3_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
           if (++stage == kT3Stages) { stage = 0; phase ^= 1u; }
         }
         umma_commit(&acc_full[1]);
+        if (tile + (int)gridDim.x < a.m_blocks) layer1(it + 1);
         // ---- layer 3: A = h2 tile (H k-blocks 0..), B = resident W3
         mbar_wait(&h_ready[1], par);
         mbar_wait(&acc_empty[2], par ^ 1u);
