@@ -185,7 +185,9 @@ class InferenceModel:
                         self._forward(static_in)
                         slot.stream.synchronize()
                         graph = torch.cuda.CUDAGraph()
-                        with torch.cuda.graph(graph, stream=slot.stream):
+                        # thread-local capture mode: other threads of the process (a serving engine's decode thread, other
+                        # slots) keep making CUDA calls while this stream captures; the default global mode makes those fail
+                        with torch.cuda.graph(graph, stream=slot.stream, capture_error_mode="thread_local"):
                             static_out = self._forward(static_in)
                         g = slot.graphs[key] = (graph, static_in, static_out)
                     except Exception:
