@@ -132,3 +132,19 @@ def test_native_arrays_over_the_arena(tmp_path):
     np.testing.assert_allclose(vf.get(0), [1, 2, 3]); np.testing.assert_allclose(vf.get(1), [4])
     with pytest.raises(ValueError):
         FloatArray(1, memory_type="TAPE")
+
+
+def test_spark_runner_pack_penv(tmp_path):
+    """SparkRunner.pack_penv (reference: pyzoo/zoo/util/spark.py:100-113 conda-packs the environment for the executors): the archive a
+    worker image needs -- the package with its native libraries, launch scripts, a lock file of the installed distributions."""
+    import tarfile
+
+    from zoo.util.spark import SparkRunner
+
+    out = SparkRunner().pack_penv(output=str(tmp_path / "penv.tar.gz"))
+    with tarfile.open(out) as t:
+        names = set(t.getnames())
+        lock = t.extractfile("requirements.lock").read().decode()
+    assert "zoo/common/nncontext.py" in names and "scripts/zoo-submit" in names and "requirements.lock" in names
+    assert not any("__pycache__" in n for n in names)
+    assert any(line.startswith("torch==") for line in lock.splitlines())
