@@ -54,6 +54,8 @@ class KerasNet(nn.Module):
                 self._engine.set_checkpoint(*p["ckpt"])
             if "clip" in p:
                 self._engine.clip = p["clip"]
+            if "drop" in p:
+                self._engine.set_drop_module_property(*p["drop"])
         return self._engine
 
     def compile(self, optimizer, loss, metrics=None):
@@ -98,6 +100,14 @@ class KerasNet(nn.Module):
         self._pending["clip"] = ("l2", float(clip_norm))
         if self._engine is not None:
             self._engine.set_gradient_clipping_by_l2_norm(clip_norm)
+
+    def set_drop_module_property(self, drop_percentage, max_drop_percentage, batch_size=100, warmup_iteration=200, micro_batches=4):
+        """Gradient dropping / straggler mitigation of `fit` (reference: the dropPercentage family of the zoo optimizer,
+        Topology.scala:1096-1100; `zoo.pipeline.straggler`)."""
+        self._pending["drop"] = (drop_percentage, max_drop_percentage, batch_size, warmup_iteration, micro_batches)
+        if self._engine is not None:
+            self._engine.set_drop_module_property(*self._pending["drop"])
+        return self
 
     def set_evaluate_status(self):
         self.eval()

@@ -159,6 +159,7 @@ class TrainingEngine:
         self._last_criterion = None
         self.autocast_dtype = None   # e.g. torch.bfloat16: run generic torch models' forward under autocast (masters stay fp32)
         self.channels_last = False
+        self._dropper = None         # GradientDropper when set_drop_module_property / conf zoo.drop.percentage turned it on
 
     # ----------------------------------------------------------------- set-up --
     @property
@@ -488,8 +489,55 @@ class TrainingEngine:
         self._after_step_shadows()
         return loss.detach()
 
+    # ------------------------------------------------------- gradient dropping --
+    def set_drop_module_property(self, drop_percentage, max_drop_percentage, batch_size=100, warmup_iteration=200, micro_batches=4):
+        """Straggler mitigation (reference: dropPercentage / maxDropPercentage / computeThresholdbatchSize / warmupIterationNum,
+        Topology.scala:1096-1100).  See `zoo.pipeline.straggler`.  `drop_percentage` 0 turns it off."""
+        from .straggler import GradientDropper
+
+        self._dropper = None if not drop_percentage else GradientDropper(self.ctx, drop_percentage, max_drop_percentage, batch_size,
+                                                                         warmup_iteration, micro_batches)
+        return self
+
+    def _drop_step(self, criterion, inputs, targets):
+        """The step with droppable micro-batches: gradient SUMS accumulate in the flat buffer, ranks agree on what was processed,
+        the sum is divided by the samples that were really processed, then the usual exchange + optimizer step."""
+        from ..ops.embedding import EmbeddingTable
+        from .straggler import batch_rows, split_batch
+
+        d = self._dropper
+        if any(isinstance(m, EmbeddingTable) and m.sparse for m in self.model.modules()):
+            raise ValueError("gradient dropping works on the dense gradient exchange; tables with their own sparse optimizer update inside "
+                             "backward and cannot take back a dropped micro-batch (build the model with sparse=False or turn dropping off)")
+        xs, ys = split_batch(inputs, d.micro_batches), split_batch(targets, d.micro_batches)
+        cuda = self.device.type == "cuda"
+        d.begin()
+        samples, loss_sum = 0, None
+        for j, (x, y) in enumerate(zip(xs, ys)):
+            if not d.may_start(j):
+                break
+            n = batch_rows(x)
+            loss, _ = self.forward_loss(criterion, x, y)
+            (loss * n).backward()            # criterions average over their batch: x n gives the sum this micro-batch contributes
+            loss_sum = loss.detach() * n if loss_sum is None else loss_sum + loss.detach() * n
+            samples += n
+            if cuda:
+                torch.cuda.synchronize()     # the pace is observed on the host
+            d.finished(j)
+        samples_all, update = d.exchange(samples)
+        reg = self.model.regularization_loss() if hasattr(self.model, "regularization_loss") else None
+        if not update:
+            self.fopt.zero_grad()
+            return loss_sum / max(samples, 1)
+        self.fopt.arena.flat_g.mul_(self.ctx.world_size / max(samples_all, 1))   # the exchange averages over ranks
+        if reg is not None:
+            reg.backward()
+        self._dp.step()
+        self._after_step_shadows()
+        return loss_sum / max(samples, 1)
+
     def _graph_enabled(self):
-        if self.device.type != "cuda":
+        if self.device.type != "cuda" or self._dropper is not None:
             return False
         if self.use_cuda_graph is not None:
             return bool(self.use_cuda_graph)
@@ -498,6 +546,8 @@ class TrainingEngine:
     def train_step(self, criterion, batch: MiniBatch):
         """One optimizer step.  Launch-bound models replay the whole step (forward, loss, backward,
         sparse + dense optimizers) from ONE CUDA graph: ~40 launches become one `cudaGraphLaunch`."""
+        if self._dropper is not None:
+            return self._drop_step(criterion, batch.inputs, batch.targets)
         if not self._graph_enabled():
             return self._eager_step(criterion, batch.inputs, batch.targets)
         g = self._graph
@@ -572,6 +622,10 @@ class TrainingEngine:
         local_bs = batch_size // ctx.world_size
         metrics = [to_metric(m, criterion) for m in (validation_method or [])]
         conf = ctx.conf
+        if self._dropper is None and float(conf.get("zoo.drop.percentage", 0) or 0) > 0:
+            self.set_drop_module_property(float(conf.get("zoo.drop.percentage")), float(conf.get("zoo.drop.maxPercentage", conf.get("zoo.drop.percentage"))),
+                                          int(conf.get("zoo.drop.computeThresholdBatchSize", 100)), int(conf.get("zoo.drop.warmupIterationNum", 200)),
+                                          int(conf.get("zoo.drop.microBatches", 4)))
         retry_budget, retry_window = int(conf.get("zoo.failure.retryTimes", 5)), float(conf.get("zoo.failure.retryTimeInterval", 120))
         failures, window_start = 0, time.time()
         self.state["numSlice"] = fs.num_of_slice()

@@ -46,6 +46,11 @@ class Estimator:
 
     set_gradient_clipping_by_l2_norm = set_l2_norm_gradient_clipping
 
+    def set_drop_module_property(self, drop_percentage, max_drop_percentage, batch_size=100, warmup_iteration=200, micro_batches=4):
+        """Gradient dropping / straggler mitigation (Topology.scala:1096-1100; `zoo.pipeline.straggler`)."""
+        self.engine.set_drop_module_property(drop_percentage, max_drop_percentage, batch_size, warmup_iteration, micro_batches)
+        return self
+
     def set_tensorboard(self, log_dir, app_name):
         self.engine.set_tensorboard(log_dir, app_name)
 
@@ -211,6 +216,11 @@ class TorchEstimator:
 
     def clear_gradient_clipping(self):
         self.engine.clear_gradient_clipping()
+
+    def set_drop_module_property(self, drop_percentage, max_drop_percentage, batch_size=100, warmup_iteration=200, micro_batches=4):
+        """Gradient dropping / straggler mitigation (Topology.scala:1096-1100; `zoo.pipeline.straggler`)."""
+        self.engine.set_drop_module_property(drop_percentage, max_drop_percentage, batch_size, warmup_iteration, micro_batches)
+        return self
 
     def shutdown(self):
         self.engine.close()
