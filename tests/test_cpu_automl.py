@@ -198,3 +198,61 @@ def test_forecasters():
     assert lt.shape == (400, 2, 2, 2) and st.shape == (400, 2, 2)
     with pytest.raises(ValueError):
         mt.preprocess_input(x[:, :5])
+
+
+def test_keras_recipe_forecasters():
+    """`VanillaLSTM` / `LSTMSeq2Seq` with the reference's Keras-recipe architecture, defaults and training scheme
+    (pyzoo/zoo/automl/model/VanillaLSTM.py:50-90, Seq2Seq.py:50-165), save / restore round trip."""
+    import os
+    import tempfile
+
+    from zoo.automl.model.Seq2Seq import LSTMSeq2Seq
+    from zoo.automl.model.time_sequence import TimeSequenceModel
+    from zoo.automl.model.VanillaLSTM import VanillaLSTM
+
+    torch.manual_seed(0)
+    rng = np.random.RandomState(0)
+    t = np.arange(400, dtype=np.float32)
+    series = np.sin(t / 6.0) + 0.05 * rng.randn(400).astype(np.float32)
+    past, fut = 12, 3
+    x = np.stack([np.stack([series[i:i + past], np.cos(t[i:i + past] / 6.0)], -1) for i in range(380)]).astype(np.float32)
+    y1 = np.stack([series[i + past] for i in range(380)]).astype(np.float32)
+    y3 = np.stack([series[i + past:i + past + fut] for i in range(380)]).astype(np.float32)
+
+    m = VanillaLSTM(future_seq_len=1)
+    first = m.fit_eval(x, y1, epochs=1, batch_size=64, lr=0.01)
+    last = m.fit_eval(x, y1, epochs=15, batch_size=64, lr=0.01)
+    assert last < first and last < 0.1, (first, last)
+    assert type(m.optimizer).__name__ == "RMSprop" and m.model.lstm1.hidden_size == 20 and m.model.lstm2.hidden_size == 10
+    mean, std = m.predict_with_uncertainty(x[:16], n_iter=5)
+    assert mean.shape == (16, 1) and (std > 0).any()
+
+    s = LSTMSeq2Seq(future_seq_len=fut)
+    first = s.fit_eval(x, y3, epochs=1, batch_size=64, lr=0.01, latent_dim=32, dropout=0.0)
+    last = s.fit_eval(x, y3, epochs=15, batch_size=64, lr=0.01, latent_dim=32, dropout=0.0)
+    assert last < first and last < 0.15, (first, last)
+    p = s.predict(x[:10])
+    assert p.shape == (10, fut)
+    # teacher-forced training output and step-wise decoding agree when the fed-back values are the truth
+    with torch.no_grad():
+        xb, yb = torch.from_numpy(x[:4]), torch.from_numpy(s._prepare_y(y3[:4]))
+        s.model.eval()
+        tf = s.model(xb, torch.cat([xb[:, -1:, :1], yb[:, :-1]], 1))
+        assert torch.allclose(tf[:, 0], s.model(xb)[:, 0], atol=1e-5)          # the first step sees the same input either way
+    with tempfile.TemporaryDirectory() as d:
+        s.save(os.path.join(d, "m.pt"), os.path.join(d, "c.json"))
+        from zoo.automl.common.util import load_config
+
+        r = LSTMSeq2Seq(future_seq_len=fut).restore(os.path.join(d, "m.pt"), **load_config(os.path.join(d, "c.json")))
+        assert np.allclose(r.predict(x[:10]), p, atol=1e-6)
+
+    # two target columns: y [n, future, 2]
+    y2c = np.stack([y3, -y3], -1)
+    x2c = np.concatenate([x[..., :1], -x[..., :1], x[..., 1:]], -1)
+    s2 = LSTMSeq2Seq(future_seq_len=fut)
+    s2.fit_eval(x2c, y2c, epochs=2, batch_size=64, latent_dim=16)
+    assert s2.predict(x2c[:5]).shape == (5, fut, 2) and s2.model.decoder_dense.out_features == 2
+
+    ts = TimeSequenceModel(future_seq_len=fut)
+    ts.fit_eval(x, y3, model="Seq2seq_keras", epochs=1, latent_dim=8)
+    assert isinstance(ts.model, LSTMSeq2Seq) and ts.predict(x[:3]).shape == (3, fut)

@@ -133,3 +133,27 @@ def test_automl_remote_helpers(tmp_path):
     assert get_remote_list(remote) == ["ppl.zip"]
     m = M()
     assert restore_hdfs(z, remote, None, m) == {"a": 1} and m.got == "weights"
+
+
+def test_zoo_optimizer_wrapper_and_fake_optim_method():
+    """ZooOptimizer hands the wrapped description to the engine unchanged; FakeOptimMethod leaves the weights where they are
+    (reference: pyzoo/zoo/tfpark/zoo_optimizer.py:22-140)."""
+    import numpy as np
+    import torch
+
+    from zoo.common.triggers import MaxIteration
+    from zoo.feature.common import FeatureSet
+    from zoo.pipeline.api.keras.optimizers import Adam, to_opt_config
+    from zoo.pipeline.estimator import Estimator
+    from zoo.tfpark.unsupported import ZooOptimizer as FromOldHome
+    from zoo.tfpark.zoo_optimizer import FakeOptimMethod, ZooOptimizer
+
+    assert FromOldHome is ZooOptimizer
+    wrapped = ZooOptimizer(ZooOptimizer(Adam(lr=0.02)))
+    cfg, ref = to_opt_config(wrapped), to_opt_config(Adam(lr=0.02))
+    assert (cfg.name, cfg.lr) == (ref.name, ref.lr) and wrapped.lr == 0.02 and wrapped.name == "Adam"
+    x, y = np.random.RandomState(0).randn(16, 4).astype(np.float32), np.zeros((16, 1), np.float32)
+    m = torch.nn.Linear(4, 1)
+    before = [p.detach().clone() for p in m.parameters()]
+    Estimator(m, FakeOptimMethod()).engine.train(FeatureSet.numpy(x, y), "mse", MaxIteration(2), batch_size=8)
+    assert all(torch.equal(a, b) for a, b in zip(m.parameters(), before))

@@ -6,9 +6,12 @@ from .abstract import BaseModel
 from .MTNet import MTNet
 from .Seq2Seq_pytorch import Seq2SeqPytorch
 from .TCN import TCNPytorch
+from .Seq2Seq import LSTMSeq2Seq
+from .VanillaLSTM import VanillaLSTM
 from .VanillaLSTM_pytorch import VanillaLSTMPytorch
 
-MODELS = {"lstm": VanillaLSTMPytorch, "vanillalstm": VanillaLSTMPytorch, "seq2seq": Seq2SeqPytorch, "lstmseq2seq": Seq2SeqPytorch,
+# "<name>_keras": the reference's Keras recipes (two stacked LSTMs / single-layer teacher-forced encoder-decoder, RMSprop)
+MODELS = {"lstm_keras": VanillaLSTM, "seq2seq_keras": LSTMSeq2Seq, "lstm": VanillaLSTMPytorch, "vanillalstm": VanillaLSTMPytorch, "seq2seq": Seq2SeqPytorch, "lstmseq2seq": Seq2SeqPytorch,
           "mtnet": MTNet, "tcn": TCNPytorch}
 
 

@@ -51,7 +51,13 @@ class TorchForecastModel(BaseModel):
             self._get_configs(config)
             self.config = {k: config[k] for k in config if isinstance(config[k], (int, float, str, bool, list, np.integer, np.floating))}
             self.model = self._build(config).to(self.device)
-            self.optimizer = torch.optim.Adam(self.model.parameters(), lr=self.lr)
+            self.optimizer = self._make_optimizer()
+
+    def _make_optimizer(self):
+        return torch.optim.Adam(self.model.parameters(), lr=self.lr)
+
+    def _train_loss(self, xb, yb):
+        return self.criterion(self.model(xb).reshape(yb.shape), yb)
 
     def _batches(self, x, y=None, shuffle=False):
         n = len(x)
@@ -70,7 +76,7 @@ class TorchForecastModel(BaseModel):
             self.model.train()
             for xb, yb in self._batches(x, y2, shuffle=True):
                 self.optimizer.zero_grad(set_to_none=True)
-                loss = self.criterion(self.model(xb).reshape(yb.shape), yb)
+                loss = self._train_loss(xb, yb)
                 loss.backward()
                 self.optimizer.step()
         vx, vy = validation_data if validation_data is not None else (x, y)
@@ -115,5 +121,5 @@ class TorchForecastModel(BaseModel):
         self.config = dict(config)
         self.model = self._build(config).to(self.device)
         self.model.load_state_dict(torch.load(model_path, map_location=self.device))
-        self.optimizer = torch.optim.Adam(self.model.parameters(), lr=self.lr)
+        self.optimizer = self._make_optimizer()
         return self
