@@ -13,6 +13,7 @@ import numpy as np
 import torch
 import torch.nn as nn
 
+from zoo.common.dictionary import ZooDictionary
 from zoo.models.seq2seq import Bridge, RNNDecoder, RNNEncoder, Seq2seq
 from zoo.pipeline.api.keras.objectives import SparseCategoricalCrossEntropy
 from zoo.pipeline.api.keras.optimizers import Adam
@@ -21,6 +22,8 @@ torch.manual_seed(0)
 rng = np.random.RandomState(0)
 VOCAB, PAD, START, END = 40, 0, 1, 2
 SEQ, EMBED, HIDDEN = 6, int(os.environ.get("EMBED", 32)), int(os.environ.get("HIDDEN", 64))
+# the example's idx2w / w2idx files become a ZooDictionary (Train.scala:70); it turns token ids back into words for the printout
+dictionary = ZooDictionary(index2word=dict({PAD: "<pad>", START: "SENTENCESTART", END: "SENTENCEEND"}, **{i: "word%02d" % i for i in range(3, VOCAB)}))
 reply = rng.permutation(np.arange(3, VOCAB))                    # word w is answered by reply[w - 3]
 n = int(os.environ.get("PAIRS", 3000))
 queries = rng.randint(3, VOCAB, (n, SEQ))
@@ -41,6 +44,7 @@ hits = 0
 for q, want in zip(queries[:50], answers[:50]):
     got = model.infer(q, start_sign=np.array([START]), max_seq_len=5, stop_sign=np.array([END]), build_output=to_word).reshape(-1)
     hits += int(len(got) >= 4 and (got[:4] == want).all())
-print("Query>", queries[0].tolist(), "\nAnswer>", model.infer(queries[0], np.array([START]), 5, np.array([END]), to_word).reshape(-1).tolist(),
-      "(expected", answers[0].tolist() + [END], ")")
+said = model.infer(queries[0], np.array([START]), 5, np.array([END]), to_word).reshape(-1).tolist()
+print("Query>", " ".join(dictionary.decode(queries[0])), "\nAnswer>", " ".join(dictionary.decode(said)),
+      "(expected", " ".join(dictionary.decode(answers[0].tolist() + [END])), ")")
 print("exact answers on 50 training queries: %d/50" % hits)

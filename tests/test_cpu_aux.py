@@ -5,6 +5,7 @@ import subprocess
 import sys
 import time
 
+import pytest
 import torch
 
 from zoo.utils.profiler import PhaseTimer, nvtx_range, throughputing, time_it
@@ -148,3 +149,36 @@ def test_spark_runner_pack_penv(tmp_path):
     assert "zoo/common/nncontext.py" in names and "scripts/zoo-submit" in names and "requirements.lock" in names
     assert not any("__pycache__" in n for n in names)
     assert any(line.startswith("torch==") for line in lock.splitlines())
+
+
+def test_zoo_dictionary_and_tensor_operation(tmp_path):
+    """ZooDictionary (common/ZooDictionary.scala:27-140) and TensorOperation (common/TensorOperation.scala:25-110)."""
+    import torch
+
+    from zoo.common.dictionary import ZooDictionary
+    from zoo.common.tensor_operation import TensorOperation, div_tensor, expand_size, sub_tensor
+
+    sentences = [["the", "cat", "sat"], ["the", "dog", "sat"], ["a", "cat", "ran", "the", "end"]]
+    d = ZooDictionary(sentences, vocab_size=3, seed=0)
+    assert d.vocabulary() == ["the", "cat", "sat"] and d.get_vocab_size() == 3 and d.get_discard_size() == 4
+    assert d.get_index("the") == 0 and d.get_index("zebra") == 3                 # unknown word -> vocab_size
+    assert d.get_word(1) == "cat" and d.get_word(99) in d.discard_vocab()        # unknown index -> a discarded word
+    assert d.add_word("dog") == 3 and d.getIndex("dog") == 3 and "dog" not in d.discardVocab()
+    assert d.encode(["the", "dog", "flew"]) == [0, 3, 4] and d.decode([0, 3]) == ["the", "dog"]
+    d.save(str(tmp_path / "dict.json"))
+    r = ZooDictionary.load(str(tmp_path / "dict.json"))
+    assert r.word2index() == d.word2index() and r.discard_vocab() == d.discard_vocab()
+    m = ZooDictionary(index2word={0: "x", 1: "y"})
+    assert m.get_index("y") == 1 and m.get_word(7) in ("x", "y")
+
+    assert expand_size(torch.zeros(2, 3, 4), torch.zeros(3, 1)) == [2, 3, 4]
+    with pytest.raises(ValueError):
+        expand_size(torch.zeros(2, 3), torch.zeros(4))
+    x, mean = torch.arange(24.0).view(2, 3, 4), torch.arange(24.0).view(2, 3, 4).mean(-1, keepdim=True)
+    want = x.clone() - mean
+    assert sub_tensor(x, mean) is x and torch.equal(x, want)
+    std = want.pow(2).mean(-1, keepdim=True).sqrt()
+    assert torch.allclose(div_tensor(x, std), want / std)
+    small = torch.ones(3, 1)
+    TensorOperation.subTensor(small, torch.arange(4.0))                          # the first argument grows to the broadcast size
+    assert small.shape == (3, 4) and torch.equal(small[1], 1 - torch.arange(4.0))

@@ -161,6 +161,16 @@ class TensorToSample(Preprocessing):
         return x if isinstance(x, Sample) else Sample(x)
 
 
+class MultiTensorsToSample(Preprocessing):
+    """A list of tensors -> one Sample whose feature is all of them, no label (reference:
+    feature/common/MultiTensorsToSample.scala:27-33; used behind `SeqToMultipleTensors` for multi-input models)."""
+
+    def apply(self, x):
+        if isinstance(x, Sample):
+            return x
+        return Sample(list(x) if isinstance(x, (tuple, list)) else [x])
+
+
 class FeatureLabelPreprocessing(Preprocessing):
     """(feature, label) -> Sample using one transformer per side (common.py:188-200)."""
 

@@ -4,6 +4,8 @@ random ops draw from numpy's global RNG.  For whole batches on the GPU see `zoo.
 (kernel K13: resize + crop + normalise + layout in one pass)."""
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 from ..common import ChainedPreprocessing, Preprocessing, Sample  # noqa: F401
@@ -358,3 +360,106 @@ class ImageRandomPreprocessing(Preprocessing):
 
     def apply(self, f):
         return self.preprocessing(f) if np.random.rand() < self.prob else f
+
+
+ImagePixelNormalizer = ImagePixelNormalize      # the Scala name (feature/image/ImagePixelNormalizer.scala)
+ImageProcessing = ImagePreprocessing            # the Scala base-class name (feature/image/ImageProcessing.scala)
+
+
+class ImageChannelScaledNormalizer(ImagePreprocessing):
+    """`(pixel - channel mean) * scale` in one pass (reference: feature/image/ImageChannelScaledNormalizer.scala:25-50; the means
+    are given as R, G, B while the mat is BGR)."""
+
+    def __init__(self, mean_r, mean_g, mean_b, scale, bigdl_type="float"):
+        self.mean = np.array([mean_b, mean_g, mean_r], dtype=np.float32)
+        self.scale = np.float32(scale)
+
+    def transform_mat(self, mat, f):
+        return (mat.astype(np.float32) - self.mean[:mat.shape[2]]) * self.scale
+
+
+class ImageRandomCropper(_Crop):
+    """Crop `crop_width x crop_height` at a random (`cropper_method="random"`) or the centre (`"center"`) position and, when
+    `mirror` is set, flip the crop horizontally with probability 1/2 (feature/image/ImageRandomCropper.scala:27-62)."""
+
+    def __init__(self, crop_width, crop_height, mirror, cropper_method="random", channels=3, bigdl_type="float"):
+        method = str(cropper_method).lower()
+        if method not in ("random", "center", "croprandom", "cropcenter"):
+            raise ValueError(f"cropper_method {cropper_method!r}: expected 'random' or 'center'")
+        self.cw, self.ch, self.mirror, self.center, self.channels = int(crop_width), int(crop_height), bool(mirror), "center" in method, channels
+
+    def transform_mat(self, mat, f):
+        h, w = mat.shape[:2]
+        if h < self.ch or w < self.cw:
+            raise ValueError(f"image {h}x{w} is smaller than the crop {self.ch}x{self.cw}")
+        if self.center:
+            x, y = (w - self.cw) // 2, (h - self.ch) // 2
+        else:
+            x, y = np.random.randint(0, w - self.cw + 1), np.random.randint(0, h - self.ch + 1)
+        out = self._crop(mat, x, y, x + self.cw, y + self.ch)
+        return out[:, ::-1].copy() if self.mirror and np.random.rand() < 0.5 else out
+
+
+class ImageRandomResize(ImagePreprocessing):
+    """Resize so that the SHORTER side becomes a size drawn uniformly from [min_size, max_size], keeping the aspect ratio
+    (feature/image/ImageRandomResize.scala; the Inception / ResNet training pipelines use it before the random crop)."""
+
+    def __init__(self, min_size, max_size, bigdl_type="float"):
+        if min_size > max_size:
+            raise ValueError("min_size must not exceed max_size")
+        self.min_size, self.max_size = int(min_size), int(max_size)
+
+    def transform_mat(self, mat, f):
+        import cv2
+
+        h, w = mat.shape[:2]
+        short = np.random.randint(self.min_size, self.max_size + 1)
+        nh, nw = (short, max(1, int(round(w * short / h)))) if h <= w else (max(1, int(round(h * short / w))), short)
+        return cv2.resize(mat, (nw, nh), interpolation=cv2.INTER_LINEAR)
+
+
+class ImageMatToFloats(ImagePreprocessing):
+    """mat -> flat float array under `out_key` (HWC order), with the size kept under "originalSize"-style keys
+    (feature/image/ImageMatToFloats.scala:28-50).  `valid_*` size the reusable buffer when `share_buffer` is on: with a shared
+    buffer the array is only valid until the next feature passes through, as in the reference."""
+
+    def __init__(self, valid_height=300, valid_width=300, valid_channel=3, out_key="floats", share_buffer=True, bigdl_type="float"):
+        self.out_key, self.share = out_key, bool(share_buffer)
+        self._buf = np.empty(int(valid_height) * int(valid_width) * int(valid_channel), dtype=np.float32) if self.share else None
+
+    def apply(self, f):
+        mat = np.asarray(f["mat"])
+        n = mat.size
+        if self.share:
+            if self._buf.size < n:
+                self._buf = np.empty(n, dtype=np.float32)
+            out = self._buf[:n]
+            np.copyto(out, mat.reshape(-1), casting="unsafe")
+        else:
+            out = mat.astype(np.float32).reshape(-1)
+        f[self.out_key] = out
+        f["size"] = mat.shape
+        return f
+
+
+class BufferedImageResize(ImagePreprocessing):
+    """Resize the ENCODED image under `bytes` and re-encode it in its own format, taken from the uri's extension
+    (feature/image/BufferedImageResize.scala:27-50; there through java.awt with SCALE_SMOOTH, here OpenCV INTER_AREA)."""
+
+    def __init__(self, resize_h, resize_w, bigdl_type="float"):
+        self.h, self.w = int(resize_h), int(resize_w)
+
+    def apply(self, f):
+        import cv2
+
+        img = cv2.imdecode(np.frombuffer(f["bytes"], np.uint8), cv2.IMREAD_UNCHANGED)
+        if img is None:
+            raise ValueError(f"cannot decode image {f.get('uri')}")
+        if img.shape[:2] != (self.h, self.w):
+            ext = os.path.splitext(str(f.get("uri", "")))[1].lower() or ".png"
+            ok, enc = cv2.imencode(ext if ext in (".jpg", ".jpeg", ".png", ".bmp", ".webp", ".tif", ".tiff") else ".png",
+                                   cv2.resize(img, (self.w, self.h), interpolation=cv2.INTER_AREA))
+            if not ok:
+                raise ValueError(f"cannot encode image {f.get('uri')}")
+            f["bytes"] = enc.tobytes()
+        return f
