@@ -23,7 +23,9 @@ rng = np.random.RandomState(0)
 VOCAB, PAD, START, END = 40, 0, 1, 2
 SEQ, EMBED, HIDDEN = 6, int(os.environ.get("EMBED", 32)), int(os.environ.get("HIDDEN", 64))
 # the example's idx2w / w2idx files become a ZooDictionary (Train.scala:70); it turns token ids back into words for the printout
-dictionary = ZooDictionary(index2word=dict({PAD: "<pad>", START: "SENTENCESTART", END: "SENTENCEEND"}, **{i: "word%02d" % i for i in range(3, VOCAB)}))
+idx2w = {PAD: "<pad>", START: "SENTENCESTART", END: "SENTENCEEND"}
+idx2w.update({i: "word%02d" % i for i in range(3, VOCAB)})
+dictionary = ZooDictionary(index2word=idx2w)
 reply = rng.permutation(np.arange(3, VOCAB))                    # word w is answered by reply[w - 3]
 n = int(os.environ.get("PAIRS", 3000))
 queries = rng.randint(3, VOCAB, (n, SEQ))
