@@ -23,7 +23,28 @@ _nl.register_cuda_sigs({
     "zoo_tcn_conv_dgrad": [_V, _V, _V, _I, _I, _I, _I, _I, _I, _V],
     "zoo_tcn_prep_grad": [_V, _V, _V, _V, _V, _L, _I, _F, _V],
     "zoo_tcn_conv_wgrad": [_V, _V, _V, _I, _I, _I, _I, _I, _I, _V],
+    # TF32 tensor-core forms (csrc/ops/tcn_mma.cu)
+    "zoo_tcn_mma_supported": [_I, _I, _I, _I, _I],
+    "zoo_tcn_mma_scratch_elems": [_I, _I, _I],
+    "zoo_tcn_conv_forward_mma": [_V, _V, _V, _V, _V, _V, _I, _I, _I, _I, _I, _I, _I, _F, C.c_ulonglong, _V],
+    "zoo_tcn_conv_dgrad_mma": [_V, _V, _V, _V, _I, _I, _I, _I, _I, _I, _V],
+    "zoo_tcn_conv_wgrad_mma": [_V, _V, _V, _I, _I, _I, _I, _I, _I, _V],
 })
+
+
+def mma_path(Cin, Cout, T, K, dilation):
+    """True when the TF32 tensor-core kernels take this layer (`ZOO_TCN_MMA=0` forces the fp32 CUDA-core kernels)."""
+    import os
+
+    if os.environ.get("ZOO_TCN_MMA", "1") == "0":
+        return False
+    return bool(_nl.cuda_lib().zoo_tcn_mma_supported(Cin, Cout, T, K, dilation))
+
+
+def _mma_scratch(x, Cin, Cout, K):
+    lib = _nl.cuda_lib()
+    lib.zoo_tcn_mma_scratch_elems.restype = C.c_longlong
+    return torch.empty(int(lib.zoo_tcn_mma_scratch_elems(Cin, Cout, K)), dtype=torch.float32, device=x.device)
 
 
 def causal_conv1d_reference(x, w, bias=None, dilation=1, relu=True, res=None):
@@ -41,17 +62,24 @@ class _CausalConvFn(torch.autograd.Function):
         B, Cin, T = x.shape
         Cout, _, K = w.shape
         out = torch.empty((B, Cout, T), dtype=torch.float32, device=x.device)
-        _nl.check(_nl.cuda_lib().zoo_tcn_conv_forward(x.data_ptr(), w.data_ptr(), _nl.ptr(bias), _nl.ptr(res), out.data_ptr(), B,
-                                                      Cin, Cout, T, K, dilation, int(relu), float(drop_p), int(seed),
-                                                      _nl.stream_ptr()), "zoo_tcn_conv_forward")
+        mma = mma_path(Cin, Cout, T, K, dilation)
+        if mma:
+            wt = _mma_scratch(x, Cin, Cout, K)
+            _nl.check(_nl.cuda_lib().zoo_tcn_conv_forward_mma(x.data_ptr(), w.data_ptr(), wt.data_ptr(), _nl.ptr(bias), _nl.ptr(res),
+                                                              out.data_ptr(), B, Cin, Cout, T, K, dilation, int(relu), float(drop_p),
+                                                              int(seed), _nl.stream_ptr()), "zoo_tcn_conv_forward_mma")
+        else:
+            _nl.check(_nl.cuda_lib().zoo_tcn_conv_forward(x.data_ptr(), w.data_ptr(), _nl.ptr(bias), _nl.ptr(res), out.data_ptr(), B,
+                                                          Cin, Cout, T, K, dilation, int(relu), float(drop_p), int(seed),
+                                                          _nl.stream_ptr()), "zoo_tcn_conv_forward")
         ctx.save_for_backward(x, w, res, out)
-        ctx.cfg = (dilation, relu, drop_p, bias is not None)
+        ctx.cfg = (dilation, relu, drop_p, bias is not None, mma)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         x, w, res, out = ctx.saved_tensors
-        dilation, relu, drop_p, has_bias = ctx.cfg
+        dilation, relu, drop_p, has_bias, mma = ctx.cfg
         B, Cin, T = x.shape
         Cout, _, K = w.shape
         lib, st = _nl.cuda_lib(), _nl.stream_ptr()
@@ -63,12 +91,18 @@ class _CausalConvFn(torch.autograd.Function):
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
-            _nl.check(lib.zoo_tcn_conv_dgrad(g.data_ptr(), w.data_ptr(), dx.data_ptr(), B, Cin, Cout, T, K, dilation, st),
-                      "zoo_tcn_conv_dgrad")
+            if mma:
+                wt = _mma_scratch(x, Cin, Cout, K)
+                _nl.check(lib.zoo_tcn_conv_dgrad_mma(g.data_ptr(), w.data_ptr(), wt.data_ptr(), dx.data_ptr(), B, Cin, Cout, T, K, dilation, st),
+                          "zoo_tcn_conv_dgrad_mma")
+            else:
+                _nl.check(lib.zoo_tcn_conv_dgrad(g.data_ptr(), w.data_ptr(), dx.data_ptr(), B, Cin, Cout, T, K, dilation, st),
+                          "zoo_tcn_conv_dgrad")
         dw = None
         if ctx.needs_input_grad[1]:
             dw = torch.zeros_like(w)
-            _nl.check(lib.zoo_tcn_conv_wgrad(g.data_ptr(), x.data_ptr(), dw.data_ptr(), B, Cin, Cout, T, K, dilation, st), "zoo_tcn_conv_wgrad")
+            fn = lib.zoo_tcn_conv_wgrad_mma if mma else lib.zoo_tcn_conv_wgrad
+            _nl.check(fn(g.data_ptr(), x.data_ptr(), dw.data_ptr(), B, Cin, Cout, T, K, dilation, st), "zoo_tcn_conv_wgrad")
         db = g.sum((0, 2)) if (has_bias and ctx.needs_input_grad[2]) else None
         return dx, dw, db, dres, None, None, None, None
 
