@@ -115,3 +115,104 @@ def test_reference_frozen_graph_written_by_tensorflow():
     x = torch.rand(5, w1.shape[0])
     want = torch.sigmoid(torch.relu(x @ torch.from_numpy(w1) + torch.from_numpy(b1)) @ torch.from_numpy(w2) + torch.from_numpy(b2))
     torch.testing.assert_close(net(x), want)
+
+
+_SM = "/root/reference/zoo/src/test/resources/"
+
+
+@pytest.mark.skipif(not os.path.exists(_SM + "saved-model-signature/saved_model.pb"), reason="reference test resources are not on this machine")
+def test_reference_saved_models_written_by_tensorflow():
+    """SavedModel directories written by real TensorFlow (the fixtures of TFNetSpec.scala:138-176 and pyzoo test_tfnet.py:80-85):
+    saved_model.pb is decoded, the variables are read from the TensorBundle (LevelDB-format index + data shard), frozen into the
+    graph and the result matches a numpy restatement built from the same variables."""
+    from zoo.pipeline.api.net import TFNet
+    from zoo.tfpark.saved_model import read_bundle, read_saved_model, read_table
+
+    # -- the signature model: Placeholder [?, 4] -> dense(10); ref variables (VariableV2)
+    path = _SM + "saved-model-signature"
+    meta = read_saved_model(path)[0]
+    assert meta.tags == ["serve"] and meta.signatures == {"serving_default": ({"input": "Placeholder:0"}, {"output": "dense/BiasAdd:0"})}
+    keys = [k for k, _ in read_table(path + "/variables/variables.index")]
+    assert keys == [b"", b"dense/bias", b"dense/kernel"]                      # header entry first, then the variables in key order
+    v = read_bundle(path + "/variables/variables")
+    x = torch.ones(4, 4)
+    want = x.numpy() @ v["dense/kernel"] + v["dense/bias"]
+    for kw in ({}, {"inputs": ["Placeholder:0"]}, {"outputs": ["dense/BiasAdd:0"]}, {"signature": "serving_default", "tag": "serve"}):
+        out = TFNet.from_saved_model(path, **kw)(x)
+        assert out.shape == (4, 10) and np.allclose(out.numpy(), want, atol=1e-6)
+    with pytest.raises(ValueError):
+        TFNet.from_saved_model(path, tag="train")
+
+    # -- the Keras model with resource variables: flatten -> dense/relu -> BN -> dense/relu -> BN -> dense/softmax;
+    #    BatchNorm picks moving statistics through Switch / Merge on the (false) learning phase
+    path = _SM + "saved-model-resource"
+    v = read_bundle(path + "/variables/variables")
+    assert v["dense/kernel"].shape == (784, 64) and v["Adam/iterations"].shape == ()
+    net = TFNet.from_saved_model(path, inputs=["flatten_input:0"], outputs=["dense_2/Softmax:0"])
+    x = np.random.RandomState(0).rand(6, 28, 28, 1).astype(np.float32)
+
+    def bn(h, name):
+        return (h - v[name + "/moving_mean"]) / np.sqrt(v[name + "/moving_variance"] + 1e-3) * v[name + "/gamma"] + v[name + "/beta"]
+
+    h = bn(np.maximum(x.reshape(6, -1) @ v["dense/kernel"] + v["dense/bias"], 0), "batch_normalization_v1")
+    h = bn(np.maximum(h @ v["dense_1/kernel"] + v["dense_1/bias"], 0), "batch_normalization_v1_1")
+    logits = h @ v["dense_2/kernel"] + v["dense_2/bias"]
+    want = np.exp(logits - logits.max(-1, keepdims=True))
+    want /= want.sum(-1, keepdims=True)
+    assert np.allclose(net.predict(x), want, atol=1e-5)
+    assert np.allclose(TFNet.from_saved_model(path)(torch.from_numpy(x)).numpy(), want, atol=1e-5)      # the signature names the same tensors
+
+
+def test_table_reader_handles_prefix_compression_and_snappy():
+    """The LevelDB-format table reader on a hand-built table: shared key prefixes, two data blocks, one of them snappy-compressed."""
+    import struct
+
+    from zoo.tfpark.saved_model import _snappy_uncompress, read_table
+    from zoo.util.protowire import write_varint as vi
+
+    def block(pairs):
+        out, prev = b"", b""
+        for k, val in pairs:
+            shared = 0
+            while shared < min(len(prev), len(k)) and prev[shared] == k[shared]:
+                shared += 1
+            out += vi(shared) + vi(len(k) - shared) + vi(len(val)) + k[shared:] + val
+            prev = k
+        return out + struct.pack("<II", 0, 1)                               # one restart point at offset 0
+
+    def snappy_literal(data):                                               # a valid snappy stream made of one literal
+        assert len(data) < 60
+        return vi(len(data)) + bytes([(len(data) - 1) << 2]) + data
+
+    assert _snappy_uncompress(vi(8) + bytes([(4 - 1) << 2]) + b"abcd" + bytes([(0 << 5) | ((4 - 4) << 2) | 1, 4])) == b"abcdabcd"   # literal + copy
+    b1 = block([(b"layer/bias", b"B"), (b"layer/kernel", b"K")])
+    b2 = block([(b"other", b"O")])
+    file = b1 + b"\x00" + b"\x00" * 4
+    off2 = len(file)
+    c2 = snappy_literal(b2)
+    file += c2 + b"\x01" + b"\x00" * 4
+    index = block([(b"layer/kernel", vi(0) + vi(len(b1))), (b"other", vi(off2) + vi(len(c2)))])
+    ioff = len(file)
+    file += index + b"\x00" + b"\x00" * 4
+    footer = vi(0) + vi(0) + vi(ioff) + vi(len(index))
+    file += footer + b"\x00" * (40 - len(footer)) + struct.pack("<Q", 0xDB4775248B80FB57)
+    import tempfile
+
+    with tempfile.NamedTemporaryFile(suffix=".index", delete=False) as f:
+        f.write(file)
+    try:
+        assert read_table(f.name) == [(b"layer/bias", b"B"), (b"layer/kernel", b"K"), (b"other", b"O")]
+    finally:
+        os.unlink(f.name)
+
+
+@pytest.mark.skipif(not os.path.exists(_SM + "saved-model-signature/saved_model.pb"), reason="reference test resources are not on this machine")
+def test_saved_model_through_inference_model_and_net_load():
+    from zoo.pipeline.api.net import Net
+    from zoo.pipeline.inference import InferenceModel
+
+    x = np.ones((3, 4), np.float32)
+    a = InferenceModel().load_tensorflow(_SM + "saved-model-signature", model_type="savedModel").predict(x)
+    b = InferenceModel().load_tf(_SM + "saved-model-signature").predict(x)                       # recognised by its saved_model.pb
+    c = Net.load_tf(_SM + "saved-model-signature")(torch.from_numpy(x)).detach().numpy()
+    assert np.asarray(a).shape == (3, 10) and np.allclose(a, b) and np.allclose(a, c, atol=1e-6)

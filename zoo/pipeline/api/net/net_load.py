@@ -134,8 +134,12 @@ class Net:
     def load_tf(path, inputs=None, outputs=None, byte_order="little_endian", bin_file=None, bigdl_type="float"):
         """A frozen GraphDef (`.pb` + input / output names) or an export folder (frozen_inference_graph.pb + graph_meta.json) ->
         GraphNet over the imported torch graph (zoo.tfpark.graphdef; Net.scala loadTF)."""
+        import os
+
         from .tfnet import TFNet
 
+        if os.path.isdir(path) and os.path.exists(os.path.join(path, "saved_model.pb")):      # a SavedModel directory
+            return GraphNet(TFNet.from_saved_model(path, inputs=inputs, outputs=outputs))
         return GraphNet(TFNet(path, inputs, outputs))
 
 

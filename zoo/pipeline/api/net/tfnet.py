@@ -44,11 +44,21 @@ class TFNet(nn.Module):
 
     @staticmethod
     def from_saved_model(model_path, tag=None, signature=None, inputs=None, outputs=None, tf_session_config=None, init_op=None):
-        pb = os.path.join(model_path, "frozen_inference_graph.pb")
-        if os.path.exists(pb):
+        """A SavedModel directory (`saved_model.pb` + `variables/`): the meta graph tagged `tag` ("serve"), variables restored from
+        the bundle and frozen into the graph, run between `inputs` / `outputs` or the tensors of `signature` ("serving_default").
+        Reference: TFNet.fromSavedModel, TFNet.scala:612-716.  A folder written by `export_tf` is accepted too."""
+        if os.path.exists(os.path.join(model_path, "frozen_inference_graph.pb")) and not os.path.exists(os.path.join(model_path, "saved_model.pb")):
             return TFNet(model_path, inputs, outputs)
-        raise NotImplementedError("TFNet.from_saved_model needs variables frozen into the graph: freeze the SavedModel "
-                                  "(constants instead of variables) and load the .pb with TFNet.from_frozen_graph")
+        from ....tfpark.graphdef import GraphDefModule
+        from ....tfpark.saved_model import load_saved_model
+
+        nodes, ins, outs = load_saved_model(model_path, tag, signature, inputs, outputs)
+        net = TFNet.__new__(TFNet)
+        nn.Module.__init__(net)
+        net.path = model_path
+        net.graph = GraphDefModule(nodes, ins, outs)
+        net.input_names, net.output_names = net.graph.input_names, net.graph.output_names
+        return net
 
     @staticmethod
     def from_session(sess, inputs, outputs, generate_backward=False, allow_non_differentiable_input=True):

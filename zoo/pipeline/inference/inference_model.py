@@ -106,19 +106,24 @@ class InferenceModel:
         return self._install(load_caffe(model_path, weight_path))
 
     def load_tensorflow(self, model_path, model_type="frozenModel", intra_op_parallelism_threads=1, inter_op_parallelism_threads=1,
-                        use_per_session_threads=True, inputs=None, outputs=None):
-        """A frozen GraphDef (`.pb` + input / output names) or an export folder with graph_meta.json, imported into torch
-        (zoo.tfpark.graphdef; reference: doLoadTF / doLoadTensorflow, frozen models)."""
+                        use_per_session_threads=True, inputs=None, outputs=None, tag=None, signature=None):
+        """`model_type` "frozenModel": a frozen GraphDef (`.pb` + input / output names) or an export folder with graph_meta.json;
+        "savedModel": a SavedModel directory (saved_model.pb + variables/), variables read from the bundle and frozen
+        (zoo.tfpark.saved_model).  Both are imported into torch (zoo.tfpark.graphdef; reference: doLoadTF / doLoadTensorflow)."""
+        import os
+
         from ..api.net.tfnet import TFNet
 
-        if model_type not in ("frozenModel", "frozen_model", None):
-            raise NotImplementedError(f"load_tensorflow(model_type={model_type!r}): only frozen graphs can be imported without a TensorFlow "
-                                      "runtime; freeze the SavedModel first")
+        kind = (model_type or "frozenModel").replace("_", "").lower()
+        if kind == "savedmodel" or (os.path.isdir(model_path) and os.path.exists(os.path.join(model_path, "saved_model.pb"))):
+            return self._install(TFNet.from_saved_model(model_path, tag=tag, signature=signature, inputs=inputs, outputs=outputs))
+        if kind != "frozenmodel":
+            raise ValueError(f"load_tensorflow: model_type {model_type!r} (expected 'frozenModel' or 'savedModel')")
         return self._install(TFNet(model_path, inputs, outputs))
 
     def load_tf(self, model_path, backend="tensorflow", intra_op_parallelism_threads=1, inter_op_parallelism_threads=1,
-                use_per_session_threads=True, inputs=None, outputs=None):
-        return self.load_tensorflow(model_path, "frozenModel", inputs=inputs, outputs=outputs)
+                use_per_session_threads=True, inputs=None, outputs=None, model_type=None, tag=None, signature=None):
+        return self.load_tensorflow(model_path, model_type or "frozenModel", inputs=inputs, outputs=outputs, tag=tag, signature=signature)
 
     def load_openvino(self, model_path, weight_path, batch_size=0):
         """OpenVINO IR (`.xml` + `.bin`) is the reference's low-precision CPU engine.  Its job -- 8-bit inference -- is done here by

@@ -261,6 +261,26 @@ _OPS = {
 }
 
 
+class _Dead:
+    """Value of a tensor on the branch a `Switch` did not take (TensorFlow's dead tensors): every op fed by it is skipped, `Merge`
+    forwards its live input.  Keras graphs pick the training or the inference form of BatchNorm / Dropout this way."""
+
+    def __repr__(self):
+        return "<dead tensor>"
+
+
+_DEAD = _Dead()
+
+
+def _switch(n, x, pred):
+    take = bool(pred.reshape(-1)[0]) if torch.is_tensor(pred) else bool(pred)
+    return (_DEAD, x) if take else (x, _DEAD)          # output 0 = false branch, output 1 = true branch
+
+
+_OPS["Switch"] = _switch
+_OPS["RefSwitch"] = _switch
+
+
 class GraphDefModule(nn.Module):
     """A frozen GraphDef as a torch module: `forward(*inputs)` feeds `input_names` (placeholders) and returns `output_names`."""
 
@@ -270,14 +290,6 @@ class GraphDefModule(nn.Module):
         consumed = {i.split(":")[0].lstrip("^") for n in nodes for i in n.inputs}
         self.input_names = [self._strip(n) for n in (input_names or [n.name for n in nodes if n.op == "Placeholder"])]
         self.output_names = list(output_names or [n.name for n in nodes if n.name not in consumed and n.op not in ("NoOp", "Const", "Placeholder")])
-        self._const = {}
-        for k, n in enumerate(nodes):
-            if n.op == "Const":
-                arr = n.a("value")
-                t = torch.from_numpy(np.ascontiguousarray(arr)) if arr.dtype != np.float64 else torch.from_numpy(arr.astype(np.float32))
-                key = f"c{k}"
-                self.register_buffer(key, t, persistent=True)
-                self._const[n.name] = key
         for name in self.output_names:
             if self._strip(name) not in self.nodes:
                 raise KeyError(f"output {name!r} is not a node of the graph")
@@ -298,6 +310,16 @@ class GraphDefModule(nn.Module):
                 dep = self._strip(i.lstrip("^"))
                 if dep not in seen and not i.startswith("^"):
                     stack.append((dep, False))
+
+        # constants the outputs depend on become buffers (a training graph also carries string constants of its saver, unused here)
+        self._const, needed = {}, set(self.order)
+        for k, n in enumerate(nodes):
+            if n.op == "Const" and n.name in needed:
+                arr = n.a("value")
+                t = torch.from_numpy(arr.copy(order="C")) if arr.dtype != np.float64 else torch.from_numpy(arr.astype(np.float32))   # (ascontiguousarray would turn a scalar into shape [1])
+                key = f"c{k}"
+                self.register_buffer(key, t, persistent=True)
+                self._const[n.name] = key
 
     @staticmethod
     def _strip(name):
@@ -323,12 +345,21 @@ class GraphDefModule(nn.Module):
                 continue
             if node.op == "Placeholder":
                 raise ValueError(f"placeholder {name!r} was not fed (inputs: {self.input_names})")
+            args = [get(i) for i in node.inputs if not i.startswith("^")]
+            if node.op in ("Merge", "RefMerge"):
+                live = [(k, a) for k, a in enumerate(args) if a is not _DEAD]
+                vals[name] = (live[0][1], torch.tensor(live[0][0], dtype=torch.int32)) if live else (_DEAD, _DEAD)
+                continue
+            if any(a is _DEAD for a in args):
+                vals[name] = (_DEAD, _DEAD) if node.op in ("Switch", "RefSwitch") else _DEAD
+                continue
             fn = _OPS.get(node.op)
             if fn is None:
                 raise NotImplementedError(f"TensorFlow op {node.op!r} (node {name!r}) is not supported by the GraphDef importer")
-            args = [get(i) for i in node.inputs if not i.startswith("^")]
             if dev is not None:       # tensors created on the host by shape arithmetic follow the data
                 args = [a.to(dev) if torch.is_tensor(a) and a.device != dev and a.is_floating_point() else a for a in args]
             vals[name] = fn(node, *args)
         outs = [get(o) for o in self.output_names]
+        if any(o is _DEAD for o in outs):
+            raise ValueError("an output sits on a branch the graph's Switch ops did not take")
         return outs[0] if len(outs) == 1 else tuple(outs)
