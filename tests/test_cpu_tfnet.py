@@ -216,3 +216,59 @@ def test_saved_model_through_inference_model_and_net_load():
     b = InferenceModel().load_tf(_SM + "saved-model-signature").predict(x)                       # recognised by its saved_model.pb
     c = Net.load_tf(_SM + "saved-model-signature")(torch.from_numpy(x)).detach().numpy()
     assert np.asarray(a).shape == (3, 10) and np.allclose(a, b) and np.allclose(a, c, atol=1e-6)
+
+
+@pytest.mark.skipif(not os.path.exists(_SM + "tfnet_training/graph_meta.json"), reason="reference test resources are not on this machine")
+def test_reference_training_export_is_trainable_and_its_gradient_nodes_agree_with_autograd():
+    """tfnet_training is an `export_tf(generate_backward=True)` folder written by TensorFlow (TFNetSpec.scala:126-136): forward
+    graph + explicit gradient nodes + the list of variables.  The variables become parameters of the imported module; torch autograd
+    through the imported forward ops must equal what the graph's own SigmoidGrad / ReluGrad / BiasAddGrad / MatMul nodes compute."""
+    import json
+
+    from zoo.pipeline.api.net import TFNet
+    from zoo.tfpark.graphdef import GraphDefModule, read_graphdef
+
+    folder = _SM + "tfnet_training"
+    meta = json.load(open(folder + "/graph_meta.json"))
+    net = TFNet.from_export_folder(folder)
+    params = dict(net.named_parameters())
+    assert len(params) == 4 and sorted(tuple(p.shape) for p in params.values()) == [(2,), (4, 10), (10,), (10, 2)]
+    torch.manual_seed(0)
+    x, gy = torch.rand(2, 4, requires_grad=True), torch.rand(2, 2)
+    out = net(x)
+    out.backward(gy)
+    nodes = read_graphdef(folder + "/frozen_inference_graph.pb")
+    grads = GraphDefModule(nodes, ["Placeholder:0", "dense_1/Sigmoid_grad:0"], meta["grad_inputs"] + meta["grad_variables"])
+    with torch.no_grad():
+        gx, *gvars = grads(x.detach(), gy)
+    assert torch.allclose(x.grad, gx, atol=1e-6)
+    by_name = {net.graph.nodes[n].name: getattr(net.graph, k) for n, k in net.graph._const.items()}
+    for var, g in zip(meta["variables"], gvars):
+        assert torch.allclose(by_name[var.split(":")[0]].grad, g, atol=1e-6), var
+    # and it trains: a few SGD steps on the parameters lower a loss
+    opt = torch.optim.SGD(net.parameters(), lr=0.5)
+    tgt = torch.tensor([[1.0, 0.0], [0.0, 1.0]])
+    first = None
+    for _ in range(50):
+        opt.zero_grad()
+        loss = ((net(x.detach()) - tgt) ** 2).mean()
+        loss.backward()
+        opt.step()
+        first = first if first is not None else float(loss.detach())
+    assert float(loss.detach()) < first * 0.7
+
+
+@pytest.mark.skipif(not os.path.exists(_SM + "tf/multi_type_inputs_outputs.pb"), reason="reference test resources are not on this machine")
+def test_reference_multi_type_and_string_graphs():
+    """tf/multi_type_inputs_outputs.pb (five placeholders of different dtypes, TFNetSpec.scala:100-124) and tfnet_string (a string
+    placeholder through StringToNumber)."""
+    from zoo.pipeline.api.net import TFNet
+
+    names = ["float", "double", "int", "long", "uint8"]
+    net = TFNet.from_frozen_graph(_SM + "tf/multi_type_inputs_outputs.pb", [f"{n}_input:0" for n in names], [f"{n}_output:0" for n in names])
+    ins = [torch.ones(3, 1, dtype=t) * 2 for t in (torch.float32, torch.float64, torch.int32, torch.int64, torch.uint8)]
+    outs = net(*ins)
+    assert [o.dtype for o in outs] == [i.dtype for i in ins] and all(torch.equal(o, i) for o, i in zip(outs, ins))
+    snet = TFNet.from_export_folder(_SM + "tfnet_string")
+    got = snet(["1.5", b"2", "3e2"])
+    assert got.dtype == torch.float32 and got.tolist() == [1.5, 2.0, 300.0]

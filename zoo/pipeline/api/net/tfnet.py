@@ -22,13 +22,15 @@ class TFNet(nn.Module):
         super().__init__()
         from ....tfpark.graphdef import GraphDefModule, read_graphdef
 
+        trainable = None
         if os.path.isdir(path):
             meta = json.load(open(os.path.join(path, "graph_meta.json")))
             input_names = input_names or meta["input_names"]
             output_names = output_names or meta["output_names"]
+            trainable = meta.get("variables")        # a training export (export_tf(generate_backward=True)): its variables are trainable here too
             path = os.path.join(path, "frozen_inference_graph.pb")
         self.path = path
-        self.graph = GraphDefModule(read_graphdef(path), input_names, output_names)
+        self.graph = GraphDefModule(read_graphdef(path), input_names, output_names, trainable=trainable)
         self.input_names, self.output_names = self.graph.input_names, self.graph.output_names
 
     @staticmethod

@@ -281,10 +281,32 @@ _OPS["Switch"] = _switch
 _OPS["RefSwitch"] = _switch
 
 
+def _string_to_number(n, x):
+    """Strings cannot live in a torch tensor: a string input is a list / object array of str or bytes."""
+    flat = np.asarray(x, dtype=object).reshape(-1)
+    vals = [float(v.decode() if isinstance(v, (bytes, bytearray)) else v) for v in flat]
+    return torch.tensor(vals, dtype=_T[n.a("out_type", 1)]).reshape(np.asarray(x, dtype=object).shape)
+
+
+# the gradient ops `export_tf(generate_backward=True)` leaves in a graph (reference: TFNet backward through exported gradients,
+# TFNet.scala:300-380); torch autograd differentiates the imported forward ops anyway, these let the exported nodes be evaluated
+_OPS.update({
+    "StringToNumber": _string_to_number,
+    "BiasAddGrad": lambda n, g: g.sum(tuple(range(g.dim() - 1))) if _nhwc(n) else g.sum(tuple(d for d in range(g.dim()) if d != 1)),
+    "ReluGrad": lambda n, g, features: g * (features > 0).to(g.dtype),
+    "Relu6Grad": lambda n, g, features: g * ((features > 0) & (features < 6)).to(g.dtype),
+    "SigmoidGrad": lambda n, y, dy: dy * y * (1 - y),
+    "TanhGrad": lambda n, y, dy: dy * (1 - y * y),
+    "SoftplusGrad": lambda n, g, features: g * torch.sigmoid(features),
+})
+
+
 class GraphDefModule(nn.Module):
     """A frozen GraphDef as a torch module: `forward(*inputs)` feeds `input_names` (placeholders) and returns `output_names`."""
 
-    def __init__(self, nodes, input_names=None, output_names=None):
+    def __init__(self, nodes, input_names=None, output_names=None, trainable=None):
+        """`trainable`: names of constants (frozen variables, e.g. "dense/kernel:0") that become `nn.Parameter`s instead of buffers,
+        so the imported graph can be fine-tuned -- the reference trains a TFNet through the gradients its export wrote out."""
         super().__init__()
         self.nodes = {n.name: n for n in nodes}
         consumed = {i.split(":")[0].lstrip("^") for n in nodes for i in n.inputs}
@@ -312,13 +334,16 @@ class GraphDefModule(nn.Module):
                     stack.append((dep, False))
 
         # constants the outputs depend on become buffers (a training graph also carries string constants of its saver, unused here)
-        self._const, needed = {}, set(self.order)
+        self._const, needed, train = {}, set(self.order), {self._strip(v) for v in (trainable or [])}
         for k, n in enumerate(nodes):
             if n.op == "Const" and n.name in needed:
                 arr = n.a("value")
                 t = torch.from_numpy(arr.copy(order="C")) if arr.dtype != np.float64 else torch.from_numpy(arr.astype(np.float32))   # (ascontiguousarray would turn a scalar into shape [1])
                 key = f"c{k}"
-                self.register_buffer(key, t, persistent=True)
+                if n.name in train and t.is_floating_point():
+                    self.register_parameter(key, nn.Parameter(t))
+                else:
+                    self.register_buffer(key, t, persistent=True)
                 self._const[n.name] = key
 
     @staticmethod
@@ -326,12 +351,13 @@ class GraphDefModule(nn.Module):
         return name.split(":")[0]
 
     def forward(self, *xs):
-        if len(xs) == 1 and isinstance(xs[0], (tuple, list)):
-            xs = tuple(xs[0])
+        if len(xs) == 1 and isinstance(xs[0], (tuple, list)) and not (len(self.input_names) == 1 and xs[0] and isinstance(xs[0][0], (str, bytes))):
+            xs = tuple(xs[0])              # (a list of strings is ONE string input)
         if len(xs) != len(self.input_names):
             raise ValueError(f"expected {len(self.input_names)} inputs ({self.input_names}), got {len(xs)}")
         dev = xs[0].device if xs and torch.is_tensor(xs[0]) else None
-        vals = {n: (x if torch.is_tensor(x) else torch.as_tensor(np.asarray(x))) for n, x in zip(self.input_names, xs)}
+        as_t = lambda x: x if torch.is_tensor(x) else (x if np.asarray(x).dtype.kind in "OSU" else torch.as_tensor(np.asarray(x)))   # strings stay lists
+        vals = {n: as_t(x) for n, x in zip(self.input_names, xs)}
 
         def get(ref):
             name, _, port = ref.partition(":")
