@@ -91,3 +91,41 @@ def test_reference_saved_models_load_and_run():
     # the two Keras-style models of NetSpec "net load model": forward on Tensor(2, 3, 5)
     assert load_bigdl(REF + "/zoo_keras/small_seq.model")(torch.rand(2, 3, 5)).numel() == 30
     assert load_bigdl(REF + "/zoo_keras/small_model.model")(torch.rand(2, 3, 5)).shape == (2, 3, 7)
+
+
+def test_separate_weight_file_and_reference_nnmodel_directory(tmp_path):
+    """`saveModule(path, weightPath)`: definition and weights apart (weight file: big-endian records keyed by storage id + MD5),
+    and the NNModel directory the reference's NNEstimatorSpec.scala:467-485 loads (models/nnframes_keras: metadata JSON + module +
+    weight + a Java-serialized samplePreprocessing)."""
+    import pandas as pd
+
+    from zoo.models.bigdl import load_bigdl, save_bigdl
+    from zoo.models.bigdl.bigdl_loader import read_weight_file
+    from zoo.pipeline.api.net import Net
+    from zoo.pipeline.nnframes import NNModel
+
+    torch.manual_seed(0)
+    net = nn.Sequential(nn.Linear(6, 5), nn.ReLU(), nn.Linear(5, 2)).eval()
+    d, w = str(tmp_path / "m.bigdl"), str(tmp_path / "m.weight")
+    save_bigdl(net, d, w)
+    assert len(open(d, "rb").read()) < len(save_bigdl(net)) - 4 * 40              # the definition carries no tensor data
+    ws = read_weight_file(w)
+    assert sorted(v.size for v in ws.values()) == [2, 5, 10, 30]
+    x = torch.randn(3, 6)
+    assert torch.allclose(load_bigdl(d, w)(x), net(x), atol=1e-6)
+    assert torch.allclose(Net.load_bigdl(d, w)(x), net(x), atol=1e-6)
+    with pytest.raises(Exception):
+        load_bigdl(d)                                                              # storages missing without the weight file
+
+    ref = "/root/reference/zoo/src/test/resources/models/nnframes_keras"
+    if not os.path.exists(ref):
+        pytest.skip("reference test resources are not on this machine")
+    ws = read_weight_file(ref + "/weight")
+    assert sorted(v.size for v in ws.values()) == [2, 12]
+    m = NNModel.load(ref)
+    assert m.getBatchSize() == 10 and m.getFeaturesCol() == "features" and m.getPredictionCol() == "prediction"
+    kernel = next(v for v in ws.values() if v.size == 12).reshape(2, 6)           # Dense(2) on Input(6): BigDL Linear weight [out, in]
+    df = pd.DataFrame({"features": [list(map(float, range(6))), [1.0] * 6]})
+    out = m.setBatchSize(8).transform(df)
+    want = np.asarray(df["features"].tolist(), np.float32) @ kernel.T
+    assert np.allclose(np.asarray(out["prediction"].tolist(), np.float32), want, atol=1e-5)

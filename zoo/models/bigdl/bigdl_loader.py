@@ -209,13 +209,21 @@ class _Ctx:
         v = _attr_value(self._a[key], self.storages)
         return default if v is None else v
 
+    # BigDL 0.5 / 0.6 files carry `weight` and `bias`; later versions write the layer's parameters() list instead
+    # (`hasParameters` + `parameters`: weight first, bias second)
     @property
     def weight(self):
-        return _tensor(pw.one(self.mod, "weight"), self.storages)
+        t = pw.one(self.mod, "weight")
+        if t is None and self.mod.get("parameters"):
+            t = self.mod["parameters"][0]
+        return _tensor(t, self.storages)
 
     @property
     def bias(self):
-        return _tensor(pw.one(self.mod, "bias"), self.storages)
+        t = pw.one(self.mod, "bias")
+        if t is None and pw.one(self.mod, "weight") is None and len(self.mod.get("parameters", [])) > 1:
+            t = self.mod["parameters"][1]
+        return _tensor(t, self.storages)
 
     @property
     def parameters(self):
@@ -501,8 +509,36 @@ def _time_distributed(ctx):
 
 
 # ------------------------------------------------------------------------------------------------------------------ loader --
+WEIGHT_MAGIC = 3721
+
+
+def read_weight_file(path_or_bytes):
+    """The separate weight file of `saveModule(path, weightPath)` -> {storage id: flat float array}.
+
+    Layout (big-endian, written through a Java DataOutputStream): int magic 3721, int n, then n records of (int storage id, long
+    element count, that many floats), then an int length and an MD5 digest of the payload."""
+    import struct
+
+    buf = path_or_bytes
+    if not isinstance(buf, (bytes, bytearray, memoryview)):
+        from ...util import filesystem as zfs
+
+        with zfs.open_file(path_or_bytes, "rb") as fh:
+            buf = fh.read()
+    magic, n = struct.unpack_from(">ii", buf, 0)
+    if magic != WEIGHT_MAGIC:
+        raise BigDLConversionException(f"not a BigDL weight file (magic {magic}, expected {WEIGHT_MAGIC})")
+    out, pos = {}, 8
+    for _ in range(n):
+        sid, count = struct.unpack_from(">iq", buf, pos)
+        pos += 12
+        out[sid] = np.frombuffer(buf, dtype=">f4", count=count, offset=pos).astype(np.float32)
+        pos += 4 * count
+    return out
+
+
 class BigDLLoader:
-    def __init__(self, path_or_bytes):
+    def __init__(self, path_or_bytes, weight_path=None):
         if isinstance(path_or_bytes, (bytes, bytearray, memoryview)):
             buf = bytes(path_or_bytes)
         else:
@@ -514,6 +550,8 @@ class BigDLLoader:
         if "moduleType" not in self.root:
             raise BigDLConversionException("not a BigDL model file (no moduleType in the root message)")
         self.storages = _collect_storages(self.root)
+        if weight_path is not None:                   # definition and weights saved apart: storages are looked up by id in the weight file
+            self.storages.update(read_weight_file(weight_path))
 
     def convert(self, mod):
         mtype = pw.one(mod, "moduleType", "")
@@ -537,6 +575,7 @@ class BigDLLoader:
         return net.train(bool(pw.one(self.root, "train", False)))
 
 
-def load_bigdl(path_or_bytes):
-    """BigDL / zoo model file -> torch module (eval mode unless the file says it was saved in training mode)."""
-    return BigDLLoader(path_or_bytes).load()
+def load_bigdl(path_or_bytes, weight_path=None):
+    """BigDL / zoo model file (+ the separate weight file of `saveModule(path, weightPath)`) -> torch module (eval mode unless the
+    file says it was saved in training mode)."""
+    return BigDLLoader(path_or_bytes, weight_path).load()

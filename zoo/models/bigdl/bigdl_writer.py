@@ -122,15 +122,35 @@ class _Writer:
         raise NotImplementedError(f"save_bigdl: no BigDL counterpart registered for {type(mod).__name__}")
 
 
-def save_bigdl(model: nn.Module, path=None):
-    """Serialize `model` in BigDL's module format; returns the bytes (and writes them to `path` when given)."""
+def save_bigdl(model: nn.Module, path=None, weight_path=None):
+    """Serialize `model` in BigDL's module format; returns the bytes (and writes them to `path` when given).  With `weight_path`
+    the definition file carries no tensor data and the weights go to that file in BigDL's separate weight-file layout
+    (`saveModule(path, weightPath)`; see `bigdl_loader.read_weight_file`)."""
+    import hashlib
+    import struct
+
+    from ...util import filesystem as zfs
+
     w = _Writer()
     root = w.convert(model.eval() if not isinstance(model, nn.Sequential) else model)
-    root["attr"] = list(root["attr"]) + [{"key": "global_storage", "value": {"nameAttrListValue": {"name": "global_storage", "attr": w.storage_entries}}}]
+    entries = w.storage_entries
+    if weight_path is not None:
+        payload, kept = b"", []
+        for e in entries:
+            tv = e["value"]["tensorValue"]
+            st = tv["storage"]
+            data = np.asarray(st.get("float_data", []), dtype=">f4")
+            payload += struct.pack(">iq", int(st["id"]), data.size) + data.tobytes()
+            kept.append({"key": e["key"], "value": {"dataType": e["value"].get("dataType", S.DT_TENSOR),
+                                                     "tensorValue": dict(tv, storage={"datatype": st.get("datatype", S.DT_FLOAT), "id": st["id"]})}})
+        blob = struct.pack(">ii", 3721, len(entries)) + payload
+        blob += struct.pack(">i", 16) + hashlib.md5(blob).digest()
+        with zfs.open_file(weight_path, "wb") as fh:
+            fh.write(blob)
+        entries = kept
+    root["attr"] = list(root["attr"]) + [{"key": "global_storage", "value": {"nameAttrListValue": {"name": "global_storage", "attr": entries}}}]
     buf = pw.encode(root, S.MODULE)
     if path is not None:
-        from ...util import filesystem as zfs
-
         with zfs.open_file(path, "wb") as fh:
             fh.write(buf)
     return buf

@@ -44,15 +44,16 @@ class Net:
         if head not in (b"PK", b"\x80\x02", b"\x80\x03", b"\x80\x04", b"\x80\x05"):
             from ....models.bigdl import load_bigdl as _load
 
-            return GraphNet(_load(model_path))
+            return GraphNet(_load(model_path, weight_path))
         return Net.load(model_path, weight_path)
 
     @staticmethod
-    def save_bigdl(model, path):
-        """Write a feed-forward torch model in BigDL's module format (loadable by BigDL / Analytics Zoo and by `load_bigdl`)."""
+    def save_bigdl(model, path, weight_path=None):
+        """Write a feed-forward torch model in BigDL's module format (loadable by BigDL / Analytics Zoo and by `load_bigdl`);
+        with `weight_path` the weights go to BigDL's separate weight file (`saveModule(path, weightPath)`)."""
         from ....models.bigdl import save_bigdl as _save
 
-        _save(getattr(model, "model", model) if not isinstance(model, torch.nn.Module) else model, path)
+        _save(getattr(model, "model", model) if not isinstance(model, torch.nn.Module) else model, path, weight_path)
         return path
 
     @staticmethod

@@ -162,16 +162,33 @@ class NNModel(_Params):
 
     @classmethod
     def load(cls, path):
+        """A directory written by `save` here, or by the reference's NNModel writer (NNEstimator.scala:805-918: `metadata/part-00000`
+        JSON, `module` + `weight` in BigDL's format, `samplePreprocessing` Java-serialized -- the latter cannot be decoded outside
+        a JVM, so such a model gets the default array-to-tensor preprocessing)."""
         with open(os.path.join(path, "metadata", "part-00000")) as f:
             meta = json.loads(f.readline())
-        if meta["modelType"] == "TorchNet":
+        module_file = os.path.join(path, "module")
+        with open(module_file, "rb") as f:
+            head = f.read(2) if os.path.exists(module_file) else b""
+        prep = None
+        if meta.get("modelType") == "TorchNet":
             from ..api.net.torch_net import TorchNet
 
             model = TorchNet(os.path.join(path, "torchscript.pt"))
-        else:
-            model = torch.load(os.path.join(path, "module"), map_location="cpu", weights_only=False)
-        with open(os.path.join(path, "samplePreprocessing"), "rb") as f:
-            prep = pickle.load(f)
+        elif head in (b"PK", b"\x80\x02", b"\x80\x03", b"\x80\x04", b"\x80\x05"):
+            model = torch.load(module_file, map_location="cpu", weights_only=False)
+        else:                                                      # the reference's own persistence
+            from ...models.bigdl import load_bigdl
+
+            weight_file = os.path.join(path, "weight")
+            model = load_bigdl(module_file, weight_file if os.path.exists(weight_file) else None)
+        try:
+            with open(os.path.join(path, "samplePreprocessing"), "rb") as f:
+                if f.read(2) != b"\xac\xed":                      # 0xACED: a Java object stream
+                    f.seek(0)
+                    prep = pickle.load(f)
+        except (OSError, pickle.UnpicklingError, EOFError):
+            prep = None
         klass = NNClassifierModel if meta["class"].endswith("NNClassifierModel") else NNModel
         m = klass(model, prep)
         pm = meta["paramMap"]
