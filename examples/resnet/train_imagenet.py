@@ -4,8 +4,10 @@ SGD momentum 0.9, weight decay 1e-4 (not on BN / bias), label smoothing-free cro
 batch 8192, Top1 / Top5 / loss validation every epoch, checkpoints under `--cache`).
 
 The same recipe on this framework's engine: bf16 autocast + channels_last through cuDNN, data-parallel over the visible GPUs
-when launched with `python -m torch.distributed.run`.  Images are generated (no ImageNet in the build environment); `--depth`
-chooses the torchvision ResNet."""
+when launched with `python -m torch.distributed.run`.  With `-f / --folder` the data are the reference's ImageNet SequenceFiles
+(`<folder>/train`, `<folder>/val`, read with `ImageSet.read_sequence_files`, random crop + flip for training, centre crop for
+validation, channel normalisation: examples/resnet/Utils.scala:118-140); without it images are generated (no ImageNet in the
+build environment).  `--depth` chooses the torchvision ResNet."""
 import argparse
 import os
 import sys
@@ -34,6 +36,7 @@ ap.add_argument("--depth", type=int, default=18, choices=[18, 34, 50, 101, 152])
 ap.add_argument("--classes", type=int, default=4)
 ap.add_argument("--images", type=int, default=int(os.environ.get("IMAGES", 512)))
 ap.add_argument("--size", type=int, default=64)
+ap.add_argument("-f", "--folder", default=None, help="folder with train/ and val/ SequenceFiles (labels 1..classes)")
 a = ap.parse_args()
 
 rng = np.random.RandomState(0)
@@ -49,8 +52,22 @@ def make(n):
     return x, y.astype(np.int64)
 
 
-xtr, ytr = make(a.images)
-xva, yva = make(a.images // 4)
+def from_sequence_files(folder, train):
+    from zoo.feature.common import ChainedPreprocessing
+    from zoo.feature.image import ImageCenterCrop, ImageChannelNormalize, ImageHFlip, ImageMatToTensor, ImageRandomCrop, ImageRandomPreprocessing, ImageSet
+
+    crop = [ImageRandomCrop(a.size, a.size), ImageRandomPreprocessing(ImageHFlip(), 0.5)] if train else [ImageCenterCrop(a.size, a.size)]
+    chain = ChainedPreprocessing(crop + [ImageChannelNormalize(104.0, 117.0, 123.0, 57.375, 57.12, 58.395), ImageMatToTensor()])
+    feats = ImageSet.read_sequence_files(folder, class_num=a.classes).transform(chain).get_image_features()
+    return np.stack([f.get_tensor() for f in feats]).astype(np.float32), np.asarray([int(f["label"][0]) - 1 for f in feats], np.int64)
+
+
+if a.folder:
+    xtr, ytr = from_sequence_files(os.path.join(a.folder, "train"), True)
+    xva, yva = from_sequence_files(os.path.join(a.folder, "val"), False)
+else:
+    xtr, ytr = make(a.images)
+    xva, yva = make(a.images // 4)
 torch.manual_seed(0)
 net = getattr(torchvision.models, f"resnet{a.depth}")(num_classes=a.classes)
 for m in net.modules():                                      # the reference's init: last BN gamma of every residual branch = 0

@@ -88,6 +88,21 @@ class ImageSet:
         return cls(feats, label_map)
 
     @classmethod
+    def read_sequence_files(cls, path, sc=None, min_partitions=1, class_num=1000):
+        """Images with labels from Hadoop SequenceFiles (a file, or a folder of part files): key "name\\nlabel" / "label", value =
+        width, height, raw BGR pixels.  Reference: ImageSet.readSequenceFiles, ImageSet.scala:333-352 (records whose label exceeds
+        `class_num` are dropped; the features carry the decoded `mat`, `label` [1] and `originalSize`)."""
+        from .seqfile import read_image_records
+
+        path = path[len("file://"):] if str(path).startswith("file://") else str(path)
+        feats = []
+        for name, label, mat in read_image_records(path, class_num):
+            feats.append(ImageFeature(uri=name, mat=mat.copy(), label=np.array([label], dtype=np.float32), originalSize=mat.shape))
+        return cls(feats)
+
+    readSequenceFiles = read_sequence_files
+
+    @classmethod
     def from_rdds(cls, image_rdd, label_rdd=None, bigdl_type="float"):
         return LocalImageSet(list(image_rdd), None if label_rdd is None else list(label_rdd))
 
