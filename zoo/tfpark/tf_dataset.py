@@ -87,7 +87,7 @@ class TFDataset:
         """TFRecord files of tf.train.Example records (read natively, `zoo.tfpark.tfrecord`).  The reference returns the serialized
         strings for a TF parsing graph; here `features` / `labels` name the Example features that become the dataset's tensors
         (all features except `labels` when `features` is None)."""
-        from .tfrecord import examples_to_arrays, read_examples
+        from .tfrecord import examples_to_arrays, is_numeric_feature, read_examples
 
         if file_path is None and isinstance(sc, str):      # from_tfrecord_file(path, ...) without a SparkContext
             sc, file_path = None, sc
@@ -97,7 +97,8 @@ class TFDataset:
             if not exs:
                 raise ValueError(f"no records in {path}")
             lab = [] if labels is None else ([labels] if isinstance(labels, str) else list(labels))
-            feats = features if features is not None else sorted(k for k in exs[0] if k not in lab)
+            # default feature set: everything that can be a tensor (numbers, encoded images) except the labels
+            feats = features if features is not None else sorted(k for k in exs[0] if k not in lab and (image_decoder is not None or is_numeric_feature(exs[0][k])))
             return examples_to_arrays(exs, feats, labels, image_decoder)
 
         x, y = load(file_path)

@@ -190,9 +190,30 @@ def read_examples(paths, check_crc=True):
             yield decode_example(payload)
 
 
+_IMAGE_MAGIC = (b"\x89PNG", b"\xff\xd8\xff", b"BM")
+
+
+def _auto_decode(b):
+    if isinstance(b, (bytes, bytearray)) and bytes(b[:4]).startswith(_IMAGE_MAGIC):
+        import cv2
+
+        img = cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_UNCHANGED)
+        if img is not None:
+            return img
+    return b
+
+
+def is_numeric_feature(value):
+    """False for bytes features that are not encoded images (they cannot become tensors)."""
+    if isinstance(value, list):
+        return all(not isinstance(_auto_decode(b), (bytes, bytearray)) for b in value)
+    return True
+
+
 def examples_to_arrays(examples, features, labels=None, image_decoder=None):
-    """Stack Example features into ndarrays.  `features` / `labels`: a name or a list of names; bytes features are decoded
-    with `image_decoder` (default: cv2.imdecode -> HWC uint8) unless it is None and the bytes are returned as an object array."""
+    """Stack Example features into ndarrays.  `features` / `labels`: a name or a list of names.  Bytes features: `image_decoder`
+    (a callable bytes -> array) decodes them; with `image_decoder=None` bytes that start with a PNG / JPEG / BMP signature are decoded
+    with cv2 (-> HW or HWC uint8) and other bytes (file names, format tags) stay an object array."""
     names_x = [features] if isinstance(features, str) else list(features)
     names_y = [] if labels is None else ([labels] if isinstance(labels, str) else list(labels))
     cols = {n: [] for n in names_x + names_y}
@@ -200,7 +221,7 @@ def examples_to_arrays(examples, features, labels=None, image_decoder=None):
         for n in cols:
             v = ex[n]
             if isinstance(v, list):                        # bytes feature
-                v = [image_decoder(b) for b in v] if image_decoder is not None else v
+                v = [image_decoder(b) for b in v] if image_decoder is not None else [_auto_decode(b) for b in v]
                 v = v[0] if len(v) == 1 else v
             cols[n].append(v)
 

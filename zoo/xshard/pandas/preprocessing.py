@@ -32,8 +32,20 @@ def _load(files, file_type, kwargs):
 
     from ...util import filesystem as zfs
 
-    reader = {"csv": pd.read_csv, "json": lambda f, **k: pd.read_json(f, **({"orient": "columns", "lines": False} | k)),
-              "parquet": pd.read_parquet}[file_type]
+    def read_json_file(f, **k):
+        """JSON lines, as the reference reads them (`orient="columns", lines=True`); a file that is one JSON document is read as such."""
+        if "lines" in k:
+            return pd.read_json(f, **({"orient": "columns"} | k))
+        data = f.read() if hasattr(f, "read") else open(f, "rb").read()
+        import io
+
+        order = (False, True) if b"\n" not in data.strip() else (True, False)      # a single line is one document, not one record
+        try:
+            return pd.read_json(io.BytesIO(data), **({"orient": "columns", "lines": order[0]} | k))
+        except ValueError:
+            return pd.read_json(io.BytesIO(data), **({"orient": "columns", "lines": order[1]} | k))
+
+    reader = {"csv": pd.read_csv, "json": read_json_file, "parquet": pd.read_parquet}[file_type]
 
     def read_one(f):
         if zfs.is_local(f):
@@ -49,7 +61,8 @@ def _load(files, file_type, kwargs):
 
 def read_file(context, file_path, file_type, **kwargs):
     files = list_files(file_path, file_type)
-    n = getattr(context, "num_workers", None) or getattr(context, "world_size", None) or 1
+    # one DataFrame per worker of the context (the reference spreads the files over its Ray nodes); without a context, one per file
+    n = getattr(context, "num_workers", None) or getattr(context, "world_size", None) or len(files)
     groups = [g for g in _chunks(files, max(1, min(n, len(files)))) if g]
     shards = XShards(groups, context).transform_shard(_load, file_type, kwargs)
     return shards
