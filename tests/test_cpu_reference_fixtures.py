@@ -133,3 +133,27 @@ def test_recommender_parquet_trains_ncf():
     before = ncf.evaluate(x, y, batch_size=128)[0]
     ncf.fit(x, y, batch_size=64, nb_epoch=8)
     assert ncf.evaluate(x, y, batch_size=128)[0] < before
+
+
+def test_roi_sequence_files_from_the_voc_devkit(tmp_path):
+    """RoiImageSeqGenerator -> ROI SequenceFiles -> SSDDataSet chains (RoiByteImageToSeq.scala, SSDDataSet.scala:31-66) over the
+    VOCdevkit excerpt: records carry the encoded image + class / box tensors and read back to the annotations."""
+    from zoo.models.image.objectdetection import PascalVoc, RoiImageSeqGenerator, SSDDataSet, load_roi_seq_files
+    from zoo.models.image.objectdetection.dataset import decode_roi_record, encode_roi_record
+
+    img, roi = decode_roi_record(encode_roi_record(b"\xff\xd8jpegbytes", [[3, 1, 2, 30, 40, 1], [7, 5, 6, 50, 60, 0]]))
+    assert img == b"\xff\xd8jpegbytes" and roi.tolist() == [[3, 1, 2, 30, 40, 1], [7, 5, 6, 50, 60, 0]]
+    assert decode_roi_record(encode_roi_record(b"x")) == (b"x", None)                          # unlabelled record
+    files = RoiImageSeqGenerator.generate(S + "VOCdevkit", str(tmp_path), "voc_2007_testcode", block_size=1, parallel=2)
+    assert len(files) == 2 and all(f.endswith(".seq") for f in files)
+    feats = load_roi_seq_files(str(tmp_path))
+    want = {d["path"]: d["roi"] for d in PascalVoc("2007", "testcode", S + "VOCdevkit").roidb()}
+    assert len(feats) == 2 and all(np.array_equal(want[f["uri"]], f["roi"]) and f["bytes"][:2] == b"\xff\xd8" for f in feats)
+    np.random.seed(0)
+    x, t = next(iter(SSDDataSet.load_ssd_val_set(str(tmp_path), resolution=300, batch_size=2)()))
+    assert x.shape == (2, 3, 300, 300) and t.shape == (15, 7) and float(t[:, 2:6].min()) >= 0 and float(t[:, 2:6].max()) <= 1
+    assert sorted(t[:, 0].tolist()) == [0.0] * 11 + [1.0] * 4
+    x, t = next(iter(SSDDataSet.load_ssd_train_set(str(tmp_path), resolution=300, batch_size=2)()))
+    assert x.shape == (2, 3, 300, 300) and t.shape[1] == 7 and len(t) >= 1                        # the random sampler keeps at least one box
+    unl = RoiImageSeqGenerator.generate(S + "VOCdevkit/VOC2007/JPEGImages", str(tmp_path / "plain"), None, block_size=10)
+    assert len(unl) == 1 and all("roi" not in f for f in load_roi_seq_files(str(tmp_path / "plain")))

@@ -143,3 +143,168 @@ def roi_batch(features, resolution=300, mean_bgr=(104.0, 117.0, 123.0)):
             rows.append(np.concatenate([np.full((len(r), 1), i, np.float32), r[:, :6]], 1))
     target = torch.from_numpy(np.concatenate(rows, 0)) if rows else torch.zeros(0, 7)
     return torch.stack(imgs), target
+
+
+# ---- ROI records in Hadoop SequenceFiles ----------------------------------------------------------------------------------------
+# Reference: RoiByteImageToSeq.scala:36-104 (writer), RoiImageSeqGenerator.scala (command line), Imdb.loadRoiSeqFiles +
+# RoiRecordToFeature (reader), ssd/SSDDataSet.scala:31-66 (the training / validation chains over those files).
+# Record: key = image path; value = int image-bytes length, int class length (4 bytes per box), the ENCODED image file, then the
+# class tensor [2, N] (labels, then difficult flags) and the box tensor [N, 4], big-endian floats.
+
+def encode_roi_record(image_bytes, roi=None):
+    import struct
+
+    roi = None if roi is None else np.asarray(roi, dtype=np.float32).reshape(-1, 6)
+    n = 0 if roi is None else len(roi)
+    out = struct.pack(">ii", len(image_bytes), n * 4) + bytes(image_bytes)
+    if n:
+        out += roi[:, 0].astype(">f4").tobytes() + roi[:, 5].astype(">f4").tobytes() + roi[:, 1:5].astype(">f4").tobytes()
+    return out
+
+
+def decode_roi_record(value):
+    """-> (encoded image bytes, roi [N, 6] = (label, x1, y1, x2, y2, difficult) or None for an unlabelled record)."""
+    import struct
+
+    img_len, class_len = struct.unpack_from(">ii", value, 0)
+    img = bytes(value[8:8 + img_len])
+    n = class_len // 4
+    if n == 0:
+        return img, None
+    pos = 8 + img_len
+    cls = np.frombuffer(value, ">f4", 2 * n, pos).astype(np.float32).reshape(2, n)
+    box = np.frombuffer(value, ">f4", 4 * n, pos + 8 * n).astype(np.float32).reshape(n, 4)
+    return img, np.concatenate([cls[0][:, None], box, cls[1][:, None]], 1)
+
+
+class RoiByteImageToSeq:
+    """roidb entries -> SequenceFiles `<base>_<k>.seq` of `block_size` records each; returns the file names."""
+
+    def __init__(self, block_size, base_file_name):
+        self.block_size, self.base = int(block_size), str(base_file_name)
+
+    def __call__(self, roidb):
+        from ....feature.image.seqfile import write_sequence_file
+
+        files, entries = [], list(roidb)
+        for k in range(0, max(len(entries), 1), self.block_size):
+            chunk = entries[k:k + self.block_size]
+            if not chunk:
+                break
+            recs = []
+            for r in chunk:
+                with open(r["path"], "rb") as fh:
+                    recs.append((str(r["path"]).encode(), encode_roi_record(fh.read(), r.get("roi"))))
+            name = f"{self.base}_{k // self.block_size}.seq"
+            write_sequence_file(name, recs)
+            files.append(name)
+        return files
+
+
+def load_roi_seq_files(folder):
+    """Every record of the `.seq` files under `folder` as an ImageFeature with `bytes`, `uri` and (when labelled) `roi`
+    (Imdb.loadRoiSeqFiles + RoiRecordToFeature(convertLabel = true))."""
+    import glob
+
+    from ....feature.image.imageset import ImageFeature
+    from ....feature.image.seqfile import read_sequence_file
+
+    feats = []
+    for p in sorted(glob.glob(os.path.join(folder, "*.seq"))):
+        for key, value in read_sequence_file(p):
+            img, roi = decode_roi_record(value)
+            f = ImageFeature(uri=key.decode(), bytes=img)
+            if roi is not None:
+                f["roi"], f["roiNormalized"] = roi, False
+            feats.append(f)
+    return feats
+
+
+class RoiImageSeqGenerator:
+    """`python -m zoo.models.image.objectdetection.dataset -f <devkit or image folder> -o <out> [-i voc_2007_trainval] [-b 12800] [-p 1]`"""
+
+    @staticmethod
+    def generate(folder, output, image_set=None, block_size=12800, parallel=1):
+        os.makedirs(output, exist_ok=True)
+        if image_set is None:                               # unlabelled images
+            roidb = [{"uri": f, "path": os.path.join(folder, f)} for f in sorted(os.listdir(folder))
+                     if f.lower().endswith((".jpg", ".jpeg", ".png", ".bmp"))]
+        else:
+            roidb = Imdb.get_imdb(image_set, folder).roidb()
+        parallel = max(1, min(int(parallel), len(roidb) or 1))
+        shares = [roidb[t::parallel] for t in range(parallel)]
+        files = []
+        from concurrent.futures import ThreadPoolExecutor
+
+        with ThreadPoolExecutor(parallel) as pool:
+            for fs in pool.map(lambda ts: RoiByteImageToSeq(block_size, os.path.join(output, f"{len(roidb)}-seq-{ts[0]}"))(ts[1]), enumerate(shares)):
+                files += fs
+        return files
+
+    @staticmethod
+    def main(argv=None):
+        import argparse
+
+        ap = argparse.ArgumentParser(description="Pascal VOC / COCO / image folder -> ROI SequenceFiles")
+        ap.add_argument("-f", "--folder", required=True, help="image folder, or the devkit path for labelled data")
+        ap.add_argument("-o", "--output", required=True)
+        ap.add_argument("-p", "--parallel", type=int, default=1)
+        ap.add_argument("-b", "--blockSize", type=int, default=12800)
+        ap.add_argument("-i", "--imageSet", default=None, help="e.g. voc_2007_test; omit for unlabelled images")
+        a = ap.parse_args(argv)
+        for f in RoiImageSeqGenerator.generate(a.folder, a.output, a.imageSet, a.blockSize, a.parallel):
+            print("Generated file", f)
+
+
+class SSDDataSet:
+    """The reference's SSD input chains over ROI SequenceFiles (ssd/SSDDataSet.scala:31-66); each yields batches
+    (images [B, 3, R, R], target [N, 7]) in the SSDMiniBatch layout."""
+
+    @staticmethod
+    def _batches(feats, chain, batch_size, resolution, shuffle):
+        order = np.random.permutation(len(feats)) if shuffle else np.arange(len(feats))
+        for k in range(0, len(order), batch_size):
+            yield roi_batch([chain(dict(feats[i])) for i in order[k:k + batch_size]], resolution)
+
+    @staticmethod
+    def load_ssd_train_set(folder, sc=None, resolution=300, batch_size=32, par_num=None):
+        from ....feature.image.imagePreprocessing import (ImageBytesToMat, ImageColorJitter, ImageHFlip, ImageRandomPreprocessing, ImageResize)
+        from ....feature.image.roi import ImageRandomSampler, ImageRoiExpand, ImageRoiHFlip, ImageRoiNormalize
+        from ....feature.common import ChainedPreprocessing
+
+        feats = load_roi_seq_files(folder)
+        flip = ChainedPreprocessing([ImageHFlip(), ImageRoiHFlip()])
+        steps = [ImageBytesToMat(), ImageRoiNormalize(), ImageColorJitter(), ImageRandomPreprocessing(ImageRoiExpand(), 0.5), ImageRandomSampler(),
+                 ImageResize(resolution, resolution, -1), ImageRandomPreprocessing(flip, 0.5)]
+
+        def chain(f):
+            from ....feature.image.imageset import ImageFeature
+
+            f = ImageFeature(**f)
+            for s in steps:
+                f = s(f)
+            return f
+
+        return lambda: SSDDataSet._batches(feats, chain, batch_size, resolution, True)
+
+    @staticmethod
+    def load_ssd_val_set(folder, sc=None, resolution=300, batch_size=32, par_num=None):
+        from ....feature.image.imagePreprocessing import ImageBytesToMat, ImageResize
+        from ....feature.image.roi import ImageRoiNormalize
+
+        feats = load_roi_seq_files(folder)
+        steps = [ImageBytesToMat(), ImageRoiNormalize(), ImageResize(resolution, resolution)]
+
+        def chain(f):
+            from ....feature.image.imageset import ImageFeature
+
+            f = ImageFeature(**f)
+            for s in steps:
+                f = s(f)
+            return f
+
+        return lambda: SSDDataSet._batches(feats, chain, batch_size, resolution, False)
+
+
+if __name__ == "__main__":
+    RoiImageSeqGenerator.main()
