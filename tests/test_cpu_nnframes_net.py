@@ -192,3 +192,49 @@ def test_nnimage_reader(tmp_path):
     assert len(df) == 3
     r = df["image"][0]
     assert (r["height"], r["width"], r["nChannels"]) == (8, 6, 3) and r["origin"].startswith("file:") and r["data"].shape == (8, 6, 3)
+
+
+def test_pojo_inference_api(tmp_path):
+    """AbstractInferenceModel / JTensor / InferenceModelFactory / FloatModel (reference: pipeline/inference/*.java,
+    InferenceModelFactory.scala, FloatModel.scala): the three predict forms, reload, weight-sharing copies."""
+    import torch
+    import torch.nn as nn
+
+    from zoo.pipeline.inference import AbstractInferenceModel, FloatModel, InferenceModelFactory, InferenceRuntimeException, JTensor
+
+    torch.manual_seed(0)
+    net = nn.Sequential(nn.Linear(4, 3), nn.ReLU(), nn.Linear(3, 2)).eval()
+    path = str(tmp_path / "model.pt")
+    torch.save(net, path)
+
+    class TextModel(AbstractInferenceModel):                 # "extend AbstractInferenceModel", as the programming guide says
+        pass
+
+    m = TextModel(2)
+    with pytest.raises(InferenceRuntimeException):
+        m.predict([1.0, 2.0, 3.0, 4.0], 1, 4)
+    m.loadPyTorch(path)
+    x = np.arange(8, dtype=np.float32).reshape(2, 4)
+    want = net(torch.from_numpy(x)).detach().numpy()
+    flat = m.predict(x.reshape(-1).tolist(), 2, 4)
+    assert isinstance(flat, list) and np.allclose(flat, want.reshape(-1), atol=1e-5)
+    recs = m.predict([[JTensor.from_ndarray(x[0])], [JTensor.from_ndarray(x[1])]])
+    assert len(recs) == 2 and len(recs[0]) == 1 and list(recs[0][0].shape) == [2] and np.allclose(recs[1][0].to_ndarray(), want[1], atol=1e-5)
+    assert np.allclose(m.predict(x), want, atol=1e-5)
+    with open(path, "rb") as f:
+        m2 = AbstractInferenceModel(True, 3)                  # (autoScalingEnabled, concurrentNum)
+        m2.loadPyTorch(f.read())
+    assert m2.auto_scaling_enabled and m2.concurrent_num == 3 and np.allclose(m2.predict(x), want, atol=1e-5)
+    torch.save(nn.Sequential(nn.Linear(4, 2)).eval(), str(tmp_path / "other.pt"))
+    m.reload(str(tmp_path / "other.pt"))
+    assert np.asarray(m.predict(x)).shape == (2, 2) and not np.allclose(m.predict(x), want, atol=1e-3)
+
+    fm = InferenceModelFactory.load_float_model_for_pytorch(path)
+    assert isinstance(fm, FloatModel) and np.allclose(fm.predict(x).numpy(), want, atol=1e-5)
+    clones = fm.copy(2)
+    assert len(clones) == 2 and clones[0].model is not fm.model and not clones[0].is_original
+    assert next(clones[0].model.parameters()).data_ptr() == next(fm.model.parameters()).data_ptr()          # weights shared
+    out = clones[1].predict([[JTensor.from_ndarray(x[0])], [JTensor.from_ndarray(x[1])]])
+    assert np.allclose(out[0][0].to_ndarray(), want[0], atol=1e-5)
+    fm.release()
+    assert fm.isReleased()
