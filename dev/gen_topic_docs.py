@@ -92,6 +92,42 @@ PAGES = {
 }
 
 
+# what the recurring constructor arguments of the Keras-style layers mean (the reference documents them per layer)
+ARG_DOC = {
+    "input_shape": "shape of one input record without the batch dimension; needed on the first layer of a `Sequential` only",
+    "name": "layer name (defaults to the lower-cased class name plus a counter)", "bigdl_type": "kept for signature compatibility; parameters are fp32 with bf16 shadows on the GPU",
+    "dim_ordering": "`\"th\"` = channels first (the default, the layout the kernels use), `\"tf\"` = channels last", "data_format": "Keras-2 name of `dim_ordering`: `\"channels_first\"` / `\"channels_last\"`",
+    "activation": "name of the activation applied to the output (`relu`, `tanh`, `sigmoid`, `softmax`, `linear`, ...) or None",
+    "inner_activation": "activation of the recurrent gates (default `hard_sigmoid`, which the persistent RNN kernels implement natively)",
+    "W_regularizer": "regularizer of the input weights, e.g. `l2(1e-4)`; its penalty is added to the training loss", "U_regularizer": "regularizer of the recurrent weights",
+    "b_regularizer": "regularizer of the bias", "kernel_regularizer": "Keras-2 name of `W_regularizer`", "bias_regularizer": "Keras-2 name of `b_regularizer`",
+    "border_mode": "`\"valid\"` (no padding) or `\"same\"` (output has the input's spatial size at stride 1)", "padding": "Keras-2 name of `border_mode`",
+    "bias": "whether the layer has a bias term", "use_bias": "Keras-2 name of `bias`", "init": "weight initializer name (`glorot_uniform`, `he_normal`, `uniform`, `zero`, ...)",
+    "kernel_initializer": "Keras-2 name of `init`", "bias_initializer": "initializer of the bias (Keras-2 style layers)",
+    "nb_filter": "number of output channels", "filters": "Keras-2 name of `nb_filter`", "nb_row": "kernel height", "nb_col": "kernel width", "kernel_size": "kernel size (Keras-2 style)",
+    "filter_length": "kernel length of a 1-D convolution", "kernel_dim1": "kernel depth of a 3-D convolution", "kernel_dim2": "kernel height of a 3-D convolution", "kernel_dim3": "kernel width of a 3-D convolution",
+    "subsample": "strides of the convolution", "subsample_length": "stride of a 1-D convolution", "strides": "strides (pooling layers: defaults to `pool_size`)", "stride": "stride of a 1-D pooling layer",
+    "atrous_rate": "dilation of the kernel", "pool_size": "pooling window", "pool_length": "pooling window of a 1-D pooling layer", "output_dim": "size of the output (units / hidden size / embedding width)",
+    "units": "Keras-2 name of `output_dim`", "input_dim": "size of the input (vocabulary size for embeddings)", "input_length": "length of the input sequences",
+    "return_sequences": "return the output of every time step instead of the last one", "go_backwards": "process the sequence in reverse",
+    "p": "dropout probability", "rate": "Keras-2 name of the dropout probability", "alpha": "slope / scale parameter of the activation", "size": "up-sampling factor", "cropping": "how much to cut from each border",
+    "mode": "merge mode (`sum`, `mul`, `concat`, `ave`, `cos`, `dot`, `max`, `sub`, `div`, `min`)", "concat_axis": "axis of the concatenation in `concat` mode", "layers": "the layers whose outputs are merged",
+    "merge_mode": "how a `Bidirectional` wrapper combines the two directions", "layer": "the wrapped layer", "n": "repetition count", "dims": "permutation of the non-batch dimensions (1-based)",
+    "target_shape": "output shape without the batch dimension (one `-1` is inferred)", "mask_value": "time steps equal to this value are skipped", "weights": "initial weights (list of arrays)",
+    "trainable": "whether the weights receive gradients", "mask_zero": "treat id 0 as padding (its row stays zero)", "zero_based_id": "ids start at 0 (default) instead of 1 as in BigDL's LookupTable",
+    "padding_value": "id whose embedding stays zero", "combiner": "`sum`, `mean` or `sqrtn` over the ids of a bag (SparseEmbedding)", "max_norm": "rows are renormalised to at most this L2 norm",
+    "embedding_file": "GloVe-format text file (`word v1 v2 ...`)", "word_index": "word -> id map (ids start at 1; 0 is padding)", "epsilon": "small constant added to the variance", "momentum": "momentum of the moving statistics",
+    "beta_init": "initializer of the shift", "gamma_init": "initializer of the scale", "hidden_size": "model width of the Transformer / BERT block", "n_block": "number of Transformer blocks",
+    "n_head": "attention heads", "intermediate_size": "width of the position-wise feed-forward layer", "hidden_drop": "dropout on the block outputs", "attn_drop": "dropout on the attention probabilities",
+    "initializer_range": "standard deviation of the truncated-normal initializer", "output_all_block": "return the output of every block instead of the last", "embedding_layer": "custom embedding layer for the inputs",
+    "bidirectional": "attend in both directions (False = causal mask)", "vocab": "vocabulary size", "seq_len": "maximum sequence length", "nb_kernel": "kernel size (ConvLSTM; square kernels)",
+    "depth_multiplier": "depth-wise output channels per input channel", "depthwise_regularizer": "regularizer of the depth-wise kernel", "pointwise_regularizer": "regularizer of the 1x1 kernel",
+    "nb_feature": "number of linear pieces of a MaxoutDense", "sigma": "standard deviation of the noise", "theta": "threshold", "value": "the constant", "constant": "the constant", "axis": "axis the op acts on",
+    "dim": "dimension the op acts on (1-based, batch excluded where the reference does so)", "dimension": "dimension the op acts on", "index": "index to select", "length": "length of the slice", "offset": "start of the slice",
+    "power": "exponent", "scale": "multiplier", "shift": "additive term", "min_value": "lower clamp", "max_value": "upper clamp", "torch_layer": "a torch module to wrap as a zoo layer",
+}
+
+
 def clean_doc(doc):
     return textwrap.dedent(doc).strip() if doc else ""
 
@@ -141,6 +177,13 @@ def describe(name, obj):
         doc = clean_doc(obj.__doc__) or clean_doc(getattr(obj.__init__, "__doc__", None) if obj.__init__ is not object.__init__ else None)
         if doc:
             lines += [doc, ""]
+        if ".keras" in (obj.__module__ or ""):                  # Keras-style layers: explain the constructor arguments from the glossary
+            try:
+                params = [p for p in inspect.signature(obj).parameters if p in ARG_DOC]
+            except (TypeError, ValueError):
+                params = []
+            if params:
+                lines += ["Arguments:", ""] + [f"* `{p}`: {ARG_DOC[p]}" for p in params] + [""]
         rows = []
         for m, v in vars(obj).items():
             if m.startswith("_"):
