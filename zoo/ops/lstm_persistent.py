@@ -62,15 +62,35 @@ def _dy_arg(dy):
     return dy, dy.data_ptr(), dy.stride(0), dy.stride(1)
 
 
+_GRU_MASK = {}        # (H, device) -> [1]*2H + [0]*H: which entries of b_hh join the input bias
+
+
+def _combined_bias(kind, b_ih, b_hh, H):
+    """The bias the input projection adds, in ONE kernel: LSTM b_ih + b_hh; GRU b_ih with b_hh folded into the r and z gates only (the
+    candidate gate's recurrent bias sits inside r * (.)).  Nothing derived from the parameters is cached: the fused optimizer writes
+    parameters through raw pointers, which torch's version counters do not see."""
+    if b_ih is None:
+        return None
+    if b_hh is None:
+        return b_ih
+    if kind == "lstm":
+        return b_ih + b_hh
+    key = (H, b_ih.device)
+    mask = _GRU_MASK.get(key)
+    if mask is None:
+        mask = _GRU_MASK[key] = torch.cat([torch.ones(2 * H, device=b_ih.device), torch.zeros(H, device=b_ih.device)])
+    return torch.addcmul(b_ih, b_hh, mask)
+
+
 class _LSTMLayerFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w_ih, w_hh, b_ih, b_hh, h0, c0, hard=False):
         B, T, Fin = x.shape
         H = w_hh.shape[1]
         x2 = x.reshape(B * T, Fin)
-        bias = None if b_ih is None else (b_ih + b_hh if b_hh is not None else b_ih)
-        gates = (torch.addmm(bias, x2, w_ih.t()) if bias is not None else x2 @ w_ih.t()).view(B, T, 4 * H)
         need = any(ctx.needs_input_grad)
+        bias = _combined_bias("lstm", b_ih, b_hh, H)
+        gates = (torch.addmm(bias, x2, w_ih.t()) if bias is not None else x2 @ w_ih.t()).view(B, T, 4 * H)
         hout = torch.empty((B, T, H), dtype=torch.float32, device=x.device)
         cout = torch.empty_like(hout) if need else None
         hT = torch.empty((B, H), dtype=torch.float32, device=x.device)
@@ -116,13 +136,9 @@ class _GRULayerFn(torch.autograd.Function):
         B, T, Fin = x.shape
         H = w_hh.shape[1]
         x2 = x.reshape(B * T, Fin)
-        bias = None
-        if b_ih is not None:
-            bias = b_ih.clone()
-            if b_hh is not None:
-                bias[:2 * H] += b_hh[:2 * H]     # the candidate gate's recurrent bias sits inside r * (.)
-        gx = (torch.addmm(bias, x2, w_ih.t()) if bias is not None else x2 @ w_ih.t()).view(B, T, 3 * H)
         need = any(ctx.needs_input_grad)
+        bias = _combined_bias("gru", b_ih, b_hh, H)
+        gx = (torch.addmm(bias, x2, w_ih.t()) if bias is not None else x2 @ w_ih.t()).view(B, T, 3 * H)
         hout = torch.empty((B, T, H), dtype=torch.float32, device=x.device)
         saved = torch.empty((B, T, 4 * H), dtype=torch.float32, device=x.device) if need else None
         hT = torch.empty((B, H), dtype=torch.float32, device=x.device)
@@ -202,5 +218,6 @@ def maybe_run(rnn, x, state=None, hard_sigmoid=False):
         hs.append(hT)
         if rnn.dropout > 0 and l + 1 < rnn.num_layers and rnn.training:
             out = F.dropout(out, rnn.dropout, True)
-    hN = torch.stack(hs)
-    return (out, (hN, torch.stack(cs))) if is_lstm else (out, hN)
+    one = len(hs) == 1                                   # a single layer: the state is a view, no stacking kernel
+    hN = hs[0].unsqueeze(0) if one else torch.stack(hs)
+    return (out, (hN, cs[0].unsqueeze(0) if one else torch.stack(cs))) if is_lstm else (out, hN)
