@@ -272,3 +272,46 @@ def test_reference_multi_type_and_string_graphs():
     snet = TFNet.from_export_folder(_SM + "tfnet_string")
     got = snet(["1.5", b"2", "3e2"])
     assert got.dtype == torch.float32 and got.tolist() == [1.5, 2.0, 300.0]
+
+
+@pytest.mark.skipif(not os.path.exists(_SM + "saved-model-signature/saved_model.pb"), reason="reference test resources are not on this machine")
+def test_tfnet_for_inference_and_graph_runner():
+    from zoo.pipeline.api.net import GraphRunner, TFNet, TFNetForInference
+
+    x = torch.ones(2, 4)
+    net = TFNetForInference.from_saved_model(_SM + "saved-model-signature")
+    assert isinstance(net, TFNetForInference) and isinstance(net, TFNet)
+    want = TFNet.from_saved_model(_SM + "saved-model-signature")(x)
+    assert torch.equal(net(x), want)
+    runner = GraphRunner(_SM + "tfnet/frozen_inference_graph.pb")
+    meta = __import__("json").load(open(_SM + "tfnet/graph_meta.json"))
+    out = runner.run([torch.rand(3, 4)], meta["input_names"], meta["output_names"])
+    assert len(out) == 1 and out[0].shape[0] == 3
+    assert runner.run([torch.rand(5, 4)], meta["input_names"], meta["output_names"])[0].shape[0] == 5 and len(runner._modules) == 1
+
+
+def test_export_tf_training_graph_round_trip(tmp_path):
+    """export_tf(generate_backward=True): the folder has the reference's training-export layout (variables, grad_variables, grad_inputs);
+    reloaded, the variables are trainable and the written gradient nodes agree with autograd of the original torch model."""
+    import json
+
+    from zoo.pipeline.api.net import TFNet
+    from zoo.tfpark.graphdef import GraphDefModule, read_graphdef
+    from zoo.util.tf import export_tf
+
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(4, 6), torch.nn.Tanh(), torch.nn.Linear(6, 3, bias=False), torch.nn.ReLU(), torch.nn.Linear(3, 2), torch.nn.Sigmoid())
+    ins, outs = export_tf(model, str(tmp_path), example_input=torch.zeros(1, 4), generate_backward=True)
+    meta = json.load(open(tmp_path / "graph_meta.json"))
+    assert ins == ["Placeholder:0"] and outs == ["dense_2/Sigmoid:0"] and meta["variables"] == ["dense/kernel:0", "dense/bias:0", "dense_1/kernel:0", "dense_2/kernel:0", "dense_2/bias:0"]
+    x, gy = torch.randn(5, 4, requires_grad=True), torch.randn(5, 2)
+    model(x).backward(gy)
+    grads = GraphDefModule(read_graphdef(str(tmp_path / "frozen_inference_graph.pb")), ["Placeholder:0", "dense_2/Sigmoid_grad:0"], meta["grad_inputs"] + meta["grad_variables"])
+    gx, *gv = grads(x.detach(), gy)
+    assert torch.allclose(gx, x.grad, atol=1e-5)
+    want = [model[0].weight.grad.t(), model[0].bias.grad, model[2].weight.grad.t(), model[4].weight.grad.t(), model[4].bias.grad]
+    assert all(torch.allclose(a, b, atol=1e-5) for a, b in zip(gv, want))
+    net = TFNet.from_export_folder(str(tmp_path))
+    assert len(list(net.parameters())) == 5 and torch.allclose(net(x.detach()), model(x.detach()), atol=1e-6)
+    with pytest.raises(NotImplementedError):
+        export_tf(torch.nn.Sequential(torch.nn.Conv2d(1, 1, 3)), str(tmp_path / "c"), example_input=torch.zeros(1, 1, 8, 8), generate_backward=True)

@@ -81,3 +81,43 @@ class TFNet(nn.Module):
             o = self.graph(*[t[i:i + batch_per_thread].to(dev) for t in xs])
             outs.append(o if torch.is_tensor(o) else o[0])
         return torch.cat(outs).float().cpu().numpy()
+
+
+class TFNetForInference(TFNet):
+    """A SavedModel loaded for inference with its variables restored (reference: TFNetForInference.scala -- the variant of TFNet
+    that keeps variables in the graph and assigns them from the checkpoint instead of freezing them).  Here restoring and freezing
+    are the same step (`zoo.tfpark.saved_model`), so this is `TFNet.from_saved_model` under the reference's class name."""
+
+    def __new__(cls, model_path, tag=None, signature=None, inputs=None, outputs=None, **_ignored):
+        net = TFNet.from_saved_model(model_path, tag=tag, signature=signature, inputs=inputs, outputs=outputs)
+        net.__class__ = cls
+        return net
+
+    def __init__(self, *a, **kw):       # built in __new__
+        pass
+
+    @staticmethod
+    def from_saved_model(model_path, tag=None, signature=None, inputs=None, outputs=None, **kw):
+        return TFNetForInference(model_path, tag, signature, inputs, outputs)
+
+    fromSavedModel = from_saved_model
+
+
+class GraphRunner:
+    """Runs named tensors of a GraphDef (reference: tfpark/GraphRunner.scala: `run(input, inputNames, outputNames, targets)` over a
+    TF session).  One imported module is kept per (inputs, outputs) pair."""
+
+    def __init__(self, graph_def, restore_op=None, restore_path_placeholder=None, save_op=None, save_path_placeholder=None, config=None):
+        from ....tfpark.graphdef import read_graphdef
+
+        self.nodes = read_graphdef(graph_def)
+        self._modules = {}
+
+    def run(self, inputs, input_names, output_names, targets=None):
+        from ....tfpark.graphdef import GraphDefModule
+
+        key = (tuple(input_names), tuple(output_names))
+        if key not in self._modules:
+            self._modules[key] = GraphDefModule(self.nodes, list(input_names), list(output_names))
+        out = self._modules[key](*inputs)
+        return list(out) if isinstance(out, tuple) else [out]

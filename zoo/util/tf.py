@@ -51,7 +51,7 @@ def export_tf(model, folder, example_input=None, inputs=None, outputs=None, gene
         raise NotImplementedError("export_tf(sess, ...) freezes a live tf.Session, and there is no TensorFlow runtime here; pass a torch "
                                   "model and an example input: export_tf(model, folder, example_input)")
     if generate_backward:
-        raise NotImplementedError("export_tf(generate_backward=True): the exported graph is an inference graph")
+        return _export_training_graph(model, folder)
     x = torch.as_tensor(np.asarray(example_input)) if not torch.is_tensor(example_input) else example_input
     model = model.eval()
     nodes = [("input", "Placeholder", [], {"dtype": np.float32})]
@@ -161,6 +161,77 @@ def export_tf(model, folder, example_input=None, inputs=None, outputs=None, gene
     os.makedirs(folder, exist_ok=True)
     write_graphdef(os.path.join(folder, "frozen_inference_graph.pb"), nodes)
     meta = {"input_names": ["input:0"], "output_names": ["output:0"]}
+    with open(os.path.join(folder, "graph_meta.json"), "w") as f:
+        json.dump(meta, f)
+    return meta["input_names"], meta["output_names"]
+
+
+def _export_training_graph(model, folder):
+    """`export_tf(..., generate_backward=True)`: forward graph + explicit gradient nodes + the metadata a trainable TFNet needs
+    (`variables`, `grad_variables`, `grad_inputs`, `temp_tensors`), in the layout of the reference's training exports
+    (pyzoo/zoo/util/tf.py:120-238; fixture zoo/src/test/resources/tfnet_training).  Covered: chains of Linear / ReLU / Sigmoid / Tanh --
+    the gradient of anything else would need TensorFlow's gradient registry."""
+    import torch.nn as nn
+
+    from ..tfpark.graphdef import write_graphdef
+
+    f32 = np.float32
+    layers = _flatten_modules(model.eval())
+    nodes, variables, temp = [("Placeholder", "Placeholder", [], {"dtype": f32})], [], []
+    cur, k, tape = "Placeholder", 0, []                       # tape: what the backward pass needs, in forward order
+    for m in layers:
+        if isinstance(m, nn.Linear):
+            name = "dense" if k == 0 else f"dense_{k}"
+            k += 1
+            nodes += [(f"{name}/kernel", "Const", [], {"dtype": f32, "value": np.ascontiguousarray(m.weight.detach().float().cpu().numpy().T)}),
+                      (f"{name}/kernel/read", "Identity", [f"{name}/kernel"], {"T": f32}),
+                      (f"{name}/MatMul", "MatMul", [cur, f"{name}/kernel/read"], {"T": f32, "transpose_a": False, "transpose_b": False})]
+            variables.append(f"{name}/kernel:0")
+            temp.append(f"{name}/kernel/read:0")
+            tape.append(("matmul", name, cur))
+            cur = f"{name}/MatMul"
+            if m.bias is not None:
+                nodes += [(f"{name}/bias", "Const", [], {"dtype": f32, "value": m.bias.detach().float().cpu().numpy().copy()}),
+                          (f"{name}/bias/read", "Identity", [f"{name}/bias"], {"T": f32}),
+                          (f"{name}/BiasAdd", "BiasAdd", [cur, f"{name}/bias/read"], {"T": f32, "data_format": "NHWC"})]
+                variables.append(f"{name}/bias:0")
+                tape.append(("bias", name, cur))
+                cur = f"{name}/BiasAdd"
+        elif isinstance(m, (nn.ReLU, nn.Sigmoid, nn.Tanh)):
+            op = {"ReLU": "Relu", "Sigmoid": "Sigmoid", "Tanh": "Tanh"}[type(m).__name__]
+            last = "dense" if k <= 1 else f"dense_{k - 1}"
+            nodes.append((f"{last}/{op}", op, [cur], {"T": f32}))
+            tape.append(("act", op, f"{last}/{op}"))
+            cur = f"{last}/{op}"
+            temp.append(cur + ":0")
+        elif isinstance(m, (nn.Dropout, nn.Identity)):
+            continue
+        else:
+            raise NotImplementedError(f"export_tf(generate_backward=True): no gradient written for layer {type(m).__name__} "
+                                      "(covered: Linear, ReLU, Sigmoid, Tanh)")
+    out = cur
+    nodes += [(f"{out}_grad", "Placeholder", [], {"dtype": f32}), ("gradients/grad_ys_0", "Identity", [f"{out}_grad"], {"T": f32})]
+    g, grad_of = "gradients/grad_ys_0", {}
+    for kind, a, b in reversed(tape):
+        if kind == "act":
+            gop = {"Relu": "ReluGrad", "Sigmoid": "SigmoidGrad", "Tanh": "TanhGrad"}[a]
+            name = f"gradients/{b}_grad/{gop}"
+            nodes.append((name, gop, [g, b] if a == "Relu" else [b, g], {"T": f32}))       # ReluGrad(gradients, features); Sigmoid/TanhGrad(y, dy)
+            g = name
+        elif kind == "bias":
+            name = f"gradients/{a}/BiasAdd_grad/BiasAddGrad"
+            nodes.append((name, "BiasAddGrad", [g], {"T": f32, "data_format": "NHWC"}))
+            grad_of[f"{a}/bias:0"] = name + ":0"
+        else:
+            dx, dw = f"gradients/{a}/MatMul_grad/MatMul", f"gradients/{a}/MatMul_grad/MatMul_1"
+            nodes += [(dx, "MatMul", [g, f"{a}/kernel/read"], {"T": f32, "transpose_a": False, "transpose_b": True}),
+                      (dw, "MatMul", [b, g], {"T": f32, "transpose_a": True, "transpose_b": False})]
+            grad_of[f"{a}/kernel:0"] = dw + ":0"
+            g = dx
+    os.makedirs(folder, exist_ok=True)
+    write_graphdef(os.path.join(folder, "frozen_inference_graph.pb"), nodes)
+    meta = {"input_names": ["Placeholder:0"], "output_names": [out + ":0"], "variables": variables, "grad_variables": [grad_of[v] for v in variables],
+            "grad_inputs": [g + ":0"], "temp_tensors": temp}
     with open(os.path.join(folder, "graph_meta.json"), "w") as f:
         json.dump(meta, f)
     return meta["input_names"], meta["output_names"]
