@@ -2,9 +2,10 @@
 pyzoo/zoo/examples/vnni/openvino/predict.py: `InferenceModel.load_tf_object_detection_as_openvino` / `load_openvino(xml, bin)`,
 read an image folder with ImageSet, resize + channel order + to-tensor, `model.predict(batch)`, print the top classes).
 
-OpenVINO IRs are not loadable on this stack (`load_openvino` raises and names this route); the engine with the same role is
-InferenceModel on a torch model: convolutions in bf16 channels_last through cuDNN and, after `quantize(calibration_batch)`, every
-Linear / Dense layer in FP8 (E4M3) on the tcgen05 GEMM kernel."""
+`load_openvino(xml, bin)` imports the IR graph into torch (`zoo.pipeline.inference.openvino_ir`; no Inference Engine here), so the
+model runs like any other: convolutions in bf16 channels_last through cuDNN and, after `quantize(calibration_batch)` -- the
+counterpart of the IR's int8 mode --, every Linear / Dense layer in FP8 (E4M3) on the tcgen05 GEMM kernel.  The IR read here is
+written first from a torch model with `save_openvino_ir` (no model zoo download on this box)."""
 import os
 import sys
 import tempfile
@@ -33,12 +34,13 @@ images = ImageSet.read(folder).transform(ChainedPreprocessing([ImageResize(256, 
 batch = torch.from_numpy(np.stack(images.get_image()))
 
 cuda = torch.cuda.is_available() and not os.environ.get("ZOO_FORCE_CPU")
-try:
-    InferenceModel().load_openvino("model.xml", "model.bin")
-except NotImplementedError as e:
-    print("load_openvino:", str(e)[:90], "...")
+from zoo.pipeline.inference.openvino_ir import save_openvino_ir  # noqa: E402
+
+xml, weights = save_openvino_ir(nn.Sequential(*[m for m in net if not isinstance(m, nn.AdaptiveAvgPool2d)][:4], nn.AvgPool2d(13, 13), *list(net)[5:]),
+                                os.path.join(folder, "model.xml"), (1, 3, 224, 224))
 model = InferenceModel(1, "cuda" if cuda else "cpu", dtype=torch.bfloat16 if cuda else None)
-model.load_torch(net)
+model.load_openvino(xml, weights)
+print("loaded OpenVINO IR:", os.path.basename(xml), "+", os.path.basename(weights), "(%d KB)" % (os.path.getsize(weights) // 1024))
 ref = model.predict(batch.numpy())
 model.quantize(batch)                                   # calibration on the batch itself; Linear layers -> FP8
 out = model.predict(batch.numpy())

@@ -53,8 +53,8 @@ def test_inference_model_pool():
     assert all(np.allclose(o, ref) for o in outs) and m.records == 45
     auto = InferenceModel(supported_concurrent_num=0, device="cpu").load_torch(TinyCls())
     assert auto.predict(x).shape == (5, 10)
-    with pytest.raises(NotImplementedError):
-        m.load_openvino("a.xml", "a.bin")
+    with pytest.raises(FileNotFoundError):
+        m.load_openvino("a.xml", "a.bin")                   # an IR importer now (tests/test_cpu_openvino_ir.py): a missing file is just missing
 
     class Two(nn.Module):
         def forward(self, a, b):

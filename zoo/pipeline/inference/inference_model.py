@@ -125,15 +125,16 @@ class InferenceModel:
                 use_per_session_threads=True, inputs=None, outputs=None, model_type=None, tag=None, signature=None):
         return self.load_tensorflow(model_path, model_type or "frozenModel", inputs=inputs, outputs=outputs, tag=tag, signature=signature)
 
-    def load_openvino(self, model_path, weight_path, batch_size=0):
-        """OpenVINO IR (`.xml` + `.bin`) is the reference's low-precision CPU engine.  Its job -- 8-bit inference -- is done here by
-        the FP8 tensor-core path: load the original model with load_torch / load_caffe / load_tf and call `quantize(calib_batch)`.
-        The IR container itself (an Intel-specific op set) is not imported."""
-        raise NotImplementedError("load_openvino: OpenVINO IR files are not imported; load the source model (load_torch / load_caffe / "
-                                  "load_tf) and call InferenceModel.quantize(calibration_batch) for 8-bit (FP8) inference")
+    def load_openvino(self, model_path, weight_path=None, batch_size=0):
+        """OpenVINO IR (`.xml` + `.bin`), the reference's CPU inference engine format (doLoadOpenVINO): the IR graph is imported as a
+        torch module (`zoo.pipeline.inference.openvino_ir`, both the <blobs> generation the reference used and IR v10+); its 8-bit
+        mode is `quantize(calibration_batch)` afterwards -- FP8 on the tensor cores."""
+        from .openvino_ir import load_openvino_ir
+
+        return self._install(load_openvino_ir(model_path, weight_path))
 
     def load_tf_as_openvino(self, *a, **kw):
-        raise NotImplementedError("the *_as_openvino loaders convert a TensorFlow model to OpenVINO IR; here: load_tf(...) followed by "
+        raise NotImplementedError("the *_as_openvino loaders run OpenVINO's Model Optimizer on a TensorFlow model; here: load_tf(...) followed by "
                                   "quantize(calibration_batch)")
 
     load_tf_object_detection_as_openvino = load_tf_image_classification_as_openvino = load_tf_as_calibrated_openvino = load_tf_as_openvino
