@@ -47,4 +47,7 @@ out = model.predict(batch.numpy())
 for uri, p in zip([f["uri"] for f in images.get_image_features()], out):
     top = np.argsort(-p)[:3]
     print(os.path.basename(uri), "->", [(int(c), round(float(p[c]), 4)) for c in top])
-print("predicted %d images; top-1 agreement FP8 vs unquantised: %.2f" % (len(out), float((out.argmax(1) == ref.argmax(1)).mean())))
+top5 = lambda p: [set(np.argsort(-r)[:5].tolist()) for r in p]
+overlap = np.mean([len(a & b) / 5.0 for a, b in zip(top5(out), top5(ref))])
+print("predicted %d images; FP8 vs unquantised: top-5 overlap %.2f, largest probability difference %.4f (fresh weights: scores are nearly flat)" %
+      (len(out), overlap, float(np.abs(out - ref).max())))

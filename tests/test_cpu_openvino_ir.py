@@ -136,7 +136,9 @@ def test_ir_details():
     with pytest.raises(NotImplementedError):
         from zoo.pipeline.inference.openvino_ir import OpenVINOModule
 
-        OpenVINOModule._new(None, mk('<layer id="1" name="x" type="NoSuchOp" version="opset1"/>'), [])
+        from types import SimpleNamespace
+
+        OpenVINOModule._new(SimpleNamespace(_linear={}), mk('<layer id="1" name="x" type="NoSuchOp" version="opset1"/>'), [])
 
 
 def test_ir_linear_layers_are_modules_and_writer_round_trip(tmp_path):
