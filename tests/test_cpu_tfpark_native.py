@@ -157,3 +157,27 @@ def test_zoo_optimizer_wrapper_and_fake_optim_method():
     before = [p.detach().clone() for p in m.parameters()]
     Estimator(m, FakeOptimMethod()).engine.train(FeatureSet.numpy(x, y), "mse", MaxIteration(2), batch_size=8)
     assert all(torch.equal(a, b) for a, b in zip(m.parameters(), before))
+
+
+def test_dataset_like_iterables_stand_in_for_tf_data():
+    """from_tf_data_dataset / FeatureSet.tf_dataset take what a tf.data pipeline is to its consumer: an iterable of elements."""
+    import numpy as np
+
+    from zoo.feature.common import FeatureSet
+    from zoo.tfpark import TFDataset
+
+    rng = np.random.RandomState(0)
+    elems = [((rng.rand(4).astype(np.float32), rng.rand(2).astype(np.float32)), np.int64(i % 3)) for i in range(10)]
+    ds = TFDataset.from_tf_data_dataset(elems, batch_size=5, validation_dataset=elems[:4])
+    b = next(iter(ds.get_training_data().batches(5, train=False)))
+    assert [tuple(t.shape) for t in b.inputs] == [(5, 4), (5, 2)] and b.targets.flatten().tolist() == [0, 1, 2, 0, 1]
+    assert ds.get_validation_data().size() == 4
+
+    class Pipeline:                                    # quacks like tf.data.Dataset
+        def as_numpy_iterator(self):
+            return iter(np.arange(12, dtype=np.float32).reshape(6, 2))
+
+    fs = FeatureSet.tf_dataset(lambda: Pipeline(), total_size=4)
+    assert fs.size() == 4
+    only_x = TFDataset.from_tf_data_dataset(Pipeline(), batch_per_thread=3)
+    assert only_x.get_training_data().size() == 6

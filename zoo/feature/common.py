@@ -439,8 +439,20 @@ class FeatureSet:
         return cls(features=list(x) if isinstance(x, tuple) else x, labels=list(y) if isinstance(y, tuple) else y, **kw)
 
     @classmethod
-    def tf_dataset(cls, *a, **kw):
-        raise NotImplementedError("tf.data input needs TensorFlow, which is not part of zoo-b200; use numpy/torch inputs")
+    def tf_dataset(cls, func, total_size=None, bigdl_type="float"):
+        """FeatureSet over a tf.data-style source (reference: FeatureSet.tf_dataset(func, total_size), common.py:330-345 -- `func` builds
+        the dataset on each executor).  `func` is a callable returning an iterable of elements (or the iterable itself); elements are
+        arrays or (features, labels) pairs; at most `total_size` of them are read."""
+        import itertools
+
+        src = func() if callable(func) else func
+        it = src.as_numpy_iterator() if hasattr(src, "as_numpy_iterator") else iter(src)
+        elems = list(itertools.islice(it, total_size) if total_size is not None else it)
+        if not elems:
+            raise ValueError("FeatureSet.tf_dataset: the dataset is empty")
+        if isinstance(elems[0], (tuple, list)) and len(elems[0]) == 2:
+            return cls.numpy(np.stack([np.asarray(e[0]) for e in elems]), np.stack([np.asarray(e[1]) for e in elems]))
+        return cls.numpy(np.stack([np.asarray(e) for e in elems]))
 
     # ---- basic ops ---------------------------------------------------------------
     def size(self):

@@ -109,8 +109,30 @@ class TFDataset:
         return TFDataset(FeatureSet.numpy(x, y), batch_size, batch_per_thread, hard_code_batch_size, val)
 
     @staticmethod
-    def from_tf_data_dataset(*a, **kw):
-        TFDataset._needs_tf("from_tf_data_dataset")
+    def from_tf_data_dataset(dataset, batch_size=-1, batch_per_thread=-1, hard_code_batch_size=False, validation_dataset=None, **kw):
+        """A `tf.data.Dataset` in the reference (pyzoo/zoo/tfpark/tf_dataset.py:560-640: the dataset graph is shipped to the executors and
+        iterated there).  There is no TensorFlow runtime here, so what is accepted is the thing a tf.data pipeline IS to its consumer:
+        any iterable of elements, an element being an array, or a (features, labels) pair whose sides are arrays or tuples of arrays.
+        A real `tf.data.Dataset` object cannot exist in this environment; one that does (a TF install next to zoo) is iterated through
+        its `as_numpy_iterator()`."""
+        def collect(ds):
+            it = ds.as_numpy_iterator() if hasattr(ds, "as_numpy_iterator") else iter(ds)
+            elems = list(it)
+            if not elems:
+                raise ValueError("from_tf_data_dataset: the dataset is empty")
+            pair = isinstance(elems[0], (tuple, list)) and len(elems[0]) == 2
+            side = lambda vals: ([np.stack([np.asarray(v[k]) for v in vals]) for k in range(len(vals[0]))] if isinstance(vals[0], (tuple, list))
+                                 else np.stack([np.asarray(v) for v in vals]))
+            if pair:
+                return side([e[0] for e in elems]), side([e[1] for e in elems])
+            return side(elems), None
+
+        x, y = collect(dataset)
+        val = None
+        if validation_dataset is not None:
+            vx, vy = collect(validation_dataset)
+            val = FeatureSet.numpy(vx, vy)
+        return TFDataset(FeatureSet.numpy(x, y), batch_size, batch_per_thread, hard_code_batch_size, val)
 
     @staticmethod
     def from_string_rdd(string_rdd, batch_size=-1, batch_per_thread=-1, hard_code_batch_size=False, validation_string_rdd=None, **kw):
