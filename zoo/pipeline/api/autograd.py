@@ -360,6 +360,8 @@ def _dry_shape_const_aware(module, parents):
 
 
 def _from_op(fn, parents, label="op"):
+    if parents and not any(isinstance(p, Variable) for p in parents) and any(torch.is_tensor(p) for p in parents):
+        return fn(*parents)          # called on tensors (e.g. a loss function given to compile): evaluate eagerly, torch autograd takes over
     parents = [p if isinstance(p, Variable) else Constant(p) for p in parents]
     op = _Op(fn, label)
     return Variable(_dry_shape_const_aware(op, parents), (op, parents))

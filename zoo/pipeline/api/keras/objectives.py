@@ -173,9 +173,19 @@ class TorchLoss(LossFunction):
     def __init__(self, fn):
         super().__init__()
         self.fn = fn
+        # a Keras / zoo style function names its first argument y_true (reference: compile wraps such a function in CustomLoss, which
+        # calls it as (y_true, y_pred)); torch criteria take (input, target)
+        try:
+            import inspect
+
+            first = next(iter(inspect.signature(fn).parameters), "")
+        except (TypeError, ValueError):
+            first = ""
+        self.true_first = first in ("y_true", "ytrue", "target", "targets", "labels", "label")
 
     def forward(self, y_pred, y_true):
-        return self.fn(y_pred, y_true)
+        out = self.fn(y_true, y_pred) if self.true_first else self.fn(y_pred, y_true)
+        return out.mean() if torch.is_tensor(out) and out.dim() > 0 else out      # per-sample losses are averaged over the batch
 
 
 _ALIASES = {
