@@ -188,3 +188,22 @@ def test_broker_socket_rejects_malformed_requests():
         c.close()
     finally:
         b.stop_server()
+
+
+def test_runtime_stress_harness_under_thread_sanitizer():
+    """The C++ runtime (broker incl. its RESP server, arena, record store) under ThreadSanitizer with the multi-threaded stress
+    harness tests/native/rt_stress.cpp (summaries from dev/tsan_runtime.sh are kept in profiles/sanitizer_runtime_*_r2.txt)."""
+    import shutil
+    import subprocess
+
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = "/tmp/rt_stress_tsan_test"
+    build = subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-pthread", "csrc/runtime/arena.cpp", "csrc/runtime/broker.cpp",
+                            "tests/native/rt_stress.cpp", "-o", exe], cwd=root, capture_output=True, text=True)
+    if build.returncode != 0 and "sanitize" in build.stderr:
+        pytest.skip("this toolchain has no ThreadSanitizer runtime")
+    assert build.returncode == 0, build.stderr[-2000:]
+    run = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert run.returncode == 0 and "RT_STRESS_OK" in run.stdout and "WARNING: ThreadSanitizer" not in run.stderr, run.stdout[-1000:] + run.stderr[-3000:]
