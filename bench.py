@@ -175,7 +175,9 @@ def main():
         setattr(eng, k, v)
     eng.prepare()
     crit = cfg["loss"].to(dev)
-    K, Wm = args.steps, max(args.warmup, 3)
+    # at least 5 untimed steps: the engine runs 3 eager steps, captures the CUDA graph inside the 4th and replays from the 5th on, so a
+    # smaller warm-up would put the capture into the timed region (the JSON line reports the warm-up that was really done)
+    K, Wm = args.steps, max(args.warmup, 5)
     from zoo.feature.common import MiniBatch
 
     # ---------------- device-timed region: batches resident in HBM -----------------------
