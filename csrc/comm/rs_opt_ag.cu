@@ -20,8 +20,15 @@
 //            every rank zeroes its own gradient range for the next iteration.
 //
 // No NCCL call, no staging buffer, no separate optimizer pass.  Each CTA only ever waits for the
-// CTA with the same index on the other GPUs, so the kernel needs no grid-wide synchronisation
-// and can share the GPU with backward kernels of the next bucket.
+// CTA with the same index on the other GPUs, so the kernel needs no grid-wide synchronisation.
+//
+// Forward-progress assumption (a plain launch, not a cooperative one): CTA b of this GPU waits for CTA b of every peer, so every
+// GPU must eventually RUN its CTA b.  That holds when the grid is co-resident (the launcher caps it at 592 = 4 CTAs x 148 SMs,
+// the kernel's occupancy at 256 threads and no shared memory) or when CTAs are dispatched in index order on every GPU and earlier
+// CTAs finish without waiting on later ones -- both true for the step as it runs today, where K1 is alone on its stream position
+// (it starts after backward).  Running it BESIDE other kernels that hold SMs for long would need the grid clamped to what is
+// co-resident next to them; until then a wait that exceeds its clock budget (~10 s) traps with the rank / CTA in
+// zoo_last_error instead of hanging.
 //
 // `emulate` != 0 runs all ranks inside one cooperative launch on ONE GPU (blockIdx.y = rank) --
 // used by the single-GPU tests; the real path is one process per GPU with IPC-mapped arenas.
