@@ -182,3 +182,70 @@ def test_zoo_dictionary_and_tensor_operation(tmp_path):
     small = torch.ones(3, 1)
     TensorOperation.subTensor(small, torch.arange(4.0))                          # the first argument grows to the broadcast size
     assert small.shape == (3, 4) and torch.equal(small[1], 1 - torch.arange(4.0))
+
+
+def test_hdf5_reader_writer_keras_weights_and_matlab_fixture(tmp_path):
+    """zoo.util.hdf5: classic-layout writer / reader round trip (groups, attributes with string arrays, contiguous datasets), Keras-layout
+    weight files through KerasModel.save_weights / load_weights and Net.load_keras, and the reference's MATLAB v7.3 volume
+    (image3d/a.mat: chunked + deflate) through the 3-D image ops (pyzoo/test/zoo/feature/image3d/test_image3d.py)."""
+    import json
+
+    import numpy as np
+    import torch
+
+    from zoo.util.hdf5 import File, write_hdf5
+
+    rng = np.random.RandomState(0)
+    tree = {"g": {"__attrs__": {"names": np.array([b"a", b"bb"]), "scale": 2.5}, "a": rng.rand(3, 4).astype(np.float32), "sub": {"bb": np.arange(6, dtype=np.int64).reshape(2, 3)}},
+            "top": rng.rand(5)}
+    p = write_hdf5(str(tmp_path / "t.h5"), tree, attrs={"title": "zoo", "n": np.int32(3)})
+    with File(p) as f:
+        assert sorted(f.keys()) == ["g", "top"] and f.attrs["title"] == b"zoo" and int(f.attrs["n"]) == 3
+        assert list(f["g"].attrs["names"]) == [b"a", b"bb"] and float(f["g"].attrs["scale"]) == 2.5
+        assert np.array_equal(f["g/a"][...], tree["g"]["a"]) and f["g/sub/bb"][1, 2] == 5 and f["top"].shape == (5,) and f["top"].dtype == np.float64
+        assert sorted(f.visit_datasets()) == ["g/a", "g/sub/bb", "top"] and "missing" not in f
+
+    from zoo.pipeline.api.keras.layers import Dense
+    from zoo.pipeline.api.keras.models import Sequential
+    from zoo.pipeline.api.net import Net
+    from zoo.tfpark import KerasModel
+
+    def build():
+        m = Sequential()
+        m.add(Dense(5, activation="relu", input_shape=(4,)))
+        m.add(Dense(2))
+        m.compile(optimizer="sgd", loss="mse")
+        return m
+
+    torch.manual_seed(0)
+    a, b = KerasModel(build()), KerasModel(build())
+    a.save_weights(str(tmp_path / "w.h5"))
+    with File(str(tmp_path / "w.h5")) as f:
+        assert len(f.attrs["layer_names"]) == 2
+    b.load_weights(str(tmp_path / "w.h5"))
+    x = torch.randn(3, 4)
+    assert torch.allclose(a.model(x), b.model(x))
+    # a file in Keras' own naming (kernels [in, out]) + the json definition -> Net.load_keras
+    ws = [p.detach().numpy() for p in a.model.parameters()]
+    write_hdf5(str(tmp_path / "k.h5"), {"dense_1": {"__attrs__": {"weight_names": np.array([b"dense_1_W", b"dense_1_b"])}, "dense_1_W": ws[0].T.copy(), "dense_1_b": ws[1]},
+                                        "dense_2": {"__attrs__": {"weight_names": np.array([b"dense_2_W", b"dense_2_b"])}, "dense_2_W": ws[2].T.copy(), "dense_2_b": ws[3]}},
+               attrs={"layer_names": np.array([b"dense_1", b"dense_2"])})
+    spec = {"class_name": "Sequential", "config": [{"class_name": "Dense", "config": {"output_dim": 5, "activation": "relu", "batch_input_shape": [None, 4]}},
+                                                   {"class_name": "Dense", "config": {"output_dim": 2}}]}
+    (tmp_path / "k.json").write_text(json.dumps(spec))
+    loaded = Net.load_keras(str(tmp_path / "k.json"), str(tmp_path / "k.h5"))
+    assert torch.allclose(loaded(x), a.model(x), atol=1e-6)
+
+    mat = "/root/reference/pyzoo/test/zoo/resources/image3d/a.mat"
+    if os.path.exists(mat):
+        from zoo.feature.image3d.transformation import CenterCrop3D, Crop3D, Rotate3D
+
+        with File(mat) as f:
+            ds = f["meniscus_im"]
+            assert ds.shape == (20, 256, 256) and ds.attrs["MATLAB_class"] == b"double"
+            vol = np.asarray(ds)
+        assert 0 < (vol > 0).sum() < vol.size // 100 and float(vol.max()) < 1.0           # a small segmented structure
+        sample = vol[..., None]
+        crop = Crop3D(start=[13, 80, 125], patch_size=[5, 40, 40])({"mat": sample, "imageTensor": sample})
+        out = crop.get("imageTensor", crop.get("mat"))
+        assert np.asarray(out).shape == (5, 40, 40, 1) and np.allclose(np.asarray(out)[..., 0], vol[13:18, 80:120, 125:165].astype(np.float32))

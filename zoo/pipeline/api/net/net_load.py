@@ -75,7 +75,7 @@ class Net:
     @staticmethod
     def load_keras(json_path=None, hdf5_path=None, by_name=False):
         """A Keras-1.2.2 model definition (`model.to_json()`) -> zoo Keras-style Sequential (the zoo layers keep Keras-1 argument
-        names, so the layer configs map one to one); weights from `hdf5_path` when h5py is importable, or from an `.npz` file holding
+        names, so the layer configs map one to one); weights from `hdf5_path` (a Keras `save_weights` HDF5 file; read with h5py, or with `zoo.util.hdf5` when h5py is absent), or from an `.npz` file holding
         the arrays of `model.get_weights()` in order (reference: Net.load_keras, net_load.py:117-140)."""
         import inspect
         import json
@@ -110,12 +110,11 @@ class Net:
                 arrays = [v for _, v in sorted(np.load(hdf5_path).items(), key=lambda kv: int("".join(ch for ch in kv[0] if ch.isdigit()) or 0))]
             else:
                 try:
-                    import h5py
-                except ImportError as e:
-                    raise NotImplementedError("Net.load_keras(hdf5_path=...): h5py is not installed; save the weights with "
-                                              "np.savez(path, *model.get_weights()) and pass the .npz file") from e
+                    import h5py as h5
+                except ImportError:
+                    from ....util import hdf5 as h5        # the built-in reader of the classic HDF5 layout (what Keras / h5py write)
                 arrays = []
-                with h5py.File(hdf5_path, "r") as f:
+                with h5.File(hdf5_path, "r") as f:
                     g = f["model_weights"] if "model_weights" in f else f
                     for lname in [n.decode() if isinstance(n, bytes) else n for n in g.attrs["layer_names"]]:
                         for wname in [n.decode() if isinstance(n, bytes) else n for n in g[lname].attrs["weight_names"]]:

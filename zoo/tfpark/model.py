@@ -47,9 +47,63 @@ class KerasModel:
                 p.copy_(torch.as_tensor(w).reshape(p.shape))
 
     def save_weights(self, filepath, overwrite=True, save_format=None):
+        """`.h5` / `.hdf5` (or save_format="h5"): a Keras-layout HDF5 file -- root attribute `layer_names`, one group per layer with
+        `weight_names` and its arrays (written by `zoo.util.hdf5`); anything else: a torch state_dict."""
+        import os
+
+        if os.path.exists(filepath) and not overwrite:
+            raise FileExistsError(filepath)
+        if save_format in ("h5", "hdf5") or str(filepath).endswith((".h5", ".hdf5")):
+            import numpy as np
+
+            from ..util.hdf5 import write_hdf5
+
+            tree, layers = {}, []
+            for lname, mod in self.model.named_modules():
+                params = [(n, p) for n, p in mod.named_parameters(recurse=False)] + [(n, b) for n, b in mod.named_buffers(recurse=False) if b.is_floating_point()]
+                if not params:
+                    continue
+                key = lname.replace(".", "_") or "model"
+                names = [f"{key}/{n}:0" for n, _ in params]
+                tree[key] = {"__attrs__": {"weight_names": np.array([n.encode() for n in names])}, key: {f"{n}:0": p.detach().float().cpu().numpy() for n, p in params}}
+                layers.append(key)
+            write_hdf5(filepath, tree, attrs={"layer_names": np.array([n.encode() for n in layers]), "backend": "torch", "keras_version": "zoo-b200"})
+            return
         torch.save(self.model.state_dict(), filepath)
 
     def load_weights(self, filepath, by_name=False):
+        with open(filepath, "rb") as f:
+            head = f.read(2048)
+        if b"\x89HDF\r\n\x1a\n" in head:
+            import numpy as np
+
+            try:
+                import h5py as h5
+            except ImportError:
+                from ..util import hdf5 as h5
+            arrays = {}
+            with h5.File(filepath, "r") as f:
+                g = f["model_weights"] if "model_weights" in f else f
+                for lname in [n.decode() if isinstance(n, bytes) else n for n in g.attrs["layer_names"]]:
+                    for wname in [n.decode() if isinstance(n, bytes) else n for n in g[lname].attrs["weight_names"]]:
+                        arrays[wname] = np.asarray(g[lname][wname])
+            own = {}
+            for lname, mod in self.model.named_modules():
+                key = lname.replace(".", "_") or "model"
+                for n, t in list(mod.named_parameters(recurse=False)) + list(mod.named_buffers(recurse=False)):
+                    own[f"{key}/{n}:0"] = t
+            if by_name or set(arrays) <= set(own):
+                pairs = [(own[k], v) for k, v in arrays.items() if k in own]
+            else:                                           # a file written by Keras itself: assign in order
+                targets = [p for p in self.model.parameters()]
+                if len(targets) != len(arrays):
+                    raise ValueError(f"the model has {len(targets)} weight tensors, the file {len(arrays)}")
+                pairs = list(zip(targets, arrays.values()))
+            with torch.no_grad():
+                for t, a in pairs:
+                    v = torch.from_numpy(np.asarray(a, dtype=np.float32))
+                    t.copy_((v.t() if v.shape != t.shape and v.dim() == 2 and v.t().shape == t.shape else v).reshape(t.shape))
+            return
         self.model.load_state_dict(torch.load(filepath, map_location="cpu"))
 
     def save_model(self, path):
