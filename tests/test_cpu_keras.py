@@ -321,3 +321,48 @@ def test_blockwise_attention_restatement_matches_dense_attention(L, causal, mask
     got = attention_blockwise_reference(q, k, v, km, causal)
     want = attention_reference(q.float(), k.float(), v.float(), None if km is None else km[:, None, None, :], causal)
     torch.testing.assert_close(got, want, atol=1e-2, rtol=1e-2)
+
+
+def test_save_to_tf_and_save_to_keras2(tmp_path):
+    """KerasNet.saveToTf / saveToKeras2 (Topology.scala:559-575; NetSpec.scala:147-192): the TF export is read back by TFNet and gives
+    the model's output; the Keras-2 export is a weights file in Keras layout plus the script that rebuilds the model."""
+    from zoo.pipeline.api.keras.layers import LSTM, Dense, Dropout, Permute, Reshape
+    from zoo.pipeline.api.keras.models import Sequential
+    from zoo.pipeline.api.net import TFNet
+    from zoo.util.hdf5 import File
+
+    torch.manual_seed(0)
+    m = Sequential()
+    m.add(Dense(8, activation="tanh", input_shape=(6,)))
+    m.add(Dropout(0.5))
+    m.add(Dense(3, activation="softmax"))
+    m.eval()
+    x = torch.randn(4, 6)
+    ins, outs = m.saveToTf(str(tmp_path / "tf"))
+    back = TFNet.from_export_folder(str(tmp_path / "tf"))
+    assert torch.allclose(back(x), m(x), atol=1e-5)
+
+    g = Sequential()
+    g.add(Reshape((13, 4), input_shape=(52,)))
+    g.add(Permute((2, 1)))
+    g.add(LSTM(10, return_sequences=True))
+    g.add(LSTM(10))
+    g.add(Dropout(0.5))
+    g.add(Dense(2, activation="softmax"))
+    weights, script = g.saveToKeras2(str(tmp_path / "model.h5"))
+    code = open(script).read()
+    compile(code, script, "exec")                                   # valid Python
+    assert "Reshape((13, 4)" in code and "Permute((2, 1)" in code and code.count("LSTM(10") == 2 and "recurrent_activation='hard_sigmoid'" in code
+    assert "Dense(2, activation='softmax'" in code and "input_shape=(52,)" in code and "model.load_weights" in code
+    with File(weights) as f:
+        layers = [n.decode() for n in f.attrs["layer_names"]]
+        assert len(layers) == 3                                     # two LSTMs and the Dense carry weights
+        dense = layers[-1]
+        kernel = next(np.asarray(f[dense][w.decode()]) for w in f[dense].attrs["weight_names"] if np.asarray(f[dense][w.decode()]).ndim == 2)
+        assert kernel.shape == (10, 2)                              # [in, out], Keras' layout
+    with pytest.raises(NotImplementedError):
+        from zoo.pipeline.api.keras.layers import Convolution2D
+
+        c = Sequential()
+        c.add(Convolution2D(2, 3, 3, input_shape=(1, 8, 8)))
+        c.saveToTf(str(tmp_path / "c"))

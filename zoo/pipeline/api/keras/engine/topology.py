@@ -213,6 +213,107 @@ class KerasNet(nn.Module):
     def to_model(self):
         return self
 
+    # ---- exporters (reference: KerasNet.saveToTf / saveToKeras2, Topology.scala:559-575 -> Net.scala NetSaver) ----------------------
+    def _export_layers(self):
+        layers = []
+        for l in (list(self.seq) if hasattr(self, "seq") else self.layers):
+            layers += l._export_layers() if isinstance(l, KerasNet) else [l]
+        if not layers:
+            raise ValueError("the model has no layers")
+        return layers
+
+    def save_to_tf(self, dir, python=None):
+        """Frozen TensorFlow graph of this model in `dir` (`frozen_inference_graph.pb` + `graph_meta.json`, the layout TFNet reads).  The
+        reference runs a generated Keras script under `python`; here the graph is written directly (`zoo.util.tf.export_tf`).  Covered:
+        stacks of Dense / Activation / Dropout / Flatten layers."""
+        import torch.nn as nn
+
+        from ..layers import core as C
+        from .....util.tf import export_tf
+
+        acts = {"relu": nn.ReLU, "sigmoid": nn.Sigmoid, "tanh": nn.Tanh, "softmax": lambda: nn.Softmax(-1), "log_softmax": lambda: nn.LogSoftmax(-1),
+                "softplus": nn.Softplus, "elu": nn.ELU, "relu6": nn.ReLU6}
+        mods = []
+        for l in self._export_layers():
+            if isinstance(l, C.Dense):
+                mods.append(l.dense)
+                if l.activation not in (None, "linear", "relu"):
+                    mods.append(acts[l.activation]())
+            elif isinstance(l, C.Activation):
+                if l.activation not in (None, "linear"):
+                    mods.append(acts[l.activation]())
+            elif isinstance(l, C.Dropout):
+                mods.append(nn.Dropout(l.p))
+            elif isinstance(l, C.Flatten):
+                mods.append(nn.Flatten())
+            else:
+                raise NotImplementedError(f"save_to_tf: no TensorFlow graph is written for layer {type(l).__name__} (covered: Dense, Activation, Dropout, Flatten)")
+        shape = self.get_input_shape()
+        example = torch.zeros((1,) + tuple(int(d) for d in shape[1:]))
+        return export_tf(nn.Sequential(*mods), dir, example_input=example)
+
+    saveToTf = save_to_tf
+
+    def save_to_keras2(self, file_path, python=None):
+        """What the reference produces with a Keras installation (a script that builds the Keras-2 model, sets the weights and calls
+        `model.save`): here the two inputs of that step are written -- `<file_path>` = the weights as a Keras-layout HDF5 file
+        (`layer_names` / `weight_names`, Dense kernels as [in, out]; `zoo.util.hdf5`) and `<file_path>.py` = the Keras-2 script that
+        rebuilds the architecture and loads them.  With `python` given (an interpreter that has Keras) the script is run.  Covered:
+        Dense, Activation, Dropout, Flatten, Reshape, Permute, LSTM, GRU, Embedding."""
+        import subprocess
+
+        import numpy as np
+
+        from .....util.hdf5 import write_hdf5
+
+        lines = ["from tensorflow.keras.models import Sequential", "from tensorflow.keras.layers import *", "", "model = Sequential(name=%r)" % (getattr(self, "zoo_name", None) or "model")]
+        tree, names = {}, []
+        first = True
+        for k, l in enumerate(self._export_layers()):
+            cname = type(l).__name__
+            lname = getattr(l, "zoo_name", None)
+            lname = lname if isinstance(lname, str) and lname else f"{cname.lower()}_{k}"
+            extra = ", input_shape=%r" % (tuple(int(d) for d in self.get_input_shape()[1:]),) if first else ""
+            first = False
+            if cname == "Dense":
+                code = f"Dense({l.output_dim}, activation={l.activation!r}, use_bias={bool(l.use_bias)}, name={lname!r}{extra})"
+            elif cname == "Activation":
+                code = f"Activation({l.activation!r}, name={lname!r}{extra})"
+            elif cname == "Dropout":
+                code = f"Dropout({l.p}, name={lname!r}{extra})"
+            elif cname == "Flatten":
+                code = f"Flatten(name={lname!r}{extra})"
+            elif cname == "Reshape":
+                code = f"Reshape({tuple(l.target_shape)!r}, name={lname!r}{extra})"
+            elif cname == "Permute":
+                code = f"Permute({tuple(l.dims)!r}, name={lname!r}{extra})"
+            elif cname in ("LSTM", "GRU"):
+                code = (f"{cname}({l.output_dim}, activation={getattr(l, 'activation', 'tanh')!r}, recurrent_activation={l.inner_activation!r}, "
+                        f"return_sequences={bool(l.return_sequences)}, go_backwards={bool(l.go_backwards)}, name={lname!r}{extra})")
+            elif cname == "Embedding":
+                code = f"Embedding({l.input_dim}, {l.output_dim}, name={lname!r}{extra})"
+            else:
+                raise NotImplementedError(f"save_to_keras2: no Keras-2 constructor is written for layer {cname}")
+            lines.append(f"model.add({code})")
+            params = [(n, p.detach().float().cpu().numpy()) for n, p in l.named_parameters()]
+            if params:
+                arrays = {}
+                for n, a in params:
+                    a = a.T.copy() if cname == "Dense" and a.ndim == 2 else a          # Keras kernels are [in, out]
+                    arrays[f"{n.replace('.', '_')}:0"] = a
+                tree[lname] = {"__attrs__": {"weight_names": np.array([f"{lname}/{n}".encode() for n in arrays])}, lname: arrays}
+                names.append(lname)
+        write_hdf5(file_path, tree, attrs={"layer_names": np.array([n.encode() for n in names]), "backend": "tensorflow", "keras_version": "2"})
+        lines += ["", f"model.load_weights({str(file_path)!r}, by_name=True)", f"model.save({str(file_path)[:-3] + '_full.h5' if str(file_path).endswith('.h5') else str(file_path) + '_full.h5'!r})", ""]
+        script = str(file_path) + ".py"
+        with open(script, "w") as f:
+            f.write("\n".join(lines))
+        if python:
+            subprocess.run([python, script], check=True)
+        return file_path, script
+
+    saveToKeras2 = save_to_keras2
+
 
 class Sequential(KerasNet):
     """Linear stack of layers: `model.add(layer)`.  The first layer needs `input_shape=`; every later
