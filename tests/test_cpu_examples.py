@@ -64,7 +64,9 @@ CASES = [
 
 @pytest.mark.parametrize("script,args,expect", CASES)
 def test_example_runs(script, args, expect):
-    env = dict(os.environ, ZOO_FORCE_CPU="1", OMP_NUM_THREADS="2", EPOCHS="2", STEPS="40", ITERS="60", BAGS="1")
+    env = dict(os.environ, OMP_NUM_THREADS="2", EPOCHS="2", STEPS="40", ITERS="60", BAGS="1")
+    if os.environ.get("ZOO_EXAMPLES_DEVICE", "cpu") != "gpu":      # ZOO_EXAMPLES_DEVICE=gpu runs the same list on the visible GPU (dev check)
+        env["ZOO_FORCE_CPU"] = "1"
     r = subprocess.run([sys.executable, os.path.join(ROOT, "examples", script), *args], capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
     assert r.returncode == 0 and expect in r.stdout, r.stdout[-1500:] + r.stderr[-3000:]
 
