@@ -48,6 +48,7 @@ print("negative ELBO per image: before %.2f after %.2f" % (before, after))
 import torch
 
 with torch.no_grad():
-    grid = torch.tensor([[a, b] for a in (-1.5, 0.0, 1.5) for b in (-1.5, 0.0, 1.5)], dtype=torch.float32)
-    imgs = decoder_out(decoder_h(grid)).reshape(-1, side, side)
+    device = next(decoder_h.parameters()).device                       # the layers live where fit() trained them
+    grid = torch.tensor([[a, b] for a in (-1.5, 0.0, 1.5) for b in (-1.5, 0.0, 1.5)], dtype=torch.float32, device=device)
+    imgs = decoder_out(decoder_h(grid)).float().cpu().reshape(-1, side, side)
 print("decoded 9 latent points; mean 'ink' per image:", [round(float(i.sum()), 1) for i in imgs], "(a 3x3 blob has 9)")
