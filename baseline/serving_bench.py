@@ -53,7 +53,8 @@ def run_serving_baseline(kind, dev, steps, warmup, batch=0, rank=0):
                 super().__init__()
                 self.mu, self.mi = torch.nn.Embedding(1_000_001, 64), torch.nn.Embedding(100_001, 64)
                 self.gu, self.gi = torch.nn.Embedding(1_000_001, 32), torch.nn.Embedding(100_001, 32)
-                self.mlp = torch.nn.Sequential(torch.nn.Linear(128, 128), torch.nn.ReLU(), torch.nn.Linear(128, 64), torch.nn.ReLU(), torch.nn.Linear(64, 32), torch.nn.ReLU())
+                self.mlp = torch.nn.Sequential(torch.nn.Linear(128, 128), torch.nn.ReLU(), torch.nn.Linear(128, 64), torch.nn.ReLU(),
+                        torch.nn.Linear(64, 32), torch.nn.ReLU())
                 self.last = torch.nn.Linear(64, 5)
 
             def forward(self, x):

@@ -217,7 +217,8 @@ def _serving(args, ctx, torch):
                           "impl": "zoo-b200", "p50_batch_ms": float(np.percentile(lat, 50)), "p99_batch_ms": float(np.percentile(lat, 99)),
                           "torch_baseline": base, "engine_stage_seconds": getattr(srv, "stage_s", None),
                           "jpeg_backend": getattr(getattr(srv, "_jpeg", None), "backend", None),
-                          "vs_torch_baseline": (float(res[0] / res[1]) / (base.get("value_all_ranks") or base["value"])) if base and base.get("value") else None,
+                          "vs_torch_baseline": (float(res[0] / res[1]) / (base.get("value_all_ranks") or base["value"]))
+                          if base and base.get("value") else None,
                           "config": {"model": kind, "global_batch": bs * ctx.world_size, "seq_len": None,
                                      "parallelism": (f"{ctx.world_size} engines in one consumer group of ONE broker (rank 0 hosts it; RESP socket)" if shared
                                                      else f"{ctx.world_size} serving replicas (one engine + in-process broker per GPU)"),

@@ -63,5 +63,6 @@ if ctx.rank == 0:
     roof770 = max(out_bytes, in_bytes) / 770e9 * 1e3
     print(f"K1_BENCH world={W} params={n / 1e6:.1f}M  fused (NVLS={nvls['p2p']}) {out['p2p']:.3f} ms  fused peer-pointer path {out['p2p-nonvls']:.3f} ms  "
           f"nccl all-reduce + optimizer {out['nccl']:.3f} ms  NVLink roofline {roof_ms:.3f} ms @900 / {roof770:.3f} ms @770 GB/s -> "
-          f"{100 * roof770 / min(out['p2p'], out['p2p-nonvls']):.0f} % of the 770 GB/s roofline; speed-up over nccl {out['nccl'] / min(out['p2p'], out['p2p-nonvls']):.2f}x")
+          f"{100 * roof770 / min(out['p2p'], out['p2p-nonvls']):.0f} % of the 770 GB/s roofline; speed-up over nccl {out['nccl'] / min(out['p2p'],
+                  out['p2p-nonvls']):.2f}x")
 torch.distributed.barrier()

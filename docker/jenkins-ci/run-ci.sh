@@ -6,6 +6,8 @@ dev/check-license
 dev/lint-python
 python dev/api_parity.py | tail -1 | grep -q "(100.0 %)"
 python -m pytest tests -x -q -m "not gpu"
+dev/tsan_runtime.sh tsan | grep -q RT_STRESS_OK
+dev/tsan_runtime.sh asan | grep -q RT_STRESS_OK
 if nvidia-smi -L >/dev/null 2>&1; then
   python -m pytest tests -x -q -m gpu
   n=$(nvidia-smi -L | wc -l)

@@ -40,6 +40,7 @@ if __name__ == "__main__":
     model.fit(x=X_, y=Y_, batch_size=32, nb_epoch=int(os.environ.get("CUSTOM_EPOCHS", 60)), distributed=False)
     w = model.get_weights()
     pred = model.predict_local(X_) if hasattr(model, "predict_local") else model.predict(X_)
-    print("weights", np.round(np.asarray(w[0]).reshape(-1), 2).tolist(), "bias", np.round(np.asarray(w[1]).reshape(-1), 2).tolist(), "(target 2, 2 and 0.4 - 1)")
+    print("weights", np.round(np.asarray(w[0]).reshape(-1), 2).tolist(), "bias", np.round(np.asarray(w[1]).reshape(-1), 2).tolist(),
+            "(target 2, 2 and 0.4 - 1)")
     print("mean absolute error on the training data: %.4f; loss points written to TensorBoard: %d" %
           (float(np.abs(np.asarray(pred) - Y_).mean()), len(model.get_train_summary("Loss"))))

@@ -34,7 +34,8 @@ chain = ChainedPreprocessing([RowToImageFeature(), ImageResize(40, 40), ImageCha
                               ImageMatToTensor(), ImageFeatureToTensor()])
 featurizer = NNModel(backbone, chain).setFeaturesCol("image").setPredictionCol("embedding").setBatchSize(32)     # stage 1: frozen extractor
 head = nn.Sequential(nn.Linear(32, 2), nn.LogSoftmax(-1))
-classifier = NNClassifier(head, SparseCategoricalCrossEntropy(log_prob_as_input=True, zero_based_label=False), SeqToTensor([32])).setFeaturesCol("embedding").setBatchSize(24) \
+classifier = NNClassifier(head, SparseCategoricalCrossEntropy(log_prob_as_input=True, zero_based_label=False),
+        SeqToTensor([32])).setFeaturesCol("embedding").setBatchSize(24) \
     .setMaxEpoch(int(os.environ.get("EPOCHS", 30))).setOptimMethod(Adam(lr=5e-2))                                   # stage 2: trainable head
 model = classifier.fit(featurizer.transform(train))
 pred = model.transform(featurizer.transform(val))

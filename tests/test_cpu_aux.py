@@ -196,7 +196,8 @@ def test_hdf5_reader_writer_keras_weights_and_matlab_fixture(tmp_path):
     from zoo.util.hdf5 import File, write_hdf5
 
     rng = np.random.RandomState(0)
-    tree = {"g": {"__attrs__": {"names": np.array([b"a", b"bb"]), "scale": 2.5}, "a": rng.rand(3, 4).astype(np.float32), "sub": {"bb": np.arange(6, dtype=np.int64).reshape(2, 3)}},
+    tree = {"g": {"__attrs__": {"names": np.array([b"a", b"bb"]), "scale": 2.5}, "a": rng.rand(3, 4).astype(np.float32), "sub": {"bb": np.arange(6,
+            dtype=np.int64).reshape(2, 3)}},
             "top": rng.rand(5)}
     p = write_hdf5(str(tmp_path / "t.h5"), tree, attrs={"title": "zoo", "n": np.int32(3)})
     with File(p) as f:
@@ -227,8 +228,10 @@ def test_hdf5_reader_writer_keras_weights_and_matlab_fixture(tmp_path):
     assert torch.allclose(a.model(x), b.model(x))
     # a file in Keras' own naming (kernels [in, out]) + the json definition -> Net.load_keras
     ws = [p.detach().numpy() for p in a.model.parameters()]
-    write_hdf5(str(tmp_path / "k.h5"), {"dense_1": {"__attrs__": {"weight_names": np.array([b"dense_1_W", b"dense_1_b"])}, "dense_1_W": ws[0].T.copy(), "dense_1_b": ws[1]},
-                                        "dense_2": {"__attrs__": {"weight_names": np.array([b"dense_2_W", b"dense_2_b"])}, "dense_2_W": ws[2].T.copy(), "dense_2_b": ws[3]}},
+    write_hdf5(str(tmp_path / "k.h5"), {"dense_1": {"__attrs__": {"weight_names": np.array([b"dense_1_W", b"dense_1_b"])},
+            "dense_1_W": ws[0].T.copy(), "dense_1_b": ws[1]},
+                                        "dense_2": {"__attrs__": {"weight_names": np.array([b"dense_2_W", b"dense_2_b"])},
+                                                "dense_2_W": ws[2].T.copy(), "dense_2_b": ws[3]}},
                attrs={"layer_names": np.array([b"dense_1", b"dense_2"])})
     spec = {"class_name": "Sequential", "config": [{"class_name": "Dense", "config": {"output_dim": 5, "activation": "relu", "batch_input_shape": [None, 4]}},
                                                    {"class_name": "Dense", "config": {"output_dim": 2}}]}

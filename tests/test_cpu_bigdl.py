@@ -14,7 +14,8 @@ REF = "/root/reference/zoo/src/test/resources/models"
 def _net():
     torch.manual_seed(0)
     net = nn.Sequential(nn.Conv2d(3, 8, 3, stride=2, padding=1), nn.BatchNorm2d(8), nn.ReLU(), nn.MaxPool2d(2), nn.Conv2d(8, 8, 3, groups=2), nn.Tanh(),
-                        nn.AvgPool2d(2), nn.Flatten(), nn.Linear(8, 16), nn.ELU(0.7), nn.Dropout(0.3), nn.Sequential(nn.Linear(16, 4), nn.LogSoftmax(-1))).eval()
+                        nn.AvgPool2d(2), nn.Flatten(), nn.Linear(8, 16), nn.ELU(0.7), nn.Dropout(0.3), nn.Sequential(nn.Linear(16, 4),
+                                nn.LogSoftmax(-1))).eval()
     with torch.no_grad():
         net[1].running_mean.uniform_(-1, 1)
         net[1].running_var.uniform_(0.5, 2)

@@ -100,4 +100,5 @@ def test_hadoop_sequence_files_of_images(tmp_path):
         s = ImageSet.read_sequence_files(ref)
         feats = s.get_image_features()
         assert len(feats) == 5 and sorted(float(f["label"][0]) for f in feats) == [91.0, 328.0, 620.0, 697.0, 733.0]
-        assert all(f["mat"].ndim == 3 and f["mat"].shape[2] == 3 and min(f["mat"].shape[:2]) == 256 for f in feats)   # shorter side scaled to 256 by the generator
+        # the generator scaled the shorter side to 256
+        assert all(f["mat"].ndim == 3 and f["mat"].shape[2] == 3 and min(f["mat"].shape[:2]) == 256 for f in feats)

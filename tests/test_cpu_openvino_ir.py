@@ -18,7 +18,8 @@ class _Bin:
 
 
 def _ports(kind, ids_dims):
-    return f"<{kind}>" + "".join(f'<port id="{i}" precision="FP32">' + "".join(f"<dim>{d}</dim>" for d in dims) + "</port>" for i, dims in ids_dims) + f"</{kind}>"
+    return f"<{kind}>" + "".join(f'<port id="{i}" precision="FP32">' + "".join(f"<dim>{d}</dim>" for d in dims) + "</port>" for i,
+            dims in ids_dims) + f"</{kind}>"
 
 
 def test_ir_v10_cnn(tmp_path):
@@ -31,22 +32,28 @@ def test_ir_v10_cnn(tmp_path):
     shp_off, shp_sz = b.add([0, -1], np.int64)
     fw_off, fw_sz = b.add(fc.weight.detach().numpy().astype(np.float16), np.float16)        # an FP16 constant, as compressed IRs carry
     fb_off, fb_sz = b.add(fc.bias.detach().numpy().reshape(1, 5))
-    const = lambda i, name, et, shape, off, sz: (f'<layer id="{i}" name="{name}" type="Const" version="opset1"><data element_type="{et}" offset="{off}" shape="{shape}" size="{sz}"/>'
+    const = lambda i, name, et, shape, off, sz: (f'<layer id="{i}" name="{name}" type="Const" version="opset1">'
+            f'<data element_type="{et}" offset="{off}" shape="{shape}" size="{sz}"/>'
                                                   + _ports("output", [(0, [])]) + "</layer>")
     layers = [
-        f'<layer id="0" name="data" type="Parameter" version="opset1"><data element_type="f32" shape="1,3,16,16"/>{_ports("output", [(0, [1, 3, 16, 16])])}</layer>',
+        f'<layer id="0" name="data" type="Parameter" version="opset1"><data element_type="f32" shape="1,3,16,16"/>'
+                f'{_ports("output", [(0, [1, 3, 16, 16])])}</layer>',
         const(1, "conv_w", "f32", "4,3,3,3", w_off, w_sz),
-        f'<layer id="2" name="conv" type="Convolution" version="opset1"><data auto_pad="explicit" dilations="1,1" pads_begin="1,1" pads_end="1,1" strides="2,2"/>'
+        f'<layer id="2" name="conv" type="Convolution" version="opset1">'
+        f'<data auto_pad="explicit" dilations="1,1" pads_begin="1,1" pads_end="1,1" strides="2,2"/>'
         f'{_ports("input", [(0, []), (1, [])])}{_ports("output", [(2, [])])}</layer>',
         const(3, "conv_b", "f32", "1,4,1,1", cb_off, cb_sz),
         f'<layer id="4" name="bias" type="Add" version="opset1">{_ports("input", [(0, []), (1, [])])}{_ports("output", [(2, [])])}</layer>',
         f'<layer id="5" name="relu" type="Relu" version="opset1">{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}</layer>',
-        f'<layer id="6" name="pool" type="MaxPool" version="opset1"><data auto_pad="explicit" kernel="2,2" pads_begin="0,0" pads_end="0,0" rounding_type="ceil" strides="2,2"/>'
+        f'<layer id="6" name="pool" type="MaxPool" version="opset1">'
+        f'<data auto_pad="explicit" kernel="2,2" pads_begin="0,0" pads_end="0,0" rounding_type="ceil" strides="2,2"/>'
         f'{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}</layer>',
         const(7, "shape", "i64", "2", shp_off, shp_sz),
-        f'<layer id="8" name="flatten" type="Reshape" version="opset1"><data special_zero="true"/>{_ports("input", [(0, []), (1, [])])}{_ports("output", [(2, [])])}</layer>',
+        f'<layer id="8" name="flatten" type="Reshape" version="opset1"><data special_zero="true"/>{_ports("input", [(0, []), (1, [])])}'
+                f'{_ports("output", [(2, [])])}</layer>',
         const(9, "fc_w", "f16", "5,64", fw_off, fw_sz),
-        f'<layer id="10" name="fc" type="MatMul" version="opset1"><data transpose_a="false" transpose_b="true"/>{_ports("input", [(0, []), (1, [])])}{_ports("output", [(2, [])])}</layer>',
+        f'<layer id="10" name="fc" type="MatMul" version="opset1"><data transpose_a="false" transpose_b="true"/>'
+                f'{_ports("input", [(0, []), (1, [])])}{_ports("output", [(2, [])])}</layer>',
         const(11, "fc_b", "f32", "1,5", fb_off, fb_sz),
         f'<layer id="12" name="fc_bias" type="Add" version="opset1">{_ports("input", [(0, []), (1, [])])}{_ports("output", [(2, [])])}</layer>',
         f'<layer id="13" name="prob" type="Softmax" version="opset1"><data axis="1"/>{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}</layer>',
@@ -90,13 +97,16 @@ def test_ir_v7_blobs_format(tmp_path):
     blob = lambda w, bb: f'<blobs><weights offset="{w[0]}" size="{w[1]}"/><biases offset="{bb[0]}" size="{bb[1]}"/></blobs>'
     layers = [
         f'<layer id="0" name="data" type="Input" precision="FP32">{_ports("output", [(0, [1, 2, 8, 8])])}</layer>',
-        f'<layer id="1" name="conv1" type="Convolution" precision="FP32"><data dilations="1,1" group="1" kernel="3,3" output="3" pads_begin="1,1" pads_end="1,1" strides="1,1"/>'
+        f'<layer id="1" name="conv1" type="Convolution" precision="FP32">'
+        f'<data dilations="1,1" group="1" kernel="3,3" output="3" pads_begin="1,1" pads_end="1,1" strides="1,1"/>'
         f'{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}{blob(cw, cb)}</layer>',
         f'<layer id="2" name="relu1" type="ReLU" precision="FP32">{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}</layer>',
         f'<layer id="3" name="scale1" type="ScaleShift" precision="FP32">{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}{blob(sw, sb)}</layer>',
-        f'<layer id="4" name="pool1" type="Pooling" precision="FP32"><data exclude-pad="false" kernel="2,2" pads_begin="0,0" pads_end="0,0" pool-method="avg" rounding_type="floor" strides="2,2"/>'
+        f'<layer id="4" name="pool1" type="Pooling" precision="FP32">'
+        f'<data exclude-pad="false" kernel="2,2" pads_begin="0,0" pads_end="0,0" pool-method="avg" rounding_type="floor" strides="2,2"/>'
         f'{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}</layer>',
-        f'<layer id="5" name="fc1" type="FullyConnected" precision="FP32"><data out-size="4"/>{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}{blob(fw, fb)}</layer>',
+        f'<layer id="5" name="fc1" type="FullyConnected" precision="FP32"><data out-size="4"/>{_ports("input", [(0, [])])}'
+                f'{_ports("output", [(1, [])])}{blob(fw, fb)}</layer>',
         f'<layer id="6" name="prob" type="SoftMax" precision="FP32"><data axis="1"/>{_ports("input", [(0, [])])}{_ports("output", [(1, [])])}</layer>',
     ]
     edges = [(0, 0, 1, 0), (1, 1, 2, 0), (2, 1, 3, 0), (3, 1, 4, 0), (4, 1, 5, 0), (5, 1, 6, 0)]

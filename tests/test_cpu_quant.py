@@ -54,6 +54,7 @@ def test_inference_model_quantize_and_foreign_loaders(tmp_path):
                                          'layer { name: "r" type: "ReLU" bottom: "ip" top: "ip" }\n'
                                          'layer { name: "ip2" type: "InnerProduct" bottom: "ip" top: "ip2" inner_product_param { num_output: 4 } }\n'
                                          'layer { name: "p" type: "Softmax" bottom: "ip2" top: "p" }\n')
-    save_caffemodel(str(tmp_path / "n.caffemodel"), [("ip", "InnerProduct", [net[0].weight, net[0].bias]), ("ip2", "InnerProduct", [net[2].weight, net[2].bias])])
+    save_caffemodel(str(tmp_path / "n.caffemodel"), [("ip", "InnerProduct", [net[0].weight, net[0].bias]), ("ip2", "InnerProduct", [net[2].weight,
+            net[2].bias])])
     cm = InferenceModel(device="cpu").load_caffe(str(tmp_path / "n.prototxt"), str(tmp_path / "n.caffemodel"))
     np.testing.assert_allclose(cm.predict(x.numpy()), want, atol=1e-5)

@@ -300,13 +300,16 @@ def test_export_tf_training_graph_round_trip(tmp_path):
     from zoo.util.tf import export_tf
 
     torch.manual_seed(0)
-    model = torch.nn.Sequential(torch.nn.Linear(4, 6), torch.nn.Tanh(), torch.nn.Linear(6, 3, bias=False), torch.nn.ReLU(), torch.nn.Linear(3, 2), torch.nn.Sigmoid())
+    model = torch.nn.Sequential(torch.nn.Linear(4, 6), torch.nn.Tanh(), torch.nn.Linear(6, 3, bias=False), torch.nn.ReLU(), torch.nn.Linear(3, 2),
+            torch.nn.Sigmoid())
     ins, outs = export_tf(model, str(tmp_path), example_input=torch.zeros(1, 4), generate_backward=True)
     meta = json.load(open(tmp_path / "graph_meta.json"))
-    assert ins == ["Placeholder:0"] and outs == ["dense_2/Sigmoid:0"] and meta["variables"] == ["dense/kernel:0", "dense/bias:0", "dense_1/kernel:0", "dense_2/kernel:0", "dense_2/bias:0"]
+    assert ins == ["Placeholder:0"] and outs == ["dense_2/Sigmoid:0"] and meta["variables"] == ["dense/kernel:0", "dense/bias:0", "dense_1/kernel:0",
+            "dense_2/kernel:0", "dense_2/bias:0"]
     x, gy = torch.randn(5, 4, requires_grad=True), torch.randn(5, 2)
     model(x).backward(gy)
-    grads = GraphDefModule(read_graphdef(str(tmp_path / "frozen_inference_graph.pb")), ["Placeholder:0", "dense_2/Sigmoid_grad:0"], meta["grad_inputs"] + meta["grad_variables"])
+    grads = GraphDefModule(read_graphdef(str(tmp_path / "frozen_inference_graph.pb")), ["Placeholder:0", "dense_2/Sigmoid_grad:0"],
+            meta["grad_inputs"] + meta["grad_variables"])
     gx, *gv = grads(x.detach(), gy)
     assert torch.allclose(gx, x.grad, atol=1e-5)
     want = [model[0].weight.grad.t(), model[0].bias.grad, model[2].weight.grad.t(), model[4].weight.grad.t(), model[4].bias.grad]

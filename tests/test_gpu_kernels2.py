@@ -175,7 +175,8 @@ def test_nvjpeg_batch_decode_and_preprocess_match_cv2():
     rng = np.random.RandomState(0)
     imgs = []
     for (h, w) in [(224, 224), (180, 260), (300, 200), (64, 64)]:
-        base = cv2.GaussianBlur(cv2.resize(rng.randint(0, 256, (h // 16 + 1, w // 16 + 1, 3), dtype=np.uint8), (w, h), interpolation=cv2.INTER_CUBIC), (9, 9), 0)   # smooth content
+        base = cv2.GaussianBlur(cv2.resize(rng.randint(0, 256, (h // 16 + 1, w // 16 + 1, 3), dtype=np.uint8), (w, h), interpolation=cv2.INTER_CUBIC),
+                (9, 9), 0)   # smooth content
         imgs.append(base)
     jpgs = [cv2.imencode(".jpg", im, [cv2.IMWRITE_JPEG_QUALITY, 92])[1].tobytes() for im in imgs]
     dec = JpegBatchDecoder("cuda:0")

@@ -11,7 +11,8 @@ from .VanillaLSTM import VanillaLSTM
 from .VanillaLSTM_pytorch import VanillaLSTMPytorch
 
 # "<name>_keras": the reference's Keras recipes (two stacked LSTMs / single-layer teacher-forced encoder-decoder, RMSprop)
-MODELS = {"lstm_keras": VanillaLSTM, "seq2seq_keras": LSTMSeq2Seq, "lstm": VanillaLSTMPytorch, "vanillalstm": VanillaLSTMPytorch, "seq2seq": Seq2SeqPytorch, "lstmseq2seq": Seq2SeqPytorch,
+MODELS = {"lstm_keras": VanillaLSTM, "seq2seq_keras": LSTMSeq2Seq, "lstm": VanillaLSTMPytorch, "vanillalstm": VanillaLSTMPytorch,
+        "seq2seq": Seq2SeqPytorch, "lstmseq2seq": Seq2SeqPytorch,
           "mtnet": MTNet, "tcn": TCNPytorch}
 
 

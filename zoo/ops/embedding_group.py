@@ -141,7 +141,8 @@ class _Plan:
             for i in range(0, len(members), MAX_TABS):
                 self.groups.append({"col": col, "bag": bag, "members": members[i:i + MAX_TABS]})
         # ---- staging (sharded): gradient rows and product factors where peers can read them ----------------------------------
-        self.key = ("egplan", tuple((s.table.uid, s.col, s.bag, s.mul_table.uid if s.mul_table is not None else 0, s.mul_col) for s in specs), self.B, self.id_stride)
+        self.key = ("egplan", tuple((s.table.uid, s.col, s.bag, s.mul_table.uid if s.mul_table is not None else 0, s.mul_col) for s in specs), self.B,
+                self.id_stride)
         self.dout_buf = self.dout = None
         self.saves = {}
         for k, s in enumerate(specs):
@@ -253,7 +254,8 @@ PRE_FLUSH_HOOKS = []      # callables run right before the sparse updates of a s
 
 
 def _plan_for(specs, ids):
-    key = (tuple((s.table.uid, s.col, s.bag, s.mean, s.mul_table.uid if s.mul_table is not None else 0, s.mul_col) for s in specs), ids.shape[0], ids.shape[1], ids.device)
+    key = (tuple((s.table.uid, s.col, s.bag, s.mean, s.mul_table.uid if s.mul_table is not None else 0, s.mul_col) for s in specs), ids.shape[0],
+            ids.shape[1], ids.device)
     p = _PLANS.get(key)
     if p is None:
         p = _PLANS[key] = _Plan(specs, ids.shape[0], ids.shape[1], ids.device)

@@ -247,7 +247,8 @@ class KerasNet(nn.Module):
             elif isinstance(l, C.Flatten):
                 mods.append(nn.Flatten())
             else:
-                raise NotImplementedError(f"save_to_tf: no TensorFlow graph is written for layer {type(l).__name__} (covered: Dense, Activation, Dropout, Flatten)")
+                raise NotImplementedError(f"save_to_tf: no TensorFlow graph is written for layer {type(l).__name__} "
+                                          "(covered: Dense, Activation, Dropout, Flatten)")
         shape = self.get_input_shape()
         example = torch.zeros((1,) + tuple(int(d) for d in shape[1:]))
         return export_tf(nn.Sequential(*mods), dir, example_input=example)
@@ -266,7 +267,8 @@ class KerasNet(nn.Module):
 
         from .....util.hdf5 import write_hdf5
 
-        lines = ["from tensorflow.keras.models import Sequential", "from tensorflow.keras.layers import *", "", "model = Sequential(name=%r)" % (getattr(self, "zoo_name", None) or "model")]
+        lines = ["from tensorflow.keras.models import Sequential", "from tensorflow.keras.layers import *", "",
+                 "model = Sequential(name=%r)" % (getattr(self, "zoo_name", None) or "model")]
         tree, names = {}, []
         first = True
         for k, l in enumerate(self._export_layers()):
@@ -304,7 +306,8 @@ class KerasNet(nn.Module):
                 tree[lname] = {"__attrs__": {"weight_names": np.array([f"{lname}/{n}".encode() for n in arrays])}, lname: arrays}
                 names.append(lname)
         write_hdf5(file_path, tree, attrs={"layer_names": np.array([n.encode() for n in names]), "backend": "tensorflow", "keras_version": "2"})
-        lines += ["", f"model.load_weights({str(file_path)!r}, by_name=True)", f"model.save({str(file_path)[:-3] + '_full.h5' if str(file_path).endswith('.h5') else str(file_path) + '_full.h5'!r})", ""]
+        full = str(file_path)[:-3] + "_full.h5" if str(file_path).endswith(".h5") else str(file_path) + "_full.h5"
+        lines += ["", f"model.load_weights({str(file_path)!r}, by_name=True)", f"model.save({full!r})", ""]
         script = str(file_path) + ".py"
         with open(script, "w") as f:
             f.write("\n".join(lines))

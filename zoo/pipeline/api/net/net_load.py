@@ -75,7 +75,8 @@ class Net:
     @staticmethod
     def load_keras(json_path=None, hdf5_path=None, by_name=False):
         """A Keras-1.2.2 model definition (`model.to_json()`) -> zoo Keras-style Sequential (the zoo layers keep Keras-1 argument
-        names, so the layer configs map one to one); weights from `hdf5_path` (a Keras `save_weights` HDF5 file; read with h5py, or with `zoo.util.hdf5` when h5py is absent), or from an `.npz` file holding
+        names, so the layer configs map one to one); weights from `hdf5_path` (a Keras `save_weights` HDF5 file; read with h5py, or with
+        `zoo.util.hdf5` when h5py is absent), or from an `.npz` file holding
         the arrays of `model.get_weights()` in order (reference: Net.load_keras, net_load.py:117-140)."""
         import inspect
         import json

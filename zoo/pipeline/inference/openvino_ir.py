@@ -283,7 +283,8 @@ class OpenVINOModule(nn.Module):
             w = blob("weights").reshape(out_c, x.shape[1] // group, *kernel)
             if "strides" not in l.data and "stride-x" in l.data:
                 l.data.update(strides=f"{l.a('stride-y', 1)},{l.a('stride-x', 1)}", pads_begin=f"{l.a('pad-y', 0)},{l.a('pad-x', 0)}",
-                              pads_end=f"{l.a('pad-b', l.a('pad-y', 0))},{l.a('pad-r', l.a('pad-x', 0))}", dilations=f"{l.a('dilation-y', 1)},{l.a('dilation-x', 1)}")
+                              pads_end=f"{l.a('pad-b', l.a('pad-y', 0))},{l.a('pad-r', l.a('pad-x', 0))}", dilations=f"{l.a('dilation-y',
+                                      1)},{l.a('dilation-x', 1)}")
             return _conv(l, x, w, blob("biases"), group)
         if t == "FullyConnected" and l.id in self._linear:
             return getattr(self, self._linear[l.id])(x.reshape(x.shape[0], -1))
@@ -324,7 +325,8 @@ class OpenVINOModule(nn.Module):
         if t == "Permute":
             return x.permute(_ints(l.a("order")))
         if t == "BatchNormalization":
-            return F.batch_norm(x, blob("mean") if blob("mean") is not None else blob("weights"), blob("variance") if blob("variance") is not None else blob("biases"),
+            return F.batch_norm(x, blob("mean") if blob("mean") is not None else blob("weights"),
+                    blob("variance") if blob("variance") is not None else blob("biases"),
                                 None, None, False, 0.0, float(l.a("epsilon", 1e-5)))
         fn = _OPS10.get(t)
         if fn is None:
@@ -458,7 +460,8 @@ def save_openvino_ir(model, xml_path, input_shape, bin_path=None, name="model"):
             raise NotImplementedError(f"save_openvino_ir: no IR op written for layer {type(m).__name__}")
     connect(cur, add("Result", "result", "", 1), 0)
     with open(xml_path, "w") as f:
-        f.write(f'<?xml version="1.0" ?>\n<net name="{name}" version="10">\n<layers>\n' + "\n".join(layers) + "\n</layers>\n<edges>\n" + "\n".join(edges) + "\n</edges>\n</net>\n")
+        f.write(f'<?xml version="1.0" ?>\n<net name="{name}" '
+                f'version="10">\n<layers>\n' + "\n".join(layers) + "\n</layers>\n<edges>\n" + "\n".join(edges) + "\n</edges>\n</net>\n")
     with open(bin_path, "wb") as f:
         f.write(bytes(blob))
     return xml_path, bin_path

@@ -143,7 +143,8 @@ class ClusterServing:
                 self.model.load_tensorflow(folder)
             else:       # config.yaml: model.inputs / model.outputs name the tensors of a bare frozen graph
                 split = lambda v: [t.strip() for t in str(v).split(",") if t.strip()] if v else None
-                self.model.load_tensorflow(path, inputs=split(getattr(self.conf, "model_inputs", None)), outputs=split(getattr(self.conf, "model_outputs", None)))
+                self.model.load_tensorflow(path, inputs=split(getattr(self.conf, "model_inputs", None)), outputs=split(getattr(self.conf,
+                        "model_outputs", None)))
         elif path.endswith((".xml", ".bin")):
             self.model.load_openvino(path, None)
         else:

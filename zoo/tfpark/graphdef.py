@@ -338,7 +338,8 @@ class GraphDefModule(nn.Module):
         for k, n in enumerate(nodes):
             if n.op == "Const" and n.name in needed:
                 arr = n.a("value")
-                t = torch.from_numpy(arr.copy(order="C")) if arr.dtype != np.float64 else torch.from_numpy(arr.astype(np.float32))   # (ascontiguousarray would turn a scalar into shape [1])
+                # (ascontiguousarray would turn a scalar into shape [1])
+                t = torch.from_numpy(arr.copy(order="C")) if arr.dtype != np.float64 else torch.from_numpy(arr.astype(np.float32))
                 key = f"c{k}"
                 if n.name in train and t.is_floating_point():
                     self.register_parameter(key, nn.Parameter(t))

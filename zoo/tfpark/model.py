@@ -60,12 +60,14 @@ class KerasModel:
 
             tree, layers = {}, []
             for lname, mod in self.model.named_modules():
-                params = [(n, p) for n, p in mod.named_parameters(recurse=False)] + [(n, b) for n, b in mod.named_buffers(recurse=False) if b.is_floating_point()]
+                params = [(n, p) for n, p in mod.named_parameters(recurse=False)] + [(n, b) for n,
+                        b in mod.named_buffers(recurse=False) if b.is_floating_point()]
                 if not params:
                     continue
                 key = lname.replace(".", "_") or "model"
                 names = [f"{key}/{n}:0" for n, _ in params]
-                tree[key] = {"__attrs__": {"weight_names": np.array([n.encode() for n in names])}, key: {f"{n}:0": p.detach().float().cpu().numpy() for n, p in params}}
+                tree[key] = {"__attrs__": {"weight_names": np.array([n.encode() for n in names])},
+                        key: {f"{n}:0": p.detach().float().cpu().numpy() for n, p in params}}
                 layers.append(key)
             write_hdf5(filepath, tree, attrs={"layer_names": np.array([n.encode() for n in layers]), "backend": "torch", "keras_version": "zoo-b200"})
             return

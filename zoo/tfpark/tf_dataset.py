@@ -98,7 +98,8 @@ class TFDataset:
                 raise ValueError(f"no records in {path}")
             lab = [] if labels is None else ([labels] if isinstance(labels, str) else list(labels))
             # default feature set: everything that can be a tensor (numbers, encoded images) except the labels
-            feats = features if features is not None else sorted(k for k in exs[0] if k not in lab and (image_decoder is not None or is_numeric_feature(exs[0][k])))
+            usable = lambda k: image_decoder is not None or is_numeric_feature(exs[0][k])
+            feats = features if features is not None else sorted(k for k in exs[0] if k not in lab and usable(k))
             return examples_to_arrays(exs, feats, labels, image_decoder)
 
         x, y = load(file_path)

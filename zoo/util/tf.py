@@ -132,7 +132,8 @@ def export_tf(model, folder, example_input=None, inputs=None, outputs=None, gene
                     be = mm.bias.detach().float().cpu().numpy() if mm.affine else np.zeros(c, np.float32)
                     ins = [cur, const(f"g_{k}", g), const(f"be_{k}", be), const(f"mu_{k}", mm.running_mean.float().cpu().numpy()),
                            const(f"var_{k}", mm.running_var.float().cpu().numpy())]
-                    nodes.append((f"bn_{k}", "FusedBatchNormV3", ins, {"T": np.float32, "U": np.float32, "epsilon": float(mm.eps), "data_format": "NHWC", "is_training": False}))
+                    nodes.append((f"bn_{k}", "FusedBatchNormV3", ins, {"T": np.float32, "U": np.float32, "epsilon": float(mm.eps),
+                            "data_format": "NHWC", "is_training": False}))
                     cur = f"bn_{k}"
                 elif isinstance(mm, nn.Flatten):
                     if conv_layout and len(shape) == 4:        # the torch model flattens NCHW: put the graph's NHWC tensor in that order first
